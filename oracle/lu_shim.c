@@ -1,0 +1,85 @@
+/*
+ * oracle/lu_shim.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * The reference links a system LAPACK (CMakeLists.txt:32) that this image does
+ * not have.  Only the driver's post-process needs it (dg2d_diffusion.cpp:265 ->
+ * blaze::solve_LU, core/blaze_sparse_init.hpp:161-174 -> dgetrf_/dgetrs_), never
+ * the assemble-and-solve path.  These two routines are a plain unblocked
+ * partial-pivoting LU with the published LAPACK calling convention
+ * (column-major, 1-based pivots, 32-bit integers as blaze::blas_int_t defaults
+ * to, blaze/math/blas/Types.h:64) so oracle/_ref links without an external
+ * library.  Results that flow through here (the driver's "L2 error (mm)") are
+ * therefore "parity unpinned" against a real LAPACK.
+ */
+#include <math.h>
+#include <stddef.h>
+
+void dgetrf_(int *m, int *n, double *A, int *lda, int *ipiv, int *info)
+{
+    const int M = *m, N = *n, LD = *lda;
+    const int K = M < N ? M : N;
+    *info = 0;
+    for (int k = 0; k < K; k++) {
+        int p = k;
+        double best = fabs(A[k + (size_t)k * LD]);
+        for (int i = k + 1; i < M; i++) {
+            double v = fabs(A[i + (size_t)k * LD]);
+            if (v > best) { best = v; p = i; }
+        }
+        ipiv[k] = p + 1;
+        if (best == 0.0) { if (*info == 0) *info = k + 1; continue; }
+        if (p != k)
+            for (int j = 0; j < N; j++) {
+                double t = A[k + (size_t)j * LD];
+                A[k + (size_t)j * LD] = A[p + (size_t)j * LD];
+                A[p + (size_t)j * LD] = t;
+            }
+        const double piv = A[k + (size_t)k * LD];
+        for (int i = k + 1; i < M; i++)
+            A[i + (size_t)k * LD] /= piv;
+        for (int j = k + 1; j < N; j++) {
+            const double akj = A[k + (size_t)j * LD];
+            for (int i = k + 1; i < M; i++)
+                A[i + (size_t)j * LD] -= A[i + (size_t)k * LD] * akj;
+        }
+    }
+}
+
+void dgetrs_(char *trans, int *n, int *nrhs, double *A, int *lda, int *ipiv,
+             double *B, int *ldb, int *info, size_t ntrans)
+{
+    const int N = *n, R = *nrhs, LD = *lda, LDB = *ldb;
+    (void) ntrans;
+    *info = 0;
+    const int tr = !(*trans == 'N' || *trans == 'n');
+    for (int c = 0; c < R; c++) {
+        double *b = B + (size_t)c * LDB;
+        if (!tr) {
+            for (int k = 0; k < N; k++) {
+                int p = ipiv[k] - 1;
+                if (p != k) { double t = b[k]; b[k] = b[p]; b[p] = t; }
+            }
+            for (int k = 0; k < N; k++)            /* L y = P b */
+                for (int i = k + 1; i < N; i++)
+                    b[i] -= A[i + (size_t)k * LD] * b[k];
+            for (int k = N - 1; k >= 0; k--) {      /* U x = y */
+                b[k] /= A[k + (size_t)k * LD];
+                for (int i = 0; i < k; i++)
+                    b[i] -= A[i + (size_t)k * LD] * b[k];
+            }
+        } else {
+            for (int k = 0; k < N; k++) {           /* U^T y = b */
+                for (int i = 0; i < k; i++)
+                    b[k] -= A[i + (size_t)k * LD] * b[i];
+                b[k] /= A[k + (size_t)k * LD];
+            }
+            for (int k = N - 1; k >= 0; k--)        /* L^T z = y */
+                for (int i = k + 1; i < N; i++)
+                    b[k] -= A[i + (size_t)k * LD] * b[i];
+            for (int k = N - 1; k >= 0; k--) {
+                int p = ipiv[k] - 1;
+                if (p != k) { double t = b[k]; b[k] = b[p]; b[p] = t; }
+            }
+        }
+    }
+}

@@ -1,0 +1,142 @@
+"""ctypes binding of oracle/_ref/libyfd_ref.so -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+The library is the UNMODIFIED reference (built by oracle/Makefile from the sources
+where they lie under /root/reference; see oracle/ref_harness.cpp).  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+TRI, QUAD = 0, 1
+
+_i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+
+
+def lib_path(omp=False):
+    return os.path.join(_HERE, "_ref", "libyfd_ref_omp.so" if omp else "libyfd_ref.so")
+
+
+def available(omp=False):
+    return os.path.exists(lib_path(omp))
+
+
+class Ref:
+    """One loaded copy of the reference library (it keeps one mesh + one result)."""
+
+    def __init__(self, omp=False):
+        self.lib = L = C.CDLL(lib_path(omp))
+        L.yfd_ref_mesh_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.yfd_ref_mesh_sizes.argtypes = [C.POINTER(C.c_int64)] * 4
+        L.yfd_ref_mesh_copy.argtypes = [_f64p, _i64p, _i64p, _i32p, _i64p]
+        L.yfd_ref_set_cg.argtypes = [C.c_double, C.c_double, C.c_long, C.c_int]
+        L.yfd_ref_keep_raw_triplets.argtypes = [C.c_int]
+        L.yfd_ref_run_dg.argtypes = [C.c_int, C.c_double, C.c_int]
+        L.yfd_ref_run_cfem.argtypes = [C.c_int]
+        L.yfd_ref_result_sizes.argtypes = [C.POINTER(C.c_int64)] * 5 + [C.POINTER(C.c_int32)]
+        L.yfd_ref_result_csr.argtypes = [_i64p, _i64p, _f64p]
+        L.yfd_ref_result_pc_diag.argtypes = [_f64p]
+        L.yfd_ref_result_vectors.argtypes = [_f64p, _f64p, C.c_void_p]
+        L.yfd_ref_result_raw_triplets.argtypes = [_i64p, _i64p, _f64p]
+        L.yfd_ref_result_times.argtypes = [C.POINTER(C.c_double)] * 6
+        L.yfd_ref_cell_quadrature.argtypes = [C.c_int64, C.c_int, _f64p, C.c_int]
+        L.yfd_ref_face_quadrature.argtypes = [C.c_int64, C.c_int, _f64p, C.c_int]
+        L.yfd_ref_basis_eval.argtypes = [C.c_int64, C.c_int, C.c_double, C.c_double, _f64p, _f64p]
+        L.yfd_ref_face_geometry.argtypes = [C.c_int64, C.c_int, _f64p, C.POINTER(C.c_double)]
+        L.yfd_ref_num_threads.restype = C.c_int
+
+    # ---- mesh -----------------------------------------------------------
+    def mesh(self, mtype, levels, shatter=False):
+        self.lib.yfd_ref_mesh_create(mtype, levels, int(shatter))
+        s = [C.c_int64() for _ in range(4)]
+        self.lib.yfd_ref_mesh_sizes(*[C.byref(v) for v in s])
+        npts, ncells, nfaces, nv = [v.value for v in s]
+        pts = np.empty((npts, 2), np.float64)
+        cells = np.empty((ncells, nv), np.int64)
+        faces = np.empty((nfaces, 2), np.int64)
+        fbnd = np.empty(nfaces, np.int32)
+        owners = np.empty((nfaces, 2), np.int64)
+        self.lib.yfd_ref_mesh_copy(pts, cells, faces, fbnd, owners)
+        return dict(type=mtype, points=pts, cells=cells, faces=faces, face_boundary=fbnd, face_owners=owners)
+
+    # ---- drivers --------------------------------------------------------
+    def set_cg(self, rr_tol=1e-8, rr_max=1e4, max_iter=-1, skip_solve=False):
+        self.lib.yfd_ref_set_cg(rr_tol, rr_max, max_iter, int(skip_solve))
+
+    def run_dg(self, degree, eta=1.0, use_pc=False, raw_triplets=False):
+        """run_diffusion_solver (dg2d_diffusion.cpp:114) on the current mesh."""
+        self.lib.yfd_ref_keep_raw_triplets(int(raw_triplets))
+        rc = self.lib.yfd_ref_run_dg(degree, eta, int(use_pc))
+        if rc != 0:
+            raise RuntimeError("reference DG driver failed")
+        return self._results(raw_triplets)
+
+    def run_cfem(self, levels, raw_triplets=False):
+        """continuous_fem.cpp main() with its refinement count redirected."""
+        self.lib.yfd_ref_keep_raw_triplets(int(raw_triplets))
+        rc = self.lib.yfd_ref_run_cfem(levels)
+        if rc != 0:
+            raise RuntimeError("reference CFEM driver failed")
+        return self._results(raw_triplets)
+
+    def _results(self, raw):
+        s = [C.c_int64() for _ in range(5)]
+        hp = C.c_int32()
+        self.lib.yfd_ref_result_sizes(*[C.byref(v) for v in s], C.byref(hp))
+        n, nnz, nraw, iters, nhist = [v.value for v in s]
+        rowptr = np.empty(n + 1, np.int64)
+        colidx = np.empty(nnz, np.int64)
+        values = np.empty(nnz, np.float64)
+        self.lib.yfd_ref_result_csr(rowptr, colidx, values)
+        rhs = np.empty(n, np.float64)
+        sol = np.empty(n, np.float64)
+        hist = np.empty(max(nhist, 1), np.float64)
+        self.lib.yfd_ref_result_vectors(rhs, sol, hist.ctypes.data_as(C.c_void_p))
+        out = dict(n=n, nnz=nnz, rowptr=rowptr, colidx=colidx, values=values, rhs=rhs, sol=sol,
+                   iters=iters, history=hist[:nhist])
+        if hp.value:
+            d = np.empty(n, np.float64)
+            self.lib.yfd_ref_result_pc_diag(d)
+            out["pc_diag"] = d
+        if raw and nraw:
+            ri = np.empty(nraw, np.int64)
+            rj = np.empty(nraw, np.int64)
+            rv = np.empty(nraw, np.float64)
+            self.lib.yfd_ref_result_raw_triplets(ri, rj, rv)
+            out["raw"] = (ri, rj, rv)
+        t = [C.c_double() for _ in range(6)]
+        self.lib.yfd_ref_result_times(*[C.byref(v) for v in t])
+        out.update(t_blocks=t[0].value, t_csr=t[1].value, t_cg=t[2].value,
+                   l2_qp=t[3].value, l2_mm=t[4].value, mesh_h=t[5].value)
+        return out
+
+    # ---- probes ---------------------------------------------------------
+    def cell_quadrature(self, cell, degree):
+        buf = np.empty((128, 3), np.float64)
+        n = self.lib.yfd_ref_cell_quadrature(cell, degree, buf, 128)
+        return buf[:n].copy()
+
+    def face_quadrature(self, face, degree):
+        buf = np.empty((32, 3), np.float64)
+        n = self.lib.yfd_ref_face_quadrature(face, degree, buf, 32)
+        return buf[:n].copy()
+
+    def basis_eval(self, cell, degree, x, y):
+        phi = np.empty(64, np.float64)
+        dphi = np.empty((64, 2), np.float64)
+        n = self.lib.yfd_ref_basis_eval(cell, degree, x, y, phi, dphi)
+        return phi[:n].copy(), dphi[:n].copy()
+
+    def face_geometry(self, cell, local_face):
+        n = np.empty(2, np.float64)
+        d = C.c_double()
+        self.lib.yfd_ref_face_geometry(cell, local_face, n, C.byref(d))
+        return n, d.value
+
+    def num_threads(self):
+        return self.lib.yfd_ref_num_threads()
