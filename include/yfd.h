@@ -1,0 +1,276 @@
+/*
+ * include/yfd.h -- C ABI of libyfd_b200.so: the B200 (sm_100a) implementation of
+ * Yaourt-FEM-DG's assemble-and-solve hot path.
+ *
+ * The reference (datafl4sh/yaourt-fem-dg) has no FFI: its "API" for this path is a
+ * set of header-only C++ templates.  Each entry point below states the reference
+ * interface (file:line, relative to the reference root) whose work it replaces; the
+ * C++ shim in include/yaourt_b200/ puts the reference's own names back on top of
+ * this ABI, and INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every array argument is a caller-owned HOST
+ *     buffer unless its name starts with d_ (device pointer, for resident pipelines);
+ *   - objects live on the GPU behind opaque handles with explicit *_destroy;
+ *   - every function returns a yfd_status; yfd_last_error(ctx) gives the message.
+ *     There is NO CPU fallback: without a usable CUDA device yfd_ctx_create fails
+ *     with YFD_ERR_NO_DEVICE and nothing else can be called;
+ *   - externally visible numbering is the reference's, bit for bit: cell id = index
+ *     in the sorted cell list, face id = index in the sorted face list, DG dof =
+ *     cell*bs + local (methods/dg.hpp:75-84), CFEM dof = rank among non-Dirichlet
+ *     nodes (methods/cfem.hpp:140-148).  Internally cells are renumbered along a
+ *     space-filling curve (yfd_mesh_create, `reorder`), invisible at this boundary.
+ */
+#ifndef YFD_H
+#define YFD_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YFD_VERSION 100
+
+typedef enum yfd_status {
+    YFD_OK = 0,
+    YFD_ERR_INVALID_ARGUMENT = 1,   /* std::invalid_argument at the C++ boundary            */
+    YFD_ERR_INVALID_STATE    = 2,   /* "Assembler in invalid state" (methods/dg.hpp:72-73)  */
+    YFD_ERR_CELL_NOT_FOUND   = 3,   /* "Mesh cell not found"  (core/mesh.hpp:281)           */
+    YFD_ERR_FACE_NOT_FOUND   = 4,   /* "Mesh face not found"  (core/mesh.hpp:293)           */
+    YFD_ERR_DEGREE_TOO_HIGH  = 5,   /* "Dunavant quadrature: degree too high" (core/quadratures.hpp:579) */
+    YFD_ERR_NO_NEIGHBOURS    = 6,   /* "No neighbour information." (core/mesh.hpp:256)      */
+    YFD_ERR_TOO_MANY_OWNERS  = 7,   /* "BUG: a face has max 2 owners" (core/mesh.hpp:199)   */
+    YFD_ERR_SHAPE_MISMATCH   = 8,   /* CG: non-square A / wrong vector size -> `return false` (core/solvers.hpp:53-77) */
+    YFD_ERR_UNSUPPORTED      = 9,
+    YFD_ERR_NO_DEVICE        = 10,  /* no CUDA device / driver: there is no CPU path        */
+    YFD_ERR_CUDA             = 11,
+    YFD_ERR_COMM             = 12,  /* NCCL failure                                          */
+    YFD_ERR_OUT_OF_MEMORY    = 13
+} yfd_status;
+
+const char *yfd_status_string(yfd_status s);
+
+/* ---------------------------------------------------------------------------------- */
+/* Context: one per GPU rank.  One CUDA stream per context, re-entrant per handle.     */
+/* ---------------------------------------------------------------------------------- */
+typedef struct yfd_ctx yfd_ctx;
+
+/* `stream` = a cudaStream_t to launch on (e.g. torch's current stream) or NULL to let
+ * the context create its own non-blocking stream. */
+yfd_status  yfd_ctx_create(int device, void *stream, yfd_ctx **out);
+void        yfd_ctx_destroy(yfd_ctx *ctx);
+const char *yfd_last_error(const yfd_ctx *ctx);
+yfd_status  yfd_ctx_synchronize(yfd_ctx *ctx);
+/* kernels launched by this context so far (graph replays count their kernel nodes) */
+int64_t     yfd_ctx_launch_count(const yfd_ctx *ctx);
+/* name and SM count of the device (buf may be NULL) */
+yfd_status  yfd_ctx_device_info(const yfd_ctx *ctx, char *name, size_t cap, int *sm_count, int *cc_major, int *cc_minor);
+
+/* Multi-GPU: attach an NCCL communicator (one rank per context).  `unique_id` is the
+ * 128-byte ncclUniqueId made by rank 0 (yfd_comm_unique_id) and shipped by the host
+ * program (torch.distributed broadcast in bench.py).  The reference has no
+ * distributed layer; this is new. */
+#define YFD_COMM_ID_BYTES 128
+yfd_status  yfd_comm_unique_id(unsigned char id[YFD_COMM_ID_BYTES]);
+yfd_status  yfd_ctx_attach_comm(yfd_ctx *ctx, int rank, int nranks, const unsigned char id[YFD_COMM_ID_BYTES]);
+int         yfd_ctx_rank(const yfd_ctx *ctx);
+int         yfd_ctx_nranks(const yfd_ctx *ctx);
+
+/* ---------------------------------------------------------------------------------- */
+/* Mesher (host): replaces mesher<Mesh>::create_mesh + refine_mesh                     */
+/* (core/meshers.hpp:130-179 triangles, :302-361 quadrangles).  Same unit-square base   */
+/* meshes, same red refinement, same point / face / cell numbering.                    */
+/* ---------------------------------------------------------------------------------- */
+#define YFD_CELL_TRIANGLE   0
+#define YFD_CELL_QUADRANGLE 1
+
+typedef struct yfd_host_mesh yfd_host_mesh;
+
+yfd_status yfd_mesher_create(int cell_type, int refinement_levels, yfd_host_mesh **out);
+void       yfd_host_mesh_destroy(yfd_host_mesh *m);
+void       yfd_host_mesh_sizes(const yfd_host_mesh *m, int64_t *npoints, int64_t *ncells,
+                               int64_t *nfaces, int *verts_per_cell);
+/* borrowed pointers, valid until destroy:
+ *   points [npoints][2] f64 ; cells [ncells][nv] i64 (vertex order as in the reference,
+ *   NOT sorted inside a cell) ; faces [nfaces][2] i64 with p0 < p1, sorted ;
+ *   face_boundary [nfaces] u8 ; face_boundary_id [nfaces] i64 (0 for interior faces,
+ *   where the reference leaves it unset). */
+const double  *yfd_host_mesh_points(const yfd_host_mesh *m);
+const int64_t *yfd_host_mesh_cells(const yfd_host_mesh *m);
+const int64_t *yfd_host_mesh_faces(const yfd_host_mesh *m);
+const uint8_t *yfd_host_mesh_face_boundary(const yfd_host_mesh *m);
+const int64_t *yfd_host_mesh_face_boundary_id(const yfd_host_mesh *m);
+
+/* ---------------------------------------------------------------------------------- */
+/* Device mesh: replaces the mesh<T,2,CellT,FaceT> the drivers pass around plus         */
+/* mesh::compute_connectivity (core/mesh.hpp:176-204), face_ids / offset(face)          */
+/* (core/mesh.hpp:287-296, :329-353).                                                  */
+/* ---------------------------------------------------------------------------------- */
+typedef struct yfd_mesh yfd_mesh;
+
+#define YFD_REORDER_NONE   0    /* internal cell order = reference order                */
+#define YFD_REORDER_MORTON 1    /* internal cell order = Z-curve of cell barycentres    */
+
+/* cells must be sorted as the reference sorts them (lexicographic on the vertex tuple,
+ * core/meshers.hpp:178,:360) and faces sorted by (p0,p1) with p0<p1 (core/mesh.hpp:77-81);
+ * both are checked on the device: YFD_ERR_INVALID_ARGUMENT if not, YFD_ERR_FACE_NOT_FOUND
+ * if a cell edge is missing from `faces`, YFD_ERR_TOO_MANY_OWNERS as in the reference. */
+yfd_status yfd_mesh_create(yfd_ctx *ctx, int cell_type,
+                           int64_t npoints, const double *points,
+                           int64_t ncells, const int64_t *cells,
+                           int64_t nfaces, const int64_t *faces, const uint8_t *face_boundary,
+                           int reorder, yfd_mesh **out);
+void       yfd_mesh_destroy(yfd_mesh *m);
+void       yfd_mesh_sizes(const yfd_mesh *m, int64_t *npoints, int64_t *ncells, int64_t *nfaces, int *verts_per_cell);
+/* face_owners [nfaces][2] (i64, -1 = NO_OWNER) exactly as compute_connectivity leaves them */
+yfd_status yfd_mesh_get_face_owners(yfd_mesh *m, int64_t *owners);
+/* cell_faces [ncells][nf]: face_ids(msh, cell) in the reference's local face order
+ * (tri: p0p1,p1p2,p0p2 ; quad: p0p1,p1p2,p2p3,p0p3 ; core/mesh.hpp:329-353) */
+yfd_status yfd_mesh_get_cell_faces(yfd_mesh *m, int64_t *cell_faces);
+/* perm[internal cell] = reference cell id */
+yfd_status yfd_mesh_get_permutation(yfd_mesh *m, int64_t *perm);
+/* replace the coordinates (shatter_mesh output etc.); same count as at creation */
+yfd_status yfd_mesh_set_points(yfd_mesh *m, const double *points);
+
+/* ---------------------------------------------------------------------------------- */
+/* Sparse matrix handle (row-major CSR, fp64 values, int32 columns, int64 row offsets)  */
+/* = blaze::CompressedMatrix<double> at this boundary.                                  */
+/* ---------------------------------------------------------------------------------- */
+typedef struct yfd_csr yfd_csr;
+
+/* Replaces blaze::init_from_triplets + reduce_triplets (core/blaze_sparse_init.hpp:101-155):
+ * sort by (row,col), fold equal positions, build CSR.  Deterministic: equal positions are
+ * added in the order they appear in the input (a stable sort), explicit zeros are kept as
+ * the reference keeps them.  rows/cols/vals have `count` entries. */
+yfd_status yfd_csr_from_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t count,
+                                 const int64_t *rows, const int64_t *cols, const double *vals,
+                                 yfd_csr **out);
+/* Adopt an existing CSR (e.g. a blaze::CompressedMatrix walked row by row). */
+yfd_status yfd_csr_from_arrays(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t nnz,
+                               const int64_t *rowptr, const int64_t *colidx, const double *values,
+                               yfd_csr **out);
+void       yfd_csr_destroy(yfd_csr *A);
+void       yfd_csr_sizes(const yfd_csr *A, int64_t *nrows, int64_t *ncols, int64_t *nnz);
+/* any of the three outputs may be NULL */
+yfd_status yfd_csr_get(yfd_csr *A, int64_t *rowptr, int64_t *colidx, double *values);
+/* y = A x (host vectors): Blaze's `A*d` (blaze/math/expressions/SMatDVecMultExpr.h:204-207) */
+yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y);
+
+/* ---------------------------------------------------------------------------------- */
+/* DG-SIP diffusion: replaces the whole cell loop of run_diffusion_solver               */
+/* (dg2d_diffusion.cpp:133-201: make_basis, integrate, eval / eval_grads, K, Att, Atn,  */
+/* loc_rhs), assembler<Mesh>::assemble x2 (methods/dg.hpp:67-123) and                   */
+/* assembler::finalize (methods/dg.hpp:125-144).                                        */
+/* ---------------------------------------------------------------------------------- */
+#define YFD_FN_ZERO    0   /* data::dirichlet (dg2d_diffusion.cpp:61-66)                  */
+#define YFD_FN_SINSIN  1   /* data::rhs = 2 pi^2 sin(pi x) sin(pi y) (dg2d_diffusion.cpp:53-59) */
+#define YFD_FN_ONE     2
+
+typedef struct yfd_dg_config {
+    int     degree;             /* cfg.degree, k >= 0; basis size (k+2)(k+1)/2 (core/bases.hpp:63-74) */
+    double  eta;                /* cfg.eta; penalty = 3 k^2 eta / diameter(face) (dg2d_diffusion.cpp:127,162) */
+    int     rhs_fn;             /* YFD_FN_*                                                */
+    int     dirichlet_fn;       /* YFD_FN_*                                                */
+    int     build_preconditioner; /* assembler(msh, degree, bpc): Jacobi pc (methods/dg.hpp:88-89,133-142) */
+} yfd_dg_config;
+
+typedef struct yfd_system yfd_system;   /* lhs + rhs (+ pc) of one assembled problem, on the device */
+
+typedef struct yfd_assembly_info {
+    int64_t system_size;        /* assembler::system_size()                                */
+    int64_t nnz;
+    int64_t basis_size;
+    double  ms_elements;        /* device time: local blocks -> CSR values (CUDA events)   */
+    double  ms_structure;       /* device time: sparsity pattern (rowptr / colidx)         */
+} yfd_assembly_info;
+
+yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
+                               yfd_system **out, yfd_assembly_info *info);
+
+/* Per-cell local blocks BEFORE the scatter, for unit-level parity with the reference loop:
+ *   K   [ncells][bs][bs]      cell stiffness            (dg2d_diffusion.cpp:141-149)
+ *   Att [ncells][nf][bs][bs]  per local face            (:171-173 interior, :186-188 boundary)
+ *   Atn [ncells][nf][bs][bs]  zero where no neighbour   (:178-180)
+ *   rhs [ncells][bs]                                    (:148, :190-191)
+ * all indexed by REFERENCE cell id.  Any output may be NULL. */
+yfd_status yfd_dg_local_blocks(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
+                               double *K, double *Att, double *Atn, double *rhs);
+
+/* ---------------------------------------------------------------------------------- */
+/* Continuous P1 FEM: replaces cfem::stiffness_matrix / eval_basis_grad                 */
+/* (methods/cfem.hpp:53-89), compute_rhs (continuous_fem.cpp:33-50), and                */
+/* cfem::assembler ctor / assemble / finalize (methods/cfem.hpp:119-186).               */
+/* ---------------------------------------------------------------------------------- */
+yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn,
+                                yfd_system **out, yfd_assembly_info *info);
+/* cfem::assembler::expand (methods/cfem.hpp:190-197): sol[system_size] -> expanded[npoints] */
+yfd_status yfd_cfem_expand(yfd_system *sys, const double *sol, double *expanded);
+/* compress_map [npoints] (i64; -1 on Dirichlet nodes) */
+yfd_status yfd_cfem_get_compress_map(yfd_system *sys, int64_t *compress_map);
+
+/* ---------------------------------------------------------------------------------- */
+/* Assembled system accessors (REFERENCE numbering).                                   */
+/* ---------------------------------------------------------------------------------- */
+void       yfd_system_destroy(yfd_system *sys);
+void       yfd_system_sizes(const yfd_system *sys, int64_t *n, int64_t *nnz);
+/* assm.lhs as CSR; any output may be NULL */
+yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx, double *values);
+yfd_status yfd_system_get_rhs(yfd_system *sys, double *rhs);                 /* assm.rhs         */
+yfd_status yfd_system_get_pc_diag(yfd_system *sys, double *diag);            /* diag of assm.pc  */
+
+/* ---------------------------------------------------------------------------------- */
+/* Conjugate gradient: replaces conjugated_gradient (core/solvers.hpp:46-138 plain,     */
+/* :141-243 with the inverse-preconditioner matrix iM; the DG assembler's iM is         */
+/* diagonal, methods/dg.hpp:133-142, and is applied here as a vector scale).            */
+/* ---------------------------------------------------------------------------------- */
+typedef struct yfd_cg_params {            /* conjugated_gradient_params<T> (core/solvers.hpp:24-43) */
+    double  rr_tol;                       /* 1e-8  */
+    double  rr_max;                       /* 20    */
+    int64_t max_iter;                     /* 100   */
+    int     use_initial_guess;            /* false */
+    int     use_normal_eqns;              /* false; true -> YFD_ERR_UNSUPPORTED */
+    int     save_iteration_history;       /* false */
+    int     check_every;                  /* extension: iterations per device-side batch between
+                                             host polls of the stop flag (0 = default 64).  The
+                                             stop test itself runs on the device EVERY iteration,
+                                             so the iteration count is the reference's. */
+} yfd_cg_params;
+
+void yfd_cg_params_default(yfd_cg_params *p);
+
+typedef struct yfd_cg_info {
+    int64_t iterations;                   /* `iter` on exit                                 */
+    double  nr0;                          /* ||b - A x0||                                   */
+    double  nr;                           /* recurrence residual norm on exit               */
+    int     converged;                    /* nr/nr0 <= rr_tol (the reference returns true regardless) */
+    double  ms_solve;                     /* device time of the whole solve (CUDA events)   */
+    double  ms_spmv;                      /* average device time of one y = A d launch (measured on
+                                             a separate timing pass of `spmv_timing_reps` launches;
+                                             0 if not requested)                             */
+    int64_t history_len;                  /* entries written to `history` (iterations+1)    */
+} yfd_cg_info;
+
+/* Solve sys.lhs x = sys.rhs on the device, no host round trip of the matrix.
+ * use_pc != 0 -> the 5-argument overload with assm.pc.  x [n] in REFERENCE numbering, in/out
+ * (input read only if use_initial_guess).  history may be NULL, else cap >= max_iter+1 is not
+ * required: writing stops at history_cap. */
+yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                               double *x, yfd_cg_info *info, double *history, int64_t history_cap);
+
+/* The drop-in shape: A, b, x and optional DIAGONAL iM given as host data. */
+yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                        const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
+
+/* Time `reps` launches of y = A d for this system with CUDA events on the context's stream
+ * (bench.py's roofline leg).  Returns average ms per launch and the algorithmic CSR bytes of one
+ * launch (12 nnz + 8 (n+1) + 16 n) plus the bytes the kernel actually
+ * requests (the block kernel does not read colidx). */
+yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double *ms_per_launch,
+                                double *csr_bytes, double *kernel_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YFD_H */

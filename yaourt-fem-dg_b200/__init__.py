@@ -1,0 +1,11 @@
+"""yaourt-fem-dg_b200: B200 (sm_100a) implementation of Yaourt-FEM-DG's assemble-and-solve hot path.
+
+Everything computes in libyfd_b200.so (hand-written CUDA behind the C ABI of include/yfd.h); this
+package is the ctypes binding plus thin host-side objects.  There is no CPU fallback: importing
+works without a GPU (so the ABI can be inspected), creating a Context does not.
+"""
+from .capi import (  # noqa: F401
+    TRI, QUAD, FN_ZERO, FN_SINSIN, FN_ONE, REORDER_NONE, REORDER_MORTON,
+    YfdError, lib, lib_path, Context, HostMesh, Mesh, Csr, System, CgParams, CgInfo, AssemblyInfo,
+    declared_symbols,
+)

@@ -1,0 +1,450 @@
+"""ctypes binding of libyfd_b200.so (include/yfd.h), and small host objects over its handles.
+
+The reference's interface for this path is C++ templates; the objects here
+mirror them one to one:
+    HostMesh.create(type, r)         mesher<Mesh>::create_mesh            core/meshers.hpp:130,302
+    Mesh(ctx, ...)                   mesh + compute_connectivity          core/mesh.hpp:158-204
+    Context.dg_assemble_sip(...)     run_diffusion_solver's cell loop     dg2d_diffusion.cpp:133-201
+                                     + assembler::finalize                methods/dg.hpp:125-144
+    Context.cfem_assemble_p1(...)    continuous_fem.cpp:64-71 + cfem::assembler
+    Csr.from_triplets(...)           blaze::init_from_triplets            core/blaze_sparse_init.hpp:125
+    System.solve_cg / Csr.solve_cg   conjugated_gradient                  core/solvers.hpp:46,141
+"""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+
+TRI, QUAD = 0, 1
+FN_ZERO, FN_SINSIN, FN_ONE = 0, 1, 2
+REORDER_NONE, REORDER_MORTON = 0, 1
+
+
+class YfdError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__("yfd status %d: %s" % (status, message))
+        self.status = status
+
+
+def lib_path():
+    return os.path.join(_HERE, "lib", "libyfd_b200.so")
+
+
+def header_path():
+    return os.path.join(_ROOT, "include", "yfd.h")
+
+
+def declared_symbols():
+    """Every function include/yfd.h declares (used by the CPU test that the library exports them)."""
+    src = open(header_path()).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(yfd_[a-z0-9_]+)\s*\(", src)))
+
+
+_i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+class DgConfig(C.Structure):
+    _fields_ = [("degree", C.c_int), ("eta", C.c_double), ("rhs_fn", C.c_int), ("dirichlet_fn", C.c_int),
+                ("build_preconditioner", C.c_int)]
+
+
+class AssemblyInfo(C.Structure):
+    _fields_ = [("system_size", C.c_int64), ("nnz", C.c_int64), ("basis_size", C.c_int64),
+                ("ms_elements", C.c_double), ("ms_structure", C.c_double)]
+
+
+class CgParams(C.Structure):
+    """conjugated_gradient_params<T> (core/solvers.hpp:24-43) + check_every."""
+    _fields_ = [("rr_tol", C.c_double), ("rr_max", C.c_double), ("max_iter", C.c_int64),
+                ("use_initial_guess", C.c_int), ("use_normal_eqns", C.c_int),
+                ("save_iteration_history", C.c_int), ("check_every", C.c_int)]
+
+    def __init__(self, **kw):
+        super().__init__()
+        lib().yfd_cg_params_default(C.byref(self))
+        for k, v in kw.items():
+            if k not in dict(self._fields_):
+                raise TypeError("unknown CG parameter " + k)
+            setattr(self, k, v)
+
+
+class CgInfo(C.Structure):
+    _fields_ = [("iterations", C.c_int64), ("nr0", C.c_double), ("nr", C.c_double), ("converged", C.c_int),
+                ("ms_solve", C.c_double), ("ms_spmv", C.c_double), ("history_len", C.c_int64)]
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fail loudly if it has not been built (no fallback exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise YfdError(-1, "%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(the hot path is CUDA only, there is no CPU fallback)" % path)
+    L = C.CDLL(path)
+    vp, i64, dbl, cint = C.c_void_p, C.c_int64, C.c_double, C.c_int
+    P = C.POINTER
+    sig = {
+        "yfd_status_string": (C.c_char_p, [cint]),
+        "yfd_ctx_create": (cint, [cint, vp, P(vp)]),
+        "yfd_ctx_destroy": (None, [vp]),
+        "yfd_last_error": (C.c_char_p, [vp]),
+        "yfd_ctx_synchronize": (cint, [vp]),
+        "yfd_ctx_launch_count": (i64, [vp]),
+        "yfd_ctx_device_info": (cint, [vp, C.c_char_p, C.c_size_t, P(cint), P(cint), P(cint)]),
+        "yfd_comm_unique_id": (cint, [C.c_char_p]),
+        "yfd_ctx_attach_comm": (cint, [vp, cint, cint, C.c_char_p]),
+        "yfd_ctx_rank": (cint, [vp]),
+        "yfd_ctx_nranks": (cint, [vp]),
+        "yfd_mesher_create": (cint, [cint, cint, P(vp)]),
+        "yfd_host_mesh_destroy": (None, [vp]),
+        "yfd_host_mesh_sizes": (None, [vp, P(i64), P(i64), P(i64), P(cint)]),
+        "yfd_host_mesh_points": (P(dbl), [vp]),
+        "yfd_host_mesh_cells": (P(i64), [vp]),
+        "yfd_host_mesh_faces": (P(i64), [vp]),
+        "yfd_host_mesh_face_boundary": (P(C.c_uint8), [vp]),
+        "yfd_host_mesh_face_boundary_id": (P(i64), [vp]),
+        "yfd_mesh_create": (cint, [vp, cint, i64, _f64p, i64, _i64p, i64, _i64p, _u8p, cint, P(vp)]),
+        "yfd_mesh_destroy": (None, [vp]),
+        "yfd_mesh_sizes": (None, [vp, P(i64), P(i64), P(i64), P(cint)]),
+        "yfd_mesh_get_face_owners": (cint, [vp, _i64p]),
+        "yfd_mesh_get_cell_faces": (cint, [vp, _i64p]),
+        "yfd_mesh_get_permutation": (cint, [vp, _i64p]),
+        "yfd_mesh_set_points": (cint, [vp, _f64p]),
+        "yfd_csr_from_triplets": (cint, [vp, i64, i64, i64, _i64p, _i64p, _f64p, P(vp)]),
+        "yfd_csr_from_arrays": (cint, [vp, i64, i64, i64, _i64p, _i64p, _f64p, P(vp)]),
+        "yfd_csr_destroy": (None, [vp]),
+        "yfd_csr_sizes": (None, [vp, P(i64), P(i64), P(i64)]),
+        "yfd_csr_get": (cint, [vp, vp, vp, vp]),
+        "yfd_csr_spmv": (cint, [vp, vp, _f64p, _f64p]),
+        "yfd_dg_assemble_sip": (cint, [vp, vp, P(DgConfig), P(vp), P(AssemblyInfo)]),
+        "yfd_dg_local_blocks": (cint, [vp, vp, P(DgConfig), vp, vp, vp, vp]),
+        "yfd_cfem_assemble_p1": (cint, [vp, vp, cint, P(vp), P(AssemblyInfo)]),
+        "yfd_cfem_expand": (cint, [vp, _f64p, _f64p]),
+        "yfd_cfem_get_compress_map": (cint, [vp, _i64p]),
+        "yfd_system_destroy": (None, [vp]),
+        "yfd_system_sizes": (None, [vp, P(i64), P(i64)]),
+        "yfd_system_get_csr": (cint, [vp, vp, vp, vp]),
+        "yfd_system_get_rhs": (cint, [vp, _f64p]),
+        "yfd_system_get_pc_diag": (cint, [vp, _f64p]),
+        "yfd_cg_params_default": (None, [P(CgParams)]),
+        "yfd_system_solve_cg": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
+        "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
+        "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One GPU rank (yfd_ctx).  `stream` = raw cudaStream_t (int) to launch on, e.g.
+    torch.cuda.current_stream().cuda_stream, or None for a private stream."""
+
+    def __init__(self, device=0, stream=None):
+        self._h = C.c_void_p()
+        st = lib().yfd_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(self._h))
+        if st != 0:
+            self._h = None
+            raise YfdError(st, lib().yfd_status_string(st).decode())
+        self.device = device
+
+    def check(self, st):
+        if st != 0:
+            raise YfdError(st, lib().yfd_last_error(self._h).decode() or lib().yfd_status_string(st).decode())
+
+    def close(self):
+        if self._h:
+            lib().yfd_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self.check(lib().yfd_ctx_synchronize(self._h))
+
+    @property
+    def launches(self):
+        return lib().yfd_ctx_launch_count(self._h)
+
+    def device_info(self):
+        name = C.create_string_buffer(256)
+        sm, ma, mi = C.c_int(), C.c_int(), C.c_int()
+        self.check(lib().yfd_ctx_device_info(self._h, name, 256, C.byref(sm), C.byref(ma), C.byref(mi)))
+        return dict(name=name.value.decode(), sm_count=sm.value, cc=(ma.value, mi.value))
+
+    # ---- multi-GPU ------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(128)
+        st = lib().yfd_comm_unique_id(buf)
+        if st != 0:
+            raise YfdError(st, "ncclGetUniqueId failed")
+        return buf.raw
+
+    def attach_comm(self, rank, nranks, unique_id):
+        self.check(lib().yfd_ctx_attach_comm(self._h, rank, nranks, unique_id))
+
+    # ---- assembly -------------------------------------------------------------------
+    def dg_assemble_sip(self, mesh, degree, eta=1.0, rhs_fn=FN_SINSIN, dirichlet_fn=FN_ZERO, build_pc=False):
+        cfg = DgConfig(degree, eta, rhs_fn, dirichlet_fn, int(build_pc))
+        h = C.c_void_p()
+        info = AssemblyInfo()
+        self.check(lib().yfd_dg_assemble_sip(self._h, mesh._h, C.byref(cfg), C.byref(h), C.byref(info)))
+        return System(self, h, info)
+
+    def dg_local_blocks(self, mesh, degree, eta=1.0, rhs_fn=FN_SINSIN, dirichlet_fn=FN_ZERO):
+        cfg = DgConfig(degree, eta, rhs_fn, dirichlet_fn, 0)
+        bs = (degree + 2) * (degree + 1) // 2
+        nc, nf = mesh.ncells, mesh.nv
+        K = np.empty((nc, bs, bs)); Att = np.empty((nc, nf, bs, bs)); Atn = np.empty((nc, nf, bs, bs)); rhs = np.empty((nc, bs))
+        self.check(lib().yfd_dg_local_blocks(self._h, mesh._h, C.byref(cfg), _ptr(K), _ptr(Att), _ptr(Atn), _ptr(rhs)))
+        return K, Att, Atn, rhs
+
+    def cfem_assemble_p1(self, mesh, rhs_fn=FN_SINSIN):
+        h = C.c_void_p()
+        info = AssemblyInfo()
+        self.check(lib().yfd_cfem_assemble_p1(self._h, mesh._h, rhs_fn, C.byref(h), C.byref(info)))
+        return System(self, h, info)
+
+
+class HostMesh:
+    """Host arrays of a mesh in the reference's numbering."""
+
+    def __init__(self, cell_type, points, cells, faces, face_boundary, face_boundary_id=None):
+        self.cell_type = cell_type
+        self.points = np.ascontiguousarray(points, np.float64)
+        self.cells = np.ascontiguousarray(cells, np.int64)
+        self.faces = np.ascontiguousarray(faces, np.int64)
+        self.face_boundary = np.ascontiguousarray(face_boundary, np.uint8)
+        self.face_boundary_id = face_boundary_id
+
+    @classmethod
+    def create(cls, cell_type, levels):
+        """mesher<Mesh>::create_mesh(msh, levels) (core/meshers.hpp:130-179, :302-361)."""
+        L = lib()
+        h = C.c_void_p()
+        st = L.yfd_mesher_create(cell_type, levels, C.byref(h))
+        if st != 0:
+            raise YfdError(st, L.yfd_status_string(st).decode())
+        try:
+            a, b, c, nv = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
+            L.yfd_host_mesh_sizes(h, C.byref(a), C.byref(b), C.byref(c), C.byref(nv))
+            npts, nc, nf, nv = a.value, b.value, c.value, nv.value
+            as_arr = np.ctypeslib.as_array
+            m = cls(cell_type,
+                    as_arr(L.yfd_host_mesh_points(h), (npts, 2)).copy(),
+                    as_arr(L.yfd_host_mesh_cells(h), (nc, nv)).copy(),
+                    as_arr(L.yfd_host_mesh_faces(h), (nf, 2)).copy(),
+                    as_arr(L.yfd_host_mesh_face_boundary(h), (nf,)).copy(),
+                    as_arr(L.yfd_host_mesh_face_boundary_id(h), (nf,)).copy())
+        finally:
+            L.yfd_host_mesh_destroy(h)
+        return m
+
+
+class Mesh:
+    """Device mesh + connectivity (yfd_mesh)."""
+
+    def __init__(self, ctx, host, reorder=REORDER_MORTON):
+        self.ctx = ctx
+        self.host = host
+        self._h = C.c_void_p()
+        self.nv = host.cells.shape[1]
+        self.npoints, self.ncells, self.nfaces = len(host.points), len(host.cells), len(host.faces)
+        ctx.check(lib().yfd_mesh_create(ctx._h, host.cell_type, self.npoints, host.points, self.ncells, host.cells,
+                                        self.nfaces, host.faces, host.face_boundary, reorder, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().yfd_mesh_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def face_owners(self):
+        out = np.empty((self.nfaces, 2), np.int64)
+        self.ctx.check(lib().yfd_mesh_get_face_owners(self._h, out))
+        return out
+
+    def cell_faces(self):
+        out = np.empty((self.ncells, self.nv), np.int64)
+        self.ctx.check(lib().yfd_mesh_get_cell_faces(self._h, out))
+        return out
+
+    def permutation(self):
+        out = np.empty(self.ncells, np.int64)
+        self.ctx.check(lib().yfd_mesh_get_permutation(self._h, out))
+        return out
+
+    def set_points(self, points):
+        points = np.ascontiguousarray(points, np.float64)
+        assert points.shape == (self.npoints, 2)
+        self.ctx.check(lib().yfd_mesh_set_points(self._h, points))
+
+
+def _solve_common(ctx, call, n, params, x0, history):
+    params = params or CgParams()
+    x = np.zeros(n, np.float64) if x0 is None else np.ascontiguousarray(x0, np.float64).copy()
+    info = CgInfo()
+    hist = None
+    cap = 0
+    if history:
+        params.save_iteration_history = 1
+        cap = int(min(params.max_iter + 1, 50_000_000))
+        hist = np.zeros(cap, np.float64)
+    ctx.check(call(params, x, info, _ptr(hist), cap))
+    out = dict(x=x, iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged),
+               ms_solve=info.ms_solve)
+    if history:
+        out["history"] = hist[:info.history_len].copy()
+    return out
+
+
+class Csr:
+    """blaze::CompressedMatrix<double> on the device (yfd_csr)."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self._h = ctx, handle
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        lib().yfd_csr_sizes(handle, C.byref(a), C.byref(b), C.byref(c))
+        self.nrows, self.ncols, self.nnz = a.value, b.value, c.value
+
+    @classmethod
+    def from_triplets(cls, ctx, nrows, ncols, rows, cols, vals):
+        """blaze::init_from_triplets (core/blaze_sparse_init.hpp:125-155)."""
+        rows = np.ascontiguousarray(rows, np.int64); cols = np.ascontiguousarray(cols, np.int64)
+        vals = np.ascontiguousarray(vals, np.float64)
+        h = C.c_void_p()
+        ctx.check(lib().yfd_csr_from_triplets(ctx._h, nrows, ncols, len(vals), rows, cols, vals, C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def from_arrays(cls, ctx, nrows, ncols, rowptr, colidx, values):
+        rowptr = np.ascontiguousarray(rowptr, np.int64); colidx = np.ascontiguousarray(colidx, np.int64)
+        values = np.ascontiguousarray(values, np.float64)
+        h = C.c_void_p()
+        ctx.check(lib().yfd_csr_from_arrays(ctx._h, nrows, ncols, len(values), rowptr, colidx, values, C.byref(h)))
+        return cls(ctx, h)
+
+    def close(self):
+        if self._h:
+            lib().yfd_csr_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def get(self):
+        rowptr = np.empty(self.nrows + 1, np.int64); colidx = np.empty(self.nnz, np.int64); values = np.empty(self.nnz, np.float64)
+        self.ctx.check(lib().yfd_csr_get(self._h, _ptr(rowptr), _ptr(colidx), _ptr(values)))
+        return rowptr, colidx, values
+
+    def spmv(self, x):
+        x = np.ascontiguousarray(x, np.float64)
+        y = np.empty(self.nrows, np.float64)
+        self.ctx.check(lib().yfd_csr_spmv(self.ctx._h, self._h, x, y))
+        return y
+
+    def solve_cg(self, b, params=None, pc_diag=None, x0=None, history=False):
+        """conjugated_gradient(cgp, A, b, x[, iM]) (core/solvers.hpp:46,141); iM diagonal."""
+        b = np.ascontiguousarray(b, np.float64)
+        if b.shape != (self.nrows,):
+            raise YfdError(8, "[CG solver] Wrong size of RHS vector")
+        pc = None if pc_diag is None else np.ascontiguousarray(pc_diag, np.float64)
+        call = lambda p, x, info, h, cap: lib().yfd_cg_solve(self.ctx._h, self._h, b, x, _ptr(pc), C.byref(p), C.byref(info), h, cap)
+        return _solve_common(self.ctx, call, self.nrows, params, x0, history)
+
+
+class System:
+    """An assembled problem on the device: assm.lhs / assm.rhs / assm.pc (yfd_system)."""
+
+    def __init__(self, ctx, handle, info):
+        self.ctx, self._h, self.info = ctx, handle, info
+        self.n, self.nnz = info.system_size, info.nnz
+
+    def close(self):
+        if self._h:
+            lib().yfd_system_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def csr(self, values=True):
+        rowptr = np.empty(self.n + 1, np.int64); colidx = np.empty(self.nnz, np.int64)
+        vals = np.empty(self.nnz, np.float64) if values else None
+        self.ctx.check(lib().yfd_system_get_csr(self._h, _ptr(rowptr), _ptr(colidx), _ptr(vals)))
+        return rowptr, colidx, vals
+
+    def rhs(self):
+        out = np.empty(self.n, np.float64)
+        self.ctx.check(lib().yfd_system_get_rhs(self._h, out))
+        return out
+
+    def pc_diag(self):
+        out = np.empty(self.n, np.float64)
+        self.ctx.check(lib().yfd_system_get_pc_diag(self._h, out))
+        return out
+
+    def solve_cg(self, params=None, use_pc=False, x0=None, history=False):
+        call = lambda p, x, info, h, cap: lib().yfd_system_solve_cg(self.ctx._h, self._h, int(use_pc), C.byref(p), x, C.byref(info), h, cap)
+        if x0 is not None:
+            params = params or CgParams()
+            params.use_initial_guess = 1
+        return _solve_common(self.ctx, call, self.n, params, x0, history)
+
+    def time_spmv(self, reps=20):
+        ms, b1, b2 = C.c_double(), C.c_double(), C.c_double()
+        self.ctx.check(lib().yfd_system_time_spmv(self.ctx._h, self._h, reps, C.byref(ms), C.byref(b1), C.byref(b2)))
+        return dict(ms=ms.value, csr_bytes=b1.value, kernel_bytes=b2.value)
+
+    # CFEM only
+    def expand(self, sol):
+        sol = np.ascontiguousarray(sol, np.float64)
+        a, b = C.c_int64(), C.c_int64()
+        out = np.empty(self._npoints(), np.float64)
+        self.ctx.check(lib().yfd_cfem_expand(self._h, sol, out))
+        return out
+
+    def compress_map(self):
+        out = np.empty(self._npoints(), np.int64)
+        self.ctx.check(lib().yfd_cfem_get_compress_map(self._h, out))
+        return out
+
+    def _npoints(self):
+        if not hasattr(self, "npoints"):
+            raise YfdError(1, "set System.npoints (mesh.npoints) before CFEM expand/compress_map")
+        return self.npoints

@@ -1,0 +1,627 @@
+/*
+ * yfd_cg.cu -- SpMV kernels and the conjugate-gradient solver.
+ *
+ * Replaces conjugated_gradient (core/solvers.hpp:46-138 plain, :141-243 preconditioned) and the
+ * Blaze expression kernels it expands to: y = A*d as a sequential row-times-vector loop
+ * (blaze/math/expressions/SMatDVecMultExpr.h:204-207), three dot products / norms and three
+ * axpy-like vector expressions per iteration, each a separate pass over memory.
+ *
+ * One CG iteration here is THREE launches (the algorithm and its recurrences are the
+ * reference's, core/solvers.hpp:115-125; only the schedule differs):
+ *   K1  y = A d            fused with the partial sums of d.y
+ *   K2  x += alpha d ; r -= alpha y ; [z = iM r]      fused with r.r and r.z
+ *   K3  d = z + beta d     + iteration bookkeeping (rho, ||r||, stop test, history)
+ * Scalars never leave the device: every block writes its partial sum, the last block to finish
+ * (ticket counter) adds the partials in a fixed order, so results are bit-reproducible run to run.
+ * The stop test `nr/nr0 > rr_tol && iter < max_iter && nr/nr0 < rr_max` (core/solvers.hpp:99) is
+ * evaluated on the device after every iteration and raises a flag that turns the remaining
+ * launches of the current batch into no-ops; the host polls the flag once per batch of
+ * `check_every` iterations, replayed as one CUDA graph.
+ *
+ * SpMV kernels (HBM-bound; SURVEY.md section 8d gives the algorithmic bytes):
+ *   csr_spmv<TS>     any CSR.  A team of TS lanes per row, each lane owns 16-byte aligned quads:
+ *                    two 128-bit value loads + one 128-bit column load per quad, x through the
+ *                    read-only path, warp-shuffle team reduction.
+ *   dg_spmv<BS,TS>   DG block rows.  Same value stream (the CSR value array itself), but column
+ *                    indices are rebuilt from the per-cell block list (<= 5 ints per cell), so the
+ *                    4 B/nnz colidx stream is never read: 8 B/nnz instead of 12 B/nnz.
+ */
+#include "yfd_internal.hpp"
+#include <cmath>
+#include <algorithm>
+
+namespace yfd {
+
+constexpr int CG_THREADS = 256;
+constexpr int CG_MAX_PARTIALS = 4096;
+
+struct cg_scalars {
+    double rho;            /* r.z of the current iterate (r.r without preconditioner) */
+    double dy;             /* d.y */
+    double rr_new, rz_new;
+    double nr0, nr;
+    long long iter;
+    long long max_iter;
+    double rr_tol, rr_max;
+    int    done;
+    unsigned int ticket[3];
+};
+
+/* ---- deterministic block + grid reduction ------------------------------------------- */
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+/* sum over the block; result valid in thread 0 */
+__device__ __forceinline__ double block_sum(double v, double *sm /* [32] */)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sm[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        v = lane < (int) (blockDim.x >> 5) ? sm[lane] : 0.0;
+        v = warp_sum(v);
+    }
+    return v;
+}
+
+/* Every block contributes NV partial sums; the last block to arrive reduces all of them in index
+ * order and returns true in ALL its threads with the totals in out[] (shared). */
+template <int NV>
+__device__ __forceinline__ bool grid_sum(const double (&v)[NV], double *partials, unsigned int *ticket, double *out_sm)
+{
+    __shared__ double sm[32];
+    __shared__ bool last;
+    double t[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) t[k] = block_sum(v[k], sm);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; k++) partials[(size_t) k * CG_MAX_PARTIALS + blockIdx.x] = t[k];
+        __threadfence();
+        const unsigned int prev = atomicInc(ticket, gridDim.x - 1);    /* wraps to 0: self-resetting */
+        last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return false;
+    __threadfence();
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+        double s = 0.0;
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+            s += ((volatile double *) partials)[(size_t) k * CG_MAX_PARTIALS + b];
+        s = block_sum(s, sm);
+        if (threadIdx.x == 0) out_sm[k] = s;
+    }
+    __syncthreads();
+    return true;
+}
+
+/* ---- K1: SpMV ------------------------------------------------------------------------- */
+template <int TS>
+__device__ __forceinline__ double team_sum(double v)
+{
+#pragma unroll
+    for (int o = TS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int TS, bool WITH_DOT>
+__global__ void __launch_bounds__(CG_THREADS)
+csr_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx, const double *__restrict__ values,
+         const double *__restrict__ x, double *__restrict__ y, int64_t nrows,
+         cg_scalars *__restrict__ sc, double *__restrict__ partials)
+{
+    if (WITH_DOT && sc->done) return;
+    const int tl = threadIdx.x & (TS - 1);
+    const int team_in_warp = (threadIdx.x & 31) / TS;
+    const int64_t nteams = ((int64_t) gridDim.x * blockDim.x) / TS;
+    double dot = 0.0;
+    /* the loop bound is WARP-uniform (first row of the warp): the team reduction below is a
+     * full-mask shuffle, so every lane of the warp must take the same number of trips */
+    for (int64_t wrow = ((int64_t) blockIdx.x * blockDim.x + (threadIdx.x & ~31)) / TS; wrow < nrows; wrow += nteams) {
+        const int64_t row = wrow + team_in_warp;
+        const bool live = row < nrows;
+        const int64_t s = live ? __ldg(&rowptr[row]) : 0, e = live ? __ldg(&rowptr[row + 1]) : 0;
+        double acc = 0.0;
+        for (int64_t q = (s & ~(int64_t) 3) + 4 * tl; q < e; q += 4 * TS) {
+            const int4 c = __ldg(reinterpret_cast<const int4 *>(colidx + q));
+            const double2 v0 = __ldg(reinterpret_cast<const double2 *>(values + q));
+            const double2 v1 = __ldg(reinterpret_cast<const double2 *>(values + q + 2));
+            if (q >= s && q + 3 < e) {
+                acc += v0.x * __ldg(&x[c.x]);
+                acc += v0.y * __ldg(&x[c.y]);
+                acc += v1.x * __ldg(&x[c.z]);
+                acc += v1.y * __ldg(&x[c.w]);
+            } else {
+                if (q     >= s && q     < e) acc += v0.x * __ldg(&x[c.x]);
+                if (q + 1 >= s && q + 1 < e) acc += v0.y * __ldg(&x[c.y]);
+                if (q + 2 >= s && q + 2 < e) acc += v1.x * __ldg(&x[c.z]);
+                if (q + 3 >= s && q + 3 < e) acc += v1.y * __ldg(&x[c.w]);
+            }
+        }
+        acc = team_sum<TS>(acc);
+        if (tl == 0 && live) {
+            y[row] = acc;
+            if (WITH_DOT) dot += acc * __ldg(&x[row]);
+        }
+    }
+    if (WITH_DOT) {
+        __shared__ double tot[1];
+        const double v[1] = { dot };
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) sc->dy = tot[0];
+    }
+}
+
+template <int BS, int TS, bool WITH_DOT>
+__global__ void __launch_bounds__(CG_THREADS)
+dg_spmv(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const double *__restrict__ values,
+        const double *__restrict__ x, double *__restrict__ y, int64_t nrows,
+        cg_scalars *__restrict__ sc, double *__restrict__ partials)
+{
+    if (WITH_DOT && sc->done) return;
+    const int tl = threadIdx.x & (TS - 1);
+    const int team_in_warp = (threadIdx.x & 31) / TS;
+    const int64_t nteams = ((int64_t) gridDim.x * blockDim.x) / TS;
+    double dot = 0.0;
+    /* warp-uniform trip count, see csr_spmv */
+    for (int64_t wrow = ((int64_t) blockIdx.x * blockDim.x + (threadIdx.x & ~31)) / TS; wrow < nrows; wrow += nteams) {
+        const int64_t row = wrow + team_in_warp;
+        const bool live = row < nrows;
+        const int64_t cell = live ? row / BS : 0;
+        const int i = live ? (int) (row - cell * BS) : 0;
+        const int64_t cp = __ldg(&cellptr[cell]);
+        const int nblk = live ? (int) (__ldg(&cellptr[cell + 1]) - cp) : 0;
+        const int L = nblk * BS;
+        const int64_t s = cp * (BS * BS) + (int64_t) i * L;
+        const int32_t *bc = blk_cell + cp;
+        double acc = 0.0;
+        /* lanes own 16-byte aligned pairs of the row's value run */
+        for (int l = 2 * tl - (int) (s & 1); l < L; l += 2 * TS) {
+            const double2 v = __ldg(reinterpret_cast<const double2 *>(values + s + l));
+            if (l >= 0) {
+                const int b = l / BS, j = l - b * BS;
+                acc += v.x * __ldg(&x[(int64_t) __ldg(&bc[b]) * BS + j]);
+            }
+            if (l + 1 < L) {
+                const int b = (l + 1) / BS, j = (l + 1) - b * BS;
+                acc += v.y * __ldg(&x[(int64_t) __ldg(&bc[b]) * BS + j]);
+            }
+        }
+        acc = team_sum<TS>(acc);
+        if (tl == 0 && live) {
+            y[row] = acc;
+            if (WITH_DOT) dot += acc * __ldg(&x[row]);
+        }
+    }
+    if (WITH_DOT) {
+        __shared__ double tot[1];
+        const double v[1] = { dot };
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) sc->dy = tot[0];
+    }
+}
+
+/* ---- start-up: r = b - y ; z = iM r ; d = z ; rho = r.z ; nr0 = ||r|| --------------------- */
+__global__ void __launch_bounds__(CG_THREADS)
+cg_init(const double *__restrict__ b, const double *__restrict__ y /* A x0 or null */, const double *__restrict__ pc,
+        double *__restrict__ r, double *__restrict__ z, double *__restrict__ d, int64_t n,
+        cg_scalars *__restrict__ sc, double *__restrict__ partials, double *__restrict__ history, int64_t history_cap)
+{
+    double rr = 0.0, rz = 0.0;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const double ri = y ? b[i] - y[i] : b[i];
+        const double zi = pc ? pc[i] * ri : ri;
+        r[i] = ri;
+        if (pc) z[i] = zi;
+        d[i] = zi;
+        rr += ri * ri;
+        rz += ri * zi;
+    }
+    __shared__ double tot[2];
+    const double v[2] = { rr, rz };
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) {
+        const double nr = sqrt(tot[0]);
+        sc->rho = tot[1];
+        sc->nr0 = nr; sc->nr = nr;
+        sc->iter = 0;
+        const double rel = nr / nr;            /* nr/nr0 with nr0 = nr: 1, or NaN when b = A x0 exactly */
+        sc->done = !(rel > sc->rr_tol && 0 < sc->max_iter && rel < sc->rr_max);
+        if (history && history_cap > 0) history[0] = rel;
+    }
+}
+
+/* ---- K2 ------------------------------------------------------------------------------------ */
+__global__ void __launch_bounds__(CG_THREADS)
+cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict__ z,
+             const double *__restrict__ d, const double *__restrict__ y, const double *__restrict__ pc, int64_t n,
+             cg_scalars *__restrict__ sc, double *__restrict__ partials)
+{
+    if (sc->done) return;
+    const double alpha = sc->rho / sc->dy;                 /* core/solvers.hpp:117-118 */
+    double rr = 0.0, rz = 0.0;
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    const int64_t n2 = n >> 1;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+        double2 xv = reinterpret_cast<double2 *>(x)[i], rv = reinterpret_cast<double2 *>(r)[i];
+        const double2 dv = reinterpret_cast<const double2 *>(d)[i], yv = reinterpret_cast<const double2 *>(y)[i];
+        xv.x += alpha * dv.x; xv.y += alpha * dv.y;
+        rv.x -= alpha * yv.x; rv.y -= alpha * yv.y;
+        reinterpret_cast<double2 *>(x)[i] = xv;
+        reinterpret_cast<double2 *>(r)[i] = rv;
+        rr += rv.x * rv.x + rv.y * rv.y;
+        if (pc) {
+            const double2 pv = reinterpret_cast<const double2 *>(pc)[i];
+            const double2 zv = make_double2(pv.x * rv.x, pv.y * rv.y);
+            reinterpret_cast<double2 *>(z)[i] = zv;
+            rz += rv.x * zv.x + rv.y * zv.y;
+        }
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        const int64_t i = n - 1;
+        const double xi = x[i] + alpha * d[i], ri = r[i] - alpha * y[i];
+        x[i] = xi; r[i] = ri;
+        rr += ri * ri;
+        if (pc) { const double zi = pc[i] * ri; z[i] = zi; rz += ri * zi; }
+    }
+    __shared__ double tot[2];
+    const double v[2] = { rr, pc ? rz : rr };
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+}
+
+/* ---- K3 ------------------------------------------------------------------------------------ */
+__global__ void __launch_bounds__(CG_THREADS)
+cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, else r */, int64_t n,
+            cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap)
+{
+    if (sc->done) return;
+    const double beta = sc->rz_new / sc->rho;              /* core/solvers.hpp:121 / :226 */
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    const int64_t n2 = n >> 1;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+        const double2 zv = reinterpret_cast<const double2 *>(zr)[i];
+        double2 dv = reinterpret_cast<double2 *>(d)[i];
+        dv.x = zv.x + beta * dv.x; dv.y = zv.y + beta * dv.y;
+        reinterpret_cast<double2 *>(d)[i] = dv;
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) d[n - 1] = zr[n - 1] + beta * d[n - 1];
+    /* bookkeeping by the last block: every other block has already read rho / rz_new */
+    __shared__ bool last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last = atomicInc(&sc->ticket[2], gridDim.x - 1) == gridDim.x - 1;
+        if (last) {
+            sc->rho = sc->rz_new;
+            const double nr = sqrt(sc->rr_new);            /* nr = norm(r), core/solvers.hpp:124 */
+            sc->nr = nr;
+            const long long it = sc->iter + 1;
+            sc->iter = it;
+            const double rel = nr / sc->nr0;
+            if (history && it < history_cap) history[it] = rel;
+            sc->done = !(rel > sc->rr_tol && it < sc->max_iter && rel < sc->rr_max);
+        }
+    }
+}
+
+/* y <- b - y helper is folded into cg_init; permutation helpers for the DG system */
+__global__ void permute_blocks(const double *__restrict__ in, double *__restrict__ out, const int32_t *__restrict__ map,
+                               int64_t ncells, int bs)
+{
+    /* out[c*bs + i] = in[map[c]*bs + i] */
+    const int64_t n = ncells * bs;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t c = t / bs;
+        const int i = (int) (t - c * bs);
+        out[t] = in[(int64_t) map[c] * bs + i];
+    }
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* host side                                                                                    */
+/* -------------------------------------------------------------------------------------------- */
+struct spmv_op {
+    /* generic */
+    const int64_t *rowptr = nullptr; const int32_t *colidx = nullptr; const double *values = nullptr;
+    int64_t nrows = 0, nnz = 0;
+    /* DG block rows */
+    const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
+};
+
+static int pick_team(double avg_row)
+{
+    if (avg_row <= 6) return 2;
+    if (avg_row <= 12) return 4;
+    if (avg_row <= 28) return 8;
+    if (avg_row <= 60) return 16;
+    return 32;
+}
+
+static unsigned spmv_grid(yfd_ctx *ctx, int64_t nrows, int ts)
+{
+    const int64_t teams_per_block = CG_THREADS / ts;
+    const int64_t want = ceil_div(nrows, teams_per_block);
+    const int64_t cap = std::min<int64_t>((int64_t) ctx->sm_count * 8, CG_MAX_PARTIALS);
+    return (unsigned) std::max<int64_t>(1, std::min(want, cap));
+}
+
+template <bool WITH_DOT>
+static yfd_status launch_csr_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
+{
+    const int ts = pick_team(op.nrows ? (double) op.nnz / (double) op.nrows : 1.0);
+    const unsigned g = spmv_grid(ctx, op.nrows, ts);
+    switch (ts) {
+    case 2:  YFD_LAUNCH(ctx, (csr_spmv<2, WITH_DOT>), g, CG_THREADS, 0, op.rowptr, op.colidx, op.values, x, y, op.nrows, sc, partials); break;
+    case 4:  YFD_LAUNCH(ctx, (csr_spmv<4, WITH_DOT>), g, CG_THREADS, 0, op.rowptr, op.colidx, op.values, x, y, op.nrows, sc, partials); break;
+    case 8:  YFD_LAUNCH(ctx, (csr_spmv<8, WITH_DOT>), g, CG_THREADS, 0, op.rowptr, op.colidx, op.values, x, y, op.nrows, sc, partials); break;
+    case 16: YFD_LAUNCH(ctx, (csr_spmv<16, WITH_DOT>), g, CG_THREADS, 0, op.rowptr, op.colidx, op.values, x, y, op.nrows, sc, partials); break;
+    default: YFD_LAUNCH(ctx, (csr_spmv<32, WITH_DOT>), g, CG_THREADS, 0, op.rowptr, op.colidx, op.values, x, y, op.nrows, sc, partials); break;
+    }
+    return YFD_OK;
+}
+
+template <int BS, bool WITH_DOT>
+static yfd_status launch_dg_spmv_bs(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
+{
+    /* interior row length = (1+nf)*BS values, each lane takes 2 per pass */
+    const int L = (1 + op.nf) * BS;
+    const int ts = L <= 16 ? 4 : L <= 32 ? 8 : L <= 80 ? 16 : 32;
+    const unsigned g = spmv_grid(ctx, op.nrows, ts);
+    switch (ts) {
+    case 4:  YFD_LAUNCH(ctx, (dg_spmv<BS, 4, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
+    case 8:  YFD_LAUNCH(ctx, (dg_spmv<BS, 8, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
+    case 16: YFD_LAUNCH(ctx, (dg_spmv<BS, 16, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
+    default: YFD_LAUNCH(ctx, (dg_spmv<BS, 32, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
+    }
+    return YFD_OK;
+}
+
+template <bool WITH_DOT>
+static yfd_status launch_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
+{
+    if (op.cellptr) {
+        switch (op.bs) {
+        case 1:  return launch_dg_spmv_bs<1, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 3:  return launch_dg_spmv_bs<3, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 6:  return launch_dg_spmv_bs<6, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 10: return launch_dg_spmv_bs<10, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 15: return launch_dg_spmv_bs<15, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 21: return launch_dg_spmv_bs<21, WITH_DOT>(ctx, op, x, y, sc, partials);
+        case 28: return launch_dg_spmv_bs<28, WITH_DOT>(ctx, op, x, y, sc, partials);
+        default: break;     /* fall through to the generic kernel */
+        }
+    }
+    return launch_csr_spmv<WITH_DOT>(ctx, op, x, y, sc, partials);
+}
+
+static unsigned vec_grid(yfd_ctx *ctx, int64_t n)
+{
+    const int64_t want = ceil_div(std::max<int64_t>(n / 2, 1), CG_THREADS);
+    const int64_t cap = std::min<int64_t>((int64_t) ctx->sm_count * 8, CG_MAX_PARTIALS);
+    return (unsigned) std::max<int64_t>(1, std::min(want, cap));
+}
+
+/* The solver proper: all vectors on the device, in the operator's numbering. */
+static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, double *d_x, const double *d_pc,
+                            const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap)
+{
+    const int64_t n = op.nrows;
+    if (p->use_normal_eqns)
+        return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns (core/solvers.hpp:88-91) is not on the symmetric hot path");
+    dbuf<double> r, d, y, z, partials, hist;
+    dbuf<cg_scalars> sc;
+    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(d.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
+    YFD_TRY(sc.alloc(ctx, 1));
+    int64_t hcap = 0;
+    if (p->save_iteration_history && host_history && history_cap > 0) {
+        hcap = std::min<int64_t>(history_cap, p->max_iter + 1);
+        YFD_TRY(hist.alloc(ctx, (size_t) hcap));
+    }
+    cg_scalars h0 = {};
+    h0.max_iter = p->max_iter; h0.rr_tol = p->rr_tol; h0.rr_max = p->rr_max;
+    YFD_CUDA(ctx, cudaMemcpyAsync(sc.p, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
+
+    gpu_timer timer;
+    timer.start(ctx->stream);
+    const unsigned vg = vec_grid(ctx, n);
+    if (p->use_initial_guess) {
+        YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));          /* r0 = b - A x (core/solvers.hpp:91) */
+        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+    } else {
+        YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
+        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+    }
+
+    /* one CUDA graph = `batch` iterations */
+    int batch = p->check_every > 0 ? p->check_every : 64;
+    if ((int64_t) batch > p->max_iter) batch = (int) std::max<int64_t>(p->max_iter, 1);
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    const int64_t launches_before = ctx->launches;
+    YFD_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+    yfd_status cap_st = YFD_OK;
+    for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
+        cap_st = launch_spmv<true>(ctx, op, d.p, y.p, sc.p, partials.p);
+        if (cap_st != YFD_OK) break;
+        cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, d.p, y.p, d_pc, n, sc.p, partials.p);
+        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(d.p, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
+        ctx->launches += 2;
+    }
+    {
+        cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+        if (cap_st != YFD_OK) { if (graph) cudaGraphDestroy(graph); return cap_st; }
+        if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+    }
+    const int64_t launches_per_graph = ctx->launches - launches_before;
+    ctx->launches = launches_before;            /* capture recorded, not executed */
+    {
+        cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+        if (e != cudaSuccess) { cudaGraphDestroy(graph); return fail(ctx, YFD_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e)); }
+    }
+    cg_scalars hs = {};
+    yfd_status st = YFD_OK;
+    for (;;) {
+        cudaError_t e = cudaMemcpyAsync(&hs, sc.p, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "CG poll: %s", cudaGetErrorString(e)); break; }
+        if (hs.done) break;
+        e = cudaGraphLaunch(exec, ctx->stream);
+        if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "graph launch: %s", cudaGetErrorString(e)); break; }
+        ctx->launches += launches_per_graph;
+    }
+    timer.stop(ctx->stream);
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+    if (st != YFD_OK) return st;
+    if (hcap > 0) {
+        const int64_t len = std::min<int64_t>(hcap, hs.iter + 1);
+        YFD_TRY(hist.download(ctx, host_history, (size_t) len));
+        if (info) info->history_len = len;
+    } else if (info) info->history_len = 0;
+    if (info) {
+        info->iterations = hs.iter;
+        info->nr0 = hs.nr0;
+        info->nr = hs.nr;
+        info->converged = (hs.nr / hs.nr0 <= p->rr_tol) ? 1 : 0;
+        info->ms_solve = timer.ms();
+        info->ms_spmv = 0.0;
+    }
+    return YFD_OK;
+}
+
+static spmv_op op_of_csr(const yfd_csr *A)
+{
+    spmv_op op;
+    op.rowptr = A->rowptr.p; op.colidx = A->colidx.p; op.values = A->values.p;
+    op.nrows = A->nrows; op.nnz = A->nnz;
+    return op;
+}
+
+static spmv_op op_of_system(const yfd_system *sys, bool allow_block_kernel)
+{
+    spmv_op op = op_of_csr(&sys->A);
+    if (sys->kind == YFD_SYS_DG && allow_block_kernel) {
+        op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf;
+    }
+    return op;
+}
+
+static unsigned stream_grid(yfd_ctx *ctx, int64_t n)
+{
+    const int64_t want = ceil_div(n > 0 ? n : 1, 256), cap = (int64_t) ctx->sm_count * 16;
+    return (unsigned) (want < cap ? want : cap);
+}
+
+} // namespace yfd
+
+using namespace yfd;
+
+extern "C" {
+
+void yfd_cg_params_default(yfd_cg_params *p)
+{
+    /* conjugated_gradient_params() (core/solvers.hpp:35-42) */
+    p->rr_tol = 1e-8;
+    p->rr_max = 20;
+    p->max_iter = 100;
+    p->use_initial_guess = 0;
+    p->use_normal_eqns = 0;
+    p->save_iteration_history = 0;
+    p->check_every = 0;
+}
+
+yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y)
+{
+    if (!ctx || !A || !x || !y) return YFD_ERR_INVALID_ARGUMENT;
+    scoped_device dev(ctx->device);
+    dbuf<double> dx, dy;
+    YFD_TRY(dx.alloc(ctx, (size_t) A->ncols, 2)); YFD_TRY(dy.alloc(ctx, (size_t) A->nrows, 2));
+    YFD_TRY(dx.upload(ctx, x, (size_t) A->ncols));
+    YFD_TRY(launch_spmv<false>(ctx, op_of_csr(A), dx.p, dy.p, nullptr, nullptr));
+    return dy.download(ctx, y, (size_t) A->nrows);
+}
+
+yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                        const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    if (!ctx || !A || !b || !x || !p) return YFD_ERR_INVALID_ARGUMENT;
+    if (A->nrows != A->ncols) return fail(ctx, YFD_ERR_SHAPE_MISMATCH, "[CG solver] A square matrix is required");
+    scoped_device dev(ctx->device);
+    const int64_t n = A->nrows;
+    dbuf<double> db, dx, dpc;
+    YFD_TRY(db.alloc(ctx, (size_t) n, 2)); YFD_TRY(dx.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(db.upload(ctx, b, (size_t) n));
+    if (p->use_initial_guess) YFD_TRY(dx.upload(ctx, x, (size_t) n));
+    if (pc_diag) { YFD_TRY(dpc.alloc(ctx, (size_t) n, 2)); YFD_TRY(dpc.upload(ctx, pc_diag, (size_t) n)); }
+    YFD_TRY(cg_device(ctx, op_of_csr(A), db.p, dx.p, pc_diag ? dpc.p : nullptr, p, info, history, history_cap));
+    return dx.download(ctx, x, (size_t) n);
+}
+
+yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                               double *x, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
+    if (use_pc && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
+    scoped_device dev(ctx->device);
+    const int64_t n = sys->n;
+    dbuf<double> dx, tmp;
+    YFD_TRY(dx.alloc(ctx, (size_t) n, 2));
+    const bool permuted = sys->kind == YFD_SYS_DG;
+    if (p->use_initial_guess) {
+        if (permuted) {
+            YFD_TRY(tmp.alloc(ctx, (size_t) n));
+            YFD_TRY(tmp.upload(ctx, x, (size_t) n));
+            YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, tmp.p, dx.p, sys->perm.p, sys->ncells, sys->bs);
+        } else {
+            YFD_TRY(dx.upload(ctx, x, (size_t) n));
+        }
+    }
+    YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
+    if (permuted) {
+        if (tmp.n == 0) YFD_TRY(tmp.alloc(ctx, (size_t) n));
+        /* x_ref[rc] = x_int[iperm[rc]] */
+        YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, dx.p, tmp.p, sys->iperm.p, sys->ncells, sys->bs);
+        return tmp.download(ctx, x, (size_t) n);
+    }
+    return dx.download(ctx, x, (size_t) n);
+}
+
+yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double *ms_per_launch,
+                                double *csr_bytes, double *kernel_bytes)
+{
+    if (!ctx || !sys || reps <= 0) return YFD_ERR_INVALID_ARGUMENT;
+    scoped_device dev(ctx->device);
+    const int64_t n = sys->n;
+    dbuf<double> x, y, partials;
+    dbuf<cg_scalars> sc;
+    YFD_TRY(x.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
+    YFD_TRY(sc.alloc(ctx, 1)); YFD_TRY(sc.zero(ctx));
+    YFD_CUDA(ctx, cudaMemcpyAsync(x.p, sys->rhs.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+    const spmv_op op = op_of_system(sys, true);
+    for (int i = 0; i < 3; i++) YFD_TRY(launch_spmv<true>(ctx, op, x.p, y.p, sc.p, partials.p));
+    gpu_timer t;
+    t.start(ctx->stream);
+    for (int i = 0; i < reps; i++) YFD_TRY(launch_spmv<true>(ctx, op, x.p, y.p, sc.p, partials.p));
+    t.stop(ctx->stream);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ms_per_launch) *ms_per_launch = t.ms() / reps;
+    /* 12 nnz + row offsets + x read once + y written once */
+    if (csr_bytes) *csr_bytes = 12.0 * (double) sys->nnz + 8.0 * (double) (n + 1) + 16.0 * (double) n;
+    if (kernel_bytes) {
+        if (op.cellptr)
+            *kernel_bytes = 8.0 * (double) sys->nnz + 8.0 * (double) (sys->ncells + 1) + 4.0 * (double) sys->blk_cell.n + 16.0 * (double) n;
+        else
+            *kernel_bytes = 12.0 * (double) sys->nnz + 8.0 * (double) (n + 1) + 16.0 * (double) n;
+    }
+    return YFD_OK;
+}
+
+} /* extern "C" */

@@ -1,0 +1,80 @@
+/*
+ * yfd_comm.cpp -- NCCL attachment of a context (multi-GPU).
+ * The reference has no distributed layer.  NCCL is loaded at run time from the copy PyTorch
+ * ships (libnccl.so.2 is already mapped into any process that imported torch), so the library
+ * itself has no link-time dependency on it and single-GPU users never touch it.
+ */
+#include "yfd_internal.hpp"
+#include <dlfcn.h>
+#include <cstring>
+
+namespace {
+
+typedef struct { char internal[128]; } nccl_unique_id;
+typedef int (*fn_get_unique_id)(nccl_unique_id *);
+typedef int (*fn_comm_init_rank)(void **, int, nccl_unique_id, int);
+typedef int (*fn_comm_destroy)(void *);
+typedef const char *(*fn_get_error_string)(int);
+
+struct nccl_api {
+    void *handle = nullptr;
+    fn_get_unique_id get_unique_id = nullptr;
+    fn_comm_init_rank comm_init_rank = nullptr;
+    fn_comm_destroy comm_destroy = nullptr;
+    fn_get_error_string error_string = nullptr;
+    bool ok = false;
+};
+
+nccl_api &api()
+{
+    static nccl_api a;
+    if (a.handle || a.ok) return a;
+    const char *names[] = { "libnccl.so.2", "libnccl.so", nullptr };
+    for (int i = 0; names[i] && !a.handle; i++) a.handle = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+    if (!a.handle) return a;
+    a.get_unique_id = (fn_get_unique_id) dlsym(a.handle, "ncclGetUniqueId");
+    a.comm_init_rank = (fn_comm_init_rank) dlsym(a.handle, "ncclCommInitRank");
+    a.comm_destroy = (fn_comm_destroy) dlsym(a.handle, "ncclCommDestroy");
+    a.error_string = (fn_get_error_string) dlsym(a.handle, "ncclGetErrorString");
+    a.ok = a.get_unique_id && a.comm_init_rank && a.comm_destroy;
+    return a;
+}
+
+} // namespace
+
+extern "C" {
+
+void yfd_comm_destroy_internal(yfd_ctx *ctx)
+{
+    if (ctx && ctx->comm && api().ok) api().comm_destroy(ctx->comm);
+    if (ctx) ctx->comm = nullptr;
+}
+
+yfd_status yfd_comm_unique_id(unsigned char id[YFD_COMM_ID_BYTES])
+{
+    if (!id) return YFD_ERR_INVALID_ARGUMENT;
+    if (!api().ok) return YFD_ERR_COMM;
+    nccl_unique_id u;
+    if (api().get_unique_id(&u) != 0) return YFD_ERR_COMM;
+    static_assert(sizeof(u) == YFD_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+    std::memcpy(id, &u, sizeof(u));
+    return YFD_OK;
+}
+
+yfd_status yfd_ctx_attach_comm(yfd_ctx *ctx, int rank, int nranks, const unsigned char id[YFD_COMM_ID_BYTES])
+{
+    if (!ctx || !id || nranks < 1 || rank < 0 || rank >= nranks) return YFD_ERR_INVALID_ARGUMENT;
+    if (!api().ok) return yfd::fail(ctx, YFD_ERR_COMM, "libnccl.so.2 could not be loaded: %s", dlerror());
+    yfd::scoped_device dev(ctx->device);
+    nccl_unique_id u;
+    std::memcpy(&u, id, sizeof(u));
+    void *comm = nullptr;
+    const int rc = api().comm_init_rank(&comm, nranks, u, rank);
+    if (rc != 0) return yfd::fail(ctx, YFD_ERR_COMM, "ncclCommInitRank: %s", api().error_string ? api().error_string(rc) : "error");
+    ctx->comm = comm;
+    ctx->rank = rank;
+    ctx->nranks = nranks;
+    return YFD_OK;
+}
+
+} /* extern "C" */

@@ -1,0 +1,118 @@
+/*
+ * yfd_ctx.cu -- context lifetime, status strings, error plumbing (include/yfd.h).
+ * No reference counterpart: the reference is a single-threaded host program.
+ */
+#include "yfd_internal.hpp"
+#include <cstring>
+
+namespace yfd {
+
+yfd_status fail(yfd_ctx *ctx, yfd_status s, const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    return s;
+}
+
+} // namespace yfd
+
+extern "C" {
+
+const char *yfd_status_string(yfd_status s)
+{
+    switch (s) {
+    case YFD_OK:                   return "ok";
+    case YFD_ERR_INVALID_ARGUMENT: return "invalid argument";
+    case YFD_ERR_INVALID_STATE:    return "Assembler in invalid state";
+    case YFD_ERR_CELL_NOT_FOUND:   return "Mesh cell not found";
+    case YFD_ERR_FACE_NOT_FOUND:   return "Mesh face not found";
+    case YFD_ERR_DEGREE_TOO_HIGH:  return "Dunavant quadrature: degree too high";
+    case YFD_ERR_NO_NEIGHBOURS:    return "No neighbour information.";
+    case YFD_ERR_TOO_MANY_OWNERS:  return "BUG: a face has max 2 owners";
+    case YFD_ERR_SHAPE_MISMATCH:   return "shape mismatch";
+    case YFD_ERR_UNSUPPORTED:      return "unsupported";
+    case YFD_ERR_NO_DEVICE:        return "no CUDA device (this library has no CPU path)";
+    case YFD_ERR_CUDA:             return "CUDA error";
+    case YFD_ERR_COMM:             return "NCCL error";
+    case YFD_ERR_OUT_OF_MEMORY:    return "out of device memory";
+    }
+    return "unknown status";
+}
+
+yfd_status yfd_ctx_create(int device, void *stream, yfd_ctx **out)
+{
+    if (!out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return YFD_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev) return YFD_ERR_INVALID_ARGUMENT;
+    if (cudaSetDevice(device) != cudaSuccess) return YFD_ERR_NO_DEVICE;
+
+    yfd_ctx *ctx = new yfd_ctx();
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return YFD_ERR_NO_DEVICE; }
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->cc_major = prop.major;
+    ctx->cc_minor = prop.minor;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->name = prop.name;
+    if (stream) {
+        ctx->stream = (cudaStream_t) stream;
+        ctx->own_stream = false;
+    } else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return YFD_ERR_CUDA; }
+        ctx->own_stream = true;
+    }
+    *out = ctx;
+    return YFD_OK;
+}
+
+void yfd_comm_destroy_internal(yfd_ctx *ctx);   /* yfd_comm.cpp */
+
+void yfd_ctx_destroy(yfd_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    yfd_comm_destroy_internal(ctx);
+    if (ctx->tab_gauss_x) cudaFree(ctx->tab_gauss_x);
+    if (ctx->tab_gauss_w) cudaFree(ctx->tab_gauss_w);
+    if (ctx->tab_dunavant) cudaFree(ctx->tab_dunavant);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *yfd_last_error(const yfd_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+yfd_status yfd_ctx_synchronize(yfd_ctx *ctx)
+{
+    if (!ctx) return YFD_ERR_INVALID_ARGUMENT;
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+int64_t yfd_ctx_launch_count(const yfd_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+yfd_status yfd_ctx_device_info(const yfd_ctx *ctx, char *name, size_t cap, int *sm_count, int *cc_major, int *cc_minor)
+{
+    if (!ctx) return YFD_ERR_INVALID_ARGUMENT;
+    if (name && cap) { std::strncpy(name, ctx->name.c_str(), cap - 1); name[cap - 1] = 0; }
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (cc_major) *cc_major = ctx->cc_major;
+    if (cc_minor) *cc_minor = ctx->cc_minor;
+    return YFD_OK;
+}
+
+int yfd_ctx_rank(const yfd_ctx *ctx) { return ctx ? ctx->rank : 0; }
+int yfd_ctx_nranks(const yfd_ctx *ctx) { return ctx ? ctx->nranks : 1; }
+
+} /* extern "C" */

@@ -1,0 +1,597 @@
+/*
+ * yfd_dg.cu -- DG-SIP diffusion: batched element kernel + direct block-CSR build.
+ *
+ * Replaces the serial cell loop of run_diffusion_solver (dg2d_diffusion.cpp:133-201) and the
+ * triplet machinery behind it (assembler::assemble, methods/dg.hpp:67-123; finalize ->
+ * init_from_triplets, methods/dg.hpp:125-144) for the DG case, where the sparsity pattern is
+ * known from face_owners: row block c holds the diagonal block  K + sum_e Att_e  and one block
+ * Atn_e per neighbour, blocks ordered by column = ascending cell id.  No sort is needed; the
+ * generic sort-based path (yfd_triplets.cu) stays for CFEM and for the drop-in
+ * init_from_triplets.
+ *
+ * Kernel shape (sm_100a): one warp per cell.  Per cell the warp
+ *   1. evaluates the scaled-monomial basis  phi = xt^(d-i) yt^i,  xt = (x-xb)/(h/2)
+ *      (cell_basis_bones::eval / eval_grads, core/bases.hpp:96-155) at the physical quadrature
+ *      points (Dunavant, core/quadratures.hpp:570-627; tensor Gauss + bilinear map, :804-861;
+ *      1D Gauss on faces, :723-746) -- one lane per quadrature point -- and stages the tables
+ *      phi, d_x phi, d_y phi (cell) / phi, grad phi . n for both sides (face) in shared memory;
+ *   2. contracts them: one lane per block entry (i,j), fp64 FMA, accumulators in registers;
+ *   3. streams the finished rows straight into the CSR value array (coalesced bs-wide runs).
+ * The basis is defined in PHYSICAL coordinates scaled by the cell diameter, so tables cannot be
+ * shared between cells in general (hard part 4); only the reference rule
+ * (barycentric / Gauss abscissae and weights) is shared and read through the read-only path.
+ * Small dense contractions: FP64 FMA, no tensor cores (north_star: only if ncu shows a win).
+ */
+#include "yfd_internal.hpp"
+#include <cmath>
+
+namespace yfd {
+
+constexpr int DG_MAX_DEGREE = 6;          /* bs = 28, 25 accumulators per lane */
+constexpr int DG_WARPS = 4;               /* warps (cells) per CTA */
+
+struct dg_args {
+    const double2 *pts;
+    const int32_t *cells;
+    const int32_t *cell_faces;
+    const int2    *faces;
+    const int2    *face_owners;
+    const int32_t *perm, *iperm;
+    int64_t        ncells;
+    double         eta;                   /* 3 k^2 cfg.eta (dg2d_diffusion.cpp:127) */
+    int            rhs_fn, dir_fn;
+    const double  *cell_rule;             /* tri: (c0,c1,c2,w)[nq] ; quad: unused */
+    const double  *gx, *gw;               /* 1D Gauss rule of k+1 points (faces, quad cells) */
+    /* CSR sink (internal numbering) */
+    const int64_t *cellptr;
+    const int8_t  *slots;                 /* [ncells][NV+1] */
+    double        *values, *rhs, *pc;
+    /* per-cell block sink (reference numbering), yfd_dg_local_blocks */
+    double        *oK, *oAtt, *oAtn, *orhs;
+    int            blocks_mode;
+};
+
+__device__ __forceinline__ double eval_fn(int fn, double x, double y)
+{
+    switch (fn) {
+    case YFD_FN_SINSIN: {
+        const double sx = sin(M_PI * x), sy = sin(M_PI * y);
+        return 2.0 * M_PI * M_PI * sx * sy;         /* data::rhs, dg2d_diffusion.cpp:53-59 */
+    }
+    case YFD_FN_ONE: return 1.0;
+    default: return 0.0;
+    }
+}
+
+__host__ __device__ constexpr int dg_nq_cell(int nv, int k)
+{
+    /* Dunavant point counts for degree 2k (degree 0 uses rule 1) */
+    return nv == 4 ? (k + 1) * (k + 1)
+                   : (k == 0 ? 1 : k == 1 ? 3 : k == 2 ? 6 : k == 3 ? 12 : k == 4 ? 16 : k == 5 ? 25 : 33);
+}
+
+template <int K>
+struct basis_eval {
+    static constexpr int BS = (K + 2) * (K + 1) / 2;
+    /* phi[i], gx[i], gy[i] for all i at physical point (x,y); frame (xb,yb,h) */
+    __device__ static __forceinline__ void run(double x, double y, double xb, double yb, double h,
+                                               double *phi, double *gx, double *gy, int stride)
+    {
+        const double half_h = 0.5 * h;
+        const double bx = (x - xb) / half_h, by = (y - yb) / half_h;
+        const double ih = 2.0 / h;
+        double px[K + 1], py[K + 1];
+        px[0] = 1.0; py[0] = 1.0;
+#pragma unroll
+        for (int p = 1; p <= K; p++) { px[p] = px[p - 1] * bx; py[p] = py[p - 1] * by; }
+        int pos = 0;
+#pragma unroll
+        for (int d = 0; d <= K; d++) {
+#pragma unroll
+            for (int i = 0; i <= d; i++) {
+                const int ex = d - i, ey = i;
+                phi[pos * stride] = px[ex] * py[ey];
+                const double dx = ex == 0 ? 0.0 : (double) ex * ih * px[ex == 0 ? 0 : ex - 1];
+                const double dy = ey == 0 ? 0.0 : (double) ey * ih * py[ey == 0 ? 0 : ey - 1];
+                gx[pos * stride] = dx * py[ey];
+                gy[pos * stride] = px[ex] * dy;
+                pos++;
+            }
+        }
+    }
+};
+
+template <int NV>
+__device__ __forceinline__ void cell_frame(const double2 *P, double &xb, double &yb, double &h)
+{
+    /* barycenter (core/mesh.hpp:424-441), diameter = max pairwise vertex distance (:474-487) */
+    double sx = P[0].x, sy = P[0].y;
+#pragma unroll
+    for (int v = 1; v < NV; v++) { sx += P[v].x; sy += P[v].y; }
+    xb = sx / (double) NV; yb = sy / (double) NV;
+    double d = 0.0;
+#pragma unroll
+    for (int a = 0; a < NV; a++)
+#pragma unroll
+        for (int b = a + 1; b < NV; b++) {
+            const double dx = P[a].x - P[b].x, dy = P[a].y - P[b].y;
+            d = fmax(sqrt(dx * dx + dy * dy), d);
+        }
+    h = d;
+}
+
+template <int NV, int K>
+__global__ void __launch_bounds__(DG_WARPS * 32)
+dg_sip_cells(const dg_args a)
+{
+    constexpr int BS   = (K + 2) * (K + 1) / 2;
+    constexpr int BS2  = BS * BS;
+    constexpr int NACC = (BS2 + 31) / 32;
+    constexpr int NQ   = dg_nq_cell(NV, K);
+    constexpr int NFQ  = K + 1;
+    /* shared tables, reused between the cell phase and each face phase */
+    constexpr int CELL_DBL = NQ * (2 + 3 * BS);
+    constexpr int FACE_DBL = NFQ * (2 + 4 * BS);
+    constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
+    extern __shared__ double smem_all[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *S = smem_all + (size_t) warp * WARP_DBL;
+
+    const int64_t nwarps = (int64_t) gridDim.x * DG_WARPS;
+    for (int64_t cell = (int64_t) blockIdx.x * DG_WARPS + warp; cell < a.ncells; cell += nwarps) {
+        const int32_t rc = a.perm[cell];
+        double2 P[NV];
+#pragma unroll
+        for (int v = 0; v < NV; v++) P[v] = __ldg(&a.pts[a.cells[(int64_t) NV * rc + v]]);
+        double xb, yb, h;
+        cell_frame<NV>(P, xb, yb, h);
+
+        /* ---------------- cell quadrature: tables ---------------- */
+        double *W = S, *WF = S + NQ, *PHI = S + 2 * NQ, *DX = PHI + NQ * BS, *DY = DX + NQ * BS;
+        for (int q = lane; q < NQ; q += 32) {
+            double x, y, w;
+            if (NV == 3) {
+                /* triangle_quadrature_dunavant, core/quadratures.hpp:583-624 */
+                const double c0 = __ldg(&a.cell_rule[4 * q]), c1 = __ldg(&a.cell_rule[4 * q + 1]);
+                const double c2 = __ldg(&a.cell_rule[4 * q + 2]), cw = __ldg(&a.cell_rule[4 * q + 3]);
+                const double v0x = P[1].x - P[0].x, v0y = P[1].y - P[0].y;
+                const double v1x = P[2].x - P[0].x, v1y = P[2].y - P[0].y;
+                const double area = fabs((v0x * v1y - v0y * v1x) / 2.0);
+                x = P[0].x * c0 + P[1].x * c1 + P[2].x * c2;
+                y = P[0].y * c0 + P[1].y * c1 + P[2].y * c2;
+                w = cw * area;
+            } else {
+                /* quadrangle_quadrature + bilinear map, core/quadratures.hpp:775-861: eta outer, xi inner */
+                const int iy = q / (K + 1), ix = q - iy * (K + 1);
+                const double xi = __ldg(&a.gx[ix]), et = __ldg(&a.gx[iy]);
+                const double w2 = __ldg(&a.gw[ix]) * __ldg(&a.gw[iy]);
+                x = 0.25 * P[0].x * (1 - xi) * (1 - et) + 0.25 * P[1].x * (1 + xi) * (1 - et) +
+                    0.25 * P[2].x * (1 + xi) * (1 + et) + 0.25 * P[NV - 1].x * (1 - xi) * (1 + et);
+                y = 0.25 * P[0].y * (1 - xi) * (1 - et) + 0.25 * P[1].y * (1 + xi) * (1 - et) +
+                    0.25 * P[2].y * (1 + xi) * (1 + et) + 0.25 * P[NV - 1].y * (1 - xi) * (1 + et);
+                const double j11 = 0.25 * ((P[1].x - P[0].x) * (1 - et) + (P[2].x - P[NV - 1].x) * (1 + et));
+                const double j12 = 0.25 * ((P[1].y - P[0].y) * (1 - et) + (P[2].y - P[NV - 1].y) * (1 + et));
+                const double j21 = 0.25 * ((P[NV - 1].x - P[0].x) * (1 - xi) + (P[2].x - P[1].x) * (1 + xi));
+                const double j22 = 0.25 * ((P[NV - 1].y - P[0].y) * (1 - xi) + (P[2].y - P[1].y) * (1 + xi));
+                w = w2 * fabs(j11 * j22 - j12 * j21);
+            }
+            W[q] = w;
+            WF[q] = w * eval_fn(a.rhs_fn, x, y);
+            basis_eval<K>::run(x, y, xb, yb, h, PHI + q, DX + q, DY + q, NQ);     /* [i][q] layout */
+        }
+        __syncwarp();
+
+        /* ---------------- cell contraction: K and rhs ---------------- */
+        double accD[NACC];
+#pragma unroll
+        for (int t = 0; t < NACC; t++) {
+            const int m = t * 32 + lane;
+            double s = 0.0;
+            if (m < BS2) {
+                const int i = m / BS, j = m - i * BS;
+                for (int q = 0; q < NQ; q++)
+                    s += W[q] * (DX[i * NQ + q] * DX[j * NQ + q] + DY[i * NQ + q] * DY[j * NQ + q]);
+            }
+            accD[t] = s;
+        }
+        double rhs_i = 0.0;                     /* lanes < BS; BS <= 28 */
+        if (lane < BS)
+            for (int q = 0; q < NQ; q++) rhs_i += WF[q] * PHI[lane * NQ + q];
+
+        if (a.blocks_mode) {
+            if (a.oK) {
+#pragma unroll
+                for (int t = 0; t < NACC; t++) {
+                    const int m = t * 32 + lane;
+                    if (m < BS2) a.oK[(int64_t) rc * BS2 + m] = accD[t];
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < NACC; t++) accD[t] = 0.0;
+        }
+        __syncwarp();
+
+        /* ---------------- faces ---------------- */
+        const int64_t cp = a.blocks_mode ? 0 : a.cellptr[cell];
+        const int nblk = a.blocks_mode ? 0 : (int) (a.cellptr[cell + 1] - cp);
+        double *vrow = a.blocks_mode ? nullptr : a.values + cp * BS2;
+
+        double *FW = S, *FG = S + NFQ, *TPHI = S + 2 * NFQ, *TGN = TPHI + NFQ * BS, *NPHI = TGN + NFQ * BS, *NGN = NPHI + NFQ * BS;
+#pragma unroll 1
+        for (int e = 0; e < NV; e++) {
+            const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
+            const int2 fp = __ldg(&a.faces[f]);
+            const int2 own = __ldg(&a.face_owners[f]);
+            const int32_t nrc = own.x == rc ? own.y : own.x;     /* neighbour_via, core/mesh.hpp:249-272 */
+            const bool has_nb = nrc >= 0;
+            const double2 A = __ldg(&a.pts[fp.x]), B = __ldg(&a.pts[fp.y]);   /* p0 < p1 by point id */
+            const double ex = B.x - A.x, ey = B.y - A.y;
+            const double len = sqrt((A.x - B.x) * (A.x - B.x) + (A.y - B.y) * (A.y - B.y));   /* measure == diameter for an edge */
+            const double eta_l = a.eta / len;
+            /* normal(), core/mesh.hpp:505-530 */
+            double nx = -ey, ny = ex;
+            {
+                const double fbx = (A.x + B.x) / 2.0, fby = (A.y + B.y) / 2.0;
+                if (nx * (fbx - xb) + ny * (fby - yb) < 0.0) { nx = -nx; ny = -ny; }
+                const double inv = 1.0 / sqrt(nx * nx + ny * ny);
+                nx *= inv; ny *= inv;
+            }
+            double nxb = 0, nyb = 0, nh = 1;
+            if (has_nb) {
+                double2 Q[NV];
+#pragma unroll
+                for (int v = 0; v < NV; v++) Q[v] = __ldg(&a.pts[a.cells[(int64_t) NV * nrc + v]]);
+                cell_frame<NV>(Q, nxb, nyb, nh);
+            }
+            for (int q = lane; q < NFQ; q += 32) {
+                /* integrate(msh, face, 2k), core/quadratures.hpp:723-746 */
+                const double t = __ldg(&a.gx[q]);
+                const double x = 0.5 * (1 - t) * A.x + 0.5 * (1 + t) * B.x;
+                const double y = 0.5 * (1 - t) * A.y + 0.5 * (1 + t) * B.y;
+                const double w = __ldg(&a.gw[q]) * len * 0.5;
+                FW[q] = w;
+                FG[q] = has_nb ? 0.0 : w * eval_fn(a.dir_fn, x, y);
+                double phi[BS], gx[BS], gy[BS];
+                basis_eval<K>::run(x, y, xb, yb, h, phi, gx, gy, 1);
+#pragma unroll
+                for (int i = 0; i < BS; i++) { TPHI[i * NFQ + q] = phi[i]; TGN[i * NFQ + q] = gx[i] * nx + gy[i] * ny; }
+                if (has_nb) {
+                    basis_eval<K>::run(x, y, nxb, nyb, nh, phi, gx, gy, 1);
+#pragma unroll
+                    for (int i = 0; i < BS; i++) { NPHI[i * NFQ + q] = phi[i]; NGN[i * NFQ + q] = gx[i] * nx + gy[i] * ny; }
+                }
+            }
+            __syncwarp();
+
+            const double c = has_nb ? 0.5 : 1.0;         /* dg2d_diffusion.cpp:171-173 vs :186-188 */
+            const int slot = a.blocks_mode ? -1 : (int) a.slots[cell * (NV + 1) + 1 + e];
+#pragma unroll
+            for (int t = 0; t < NACC; t++) {
+                const int m = t * 32 + lane;
+                if (m < BS2) {
+                    const int i = m / BS, j = m - i * BS;
+                    double att = 0.0, atn = 0.0;
+                    for (int q = 0; q < NFQ; q++) {
+                        const double w = FW[q];
+                        const double ti = TPHI[i * NFQ + q], tj = TPHI[j * NFQ + q];
+                        const double gi = TGN[i * NFQ + q], gj = TGN[j * NFQ + q];
+                        att += w * (eta_l * ti * tj - c * ti * gj - c * gi * tj);
+                        if (has_nb) {
+                            const double pj = NPHI[j * NFQ + q], hj = NGN[j * NFQ + q];
+                            atn += w * (-eta_l * ti * pj - 0.5 * ti * hj + 0.5 * gi * pj);    /* :178-180 */
+                        }
+                    }
+                    accD[t] += att;
+                    if (a.blocks_mode) {
+                        if (a.oAtt) a.oAtt[((int64_t) rc * NV + e) * BS2 + m] = accD[t];
+                        if (a.oAtn) a.oAtn[((int64_t) rc * NV + e) * BS2 + m] = atn;
+                        accD[t] = 0.0;
+                    } else if (has_nb) {
+                        vrow[(int64_t) i * nblk * BS + slot * BS + j] = atn;
+                    }
+                }
+            }
+            if (!has_nb && lane < BS) {
+                /* loc_rhs -= w g (grad phi . n) ; loc_rhs += w eta_l g phi   (:190-191) */
+                for (int q = 0; q < NFQ; q++)
+                    rhs_i += FG[q] * (eta_l * TPHI[lane * NFQ + q] - TGN[lane * NFQ + q]);
+            }
+            __syncwarp();
+        }
+
+        /* ---------------- sinks ---------------- */
+        if (a.blocks_mode) {
+            if (a.orhs && lane < BS) a.orhs[(int64_t) rc * BS + lane] = rhs_i;
+        } else {
+            const int dslot = (int) a.slots[cell * (NV + 1)];
+#pragma unroll
+            for (int t = 0; t < NACC; t++) {
+                const int m = t * 32 + lane;
+                if (m < BS2) {
+                    const int i = m / BS, j = m - i * BS;
+                    vrow[(int64_t) i * nblk * BS + dslot * BS + j] = accD[t];
+                    if (a.pc && i == j) a.pc[cell * BS + i] = 1.0 / accD[t];     /* methods/dg.hpp:133-142 */
+                }
+            }
+            if (lane < BS) a.rhs[cell * BS + lane] = rhs_i;                       /* rhs[ci] = local[i], methods/dg.hpp:118 */
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------ */
+/* block structure: which blocks does row block `cell` hold, in which column order        */
+/* ------------------------------------------------------------------------------------ */
+template <int NV>
+__device__ __forceinline__ int cell_block_list(const dg_args &a, int64_t cell, int32_t *ids, int8_t *slots, int *err)
+{
+    /* ids: ascending internal ids of {cell} + neighbours; slots[0] = position of the diagonal,
+     * slots[1+e] = position of the neighbour across local face e, or -1 */
+    const int32_t rc = a.perm[cell];
+    int32_t nb[NV];
+    int n = 1;
+    ids[0] = (int32_t) cell;
+#pragma unroll
+    for (int e = 0; e < NV; e++) {
+        const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
+        const int2 own = a.face_owners[f];
+        const int32_t nrc = own.x == rc ? own.y : own.x;
+        nb[e] = nrc >= 0 ? a.iperm[nrc] : -1;
+        if (nb[e] >= 0) ids[n++] = nb[e];
+    }
+    /* insertion sort, n <= 5 */
+    for (int i = 1; i < n; i++) {
+        const int32_t v = ids[i];
+        int j = i - 1;
+        while (j >= 0 && ids[j] > v) { ids[j + 1] = ids[j]; j--; }
+        ids[j + 1] = v;
+    }
+    for (int i = 1; i < n; i++)
+        if (ids[i] == ids[i - 1]) atomicExch(err, 1);      /* two faces to the same neighbour: needs the fold path */
+    for (int s = 0; s < n; s++) if (ids[s] == (int32_t) cell) slots[0] = (int8_t) s;
+#pragma unroll
+    for (int e = 0; e < NV; e++) {
+        slots[1 + e] = -1;
+        if (nb[e] >= 0)
+            for (int s = 0; s < n; s++) if (ids[s] == nb[e]) slots[1 + e] = (int8_t) s;
+    }
+    return n;
+}
+
+template <int NV>
+__global__ void dg_count_blocks(const dg_args a, int32_t *__restrict__ nblk, int *err)
+{
+    const int64_t cell = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= a.ncells) return;
+    int32_t ids[NV + 1];
+    int8_t slots[NV + 1];
+    nblk[cell] = cell_block_list<NV>(a, cell, ids, slots, err);
+}
+
+template <int NV>
+__global__ void dg_fill_blocks(const dg_args a, int32_t *__restrict__ blk_cell, int8_t *__restrict__ slots_out, int *err)
+{
+    const int64_t cell = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= a.ncells) return;
+    int32_t ids[NV + 1];
+    int8_t slots[NV + 1];
+    const int n = cell_block_list<NV>(a, cell, ids, slots, err);
+    const int64_t cp = a.cellptr[cell];
+    for (int s = 0; s < n; s++) blk_cell[cp + s] = ids[s];
+#pragma unroll
+    for (int s = 0; s < NV + 1; s++) slots_out[cell * (NV + 1) + s] = slots[s];
+}
+
+/* rowptr + colidx of the block CSR: one warp per cell, lanes over the cell's entries */
+__global__ void dg_fill_pattern(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell,
+                                int64_t ncells, int bs, int64_t *__restrict__ rowptr, int32_t *__restrict__ colidx)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const int64_t bs2 = (int64_t) bs * bs;
+    for (int64_t cell = warp; cell < ncells; cell += nwarps) {
+        const int64_t cp = cellptr[cell];
+        const int nblk = (int) (cellptr[cell + 1] - cp);
+        const int rowlen = nblk * bs;
+        const int64_t base = cp * bs2;
+        if (lane < bs) rowptr[cell * bs + lane] = base + (int64_t) lane * rowlen;
+        if (cell == ncells - 1 && lane == 0) rowptr[ncells * bs] = base + (int64_t) bs * rowlen;
+        const int total = bs * rowlen;
+        for (int m = lane; m < total; m += 32) {
+            const int l = m % rowlen;
+            const int s = l / bs, j = l - s * bs;
+            colidx[base + m] = blk_cell[cp + s] * bs + j;
+        }
+    }
+}
+
+template <int NV, int K>
+static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
+{
+    constexpr int BS = (K + 2) * (K + 1) / 2;
+    constexpr int NQ = dg_nq_cell(NV, K);
+    constexpr int NFQ = K + 1;
+    constexpr int CELL_DBL = NQ * (2 + 3 * BS);
+    constexpr int FACE_DBL = NFQ * (2 + 4 * BS);
+    constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
+    const size_t smem = (size_t) DG_WARPS * WARP_DBL * sizeof(double);
+    if (smem > 48 * 1024)
+        YFD_CUDA(ctx, cudaFuncSetAttribute(dg_sip_cells<NV, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const int64_t want = ceil_div(a.ncells, DG_WARPS);
+    const int64_t cap = (int64_t) ctx->sm_count * 32;        /* grid-stride beyond 32 CTAs per SM */
+    const unsigned grid = (unsigned) (want < cap ? (want > 0 ? want : 1) : cap);
+    YFD_LAUNCH(ctx, (dg_sip_cells<NV, K>), grid, DG_WARPS * 32, smem, a);
+    return YFD_OK;
+}
+
+template <int NV>
+static yfd_status dispatch_cells(yfd_ctx *ctx, int degree, const dg_args &a)
+{
+    switch (degree) {
+    case 0: return launch_cells<NV, 0>(ctx, a);
+    case 1: return launch_cells<NV, 1>(ctx, a);
+    case 2: return launch_cells<NV, 2>(ctx, a);
+    case 3: return launch_cells<NV, 3>(ctx, a);
+    case 4: return launch_cells<NV, 4>(ctx, a);
+    case 5: return launch_cells<NV, 5>(ctx, a);
+    case 6: return launch_cells<NV, 6>(ctx, a);
+    }
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "DG degree %d: the element kernel is instantiated for 0..%d", degree, DG_MAX_DEGREE);
+}
+
+static yfd_status fill_common_args(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, dg_args &a)
+{
+    if (cfg->degree < 0) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "negative degree");
+    if (cfg->degree > DG_MAX_DEGREE)
+        return fail(ctx, YFD_ERR_UNSUPPORTED, "DG degree %d: the element kernel is instantiated for 0..%d", cfg->degree, DG_MAX_DEGREE);
+    quad_rule g;
+    YFD_TRY(gauss_rule_for_degree(ctx, 2 * cfg->degree, &g));
+    tri_rule t;
+    YFD_TRY(dunavant_rule_for_degree(ctx, 2 * cfg->degree, &t));
+    if (mesh->nv == 3 && t.n != dg_nq_cell(3, cfg->degree))
+        return fail(ctx, YFD_ERR_INVALID_STATE, "internal: Dunavant rule size mismatch");
+    a.pts = (const double2 *) mesh->points.p;
+    a.cells = mesh->cells.p;
+    a.cell_faces = mesh->cell_faces.p;
+    a.faces = (const int2 *) mesh->faces.p;
+    a.face_owners = (const int2 *) mesh->face_owners.p;
+    a.perm = mesh->perm.p;
+    a.iperm = mesh->iperm.p;
+    a.ncells = mesh->ncells;
+    a.eta = 3.0 * cfg->degree * cfg->degree * cfg->eta;
+    a.rhs_fn = cfg->rhs_fn;
+    a.dir_fn = cfg->dirichlet_fn;
+    a.cell_rule = t.cw;
+    a.gx = g.x; a.gw = g.w;
+    a.cellptr = nullptr; a.slots = nullptr; a.values = a.rhs = a.pc = nullptr;
+    a.oK = a.oAtt = a.oAtn = a.orhs = nullptr;
+    a.blocks_mode = 0;
+    return YFD_OK;
+}
+
+} // namespace yfd
+
+using namespace yfd;
+
+template <int NV>
+static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, dg_args &a,
+                                  yfd_system *sys, yfd_assembly_info *info)
+{
+    const int bs = sys->bs;
+    const int64_t nc = mesh->ncells, n = sys->n;
+    gpu_timer t_struct, t_elem;
+    dbuf<int32_t> nblk;
+    dbuf<int8_t> slots;
+    dbuf<int> derr;
+    int herr = 0;
+
+    /* ---- sparsity pattern: block counts -> cellptr -> block lists -> rowptr / colidx ---- */
+    t_struct.start(ctx->stream);
+    YFD_TRY(derr.alloc(ctx, 1));
+    YFD_TRY(derr.zero(ctx));
+    YFD_TRY(nblk.alloc(ctx, (size_t) nc));
+    YFD_TRY(sys->cellptr.alloc(ctx, (size_t) nc + 1));
+    const unsigned g = (unsigned) ceil_div(nc, 256);
+    YFD_LAUNCH(ctx, dg_count_blocks<NV>, g, 256, 0, a, nblk.p, derr.p);
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, nblk.p, sys->cellptr.p, nc));
+    int64_t nblocks = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&nblocks, sys->cellptr.p + nc, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t nnz = nblocks * bs * bs;
+    sys->nnz = nnz;
+    sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n; sys->A.nnz = nnz;
+    YFD_TRY(sys->blk_cell.alloc(ctx, (size_t) nblocks));
+    YFD_TRY(slots.alloc(ctx, (size_t) nc * (NV + 1)));
+    YFD_TRY(sys->A.rowptr.alloc(ctx, (size_t) n + 1));
+    YFD_TRY(sys->A.colidx.alloc(ctx, (size_t) nnz, 4));
+    YFD_TRY(sys->A.values.alloc(ctx, (size_t) nnz, 4));
+    YFD_TRY(sys->rhs.alloc(ctx, (size_t) n));
+    if (cfg->build_preconditioner) YFD_TRY(sys->pc.alloc(ctx, (size_t) n));
+    a.cellptr = sys->cellptr.p;
+    YFD_LAUNCH(ctx, dg_fill_blocks<NV>, g, 256, 0, a, sys->blk_cell.p, slots.p, derr.p);
+    {
+        const int64_t want = ceil_div(nc, 8);
+        const int64_t cap = (int64_t) ctx->sm_count * 16;
+        const unsigned gp = (unsigned) (want < cap ? want : cap);
+        YFD_LAUNCH(ctx, dg_fill_pattern, gp, 256, 0, sys->cellptr.p, sys->blk_cell.p, nc, bs, sys->A.rowptr.p, sys->A.colidx.p);
+    }
+    t_struct.stop(ctx->stream);
+    YFD_TRY(derr.download(ctx, &herr, 1));
+    if (herr) return fail(ctx, YFD_ERR_UNSUPPORTED, "two faces of one cell lead to the same neighbour; use the triplet path");
+
+    /* ---- values: the element kernel writes finished rows into the CSR ---- */
+    a.slots = slots.p;
+    a.values = sys->A.values.p;
+    a.rhs = sys->rhs.p;
+    a.pc = cfg->build_preconditioner ? sys->pc.p : nullptr;
+    t_elem.start(ctx->stream);
+    YFD_TRY(dispatch_cells<NV>(ctx, cfg->degree, a));
+    t_elem.stop(ctx->stream);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+    /* keep the permutation with the system: the mesh may be destroyed first */
+    YFD_TRY(sys->perm.alloc(ctx, (size_t) nc));
+    YFD_TRY(sys->iperm.alloc(ctx, (size_t) nc));
+    YFD_CUDA(ctx, cudaMemcpyAsync(sys->perm.p, mesh->perm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    YFD_CUDA(ctx, cudaMemcpyAsync(sys->iperm.p, mesh->iperm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (info) {
+        info->system_size = n;
+        info->nnz = sys->nnz;
+        info->basis_size = bs;
+        info->ms_elements = t_elem.ms();
+        info->ms_structure = t_struct.ms();
+    }
+    return YFD_OK;
+}
+
+extern "C" {
+
+yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, yfd_system **out, yfd_assembly_info *info)
+{
+    if (!ctx || !mesh || !cfg || !out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
+    if (mesh->ncells == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "Assembler in invalid state");   /* sys_size == 0, methods/dg.hpp:72 */
+    scoped_device dev(ctx->device);
+    dg_args a;
+    YFD_TRY(fill_common_args(ctx, mesh, cfg, a));
+    const int bs = basis_size_2d(cfg->degree);
+    const int64_t n = mesh->ncells * bs;
+    if (n >= 0x7fffffff) return fail(ctx, YFD_ERR_UNSUPPORTED, "system size %lld exceeds 32-bit column indices", (long long) n);
+
+    yfd_system *sys = new yfd_system();
+    sys->ctx = ctx; sys->kind = YFD_SYS_DG; sys->bs = bs; sys->nf = mesh->nv; sys->ncells = mesh->ncells; sys->n = n;
+    const yfd_status st = mesh->nv == 3 ? build_dg_system<3>(ctx, mesh, cfg, a, sys, info)
+                                        : build_dg_system<4>(ctx, mesh, cfg, a, sys, info);
+    if (st != YFD_OK) { cudaStreamSynchronize(ctx->stream); delete sys; return st; }
+    *out = sys;
+    return YFD_OK;
+}
+
+yfd_status yfd_dg_local_blocks(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
+                               double *K, double *Att, double *Atn, double *rhs)
+{
+    if (!ctx || !mesh || !cfg) return YFD_ERR_INVALID_ARGUMENT;
+    if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
+    scoped_device dev(ctx->device);
+    dg_args a;
+    YFD_TRY(fill_common_args(ctx, mesh, cfg, a));
+    const int bs = basis_size_2d(cfg->degree), nv = mesh->nv;
+    const int64_t nc = mesh->ncells, bs2 = (int64_t) bs * bs;
+    dbuf<double> dK, dAtt, dAtn, drhs;
+    if (K)   { YFD_TRY(dK.alloc(ctx, (size_t) (nc * bs2)));        a.oK = dK.p; }
+    if (Att) { YFD_TRY(dAtt.alloc(ctx, (size_t) (nc * nv * bs2))); a.oAtt = dAtt.p; }
+    if (Atn) { YFD_TRY(dAtn.alloc(ctx, (size_t) (nc * nv * bs2))); YFD_TRY(dAtn.zero(ctx)); a.oAtn = dAtn.p; }
+    if (rhs) { YFD_TRY(drhs.alloc(ctx, (size_t) (nc * bs)));       a.orhs = drhs.p; }
+    a.blocks_mode = 1;
+    YFD_TRY(nv == 3 ? dispatch_cells<3>(ctx, cfg->degree, a) : dispatch_cells<4>(ctx, cfg->degree, a));
+    if (K)   YFD_TRY(dK.download(ctx, K, (size_t) (nc * bs2)));
+    if (Att) YFD_TRY(dAtt.download(ctx, Att, (size_t) (nc * nv * bs2)));
+    if (Atn) YFD_TRY(dAtn.download(ctx, Atn, (size_t) (nc * nv * bs2)));
+    if (rhs) YFD_TRY(drhs.download(ctx, rhs, (size_t) (nc * bs)));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+} /* extern "C" */

@@ -1,0 +1,215 @@
+/*
+ * yfd_internal.hpp -- shared declarations of libyfd_b200.so (not part of the ABI).
+ *
+ * Everything behind include/yfd.h lives on ONE device per context and is launched on
+ * ONE stream per context.  No CPU fallback exists anywhere in this library.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdarg>
+#include <string>
+#include <vector>
+#include "yfd.h"
+
+struct yfd_ctx {
+    int           device = 0;
+    cudaStream_t  stream = nullptr;
+    bool          own_stream = false;
+    int           sm_count = 0;
+    int           cc_major = 0, cc_minor = 0;
+    size_t        smem_optin = 0;
+    std::string   name;
+    std::string   err;
+    int64_t       launches = 0;
+    /* quadrature tables on the device (yfd_tables.cu), freed by yfd_ctx_destroy */
+    double       *tab_gauss_x = nullptr, *tab_gauss_w = nullptr, *tab_dunavant = nullptr;
+    /* NCCL (yfd_comm.cpp) */
+    void         *comm = nullptr;
+    int           rank = 0, nranks = 1;
+};
+
+namespace yfd {
+
+yfd_status fail(yfd_ctx *ctx, yfd_status s, const char *fmt, ...);
+
+#define YFD_CUDA(ctx, call)                                                                   \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return yfd::fail((ctx), e_ == cudaErrorMemoryAllocation ? YFD_ERR_OUT_OF_MEMORY   \
+                                                                    : YFD_ERR_CUDA,           \
+                             "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+#define YFD_TRY(call)                                  \
+    do {                                               \
+        yfd_status s_ = (call);                        \
+        if (s_ != YFD_OK) return s_;                   \
+    } while (0)
+
+/* kernel launch on the context's stream, counted (bench.py reports gpu_launches) */
+#define YFD_LAUNCH(ctx, kernel, grid, block, smem, ...)                                        \
+    do {                                                                                      \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                      \
+        (ctx)->launches++;                                                                    \
+        cudaError_t e_ = cudaPeekAtLastError();                                               \
+        if (e_ != cudaSuccess)                                                                \
+            return yfd::fail((ctx), YFD_ERR_CUDA, "%s:%d: launch %s: %s", __FILE__, __LINE__,  \
+                             #kernel, cudaGetErrorString(e_));                                \
+    } while (0)
+
+/* device array with explicit lifetime (freed on the context's device) */
+template <typename T>
+struct dbuf {
+    T     *p = nullptr;
+    size_t n = 0;
+    dbuf() = default;
+    dbuf(const dbuf &) = delete;
+    dbuf &operator=(const dbuf &) = delete;
+    dbuf(dbuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    dbuf &operator=(dbuf &&o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~dbuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+    }
+    /* `pad` extra elements are allocated (and zeroed) past n so that aligned vector
+     * loads of the last quad never leave the allocation */
+    yfd_status alloc(yfd_ctx *ctx, size_t count, size_t pad = 0) {
+        release();
+        size_t bytes = (count + pad) * sizeof(T);
+        if (bytes == 0) bytes = sizeof(T);
+        cudaError_t e = cudaMalloc((void **) &p, bytes);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            return fail(ctx, YFD_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
+        }
+        n = count;
+        if (pad) {
+            e = cudaMemsetAsync(p + count, 0, pad * sizeof(T), ctx->stream);
+            if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+        }
+        return YFD_OK;
+    }
+    yfd_status zero(yfd_ctx *ctx) {
+        if (!n) return YFD_OK;
+        cudaError_t e = cudaMemsetAsync(p, 0, n * sizeof(T), ctx->stream);
+        if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+        return YFD_OK;
+    }
+    yfd_status upload(yfd_ctx *ctx, const T *host, size_t count) {
+        if (!count) return YFD_OK;
+        cudaError_t e = cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "H2D copy: %s", cudaGetErrorString(e));
+        return YFD_OK;
+    }
+    yfd_status download(yfd_ctx *ctx, T *host, size_t count) const {
+        if (!count) return YFD_OK;
+        cudaError_t e = cudaMemcpyAsync(host, p, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "D2H copy: %s", cudaGetErrorString(e));
+        e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "sync after D2H: %s", cudaGetErrorString(e));
+        return YFD_OK;
+    }
+};
+
+struct scoped_device {
+    int prev = -1;
+    explicit scoped_device(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~scoped_device() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct gpu_timer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    gpu_timer() { cudaEventCreate(&a); cudaEventCreate(&b); }
+    ~gpu_timer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    void start(cudaStream_t s) { cudaEventRecord(a, s); }
+    void stop(cudaStream_t s) { cudaEventRecord(b, s); }
+    double ms() { float t = 0; cudaEventSynchronize(b); cudaEventElapsedTime(&t, a, b); return (double) t; }
+};
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+inline int basis_size_2d(int k) { return (k + 2) * (k + 1) / 2; }
+
+/* ---- yfd_sort.cu: scans, radix sort, small device utilities ---- */
+/* out[i] = sum_{j<i} in[j]; out has n+1 entries (out[n] = total) */
+yfd_status exclusive_scan_i32_to_i64(yfd_ctx *ctx, const int32_t *d_in, int64_t *d_out, int64_t n);
+/* stable LSD radix sort of (key, value) pairs on key bits [0, key_bits); result ends in (keys, vals);
+ * keys_tmp / vals_tmp are scratch of the same size */
+yfd_status radix_sort_pairs(yfd_ctx *ctx, uint64_t *d_keys, uint32_t *d_vals,
+                            uint64_t *d_keys_tmp, uint32_t *d_vals_tmp, int64_t n, int key_bits);
+yfd_status fill_iota_u32(yfd_ctx *ctx, uint32_t *d, int64_t n);
+
+/* ---- yfd_mesh.cu ---- */
+yfd_status upload_narrow(yfd_ctx *ctx, const int64_t *host, int64_t n, int64_t lo, int64_t hi, dbuf<int32_t> &out, int *d_err);
+yfd_status download_widen(yfd_ctx *ctx, const int32_t *d_in, int64_t n, int64_t *host);
+
+/* ---- yfd_tables.cu: the reference's tabulated rules (include/yfd_quad_tables.h) on the device ---- */
+struct quad_rule { const double *x = nullptr, *w = nullptr; int n = 0; };   /* 1D Gauss: x[n], w[n]          */
+struct tri_rule  { const double *cw = nullptr; int n = 0; };                /* Dunavant: (c0,c1,c2,w)[n]     */
+yfd_status ensure_tables(yfd_ctx *ctx);
+/* gauss_legendre_tab(degree): rule degree/2 -> degree/2+1 points (core/quadratures.hpp:296-311) */
+yfd_status gauss_rule_for_degree(yfd_ctx *ctx, int degree, quad_rule *out);
+/* triangle_quadrature_dunavant(degree): rule max(degree,1) (core/quadratures.hpp:570-581) */
+yfd_status dunavant_rule_for_degree(yfd_ctx *ctx, int degree, tri_rule *out);
+
+} // namespace yfd
+
+/* ---- objects behind the opaque handles ---- */
+struct yfd_mesh {
+    yfd_ctx *ctx = nullptr;
+    int      cell_type = 0, nv = 3, nf = 3;
+    int64_t  npoints = 0, ncells = 0, nfaces = 0;
+    int      reorder = 0;
+    yfd::dbuf<double>   points;       /* [npoints][2]                               */
+    yfd::dbuf<int32_t>  cells;        /* [ncells][nv]    REFERENCE cell order       */
+    yfd::dbuf<int32_t>  faces;        /* [nfaces][2]                                */
+    yfd::dbuf<uint8_t>  face_bnd;     /* [nfaces]                                   */
+    yfd::dbuf<int32_t>  cell_faces;   /* [ncells][nf]    REFERENCE cell order       */
+    yfd::dbuf<int32_t>  face_owners;  /* [nfaces][2]     REFERENCE cell ids, -1 none */
+    yfd::dbuf<int32_t>  perm;         /* [ncells] internal -> reference             */
+    yfd::dbuf<int32_t>  iperm;        /* [ncells] reference -> internal             */
+};
+
+struct yfd_csr {
+    yfd_ctx *ctx = nullptr;
+    int64_t  nrows = 0, ncols = 0, nnz = 0;
+    yfd::dbuf<int64_t> rowptr;        /* [nrows+1]                                  */
+    yfd::dbuf<int32_t> colidx;        /* [nnz] (+4 pad)                             */
+    yfd::dbuf<double>  values;        /* [nnz] (+4 pad)                             */
+};
+
+enum yfd_system_kind { YFD_SYS_DG = 1, YFD_SYS_CFEM = 2 };
+
+struct yfd_system {
+    yfd_ctx *ctx = nullptr;
+    int      kind = 0;
+    int64_t  n = 0, nnz = 0;
+    /* matrix, rhs, Jacobi diagonal in INTERNAL numbering */
+    yfd_csr  A;
+    yfd::dbuf<double>  rhs;
+    yfd::dbuf<double>  pc;            /* 1/diag, empty if not built                 */
+    /* DG block structure: cell c owns rows [c*bs, (c+1)*bs); its blocks are listed in
+     * blk_cell[cellptr[c] .. cellptr[c+1]) in ascending internal cell id */
+    int      bs = 0, nf = 0;
+    int64_t  ncells = 0;
+    yfd::dbuf<int64_t> cellptr;       /* [ncells+1]                                 */
+    yfd::dbuf<int32_t> blk_cell;      /* [nblocks]                                  */
+    yfd::dbuf<int32_t> perm, iperm;   /* copies of the mesh's cell permutation      */
+    /* CFEM */
+    int64_t  npoints = 0;
+    yfd::dbuf<int32_t> compress_map;  /* [npoints], -1 on Dirichlet nodes           */
+};
+
+namespace yfd {
+/* ---- yfd_triplets.cu ---- */
+int key_bits_for(int64_t n);
+/* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order */
+yfd_status csr_from_device_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t count,
+                                    uint64_t *d_keys, int col_bits, int row_bits, const double *d_vals, yfd_csr *A);
+} // namespace yfd

@@ -1,0 +1,346 @@
+/*
+ * yfd_system.cu -- the assembled-system handle: accessors in REFERENCE numbering, and the
+ * continuous P1 assembler.
+ *
+ * CFEM replaces cfem::stiffness_matrix / eval_basis_grad (methods/cfem.hpp:53-89), compute_rhs
+ * (continuous_fem.cpp:33-50) and cfem::assembler (methods/cfem.hpp:119-186).  Unlike DG the
+ * scatter is a real irregular reduction (up to ~8 cells share a node), so it goes through the
+ * sort-based triplet path (yfd_triplets.cu): triplets are generated in the reference's push order
+ * (cell, i, j) and folded in that order, and the right-hand side -- `rhs[dof] += local` in the
+ * reference -- is folded the same way as an n x 1 matrix, which reproduces the reference's
+ * cell-order summation exactly instead of using floating-point atomics.
+ */
+#include "yfd_internal.hpp"
+#include <cmath>
+
+namespace yfd {
+
+static inline unsigned sgrid(yfd_ctx *ctx, int64_t n)
+{
+    const int64_t want = ceil_div(n > 0 ? n : 1, 256), cap = (int64_t) ctx->sm_count * 16;
+    return (unsigned) (want < cap ? want : cap);
+}
+
+/* ---- DG: internal (Z-curve) block CSR -> reference-numbered CSR --------------------------- */
+__global__ void ref_block_counts(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ iperm,
+                                 int64_t ncells, int32_t *__restrict__ nblk_ref)
+{
+    const int64_t rc = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (rc >= ncells) return;
+    const int64_t ic = iperm[rc];
+    nblk_ref[rc] = (int32_t) (cellptr[ic + 1] - cellptr[ic]);
+}
+
+/* one warp per reference cell */
+__global__ void export_ref_csr(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell,
+                               const double *__restrict__ values, const int32_t *__restrict__ perm,
+                               const int32_t *__restrict__ iperm, const int64_t *__restrict__ cellptr_ref,
+                               int64_t ncells, int bs, int64_t *__restrict__ rowptr, int64_t *__restrict__ colidx,
+                               double *__restrict__ vals_out)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const int64_t bs2 = (int64_t) bs * bs;
+    for (int64_t rc = warp; rc < ncells; rc += nwarps) {
+        const int64_t ic = iperm[rc];
+        const int64_t cpi = cellptr[ic];
+        const int nblk = (int) (cellptr[ic + 1] - cpi);
+        /* reference ids of the blocks and their rank in ascending reference order */
+        int32_t rid[8];
+        int rank[8];
+        for (int s = 0; s < nblk; s++) rid[s] = perm[blk_cell[cpi + s]];
+        for (int s = 0; s < nblk; s++) {
+            int r = 0;
+            for (int t = 0; t < nblk; t++) r += (rid[t] < rid[s]) ? 1 : 0;
+            rank[s] = r;
+        }
+        const int rowlen = nblk * bs;
+        const int64_t base_i = cpi * bs2, base_r = cellptr_ref[rc] * bs2;
+        if (rowptr) {
+            if (lane < bs) rowptr[rc * bs + lane] = base_r + (int64_t) lane * rowlen;
+            if (rc == ncells - 1 && lane == 0) rowptr[ncells * bs] = base_r + (int64_t) bs * rowlen;
+        }
+        const int total = bs * rowlen;
+        for (int m = lane; m < total; m += 32) {
+            const int i = m / rowlen, l = m - i * rowlen;
+            const int s = l / bs, j = l - s * bs;
+            const int64_t dst = base_r + (int64_t) i * rowlen + rank[s] * bs + j;
+            if (colidx) colidx[dst] = (int64_t) rid[s] * bs + j;
+            if (vals_out) vals_out[dst] = values[base_i + m];
+        }
+    }
+}
+
+__global__ void permute_rows(const double *__restrict__ in, double *__restrict__ out, const int32_t *__restrict__ map,
+                             int64_t ncells, int bs)
+{
+    const int64_t n = ncells * bs;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t c = t / bs;
+        out[t] = in[(int64_t) map[c] * bs + (t - c * bs)];
+    }
+}
+
+__global__ void invert_diag(const double *__restrict__ in, double *__restrict__ out, int64_t n)
+{
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) out[i] = in[i];
+}
+
+/* ---- CFEM ------------------------------------------------------------------------------------ */
+__global__ void mark_dirichlet(const int2 *__restrict__ faces, const uint8_t *__restrict__ fbnd, int64_t nfaces, int32_t *__restrict__ free_node)
+{
+    /* dirichlet_nodes from boundary faces (methods/cfem.hpp:119-132); free_node = !dirichlet */
+    const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= nfaces || !fbnd[f]) return;
+    const int2 p = faces[f];
+    free_node[p.x] = 0;
+    free_node[p.y] = 0;
+}
+
+__global__ void fill_i32(int32_t *p, int64_t n, int32_t v)
+{
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) p[i] = v;
+}
+
+__global__ void make_compress_map(const int32_t *__restrict__ free_node, const int64_t *__restrict__ scan, int64_t npoints, int32_t *__restrict__ cmap)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npoints) return;
+    cmap[i] = free_node[i] ? (int32_t) scan[i] : -1;         /* compress_map (methods/cfem.hpp:140-148) */
+}
+
+/* one thread per cell: 9 matrix triplets + 3 rhs triplets, in the reference's push order; entries the
+ * reference skips (Dirichlet row or column) get the sentinel row `n` and sort to the end */
+__global__ void cfem_p1_cells(const double2 *__restrict__ pts, const int32_t *__restrict__ cells, int64_t ncells,
+                              const int32_t *__restrict__ cmap, int64_t n, int col_bits, int rhs_fn,
+                              uint64_t *__restrict__ mkeys, double *__restrict__ mvals,
+                              uint64_t *__restrict__ rkeys, double *__restrict__ rvals,
+                              unsigned long long *__restrict__ counts)
+{
+    const int64_t c = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const int32_t id[3] = { cells[3 * c], cells[3 * c + 1], cells[3 * c + 2] };
+    const double2 p0 = pts[id[0]], p1 = pts[id[1]], p2 = pts[id[2]];
+    const double x0 = p0.x, y0 = p0.y, x1 = p1.x, y1 = p1.y, x2 = p2.x, y2 = p2.y;
+    /* eval_basis_grad (methods/cfem.hpp:53-75) */
+    const double m = (x1 * y2 - y1 * x2 - x0 * (y2 - y1) + y0 * (x2 - x1));
+    const double g[3][2] = { { (y1 - y2) / m, (x2 - x1) / m }, { (y2 - y0) / m, (x0 - x2) / m }, { (y0 - y1) / m, (x1 - x0) / m } };
+    /* measure (core/mesh.hpp:444-460) */
+    const double d0x = x1 - x0, d0y = y1 - y0, d1x = x2 - x0, d1y = y2 - y0;
+    const double meas = fabs(d0x * d1y - d1x * d0y) / 2.0;
+    /* compute_rhs (continuous_fem.cpp:33-50) */
+    double bval = 0.0;
+    {
+        const double bx = (x0 + x1 + x2) / 3.0, by = (y0 + y1 + y2) / 3.0;
+        if (rhs_fn == YFD_FN_SINSIN) { bval = sin(M_PI * bx) * sin(M_PI * by); bval = bval * 2.0 * M_PI * M_PI * meas / 3.0; }
+        else if (rhs_fn == YFD_FN_ONE) bval = meas / 3.0;
+    }
+    const uint64_t sentinel = (uint64_t) n << col_bits;
+    int32_t dof[3];
+    for (int i = 0; i < 3; i++) dof[i] = cmap[id[i]];
+    unsigned nm = 0, nr = 0;
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) {
+            const bool keep = dof[i] >= 0 && dof[j] >= 0;
+            /* stiffness_matrix = meas * dphi * trans(dphi) (methods/cfem.hpp:77-89) */
+            const double v = (meas * g[i][0]) * g[j][0] + (meas * g[i][1]) * g[j][1];
+            mkeys[9 * c + 3 * i + j] = keep ? (((uint64_t) dof[i] << col_bits) | (uint64_t) dof[j]) : sentinel;
+            mvals[9 * c + 3 * i + j] = v;
+            nm += keep;
+        }
+        const bool keep = dof[i] >= 0;
+        rkeys[3 * c + i] = keep ? ((uint64_t) dof[i] << 1) : ((uint64_t) n << 1);
+        rvals[3 * c + i] = bval;
+        nr += keep;
+    }
+    /* integer counts: order-independent, so atomics are deterministic here */
+    if (nm) atomicAdd(&counts[0], (unsigned long long) nm);
+    if (nr) atomicAdd(&counts[1], (unsigned long long) nr);
+}
+
+__global__ void rhs_from_fold(const int64_t *__restrict__ rowptr, const double *__restrict__ values, int64_t n, double *__restrict__ rhs)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    rhs[i] = rowptr[i + 1] > rowptr[i] ? values[rowptr[i]] : 0.0;
+}
+
+__global__ void cfem_expand(const double *__restrict__ sol, const int32_t *__restrict__ cmap, int64_t npoints, double *__restrict__ out)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npoints) return;
+    const int32_t d = cmap[i];
+    out[i] = d >= 0 ? sol[d] : 0.0;          /* expand (methods/cfem.hpp:190-197) */
+}
+
+static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system *sys, yfd_assembly_info *info)
+{
+    const int64_t np = mesh->npoints, nc = mesh->ncells, nfc = mesh->nfaces;
+    gpu_timer t_struct, t_elem;
+    dbuf<int32_t> free_node;
+    dbuf<int64_t> scan;
+    t_struct.start(ctx->stream);
+    YFD_TRY(free_node.alloc(ctx, (size_t) np));
+    YFD_TRY(scan.alloc(ctx, (size_t) np + 1));
+    YFD_LAUNCH(ctx, fill_i32, sgrid(ctx, np), 256, 0, free_node.p, np, 1);
+    YFD_LAUNCH(ctx, mark_dirichlet, (unsigned) ceil_div(std::max<int64_t>(nfc, 1), 256), 256, 0, (const int2 *) mesh->faces.p, mesh->face_bnd.p, nfc, free_node.p);
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, free_node.p, scan.p, np));
+    int64_t n = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&n, scan.p + np, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    sys->n = n; sys->npoints = np;
+    YFD_TRY(sys->compress_map.alloc(ctx, (size_t) np));
+    YFD_LAUNCH(ctx, make_compress_map, (unsigned) ceil_div(std::max<int64_t>(np, 1), 256), 256, 0, free_node.p, scan.p, np, sys->compress_map.p);
+    t_struct.stop(ctx->stream);
+
+    const int row_bits = key_bits_for(n + 1), col_bits = key_bits_for(n > 0 ? n : 1);
+    dbuf<uint64_t> mkeys, rkeys;
+    dbuf<double> mvals, rvals;
+    dbuf<unsigned long long> counts;
+    YFD_TRY(mkeys.alloc(ctx, (size_t) nc * 9)); YFD_TRY(mvals.alloc(ctx, (size_t) nc * 9));
+    YFD_TRY(rkeys.alloc(ctx, (size_t) nc * 3)); YFD_TRY(rvals.alloc(ctx, (size_t) nc * 3));
+    YFD_TRY(counts.alloc(ctx, 2)); YFD_TRY(counts.zero(ctx));
+    t_elem.start(ctx->stream);
+    YFD_LAUNCH(ctx, cfem_p1_cells, (unsigned) ceil_div(std::max<int64_t>(nc, 1), 256), 256, 0, (const double2 *) mesh->points.p, mesh->cells.p, nc,
+               sys->compress_map.p, n, col_bits, rhs_fn, mkeys.p, mvals.p, rkeys.p, rvals.p, counts.p);
+    t_elem.stop(ctx->stream);
+    unsigned long long hc[2] = { 0, 0 };
+    YFD_TRY(counts.download(ctx, hc, 2));
+    /* the fold ignores the sentinel tail: sort everything, then build from the first hc[] records.
+     * A sentinel has row n, so give the builder n+1 rows and drop the last one afterwards. */
+    yfd_csr full;
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, nc * 9, mkeys.p, col_bits, row_bits, mvals.p, &full));
+    /* rows 0..n-1 of `full` are the matrix; row n holds the folded sentinel (one entry) */
+    sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n;
+    int64_t nnz = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&nnz, full.rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    sys->A.nnz = nnz; sys->nnz = nnz;
+    sys->A.rowptr = std::move(full.rowptr);      /* first n+1 entries are exactly the matrix's offsets */
+    sys->A.rowptr.n = (size_t) n + 1;
+    sys->A.colidx = std::move(full.colidx);
+    sys->A.values = std::move(full.values);
+    sys->A.colidx.n = (size_t) nnz; sys->A.values.n = (size_t) nnz;
+
+    yfd_csr rf;
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nc * 3, rkeys.p, 1, row_bits, rvals.p, &rf));
+    YFD_TRY(sys->rhs.alloc(ctx, (size_t) n, 2));
+    YFD_LAUNCH(ctx, rhs_from_fold, (unsigned) ceil_div(std::max<int64_t>(n, 1), 256), 256, 0, rf.rowptr.p, rf.values.p, n, sys->rhs.p);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    (void) hc;
+    if (info) {
+        info->system_size = n; info->nnz = nnz; info->basis_size = 3;
+        info->ms_elements = t_elem.ms(); info->ms_structure = t_struct.ms();
+    }
+    return YFD_OK;
+}
+
+} // namespace yfd
+
+using namespace yfd;
+
+extern "C" {
+
+yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system **out, yfd_assembly_info *info)
+{
+    if (!ctx || !mesh || !out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
+    if (mesh->nv != 3) return fail(ctx, YFD_ERR_UNSUPPORTED, "continuous FEM is P1 on triangles only (methods/cfem.hpp:31-89)");
+    scoped_device dev(ctx->device);
+    yfd_system *sys = new yfd_system();
+    sys->ctx = ctx; sys->kind = YFD_SYS_CFEM; sys->bs = 1; sys->nf = 3; sys->ncells = mesh->ncells;
+    const yfd_status st = build_cfem(ctx, mesh, rhs_fn, sys, info);
+    if (st != YFD_OK) { cudaStreamSynchronize(ctx->stream); delete sys; return st; }
+    *out = sys;
+    return YFD_OK;
+}
+
+yfd_status yfd_cfem_expand(yfd_system *sys, const double *sol, double *expanded)
+{
+    if (!sys || !sol || !expanded) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_ctx *ctx = sys->ctx;
+    if (sys->kind != YFD_SYS_CFEM) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "not a CFEM system");
+    scoped_device dev(ctx->device);
+    dbuf<double> ds, de;
+    YFD_TRY(ds.alloc(ctx, (size_t) sys->n)); YFD_TRY(de.alloc(ctx, (size_t) sys->npoints));
+    YFD_TRY(ds.upload(ctx, sol, (size_t) sys->n));
+    YFD_LAUNCH(ctx, cfem_expand, (unsigned) ceil_div(std::max<int64_t>(sys->npoints, 1), 256), 256, 0, ds.p, sys->compress_map.p, sys->npoints, de.p);
+    return de.download(ctx, expanded, (size_t) sys->npoints);
+}
+
+yfd_status yfd_cfem_get_compress_map(yfd_system *sys, int64_t *compress_map)
+{
+    if (!sys || !compress_map) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->kind != YFD_SYS_CFEM) return fail(sys->ctx, YFD_ERR_INVALID_ARGUMENT, "not a CFEM system");
+    scoped_device dev(sys->ctx->device);
+    return download_widen(sys->ctx, sys->compress_map.p, sys->npoints, compress_map);
+}
+
+void yfd_system_destroy(yfd_system *sys)
+{
+    if (!sys) return;
+    scoped_device dev(sys->ctx->device);
+    cudaStreamSynchronize(sys->ctx->stream);
+    delete sys;
+}
+
+void yfd_system_sizes(const yfd_system *sys, int64_t *n, int64_t *nnz)
+{
+    if (n) *n = sys->n;
+    if (nnz) *nnz = sys->nnz;
+}
+
+yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx, double *values)
+{
+    if (!sys) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_ctx *ctx = sys->ctx;
+    scoped_device dev(ctx->device);
+    if (sys->kind != YFD_SYS_DG) return yfd_csr_get(&sys->A, rowptr, colidx, values);
+    const int64_t nc = sys->ncells, n = sys->n, nnz = sys->nnz;
+    dbuf<int32_t> nblk_ref;
+    dbuf<int64_t> cp_ref, d_rowptr, d_col;
+    dbuf<double> d_val;
+    YFD_TRY(nblk_ref.alloc(ctx, (size_t) nc));
+    YFD_TRY(cp_ref.alloc(ctx, (size_t) nc + 1));
+    YFD_LAUNCH(ctx, ref_block_counts, (unsigned) ceil_div(nc, 256), 256, 0, sys->cellptr.p, sys->iperm.p, nc, nblk_ref.p);
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, nblk_ref.p, cp_ref.p, nc));
+    if (rowptr) YFD_TRY(d_rowptr.alloc(ctx, (size_t) n + 1));
+    if (colidx) YFD_TRY(d_col.alloc(ctx, (size_t) nnz));
+    if (values) YFD_TRY(d_val.alloc(ctx, (size_t) nnz));
+    const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
+    YFD_LAUNCH(ctx, export_ref_csr, (unsigned) (want < cap ? want : cap), 256, 0, sys->cellptr.p, sys->blk_cell.p, sys->A.values.p,
+               sys->perm.p, sys->iperm.p, cp_ref.p, nc, sys->bs, d_rowptr.p, d_col.p, d_val.p);
+    if (rowptr) YFD_TRY(d_rowptr.download(ctx, rowptr, (size_t) n + 1));
+    if (colidx) YFD_TRY(d_col.download(ctx, colidx, (size_t) nnz));
+    if (values) YFD_TRY(d_val.download(ctx, values, (size_t) nnz));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+static yfd_status get_vector_ref(yfd_system *sys, const dbuf<double> &v, double *host)
+{
+    yfd_ctx *ctx = sys->ctx;
+    scoped_device dev(ctx->device);
+    if (sys->kind != YFD_SYS_DG) return v.download(ctx, host, (size_t) sys->n);
+    dbuf<double> tmp;
+    YFD_TRY(tmp.alloc(ctx, (size_t) sys->n));
+    YFD_LAUNCH(ctx, permute_rows, sgrid(ctx, sys->n), 256, 0, v.p, tmp.p, sys->iperm.p, sys->ncells, sys->bs);
+    return tmp.download(ctx, host, (size_t) sys->n);
+}
+
+yfd_status yfd_system_get_rhs(yfd_system *sys, double *rhs)
+{
+    if (!sys || !rhs) return YFD_ERR_INVALID_ARGUMENT;
+    return get_vector_ref(sys, sys->rhs, rhs);
+}
+
+yfd_status yfd_system_get_pc_diag(yfd_system *sys, double *diag)
+{
+    if (!sys || !diag) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->pc.n == 0) return fail(sys->ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
+    return get_vector_ref(sys, sys->pc, diag);
+}
+
+} /* extern "C" */
