@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- assembled+solved DOFs/s and CG SpMV HBM GB/s of the DG-SIP assemble-and-solve path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one pass of the hot path over one mesh: per-element DG-SIP blocks -> block CSR ->
+CG to rr_tol (reference algorithm, core/solvers.hpp:46-138; no preconditioner, as the reference
+driver defaults), i.e. everything run_diffusion_solver does between mesh creation and post-process
+(dg2d_diffusion.cpp:131-219).
+
+  value   DOFs / s with the mesh already resident in HBM (device-timed, max over ranks)
+  e2e     the same through the C ABI with HOST buffers: mesh arrays pinned on the host are uploaded,
+          connectivity built, system assembled and solved, solution copied back -- all in the timed region
+  roofline   the dominant kernel (the CG SpMV): algorithmic CSR bytes (12 nnz + 8(n+1)
+             + 16 n) / CUDA-event time per launch, against MEASURED_PEAKS.json
+  cpu_baseline   the UNMODIFIED reference (oracle/_ref, Blaze, -fopenmp over all host cores) on a
+                 bounded sample of the same discretisation, timed on this box's host cores
+
+`--impl reference` times only that CPU reference arm (rank 0; other ranks exit 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+import numpy as np
+
+# name -> (cell type, refinement, degree, use_pc, rr_tol, cpu sample refinement for one reference step,
+#          cpu sample refinement for the in-run cpu_baseline)
+WORKLOADS = {
+    # BASELINE.json configs[2]: "DG diffusion on quadrilaterals degree 3, ~20M dofs" -- the reference
+    # mesher only offers 10.49M (r=9) or 41.9M (r=10) dofs (size table)
+    "dg_sip_quad_k3_r9": dict(cell=1, r=9, k=3, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
+                              desc="DG-SIP diffusion, quadrangles k=3, -r 9: 1,048,576 cells, 10,485,760 dofs, nnz 523,878,400 (BASELINE configs[2])"),
+    "dg_sip_quad_k3_r8": dict(cell=1, r=8, k=3, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
+                              desc="DG-SIP diffusion, quadrangles k=3, -r 8: 262,144 cells, 2,621,440 dofs"),
+    # configs[0]: the reference's own CPU-runnable case
+    "dg_sip_tri_k1_r6": dict(cell=0, r=6, k=1, pc=False, rr_tol=1e-8, ref_r=6, base_r=6,
+                             desc="DG-SIP diffusion, triangles k=1, -r 6 (64 boundary segments per side): 16,384 cells, 49,152 dofs (BASELINE configs[0])"),
+    # configs[4] mesh one level down (r=11 is the 1e8-dof point)
+    "dg_sip_tri_k2_r9": dict(cell=0, r=9, k=2, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
+                             desc="DG-SIP diffusion, triangles k=2, -r 9: 1,048,576 cells, 6,291,456 dofs"),
+    "dg_sip_tri_k2_r11": dict(cell=0, r=11, k=2, pc=True, rr_tol=1e-10, ref_r=5, base_r=6,
+                              desc="DG-SIP diffusion, triangles k=2, -r 11: 16,777,216 cells, 100,663,296 dofs (BASELINE configs[4])"),
+}
+DEFAULT_WORKLOAD = "dg_sip_quad_k3_r9"
+
+
+def bs_of(k):
+    return (k + 2) * (k + 1) // 2
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region (B200_PROFILING.md)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_id):
+        self.gpu_id, self.rows, self.proc, self.thr = gpu_id, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_id), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thr = threading.Thread(target=self._read, daemon=True)
+        self.thr.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.thr.join(timeout=2)
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); smax.append(float(r[1])); power.append(float(r[2]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        if not sm:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
+        return dict(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(smax)), reasons=sorted(reasons),
+                    samples=len(sm), power_w_max=max(power))
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU reference arm (oracle/_ref = the unmodified reference; the only place bench.py touches oracle/)
+# ------------------------------------------------------------------------------------------------
+def reference_step(ref, wl, r):
+    """One full reference pass at refinement r: mesh (untimed) -> cell loop -> finalize -> CG."""
+    ref.mesh(wl["cell"], r)
+    ref.set_cg(rr_tol=wl["rr_tol"], rr_max=1e4, max_iter=-1)
+    out = ref.run_dg(wl["k"], eta=1.0, use_pc=wl["pc"])
+    t = out["t_blocks"] + out["t_csr"] + out["t_cg"]
+    return dict(n=out["n"], nnz=out["nnz"], iters=out["iters"], t=t, t_blocks=out["t_blocks"], t_csr=out["t_csr"], t_cg=out["t_cg"])
+
+
+def load_reference():
+    import refbind
+    omp = refbind.available(omp=True)
+    if not refbind.available(omp=omp):
+        return None, 0, None
+    cores = os.cpu_count() or 1
+    if omp:
+        os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    ref = refbind.Ref(omp=omp)
+    return ref, (ref.num_threads() if omp else 1), "reference"
+
+
+def cpu_baseline(wl, r):
+    ref, cores, kind = load_reference()
+    if ref is None:
+        return None
+    s = reference_step(ref, wl, r)
+    return dict(value=s["n"] / s["t"], unit="DOFs/s", cores=cores, kind=kind,
+                sample="unmodified reference (Blaze, -O3 -fopenmp: only its CG is threaded), same discretisation at -r %d: "
+                       "%d dofs, nnz %d, %d CG iterations to rr %.0e; blocks %.2fs + finalize %.2fs + CG %.2fs; "
+                       "%.2f ns per dof per CG iteration" % (r, s["n"], s["nnz"], s["iters"], wl["rr_tol"], s["t_blocks"],
+                                                              s["t_csr"], s["t_cg"], 1e9 * s["t_cg"] / max(1, s["n"] * s["iters"])))
+
+
+def run_reference_arm(args, wl, rank):
+    if rank != 0:
+        return 0
+    ref, cores, kind = load_reference()
+    if ref is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libyfd_ref.so not built (needs /root/reference at build time)"}))
+        return 0
+    r = wl["ref_r"]
+    for _ in range(args.warmup):
+        reference_step(ref, wl, r)
+    t0 = time.perf_counter()
+    tot = 0.0
+    last = None
+    for _ in range(args.steps):
+        last = reference_step(ref, wl, r)
+        tot += last["t"]
+    wall = time.perf_counter() - t0
+    ms = 1e3 * tot / args.steps
+    value = last["n"] / (tot / args.steps)
+    sample = ("each step = the unmodified reference's cell loop + finalize + CG at -r %d (%d dofs, nnz %d, %d iterations, rr_tol %.0e) "
+              "of the workload's discretisation; mesh creation untimed; wall %.1fs" % (r, last["n"], last["nnz"], last["iters"], wl["rr_tol"], wall))
+    line = {"impl": "reference", "metric": "assembled+solved DOFs/sec", "value": value, "unit": "DOFs/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "description": wl["desc"], "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "DOFs/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "DOFs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def pinned_like(torch, a):
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t, t.numpy()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("YFD_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile-iters", type=int, default=0,
+                    help="ncu helper: cap CG at this many iterations, one step, no warm-up; the printed line is NOT a bench value")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference_arm(args, wl, rank)
+    if args.profile_iters > 0:
+        args.warmup, args.steps, args.no_e2e, args.no_cpu_baseline = 0, 1, True, True
+    elif args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    import yaourt_fem_dg_b200 as yfd
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path is CUDA only (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torch.distributed.run --nproc-per-node %d" % (args.gpus, world, args.gpus))
+
+    stream = torch.cuda.current_stream()
+    ctx = yfd.Context(local_rank, stream=stream.cuda_stream)
+    if world > 1:
+        ids = [yfd.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.attach_comm(rank, world, ids[0])
+
+    k, bs = wl["k"], bs_of(wl["k"])
+    hm = yfd.HostMesh.create(wl["cell"], wl["r"])           # mesher: input generation, untimed
+    params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=1e4, max_iter=args.profile_iters or 2 * bs * len(hm.cells))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- resident leg: mesh in HBM before the clock starts ----------------
+    mesh = yfd.Mesh(ctx, hm)
+    n = bs * mesh.ncells
+    d_x = torch.empty(n if world == 1 else 1, dtype=torch.float64, device="cuda")
+    info = {}
+
+    def step_resident():
+        sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0, build_pc=wl["pc"])
+        res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr() if world == 1 else None)
+        info.update(res, nnz=sysm.nnz, n=sysm.n, ms_elements=sysm.info.ms_elements, ms_structure=sysm.info.ms_structure)
+        return sysm
+
+    for _ in range(args.warmup):
+        step_resident().close()
+    gpu_uuid = "GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", "")
+    sampler = ClockSampler(gpu_uuid)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = ctx.launches
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_resident().close()
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = ctx.launches - l0
+    ms_step = ms_total / args.steps
+    value = n / (ms_step * 1e-3)
+
+    # ---------------- roofline leg: the CG SpMV, CUDA events on the launching stream ----------------
+    sysm = step_resident()
+    sp = sysm.time_spmv(reps=50)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = sp["csr_bytes"] / (sp["ms"] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(args.workload)
+    roofline = {"bound": "hbm", "kernel": "dg_spmv (y = A d fused with d.y)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": sp["csr_bytes"], "kernel_requested_bytes_per_launch": sp["kernel_bytes"],
+                "kernel_requested_gbs": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9, "ms_per_launch": sp["ms"]}
+    # whole CG iteration (SpMV + 2 fused vector kernels) over the timed solve: B_cg = B_spmv + 72 n
+    it = max(1, info["iterations"])
+    cg_gbs = (sp["csr_bytes"] + 72.0 * info["n"]) * it / (info["ms_solve"] * 1e-3) / 1e9
+    sysm.close()
+
+    # ---------------- end-to-end leg: host buffers in, host solution out ----------------
+    e2e = None
+    if not args.no_e2e:
+        keep = []
+        arrs = {}
+        for nme in ("points", "cells", "faces", "face_boundary"):
+            t, a = pinned_like(torch, getattr(hm, nme))
+            keep.append(t); arrs[nme] = a
+        xt = torch.empty(n, dtype=torch.float64).pin_memory()
+        x_host = xt.numpy()
+        hm_p = yfd.HostMesh(hm.cell_type, arrs["points"], arrs["cells"], arrs["faces"], arrs["face_boundary"])
+        h2d = sum(a.nbytes for a in arrs.values())
+        d2h = x_host.nbytes
+
+        def step_e2e():
+            m2 = yfd.Mesh(ctx, hm_p)
+            s2 = ctx.dg_assemble_sip(m2, k, eta=1.0, build_pc=wl["pc"])
+            s2.solve_cg_into(params, x_host, use_pc=wl["pc"])
+            s2.close(); m2.close()
+
+        mesh.close()
+        step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        f0.record(stream)
+        for _ in range(args.steps):
+            step_e2e()
+        f1.record(stream)
+        barrier()
+        wall = (time.perf_counter() - t0) / args.steps
+        # the events are recorded before the first / after the last call, so they span the host-side work too
+        ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
+        e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
+               "path": "yfd_mesh_create -> yfd_dg_assemble_sip -> yfd_system_solve_cg (host x) through include/yfd.h"}
+
+    base = None
+    if rank == 0 and not args.no_cpu_baseline:
+        base = cpu_baseline(wl, wl["base_r"])
+
+    if rank == 0:
+        line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else {}
+        line.update({"metric": "assembled+solved DOFs/sec", "value": value, "unit": "DOFs/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(info["n"]), "nnz": int(info["nnz"]),
+                           "cg": "rr_tol %.0e, rr_max 1e4, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], "Jacobi (-p)" if wl["pc"] else "no preconditioner (reference default)"),
+                           "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
+                           "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
+                           "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"]},
+                           "cg_iteration_gbs": cg_gbs, "parallelism": "1 GPU" if world == 1 else "cells partitioned over %d GPUs, NCCL halo + allreduce" % world},
+                "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
+        print(json.dumps(line))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

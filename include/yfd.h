@@ -259,6 +259,12 @@ typedef struct yfd_cg_info {
 yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
                                double *x, yfd_cg_info *info, double *history, int64_t history_cap);
 
+/* Same solve for resident pipelines: x0 = 0, the solution is written to the DEVICE buffer d_x
+ * ([n] doubles, REFERENCE numbering; NULL = discard) and nothing but the scalars in `info`
+ * crosses PCIe. */
+yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                      double *d_x, yfd_cg_info *info);
+
 /* The drop-in shape: A, b, x and optional DIAGONAL iM given as host data. */
 yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
                         const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);

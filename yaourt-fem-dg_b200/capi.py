@@ -140,6 +140,7 @@ def lib():
         "yfd_system_get_pc_diag": (cint, [vp, _f64p]),
         "yfd_cg_params_default": (None, [P(CgParams)]),
         "yfd_system_solve_cg": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
+        "yfd_system_solve_cg_device": (cint, [vp, vp, cint, P(CgParams), vp, P(CgInfo)]),
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
     }
@@ -425,6 +426,21 @@ class System:
             params = params or CgParams()
             params.use_initial_guess = 1
         return _solve_common(self.ctx, call, self.n, params, x0, history)
+
+    def solve_cg_into(self, params, x, use_pc=False):
+        """solve_cg writing into the caller's host array `x` (e.g. pinned memory); x0 = 0 unless use_initial_guess."""
+        assert x.dtype == np.float64 and x.flags.c_contiguous and x.shape == (self.n,)
+        info = CgInfo()
+        self.ctx.check(lib().yfd_system_solve_cg(self.ctx._h, self._h, int(use_pc), C.byref(params), x, C.byref(info), None, 0))
+        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve)
+
+    def solve_cg_device(self, params=None, use_pc=False, d_x=None):
+        """Resident solve: x0 = 0, solution left in the device buffer `d_x` (raw pointer int or None)."""
+        params = params or CgParams()
+        info = CgInfo()
+        self.ctx.check(lib().yfd_system_solve_cg_device(self.ctx._h, self._h, int(use_pc), C.byref(params),
+                                                        C.c_void_p(d_x) if d_x else None, C.byref(info)))
+        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve)
 
     def time_spmv(self, reps=20):
         ms, b1, b2 = C.c_double(), C.c_double(), C.c_double()

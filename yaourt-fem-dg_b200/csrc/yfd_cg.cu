@@ -563,10 +563,10 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
     return dx.download(ctx, x, (size_t) n);
 }
 
-yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
-                               double *x, yfd_cg_info *info, double *history, int64_t history_cap)
+/* shared by the host- and device-resident entry points: x_host in/out (may be null), d_x_out device out (may be null) */
+static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                               double *x_host, double *d_x_out, yfd_cg_info *info, double *history, int64_t history_cap)
 {
-    if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
     if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
     if (use_pc && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
     scoped_device dev(ctx->device);
@@ -575,22 +575,45 @@ yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     YFD_TRY(dx.alloc(ctx, (size_t) n, 2));
     const bool permuted = sys->kind == YFD_SYS_DG;
     if (p->use_initial_guess) {
+        if (!x_host) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_initial_guess needs a host x");
         if (permuted) {
             YFD_TRY(tmp.alloc(ctx, (size_t) n));
-            YFD_TRY(tmp.upload(ctx, x, (size_t) n));
+            YFD_TRY(tmp.upload(ctx, x_host, (size_t) n));
             YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, tmp.p, dx.p, sys->perm.p, sys->ncells, sys->bs);
         } else {
-            YFD_TRY(dx.upload(ctx, x, (size_t) n));
+            YFD_TRY(dx.upload(ctx, x_host, (size_t) n));
         }
     }
     YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
     if (permuted) {
-        if (tmp.n == 0) YFD_TRY(tmp.alloc(ctx, (size_t) n));
         /* x_ref[rc] = x_int[iperm[rc]] */
-        YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, dx.p, tmp.p, sys->iperm.p, sys->ncells, sys->bs);
-        return tmp.download(ctx, x, (size_t) n);
+        double *dst = d_x_out;
+        if (!dst) { if (tmp.n == 0) YFD_TRY(tmp.alloc(ctx, (size_t) n)); dst = tmp.p; }
+        YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, dx.p, dst, sys->iperm.p, sys->ncells, sys->bs);
+        if (x_host) {
+            YFD_CUDA(ctx, cudaMemcpyAsync(x_host, dst, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    } else {
+        if (d_x_out) YFD_CUDA(ctx, cudaMemcpyAsync(d_x_out, dx.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+        if (x_host) YFD_CUDA(ctx, cudaMemcpyAsync(x_host, dx.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    return dx.download(ctx, x, (size_t) n);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                               double *x, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
+    return system_solve(ctx, sys, use_pc, p, x, nullptr, info, history, history_cap);
+}
+
+yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                      double *d_x, yfd_cg_info *info)
+{
+    if (!ctx || !sys || !p) return YFD_ERR_INVALID_ARGUMENT;
+    if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "device-resident solve starts from x = 0");
+    return system_solve(ctx, sys, use_pc, p, nullptr, d_x, info, nullptr, 0);
 }
 
 yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double *ms_per_launch,
