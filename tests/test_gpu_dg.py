@@ -150,9 +150,12 @@ def test_cg_default_params_and_stop_rules(yfd, ref, ctx):
     a = sysm.solve_cg(yfd.CgParams(rr_tol=1e-9, rr_max=1e4, max_iter=10000, check_every=1))
     b = sysm.solve_cg(yfd.CgParams(rr_tol=1e-9, rr_max=1e4, max_iter=10000, check_every=200))
     assert a["iterations"] == b["iterations"] and np.array_equal(a["x"], b["x"])
-    # warm start from the solution: no iterations needed beyond the tolerance
-    c = sysm.solve_cg(yfd.CgParams(rr_tol=1e-6, rr_max=1e4, max_iter=10000), x0=a["x"])
-    assert c["iterations"] <= 1
+    # warm start (use_initial_guess, core/solvers.hpp:79-91): r0 = b - A x0, and the stop test is relative to
+    # THAT residual, so starting from a converged x the initial residual norm is already tiny
+    c = sysm.solve_cg(yfd.CgParams(rr_tol=1e-6, rr_max=1e4, max_iter=3), x0=a["x"])
+    assert c["nr0"] <= 1e-8 * np.linalg.norm(sysm.rhs()) and c["iterations"] <= 3
+    d = sysm.solve_cg(yfd.CgParams(rr_tol=1e-9, rr_max=1e4, max_iter=10000), x0=np.zeros(sysm.n))
+    assert d["iterations"] == a["iterations"] and np.array_equal(d["x"], a["x"])
 
 
 def test_full_size_properties_tri_k1_r6(yfd, ctx):
