@@ -51,3 +51,30 @@ def block_max_rel_err(a, b, rowptr, bs):
             scale = 1.0
         worst = max(worst, np.abs(a[s:e] - b[s:e]).max() / scale)
     return worst
+
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def golden(name):
+    """A fixture file written by tools/make_golden.py from the UNMODIFIED reference."""
+    return np.load(os.path.join(GOLDEN, name))
+
+
+def golden_digests():
+    out = {}
+    with open(os.path.join(GOLDEN, "mesh_digests.txt")) as f:
+        for line in f:
+            k, v = line.rstrip("\n").split(" ", 1)
+            out[k] = v
+    return out
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    """oracle/libyfd_oracle.so, the plain-C restatement (built by __graft_entry__.build())."""
+    import oraclebind
+    if not oraclebind.available():
+        import subprocess
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"])
+    return oraclebind.Oracle()
