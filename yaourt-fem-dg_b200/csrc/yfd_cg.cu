@@ -27,90 +27,14 @@
  *                    4 B/nnz colidx stream is never read: 8 B/nnz instead of 12 B/nnz.
  */
 #include "yfd_internal.hpp"
+#include "yfd_cg_shared.cuh"
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 namespace yfd {
 
-constexpr int CG_THREADS = 256;
-constexpr int CG_MAX_PARTIALS = 4096;
-
-struct cg_scalars {
-    double rho;            /* r.z of the current iterate (r.r without preconditioner) */
-    double dy;             /* d.y */
-    double rr_new, rz_new;
-    double nr0, nr;
-    long long iter;
-    long long max_iter;
-    double rr_tol, rr_max;
-    int    done;
-    unsigned int ticket[3];
-};
-
-/* ---- deterministic block + grid reduction ------------------------------------------- */
-__device__ __forceinline__ double warp_sum(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
-/* sum over the block; result valid in thread 0 */
-__device__ __forceinline__ double block_sum(double v, double *sm /* [32] */)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    v = warp_sum(v);
-    __syncthreads();
-    if (lane == 0) sm[warp] = v;
-    __syncthreads();
-    if (warp == 0) {
-        v = lane < (int) (blockDim.x >> 5) ? sm[lane] : 0.0;
-        v = warp_sum(v);
-    }
-    return v;
-}
-
-/* Every block contributes NV partial sums; the last block to arrive reduces all of them in index
- * order and returns true in ALL its threads with the totals in out[] (shared). */
-template <int NV>
-__device__ __forceinline__ bool grid_sum(const double (&v)[NV], double *partials, unsigned int *ticket, double *out_sm)
-{
-    __shared__ double sm[32];
-    __shared__ bool last;
-    double t[NV];
-#pragma unroll
-    for (int k = 0; k < NV; k++) t[k] = block_sum(v[k], sm);
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int k = 0; k < NV; k++) partials[(size_t) k * CG_MAX_PARTIALS + blockIdx.x] = t[k];
-        __threadfence();
-        const unsigned int prev = atomicInc(ticket, gridDim.x - 1);    /* wraps to 0: self-resetting */
-        last = (prev == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!last) return false;
-    __threadfence();
-#pragma unroll
-    for (int k = 0; k < NV; k++) {
-        double s = 0.0;
-        for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x)
-            s += ((volatile double *) partials)[(size_t) k * CG_MAX_PARTIALS + b];
-        s = block_sum(s, sm);
-        if (threadIdx.x == 0) out_sm[k] = s;
-    }
-    __syncthreads();
-    return true;
-}
-
 /* ---- K1: SpMV ------------------------------------------------------------------------- */
-template <int TS>
-__device__ __forceinline__ double team_sum(double v)
-{
-#pragma unroll
-    for (int o = TS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
 template <int TS, bool WITH_DOT>
 __global__ void __launch_bounds__(CG_THREADS)
 csr_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx, const double *__restrict__ values,
@@ -330,7 +254,16 @@ struct spmv_op {
     int64_t nrows = 0, nnz = 0;
     /* DG block rows */
     const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
+    int64_t ncells = 0;
 };
+
+/* YFD_SPMV=rows selects the first-generation team-per-row kernel (A/B measurements); default = TMA stream */
+static bool use_tma_spmv()
+{
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("YFD_SPMV"); v = (e && e[0] == 'r') ? 0 : 1; }
+    return v == 1;
+}
 
 static int pick_team(double avg_row)
 {
@@ -383,6 +316,11 @@ static yfd_status launch_dg_spmv_bs(yfd_ctx *ctx, const spmv_op &op, const doubl
 template <bool WITH_DOT>
 static yfd_status launch_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
 {
+    if (op.cellptr && use_tma_spmv()) {
+        const int64_t before = ctx->launches;
+        const yfd_status st = launch_dg_spmv_tma<WITH_DOT>(ctx, op.bs, op.nf, op.cellptr, op.blk_cell, op.values, op.ncells, x, y, sc, partials);
+        if (st != YFD_ERR_UNSUPPORTED || ctx->launches != before) return st;
+    }
     if (op.cellptr) {
         switch (op.bs) {
         case 1:  return launch_dg_spmv_bs<1, WITH_DOT>(ctx, op, x, y, sc, partials);
@@ -507,7 +445,7 @@ static spmv_op op_of_system(const yfd_system *sys, bool allow_block_kernel)
 {
     spmv_op op = op_of_csr(&sys->A);
     if (sys->kind == YFD_SYS_DG && allow_block_kernel) {
-        op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf;
+        op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf; op.ncells = sys->ncells;
     }
     return op;
 }

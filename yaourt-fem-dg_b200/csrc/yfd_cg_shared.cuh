@@ -1,0 +1,94 @@
+/*
+ * yfd_cg_shared.cuh -- device-side pieces shared by the solver kernels (yfd_cg.cu, yfd_spmv_tma.cu):
+ * the device-resident CG scalars and the deterministic block / grid reductions.
+ */
+#pragma once
+#include "yfd_internal.hpp"
+
+namespace yfd {
+
+constexpr int CG_THREADS = 256;
+constexpr int CG_MAX_PARTIALS = 4096;
+
+struct cg_scalars {
+    double rho;            /* r.z of the current iterate (r.r without preconditioner) */
+    double dy;             /* d.y */
+    double rr_new, rz_new;
+    double nr0, nr;
+    long long iter;
+    long long max_iter;
+    double rr_tol, rr_max;
+    int    done;
+    unsigned int ticket[3];
+};
+
+/* ---- deterministic block + grid reduction ------------------------------------------- */
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+/* sum over the block; result valid in thread 0 */
+__device__ __forceinline__ double block_sum(double v, double *sm /* [32] */)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sm[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        v = lane < (int) (blockDim.x >> 5) ? sm[lane] : 0.0;
+        v = warp_sum(v);
+    }
+    return v;
+}
+
+/* Every block contributes NV partial sums; the last block to arrive reduces all of them in index
+ * order and returns true in ALL its threads with the totals in out[] (shared). */
+template <int NV>
+__device__ __forceinline__ bool grid_sum(const double (&v)[NV], double *partials, unsigned int *ticket, double *out_sm)
+{
+    __shared__ double sm[32];
+    __shared__ bool last;
+    double t[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) t[k] = block_sum(v[k], sm);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; k++) partials[(size_t) k * CG_MAX_PARTIALS + blockIdx.x] = t[k];
+        __threadfence();
+        const unsigned int prev = atomicInc(ticket, gridDim.x - 1);    /* wraps to 0: self-resetting */
+        last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return false;
+    __threadfence();
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+        double s = 0.0;
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+            s += ((volatile double *) partials)[(size_t) k * CG_MAX_PARTIALS + b];
+        s = block_sum(s, sm);
+        if (threadIdx.x == 0) out_sm[k] = s;
+    }
+    __syncthreads();
+    return true;
+}
+
+template <int TS>
+__device__ __forceinline__ double team_sum(double v)
+{
+#pragma unroll
+    for (int o = TS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+
+/* yfd_spmv_tma.cu: TMA-streamed DG block-row SpMV; YFD_ERR_UNSUPPORTED if bs has no instantiation */
+template <bool WITH_DOT>
+yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellptr, const int32_t *blk_cell, const double *values,
+                              int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials);
+
+} // namespace yfd

@@ -64,6 +64,7 @@ yfd_status yfd_ctx_create(int device, void *stream, yfd_ctx **out)
     ctx->cc_major = prop.major;
     ctx->cc_minor = prop.minor;
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     ctx->name = prop.name;
     if (stream) {
         ctx->stream = (cudaStream_t) stream;

@@ -490,7 +490,7 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     YFD_TRY(derr.alloc(ctx, 1));
     YFD_TRY(derr.zero(ctx));
     YFD_TRY(nblk.alloc(ctx, (size_t) nc));
-    YFD_TRY(sys->cellptr.alloc(ctx, (size_t) nc + 1));
+    YFD_TRY(sys->cellptr.alloc(ctx, (size_t) nc + 1, 2));      /* padded: bulk copies round up to 16 B */
     const unsigned g = (unsigned) ceil_div(nc, 256);
     YFD_LAUNCH(ctx, dg_count_blocks<NV>, g, 256, 0, a, nblk.p, derr.p);
     YFD_TRY(exclusive_scan_i32_to_i64(ctx, nblk.p, sys->cellptr.p, nc));
@@ -500,7 +500,7 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     const int64_t nnz = nblocks * bs * bs;
     sys->nnz = nnz;
     sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n; sys->A.nnz = nnz;
-    YFD_TRY(sys->blk_cell.alloc(ctx, (size_t) nblocks));
+    YFD_TRY(sys->blk_cell.alloc(ctx, (size_t) nblocks, 4));
     YFD_TRY(slots.alloc(ctx, (size_t) nc * (NV + 1)));
     YFD_TRY(sys->A.rowptr.alloc(ctx, (size_t) n + 1));
     YFD_TRY(sys->A.colidx.alloc(ctx, (size_t) nnz, 4));

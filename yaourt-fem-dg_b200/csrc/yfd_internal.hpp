@@ -19,7 +19,7 @@ struct yfd_ctx {
     bool          own_stream = false;
     int           sm_count = 0;
     int           cc_major = 0, cc_minor = 0;
-    size_t        smem_optin = 0;
+    size_t        smem_optin = 0, smem_per_sm = 0;
     std::string   name;
     std::string   err;
     int64_t       launches = 0;
