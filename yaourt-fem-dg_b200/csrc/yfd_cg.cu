@@ -22,9 +22,9 @@
  *   csr_spmv<TS>     any CSR.  A team of TS lanes per row, each lane owns 16-byte aligned quads:
  *                    two 128-bit value loads + one 128-bit column load per quad, x through the
  *                    read-only path, warp-shuffle team reduction.
- *   dg_spmv<BS,TS>   DG block rows.  Same value stream (the CSR value array itself), but column
- *                    indices are rebuilt from the per-cell block list (<= 5 ints per cell), so the
- *                    4 B/nnz colidx stream is never read: 8 B/nnz instead of 12 B/nnz.
+ *   dg_spmv_tma<BS>  DG block rows (yfd_spmv_tma.cu): the value stream is fed by the TMA engine into per-warp
+ *                    shared-memory rings; column indices are rebuilt from the per-cell block list (<= 5 ints
+ *                    per cell), so the 4 B/nnz colidx stream is never read: 8 B/nnz instead of 12 B/nnz.
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
@@ -67,54 +67,6 @@ csr_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
                 if (q + 1 >= s && q + 1 < e) acc += v0.y * __ldg(&x[c.y]);
                 if (q + 2 >= s && q + 2 < e) acc += v1.x * __ldg(&x[c.z]);
                 if (q + 3 >= s && q + 3 < e) acc += v1.y * __ldg(&x[c.w]);
-            }
-        }
-        acc = team_sum<TS>(acc);
-        if (tl == 0 && live) {
-            y[row] = acc;
-            if (WITH_DOT) dot += acc * __ldg(&x[row]);
-        }
-    }
-    if (WITH_DOT) {
-        __shared__ double tot[1];
-        const double v[1] = { dot };
-        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) sc->dy = tot[0];
-    }
-}
-
-template <int BS, int TS, bool WITH_DOT>
-__global__ void __launch_bounds__(CG_THREADS)
-dg_spmv(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const double *__restrict__ values,
-        const double *__restrict__ x, double *__restrict__ y, int64_t nrows,
-        cg_scalars *__restrict__ sc, double *__restrict__ partials)
-{
-    if (WITH_DOT && sc->done) return;
-    const int tl = threadIdx.x & (TS - 1);
-    const int team_in_warp = (threadIdx.x & 31) / TS;
-    const int64_t nteams = ((int64_t) gridDim.x * blockDim.x) / TS;
-    double dot = 0.0;
-    /* warp-uniform trip count, see csr_spmv */
-    for (int64_t wrow = ((int64_t) blockIdx.x * blockDim.x + (threadIdx.x & ~31)) / TS; wrow < nrows; wrow += nteams) {
-        const int64_t row = wrow + team_in_warp;
-        const bool live = row < nrows;
-        const int64_t cell = live ? row / BS : 0;
-        const int i = live ? (int) (row - cell * BS) : 0;
-        const int64_t cp = __ldg(&cellptr[cell]);
-        const int nblk = live ? (int) (__ldg(&cellptr[cell + 1]) - cp) : 0;
-        const int L = nblk * BS;
-        const int64_t s = cp * (BS * BS) + (int64_t) i * L;
-        const int32_t *bc = blk_cell + cp;
-        double acc = 0.0;
-        /* lanes own 16-byte aligned pairs of the row's value run */
-        for (int l = 2 * tl - (int) (s & 1); l < L; l += 2 * TS) {
-            const double2 v = __ldg(reinterpret_cast<const double2 *>(values + s + l));
-            if (l >= 0) {
-                const int b = l / BS, j = l - b * BS;
-                acc += v.x * __ldg(&x[(int64_t) __ldg(&bc[b]) * BS + j]);
-            }
-            if (l + 1 < L) {
-                const int b = (l + 1) / BS, j = (l + 1) - b * BS;
-                acc += v.y * __ldg(&x[(int64_t) __ldg(&bc[b]) * BS + j]);
             }
         }
         acc = team_sum<TS>(acc);
@@ -257,14 +209,6 @@ struct spmv_op {
     int64_t ncells = 0;
 };
 
-/* YFD_SPMV=rows selects the first-generation team-per-row kernel (A/B measurements); default = TMA stream */
-static bool use_tma_spmv()
-{
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("YFD_SPMV"); v = (e && e[0] == 'r') ? 0 : 1; }
-    return v == 1;
-}
-
 static int pick_team(double avg_row)
 {
     if (avg_row <= 6) return 2;
@@ -297,42 +241,11 @@ static yfd_status launch_csr_spmv(yfd_ctx *ctx, const spmv_op &op, const double 
     return YFD_OK;
 }
 
-template <int BS, bool WITH_DOT>
-static yfd_status launch_dg_spmv_bs(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
-{
-    /* interior row length = (1+nf)*BS values, each lane takes 2 per pass */
-    const int L = (1 + op.nf) * BS;
-    const int ts = L <= 16 ? 4 : L <= 32 ? 8 : L <= 80 ? 16 : 32;
-    const unsigned g = spmv_grid(ctx, op.nrows, ts);
-    switch (ts) {
-    case 4:  YFD_LAUNCH(ctx, (dg_spmv<BS, 4, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
-    case 8:  YFD_LAUNCH(ctx, (dg_spmv<BS, 8, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
-    case 16: YFD_LAUNCH(ctx, (dg_spmv<BS, 16, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
-    default: YFD_LAUNCH(ctx, (dg_spmv<BS, 32, WITH_DOT>), g, CG_THREADS, 0, op.cellptr, op.blk_cell, op.values, x, y, op.nrows, sc, partials); break;
-    }
-    return YFD_OK;
-}
-
 template <bool WITH_DOT>
 static yfd_status launch_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
 {
-    if (op.cellptr && use_tma_spmv()) {
-        const int64_t before = ctx->launches;
-        const yfd_status st = launch_dg_spmv_tma<WITH_DOT>(ctx, op.bs, op.nf, op.cellptr, op.blk_cell, op.values, op.ncells, x, y, sc, partials);
-        if (st != YFD_ERR_UNSUPPORTED || ctx->launches != before) return st;
-    }
-    if (op.cellptr) {
-        switch (op.bs) {
-        case 1:  return launch_dg_spmv_bs<1, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 3:  return launch_dg_spmv_bs<3, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 6:  return launch_dg_spmv_bs<6, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 10: return launch_dg_spmv_bs<10, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 15: return launch_dg_spmv_bs<15, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 21: return launch_dg_spmv_bs<21, WITH_DOT>(ctx, op, x, y, sc, partials);
-        case 28: return launch_dg_spmv_bs<28, WITH_DOT>(ctx, op, x, y, sc, partials);
-        default: break;     /* fall through to the generic kernel */
-        }
-    }
+    if (op.cellptr)         /* DG block rows: the TMA-streamed kernel (yfd_spmv_tma.cu); there is no other path for them */
+        return launch_dg_spmv_tma<WITH_DOT>(ctx, op.bs, op.nf, op.cellptr, op.blk_cell, op.values, op.ncells, x, y, sc, partials);
     return launch_csr_spmv<WITH_DOT>(ctx, op, x, y, sc, partials);
 }
 
@@ -444,7 +357,8 @@ static spmv_op op_of_csr(const yfd_csr *A)
 static spmv_op op_of_system(const yfd_system *sys, bool allow_block_kernel)
 {
     spmv_op op = op_of_csr(&sys->A);
-    if (sys->kind == YFD_SYS_DG && allow_block_kernel) {
+    (void) allow_block_kernel;
+    if (sys->kind == YFD_SYS_DG) {
         op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf; op.ncells = sys->ncells;
     }
     return op;

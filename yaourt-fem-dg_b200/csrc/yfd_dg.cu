@@ -5,7 +5,8 @@
  * triplet machinery behind it (assembler::assemble, methods/dg.hpp:67-123; finalize ->
  * init_from_triplets, methods/dg.hpp:125-144) for the DG case, where the sparsity pattern is
  * known from face_owners: row block c holds the diagonal block  K + sum_e Att_e  and one block
- * Atn_e per neighbour, blocks ordered by column = ascending cell id.  No sort is needed; the
+ * Atn_e per neighbour, blocks ordered by column = ascending cell id, stored transposed inside the
+ * cell (W[l][i], see yfd_spmv_tma.cu) so the SpMV warps read consecutive words.  No sort is needed; the
  * generic sort-based path (yfd_triplets.cu) stays for CFEM and for the drop-in
  * init_from_triplets.
  *
@@ -16,7 +17,7 @@
  *      1D Gauss on faces, :723-746) -- one lane per quadrature point -- and stages the tables
  *      phi, d_x phi, d_y phi (cell) / phi, grad phi . n for both sides (face) in shared memory;
  *   2. contracts them: one lane per block entry (i,j), fp64 FMA, accumulators in registers;
- *   3. streams the finished rows straight into the CSR value array (coalesced bs-wide runs).
+ *   3. streams the finished blocks straight into the matrix value array (coalesced bs-wide runs).
  * The basis is defined in PHYSICAL coordinates scaled by the cell diameter, so tables cannot be
  * shared between cells in general (hard part 4); only the reference rule
  * (barycentric / Gauss abscissae and weights) is shared and read through the read-only path.
@@ -188,7 +189,7 @@ dg_sip_cells(const dg_args a)
             const int m = t * 32 + lane;
             double s = 0.0;
             if (m < BS2) {
-                const int i = m / BS, j = m - i * BS;
+                const int j = m / BS, i = m - j * BS;
                 for (int q = 0; q < NQ; q++)
                     s += W[q] * (DX[i * NQ + q] * DX[j * NQ + q] + DY[i * NQ + q] * DY[j * NQ + q]);
             }
@@ -203,7 +204,7 @@ dg_sip_cells(const dg_args a)
 #pragma unroll
                 for (int t = 0; t < NACC; t++) {
                     const int m = t * 32 + lane;
-                    if (m < BS2) a.oK[(int64_t) rc * BS2 + m] = accD[t];
+                    if (m < BS2) { const int j = m / BS, i = m - j * BS; a.oK[(int64_t) rc * BS2 + i * BS + j] = accD[t]; }
                 }
             }
 #pragma unroll
@@ -213,7 +214,6 @@ dg_sip_cells(const dg_args a)
 
         /* ---------------- faces ---------------- */
         const int64_t cp = a.blocks_mode ? 0 : a.cellptr[cell];
-        const int nblk = a.blocks_mode ? 0 : (int) (a.cellptr[cell + 1] - cp);
         double *vrow = a.blocks_mode ? nullptr : a.values + cp * BS2;
 
         double *FW = S, *FG = S + NFQ, *TPHI = S + 2 * NFQ, *TGN = TPHI + NFQ * BS, *NPHI = TGN + NFQ * BS, *NGN = NPHI + NFQ * BS;
@@ -269,7 +269,7 @@ dg_sip_cells(const dg_args a)
             for (int t = 0; t < NACC; t++) {
                 const int m = t * 32 + lane;
                 if (m < BS2) {
-                    const int i = m / BS, j = m - i * BS;
+                    const int j = m / BS, i = m - j * BS;          /* i fastest: W[l][i] runs are contiguous */
                     double att = 0.0, atn = 0.0;
                     for (int q = 0; q < NFQ; q++) {
                         const double w = FW[q];
@@ -283,11 +283,11 @@ dg_sip_cells(const dg_args a)
                     }
                     accD[t] += att;
                     if (a.blocks_mode) {
-                        if (a.oAtt) a.oAtt[((int64_t) rc * NV + e) * BS2 + m] = accD[t];
-                        if (a.oAtn) a.oAtn[((int64_t) rc * NV + e) * BS2 + m] = atn;
+                        if (a.oAtt) a.oAtt[((int64_t) rc * NV + e) * BS2 + i * BS + j] = accD[t];
+                        if (a.oAtn) a.oAtn[((int64_t) rc * NV + e) * BS2 + i * BS + j] = atn;
                         accD[t] = 0.0;
                     } else if (has_nb) {
-                        vrow[(int64_t) i * nblk * BS + slot * BS + j] = atn;
+                        vrow[(slot * BS + j) * BS + i] = atn;
                     }
                 }
             }
@@ -308,8 +308,8 @@ dg_sip_cells(const dg_args a)
             for (int t = 0; t < NACC; t++) {
                 const int m = t * 32 + lane;
                 if (m < BS2) {
-                    const int i = m / BS, j = m - i * BS;
-                    vrow[(int64_t) i * nblk * BS + dslot * BS + j] = accD[t];
+                    const int j = m / BS, i = m - j * BS;
+                    vrow[(dslot * BS + j) * BS + i] = accD[t];
                     if (a.pc && i == j) a.pc[cell * BS + i] = 1.0 / accD[t];     /* methods/dg.hpp:133-142 */
                 }
             }
@@ -379,30 +379,6 @@ __global__ void dg_fill_blocks(const dg_args a, int32_t *__restrict__ blk_cell, 
     for (int s = 0; s < n; s++) blk_cell[cp + s] = ids[s];
 #pragma unroll
     for (int s = 0; s < NV + 1; s++) slots_out[cell * (NV + 1) + s] = slots[s];
-}
-
-/* rowptr + colidx of the block CSR: one warp per cell, lanes over the cell's entries */
-__global__ void dg_fill_pattern(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell,
-                                int64_t ncells, int bs, int64_t *__restrict__ rowptr, int32_t *__restrict__ colidx)
-{
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    const int64_t bs2 = (int64_t) bs * bs;
-    for (int64_t cell = warp; cell < ncells; cell += nwarps) {
-        const int64_t cp = cellptr[cell];
-        const int nblk = (int) (cellptr[cell + 1] - cp);
-        const int rowlen = nblk * bs;
-        const int64_t base = cp * bs2;
-        if (lane < bs) rowptr[cell * bs + lane] = base + (int64_t) lane * rowlen;
-        if (cell == ncells - 1 && lane == 0) rowptr[ncells * bs] = base + (int64_t) bs * rowlen;
-        const int total = bs * rowlen;
-        for (int m = lane; m < total; m += 32) {
-            const int l = m % rowlen;
-            const int s = l / bs, j = l - s * bs;
-            colidx[base + m] = blk_cell[cp + s] * bs + j;
-        }
-    }
 }
 
 template <int NV, int K>
@@ -502,19 +478,12 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n; sys->A.nnz = nnz;
     YFD_TRY(sys->blk_cell.alloc(ctx, (size_t) nblocks, 4));
     YFD_TRY(slots.alloc(ctx, (size_t) nc * (NV + 1)));
-    YFD_TRY(sys->A.rowptr.alloc(ctx, (size_t) n + 1));
-    YFD_TRY(sys->A.colidx.alloc(ctx, (size_t) nnz, 4));
+    /* no per-entry row offsets / column indices are stored for DG: the pattern IS cellptr + blk_cell */
     YFD_TRY(sys->A.values.alloc(ctx, (size_t) nnz, 4));
     YFD_TRY(sys->rhs.alloc(ctx, (size_t) n));
     if (cfg->build_preconditioner) YFD_TRY(sys->pc.alloc(ctx, (size_t) n));
     a.cellptr = sys->cellptr.p;
     YFD_LAUNCH(ctx, dg_fill_blocks<NV>, g, 256, 0, a, sys->blk_cell.p, slots.p, derr.p);
-    {
-        const int64_t want = ceil_div(nc, 8);
-        const int64_t cap = (int64_t) ctx->sm_count * 16;
-        const unsigned gp = (unsigned) (want < cap ? want : cap);
-        YFD_LAUNCH(ctx, dg_fill_pattern, gp, 256, 0, sys->cellptr.p, sys->blk_cell.p, nc, bs, sys->A.rowptr.p, sys->A.colidx.p);
-    }
     t_struct.stop(ctx->stream);
     YFD_TRY(derr.download(ctx, &herr, 1));
     if (herr) return fail(ctx, YFD_ERR_UNSUPPORTED, "two faces of one cell lead to the same neighbour; use the triplet path");

@@ -1,32 +1,37 @@
 /*
  * yfd_spmv_tma.cu -- the CG hot kernel: y = A d (+ partial sums of d.y) for DG block rows, with the
- * matrix streamed by the TMA engine.
+ * matrix streamed by the TMA engine into per-warp shared-memory rings.
  *
  * Replaces Blaze's sparse-row times dense-vector loop behind `y = A*d` in conjugated_gradient
  * (core/solvers.hpp:115; blaze/math/expressions/SMatDVecMultExpr.h:204-207).
  *
- * Why this shape.  In internal (Z-curve) cell order the value array of the block CSR is ONE contiguous
- * stream: cell c owns values [cellptr[c] bs^2, cellptr[c+1] bs^2), rows back to back.  A row-per-team
- * kernel needs three dependent load rounds per row (offsets -> values / block list -> x) and keeps only
- * ~10 KB per SM in flight (profiles/README.md, r01 v1: 2.6 TB/s).  Here each CTA walks a static list of
- * chunks (a fixed number of consecutive cells, <= 32 KB of values); one thread feeds a 3-4 stage ring with
- * cp.async.bulk (global -> shared, completion counted on an mbarrier): the chunk's values, its slice of
- * cellptr and its slice of the block list.  Two resident CTAs x (stages-1) x 32 KB are in flight per SM
- * with no registers held for them.  The consumers then
- *   A. gather the x entries of every block in the chunk into shared memory (independent loads, one round),
- *   B. form the rows: a team of TS lanes per row, both operands from shared memory, warp-shuffle reduce,
- *      y written once, d.y accumulated per thread and reduced deterministically over the grid (last block).
- * Chunks are assigned round-robin by block index, so results are bit-reproducible run to run.
- * The 4 B/nnz column-index stream of CSR is never read: columns come from the block list (<= 5 ints/cell).
+ * Matrix layout in HBM ("block rows, transposed"): cells in internal (Z-curve) order; cell c owns the
+ * contiguous values [cellptr[c] bs^2, cellptr[c+1] bs^2) holding W_c[l][i] = A(row c*bs+i, l-th column of the
+ * block row), l = slot*bs + j over the cell's blocks in ascending column order.  Same entries and same
+ * count as the CSR value array (8 B/nnz), only transposed inside each cell so that the lanes of a warp --
+ * one lane per matrix row -- read consecutive shared-memory words.  Column indices are never stored per
+ * entry: they follow from the block list (<= 5 ints per cell).  yfd_system_get_csr re-emits reference CSR.
+ *
+ * Kernel shape (profiles/README.md records why the first two generations stalled at 2.6-2.8 TB/s: three
+ * dependent load rounds per row, then ~1.5 warp instructions per non-zero in a team-per-row reduction):
+ *   - every WARP is an autonomous pipeline: it owns a static, round-robin list of chunks (as many consecutive
+ *     cells as give <= 32 rows), and a ring of NS stages in shared memory with one mbarrier each;
+ *   - lane 0 feeds the ring with cp.async.bulk (global -> shared, complete_tx on the mbarrier): the chunk's
+ *     values (L2 evict_first), its cellptr slice and its block-list slice.  No registers are held for data
+ *     in flight and there is no __syncthreads anywhere in the loop;
+ *   - the x entries of chunk k+1 are gathered into registers (<= 5 per lane) while chunk k is multiplied;
+ *   - lane r forms row r of the chunk serially from shared memory (2 LDS + 1 DFMA per non-zero, four
+ *     independent accumulators), writes y[r] coalesced, and accumulates d.y, reduced over the grid by
+ *     the last block in a fixed order: bit-reproducible run to run.
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
+#include <cstdlib>
 
 namespace yfd {
 
-constexpr int TMA_THREADS = 256;
-constexpr int TMA_STAGE_VALUE_BYTES = 32 * 1024;
-constexpr int TMA_MAX_CHUNK_CELLS = 256;
+constexpr int TMA_MAX_WARPS = 16;          /* warps per CTA, one CTA per SM */
+constexpr int TMA_XPL = 5;                 /* gathered x entries per lane: chunk blocks * bs <= 160 */
 
 /* ---- PTX wrappers (sm_100a): mbarrier + bulk async copy -------------------------------------- */
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -70,144 +75,155 @@ __device__ __forceinline__ void bulk_g2s_plain(void *dst, const void *src, uint3
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+
 struct tma_layout {
-    int G;              /* cells per chunk */
+    int G;              /* cells per chunk (rows = G*bs <= 32) */
     int nstages;
+    int nwarps;         /* warps per CTA */
     int v_bytes;        /* per stage: values (incl. 16 B of skew room) */
     int bc_bytes;       /* per stage: block list slice */
     int cp_bytes;       /* per stage: cellptr slice */
-    int xs_bytes;       /* one gather buffer */
     int stage_bytes;
-    int total_bytes;
+    int xs_bytes;       /* per warp: gathered x */
+    int warp_bytes;     /* per warp: stages + xs + barriers */
 };
 
 __host__ __device__ inline int round16(int b) { return (b + 15) & ~15; }
 
-/* One chunk's three source ranges, 16-byte aligned down / rounded up. */
-struct chunk_src {
-    const char *v_src, *bc_src, *cp_src;
-    uint32_t v_bytes, bc_bytes, cp_bytes;
-};
-
-template <int BS>
-__device__ __forceinline__ chunk_src chunk_ranges(const int64_t *cellptr, const int32_t *blk_cell, const double *values,
-                                                  int64_t c0, int ncell, int64_t lo, int64_t hi)
-{
-    chunk_src s;
-    const uint64_t vb0 = (uint64_t) lo * (BS * BS * 8), vb1 = (uint64_t) hi * (BS * BS * 8);
-    const uint64_t va = vb0 & ~(uint64_t) 15;
-    s.v_src = (const char *) values + va;
-    s.v_bytes = (uint32_t) (((vb1 - va) + 15) & ~(uint64_t) 15);
-    const uint64_t bb0 = (uint64_t) lo * 4, bb1 = (uint64_t) hi * 4, ba = bb0 & ~(uint64_t) 15;
-    s.bc_src = (const char *) blk_cell + ba;
-    s.bc_bytes = (uint32_t) (((bb1 - ba) + 15) & ~(uint64_t) 15);
-    const uint64_t cb0 = (uint64_t) c0 * 8, cb1 = (uint64_t) (c0 + ncell + 1) * 8, ca = cb0 & ~(uint64_t) 15;
-    s.cp_src = (const char *) cellptr + ca;
-    s.cp_bytes = (uint32_t) (((cb1 - ca) + 15) & ~(uint64_t) 15);
-    return s;
-}
-
-template <int BS, int TS, bool WITH_DOT>
-__global__ void __launch_bounds__(TMA_THREADS, 2)
+template <int BS, bool WITH_DOT>
+__global__ void __launch_bounds__(TMA_MAX_WARPS * 32, 1)
 dg_spmv_tma(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const double *__restrict__ values,
             const double *__restrict__ x, double *__restrict__ y, int64_t ncells, int64_t nchunks, const tma_layout lay,
             cg_scalars *__restrict__ sc, double *__restrict__ partials)
 {
     if (WITH_DOT && sc->done) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    __shared__ __align__(8) uint64_t full_bar[4];
     constexpr int BS2 = BS * BS;
-    constexpr int NT = TMA_THREADS / TS;            /* teams per CTA */
-    const int tid = threadIdx.x;
-    const int tl = tid & (TS - 1), team = tid / TS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int G = lay.G, NS = lay.nstages;
-    double *xs = reinterpret_cast<double *>(smem_raw + (size_t) NS * lay.stage_bytes);
+    unsigned char *wbase = smem_raw + (size_t) warp * lay.warp_bytes;
+    double *xs = reinterpret_cast<double *>(wbase + (size_t) NS * lay.stage_bytes);
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(wbase + (size_t) NS * lay.stage_bytes + lay.xs_bytes);
 
-    if (tid == 0) {
+    if (lane == 0) {
         for (int s = 0; s < NS; s++) mbar_init(&full_bar[s], 1);
         fence_proxy_async();
     }
-    __syncthreads();
+    __syncwarp();
 
-    /* producer state (thread 0): the next chunk to issue and its block range, fetched one step ahead */
-    const int64_t my_first = blockIdx.x, stride = gridDim.x;
-    const int64_t my_count = my_first < nchunks ? (nchunks - my_first + stride - 1) / stride : 0;
+    const int64_t gw = (int64_t) blockIdx.x * lay.nwarps + warp, stride = (int64_t) gridDim.x * lay.nwarps;
+    const int64_t my_count = gw < nchunks ? (nchunks - gw + stride - 1) / stride : 0;
+
+    /* ---- producer side (lane 0) ---- */
     uint64_t policy = 0;
-    int64_t issue_k = 0;                /* index into my chunk list */
-    int64_t nx_lo = 0, nx_hi = 0;
+    int64_t nx_lo = 0, nx_hi = 0;               /* block range of the next chunk to issue, fetched a step ahead */
     auto fetch_bounds = [&](int64_t k) {
         if (k < my_count) {
-            const int64_t c0 = (my_first + k * stride) * G;
+            const int64_t c0 = (gw + k * stride) * G;
             const int64_t c1 = c0 + G < ncells ? c0 + G : ncells;
             nx_lo = __ldg(&cellptr[c0]); nx_hi = __ldg(&cellptr[c1]);
         }
     };
-    auto issue = [&](int64_t k) {       /* bounds of chunk k are in nx_lo / nx_hi */
+    auto issue = [&](int64_t k) {
         const int s = (int) (k % NS);
-        const int64_t c0 = (my_first + k * stride) * G;
+        const int64_t c0 = (gw + k * stride) * G;
         const int ncell = (int) ((c0 + G < ncells ? c0 + G : ncells) - c0);
-        const chunk_src r = chunk_ranges<BS>(cellptr, blk_cell, values, c0, ncell, nx_lo, nx_hi);
-        unsigned char *st = smem_raw + (size_t) s * lay.stage_bytes;
+        /* three source ranges, aligned down to 16 B / rounded up (arrays are padded) */
+        const uint64_t vb0 = (uint64_t) nx_lo * (BS2 * 8), vb1 = (uint64_t) nx_hi * (BS2 * 8), va = vb0 & ~(uint64_t) 15;
+        const uint32_t vbytes = (uint32_t) (((vb1 - va) + 15) & ~(uint64_t) 15);
+        const uint64_t bb0 = (uint64_t) nx_lo * 4, bb1 = (uint64_t) nx_hi * 4, ba = bb0 & ~(uint64_t) 15;
+        const uint32_t bbytes = (uint32_t) (((bb1 - ba) + 15) & ~(uint64_t) 15);
+        const uint64_t cb0 = (uint64_t) c0 * 8, cb1 = (uint64_t) (c0 + ncell + 1) * 8, ca = cb0 & ~(uint64_t) 15;
+        const uint32_t cbytes = (uint32_t) (((cb1 - ca) + 15) & ~(uint64_t) 15);
+        unsigned char *st = wbase + (size_t) s * lay.stage_bytes;
         fence_proxy_async();
-        mbar_expect_tx(&full_bar[s], r.v_bytes + r.bc_bytes + r.cp_bytes);
-        bulk_g2s(st, r.v_src, r.v_bytes, &full_bar[s], policy);
-        bulk_g2s_plain(st + lay.v_bytes, r.bc_src, r.bc_bytes, &full_bar[s]);
-        bulk_g2s_plain(st + lay.v_bytes + lay.bc_bytes, r.cp_src, r.cp_bytes, &full_bar[s]);
+        mbar_expect_tx(&full_bar[s], vbytes + bbytes + cbytes);
+        bulk_g2s(st, (const char *) values + va, vbytes, &full_bar[s], policy);
+        bulk_g2s_plain(st + lay.v_bytes, (const char *) blk_cell + ba, bbytes, &full_bar[s]);
+        bulk_g2s_plain(st + lay.v_bytes + lay.bc_bytes, (const char *) cellptr + ca, cbytes, &full_bar[s]);
     };
-    if (tid == 0) {
+    if (lane == 0) {
         policy = policy_evict_first();
-        for (; issue_k < NS - 1 && issue_k < my_count; issue_k++) { fetch_bounds(issue_k); issue(issue_k); }
-        fetch_bounds(issue_k);
+        int64_t k = 0;
+        for (; k < NS && k < my_count; k++) { fetch_bounds(k); issue(k); }
+        fetch_bounds(k);
     }
 
-    double dot = 0.0;
-    for (int64_t k = 0; k < my_count; k++) {
-        if (tid == 0 && issue_k < my_count) {
-            issue(issue_k);             /* into the stage consumed at iteration k-1 (all threads passed its last barrier) */
-            issue_k++;
-            fetch_bounds(issue_k);      /* latency hidden behind this iteration's work */
-        }
+    /* ---- consumer side ---- */
+    struct chunk_view { const int64_t *CP; const double *V; const int32_t *BC; int64_t lo, c0; int ncell, nblocks; };
+    auto view = [&](int64_t k) {
+        chunk_view v;
         const int s = (int) (k % NS);
-        mbar_wait(&full_bar[s], (uint32_t) ((k / NS) & 1));
-
-        const int64_t c0 = (my_first + k * stride) * G;
-        const int ncell = (int) ((c0 + G < ncells ? c0 + G : ncells) - c0);
-        const unsigned char *st = smem_raw + (size_t) s * lay.stage_bytes;
-        const int64_t *CP = reinterpret_cast<const int64_t *>(st + lay.v_bytes + lay.bc_bytes + ((c0 & 1) ? 8 : 0));
-        const int64_t lo = CP[0];
-        const int nblocks = (int) (CP[ncell] - lo);
-        const double *V = reinterpret_cast<const double *>(st + (((uint64_t) lo * (BS2 * 8)) & 15));
-        const int32_t *BC = reinterpret_cast<const int32_t *>(st + lay.v_bytes + (((uint64_t) lo * 4) & 15));
-
-        /* ---- A: gather x for every block of the chunk ---- */
-        for (int t = tid; t < nblocks * BS; t += TMA_THREADS) {
-            const int b = t / BS, j = t - b * BS;
-            xs[t] = __ldg(&x[(int64_t) BC[b] * BS + j]);
-        }
-        __syncthreads();
-
-        /* ---- B: rows ---- */
-        const int nrows = ncell * BS;
-        for (int r0 = 0; r0 < nrows; r0 += NT) {
-            const int r = r0 + team;
-            const bool live = r < nrows;
-            double acc = 0.0;
-            if (live) {
-                const int i = r / BS, irow = r - i * BS;
-                const int cr = (int) (CP[i] - lo);
-                const int L = (int) (CP[i + 1] - CP[i]) * BS;
-                const double *vrow = V + (size_t) cr * BS2 + irow * L;
-                const double *xr = xs + cr * BS;
-                for (int l = tl; l < L; l += TS) acc += vrow[l] * xr[l];
-            }
-            acc = team_sum<TS>(acc);
-            if (live && tl == 0) {
-                const int64_t row = c0 * BS + r;
-                y[row] = acc;
-                if (WITH_DOT) dot += acc * __ldg(&x[row]);
+        v.c0 = (gw + k * stride) * G;
+        v.ncell = (int) ((v.c0 + G < ncells ? v.c0 + G : ncells) - v.c0);
+        const unsigned char *st = wbase + (size_t) s * lay.stage_bytes;
+        v.CP = reinterpret_cast<const int64_t *>(st + lay.v_bytes + lay.bc_bytes + ((v.c0 & 1) ? 8 : 0));
+        v.lo = v.CP[0];
+        v.nblocks = (int) (v.CP[v.ncell] - v.lo);
+        v.V = reinterpret_cast<const double *>(st + (((uint64_t) v.lo * (BS2 * 8)) & 15));
+        v.BC = reinterpret_cast<const int32_t *>(st + lay.v_bytes + (((uint64_t) v.lo * 4) & 15));
+        return v;
+    };
+    double xg[TMA_XPL];
+    auto gather = [&](const chunk_view &v) {
+        const int nx = v.nblocks * BS;
+#pragma unroll
+        for (int u = 0; u < TMA_XPL; u++) {
+            const int t = lane + 32 * u;
+            xg[u] = 0.0;
+            if (t < nx) {
+                const int b = t / BS, j = t - b * BS;
+                xg[u] = __ldg(&x[(int64_t) v.BC[b] * BS + j]);
             }
         }
-        __syncthreads();
+    };
+
+    double dot = 0.0;
+    chunk_view cur;
+    if (my_count > 0) {
+        mbar_wait(&full_bar[0], 0);
+        cur = view(0);
+        gather(cur);
+    }
+    for (int64_t k = 0; k < my_count; k++) {
+#pragma unroll
+        for (int u = 0; u < TMA_XPL; u++) xs[lane + 32 * u] = xg[u];
+        __syncwarp();
+        chunk_view nxt;
+        const bool has_next = k + 1 < my_count;
+        if (has_next) {
+            mbar_wait(&full_bar[(k + 1) % NS], (uint32_t) (((k + 1) / NS) & 1));
+            nxt = view(k + 1);
+            gather(nxt);                         /* loads stay in flight during the multiply below */
+        }
+        /* ---- rows of chunk k: lane r <-> row r ---- */
+        const int nrows = cur.ncell * BS;
+        if (lane < nrows) {
+            const int i = lane / BS, irow = lane - i * BS;
+            const int cr = (int) (cur.CP[i] - cur.lo);
+            const int L = (int) (cur.CP[i + 1] - cur.CP[i]) * BS;
+            const double *w = cur.V + (size_t) cr * BS2 + irow;
+            const double *xr = xs + cr * BS;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int l = 0;
+            for (; l + 3 < L; l += 4) {
+                a0 += w[(l) * BS] * xr[l];
+                a1 += w[(l + 1) * BS] * xr[l + 1];
+                a2 += w[(l + 2) * BS] * xr[l + 2];
+                a3 += w[(l + 3) * BS] * xr[l + 3];
+            }
+            for (; l < L; l++) a0 += w[l * BS] * xr[l];
+            const double acc = (a0 + a1) + (a2 + a3);
+            const int64_t row = cur.c0 * BS + lane;
+            y[row] = acc;
+            if (WITH_DOT) dot += acc * __ldg(&x[row]);
+        }
+        __syncwarp();
+        if (lane == 0 && k + NS < my_count) {
+            issue(k + NS);                       /* refill the stage just consumed */
+            fetch_bounds(k + NS + 1);
+        }
+        cur = nxt;
     }
     if (WITH_DOT) {
         __shared__ double tot[1];
@@ -217,41 +233,42 @@ dg_spmv_tma(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk
 }
 
 /* ---- host side ------------------------------------------------------------------------------- */
+static int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
+
 static tma_layout make_layout(yfd_ctx *ctx, int bs, int nf)
 {
     tma_layout l;
     const int mb = nf + 1;
-    int G = TMA_STAGE_VALUE_BYTES / (mb * bs * bs * 8);
+    int G = 32 / bs;
     if (G < 1) G = 1;
-    if (G > TMA_MAX_CHUNK_CELLS) G = TMA_MAX_CHUNK_CELLS;
-    if (G > 1) G &= ~1;
+    while (G > 1 && G * mb * bs > 32 * TMA_XPL) G--;
     l.G = G;
     l.v_bytes = round16(G * mb * bs * bs * 8) + 16;
     l.bc_bytes = round16(G * mb * 4) + 16;
     l.cp_bytes = round16((G + 1) * 8) + 16;
     l.stage_bytes = (l.v_bytes + l.bc_bytes + l.cp_bytes + 127) & ~127;
-    l.xs_bytes = round16(G * mb * bs * 8);
-    /* two CTAs per SM: leave room for static shared memory and the driver's reserve */
-    const int budget = (int) (ctx->smem_per_sm / 2) - 2048 - l.xs_bytes;
-    int ns = budget / l.stage_bytes;
-    if (ns > 4) ns = 4;
+    l.xs_bytes = 32 * TMA_XPL * 8;
+    const int budget = (int) ctx->smem_optin - 1024;
+    int ns = env_int("YFD_SPMV_STAGES", 0);
+    if (ns < 2 || ns > 8) {
+        /* as many warps as fit with 2 stages; then deepen the rings while the warp count holds */
+        ns = 2;
+        int w = budget / (ns * l.stage_bytes + l.xs_bytes + 128);
+        if (w > TMA_MAX_WARPS) w = TMA_MAX_WARPS;
+        while (ns < 4 && w >= 1 && budget / ((ns + 1) * l.stage_bytes + l.xs_bytes + 128) >= w) ns++;
+    }
     l.nstages = ns;
-    l.total_bytes = ns * l.stage_bytes + l.xs_bytes;
+    l.warp_bytes = (ns * l.stage_bytes + l.xs_bytes + 128 + 127) & ~127;
+    int w = budget / l.warp_bytes;
+    if (w > TMA_MAX_WARPS) w = TMA_MAX_WARPS;
+    const int wcap = env_int("YFD_SPMV_WARPS", 0);
+    if (wcap >= 1 && wcap < w) w = wcap;
+    l.nwarps = w;
     return l;
-}
-
-template <int BS, int TS, bool WITH_DOT>
-static yfd_status launch_tma(yfd_ctx *ctx, const tma_layout &l, const int64_t *cellptr, const int32_t *blk_cell, const double *values,
-                             int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials)
-{
-    auto kern = dg_spmv_tma<BS, TS, WITH_DOT>;
-    YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, l.total_bytes));
-    const int64_t nchunks = ceil_div(ncells, l.G);
-    int64_t grid = (int64_t) ctx->sm_count * 2;
-    if (grid > nchunks) grid = nchunks;
-    if (grid > CG_MAX_PARTIALS) grid = CG_MAX_PARTIALS;
-    YFD_LAUNCH(ctx, kern, (unsigned) grid, TMA_THREADS, (size_t) l.total_bytes, cellptr, blk_cell, values, x, y, ncells, nchunks, l, sc, partials);
-    return YFD_OK;
 }
 
 template <int BS, bool WITH_DOT>
@@ -259,10 +276,16 @@ static yfd_status launch_tma_bs(yfd_ctx *ctx, int nf, const int64_t *cellptr, co
                                 int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials)
 {
     const tma_layout l = make_layout(ctx, BS, nf);
-    if (l.nstages < 2) return YFD_ERR_UNSUPPORTED;
-    constexpr int LMAX = 5 * BS;
-    constexpr int TS = LMAX <= 8 ? 4 : LMAX <= 32 ? 8 : LMAX <= 80 ? 16 : 32;
-    return launch_tma<BS, TS, WITH_DOT>(ctx, l, cellptr, blk_cell, values, ncells, x, y, sc, partials);
+    if (l.nwarps < 1) return fail(ctx, YFD_ERR_UNSUPPORTED, "block size %d does not fit the shared-memory ring", BS);
+    auto kern = dg_spmv_tma<BS, WITH_DOT>;
+    const int smem = l.nwarps * l.warp_bytes;
+    YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int64_t nchunks = ceil_div(ncells, l.G);
+    int64_t grid = ceil_div(nchunks, l.nwarps);
+    if (grid > ctx->sm_count) grid = ctx->sm_count;
+    if (grid < 1) grid = 1;
+    YFD_LAUNCH(ctx, kern, (unsigned) grid, l.nwarps * 32, (size_t) smem, cellptr, blk_cell, values, x, y, ncells, nchunks, l, sc, partials);
+    return YFD_OK;
 }
 
 template <bool WITH_DOT>
@@ -278,7 +301,7 @@ yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellp
     case 21: return launch_tma_bs<21, WITH_DOT>(ctx, nf, cellptr, blk_cell, values, ncells, x, y, sc, partials);
     case 28: return launch_tma_bs<28, WITH_DOT>(ctx, nf, cellptr, blk_cell, values, ncells, x, y, sc, partials);
     }
-    return YFD_ERR_UNSUPPORTED;
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "no SpMV instantiation for block size %d", bs);
 }
 
 template yfd_status launch_dg_spmv_tma<true>(yfd_ctx *, int, int, const int64_t *, const int32_t *, const double *, int64_t, const double *, double *, cg_scalars *, double *);

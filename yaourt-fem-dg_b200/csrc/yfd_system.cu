@@ -67,7 +67,7 @@ __global__ void export_ref_csr(const int64_t *__restrict__ cellptr, const int32_
             const int s = l / bs, j = l - s * bs;
             const int64_t dst = base_r + (int64_t) i * rowlen + rank[s] * bs + j;
             if (colidx) colidx[dst] = (int64_t) rid[s] * bs + j;
-            if (vals_out) vals_out[dst] = values[base_i + m];
+            if (vals_out) vals_out[dst] = values[base_i + (int64_t) l * bs + i];      /* W[l][i] -> CSR row i */
         }
     }
 }
