@@ -30,7 +30,9 @@
 
 namespace yfd {
 
-constexpr int TMA_MAX_WARPS = 16;          /* warps per CTA, one CTA per SM */
+/* warps per CTA (one CTA per SM): as many as the shared-memory rings allow -- throughput follows the number
+ * of independent pipelines, not their depth (tools/spmv_sweep.py).  Small blocks fit more than 16 rings. */
+__host__ __device__ constexpr int tma_max_warps(int bs) { return bs <= 3 ? 32 : 16; }
 constexpr int TMA_XPL = 5;                 /* gathered x entries per lane: chunk blocks * bs <= 160 */
 
 /* ---- PTX wrappers (sm_100a): mbarrier + bulk async copy -------------------------------------- */
@@ -91,7 +93,7 @@ struct tma_layout {
 __host__ __device__ inline int round16(int b) { return (b + 15) & ~15; }
 
 template <int BS, bool WITH_DOT>
-__global__ void __launch_bounds__(TMA_MAX_WARPS * 32, 1)
+__global__ void __launch_bounds__(tma_max_warps(BS) * 32, 1)
 dg_spmv_tma(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const double *__restrict__ values,
             const double *__restrict__ x, double *__restrict__ y, int64_t ncells, int64_t nchunks, const tma_layout lay,
             cg_scalars *__restrict__ sc, double *__restrict__ partials)
@@ -258,13 +260,13 @@ static tma_layout make_layout(yfd_ctx *ctx, int bs, int nf)
         /* as many warps as fit with 2 stages; then deepen the rings while the warp count holds */
         ns = 2;
         int w = budget / (ns * l.stage_bytes + l.xs_bytes + 128);
-        if (w > TMA_MAX_WARPS) w = TMA_MAX_WARPS;
+        if (w > tma_max_warps(bs)) w = tma_max_warps(bs);
         while (ns < 4 && w >= 1 && budget / ((ns + 1) * l.stage_bytes + l.xs_bytes + 128) >= w) ns++;
     }
     l.nstages = ns;
     l.warp_bytes = (ns * l.stage_bytes + l.xs_bytes + 128 + 127) & ~127;
     int w = budget / l.warp_bytes;
-    if (w > TMA_MAX_WARPS) w = TMA_MAX_WARPS;
+    if (w > tma_max_warps(bs)) w = tma_max_warps(bs);
     const int wcap = env_int("YFD_SPMV_WARPS", 0);
     if (wcap >= 1 && wcap < w) w = wcap;
     l.nwarps = w;
