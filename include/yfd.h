@@ -134,6 +134,27 @@ yfd_status yfd_mesh_get_permutation(yfd_mesh *m, int64_t *perm);
 /* replace the coordinates (shatter_mesh output etc.); same count as at creation */
 yfd_status yfd_mesh_set_points(yfd_mesh *m, const double *points);
 
+/* neighbours [ncells][nf] in INTERNAL cell order and ids: the cell across each local face, -1 on the
+ * boundary (neighbour_via, core/mesh.hpp:249-272, for every cell at once) */
+yfd_status yfd_mesh_get_neighbours(yfd_mesh *m, int64_t *neighbours);
+
+/* ---------------------------------------------------------------------------------- */
+/* Partition plan (host, no CUDA): new, SURVEY.md section 8e.  Cells are split into     */
+/* `nranks` contiguous blocks of the internal order; from the neighbour table each rank  */
+/* derives its halo (grouped by owner rank) and its per-peer send lists.  The assembly   */
+/* and solve entry points below build and use this plan themselves when the context has  */
+/* a communicator attached; it is exposed so host programs and tests can inspect it.     */
+/* ---------------------------------------------------------------------------------- */
+typedef struct yfd_partition yfd_partition;
+yfd_status yfd_partition_create(int64_t ncells, int nf, const int64_t *neighbours, int nranks, int rank, yfd_partition **out);
+void       yfd_partition_destroy(yfd_partition *p);
+void       yfd_partition_sizes(const yfd_partition *p, int64_t *cell_begin, int64_t *cell_end, int64_t *nhalo,
+                               int64_t *nsend, int *npeers);
+/* halo_cells [nhalo], send_cells [nsend]: internal cell ids grouped by peer (peers ascending), ids ascending;
+ * peers / recv_counts / send_counts [npeers] (counts in cells).  Any output may be NULL. */
+yfd_status yfd_partition_get(const yfd_partition *p, int64_t *halo_cells, int64_t *send_cells, int32_t *peers,
+                             int64_t *recv_counts, int64_t *send_counts);
+
 /* ---------------------------------------------------------------------------------- */
 /* Sparse matrix handle (row-major CSR, fp64 values, int32 columns, int64 row offsets)  */
 /* = blaze::CompressedMatrix<double> at this boundary.                                  */
@@ -186,6 +207,9 @@ typedef struct yfd_assembly_info {
     double  ms_structure;       /* device time: sparsity pattern (rowptr / colidx)         */
 } yfd_assembly_info;
 
+/* With a communicator attached to ctx (yfd_ctx_attach_comm, nranks > 1) every rank passes the SAME
+ * replicated mesh and assembles only the block rows of its own contiguous block of cells; the solve
+ * entry points then exchange halos and reduce scalars over NCCL.  system_size stays the global size. */
 yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
                                yfd_system **out, yfd_assembly_info *info);
 
@@ -215,6 +239,8 @@ yfd_status yfd_cfem_get_compress_map(yfd_system *sys, int64_t *compress_map);
 /* ---------------------------------------------------------------------------------- */
 void       yfd_system_destroy(yfd_system *sys);
 void       yfd_system_sizes(const yfd_system *sys, int64_t *n, int64_t *nnz);
+/* distributed systems: rows / non-zeros / halo dofs held by this rank, and the first owned row in internal order */
+void       yfd_system_local_sizes(const yfd_system *sys, int64_t *n_local, int64_t *nnz_local, int64_t *n_halo, int64_t *row_begin);
 /* assm.lhs as CSR; any output may be NULL */
 yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx, double *values);
 yfd_status yfd_system_get_rhs(yfd_system *sys, double *rhs);                 /* assm.rhs         */

@@ -1,0 +1,64 @@
+#!/usr/bin/env python3
+"""Multi-GPU parity check (run under torchrun on the GPU box; the driver's pytest -m gpu tier has one GPU):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py
+
+Every rank assembles its block of the replicated mesh, the ranks solve together (NCCL halo exchange + scalar
+all-reduce), and rank 0 compares the gathered solution / rhs with the UNMODIFIED reference (oracle/_ref)."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import torch
+import torch.distributed as dist
+import yaourt_fem_dg_b200 as yfd
+
+rank, world, lrank = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lrank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", lrank))
+ctx = yfd.Context(lrank, stream=torch.cuda.current_stream().cuda_stream)
+ids = [yfd.Context.comm_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(ids, src=0)
+ctx.attach_comm(rank, world, ids[0])
+
+import refbind
+ref = refbind.Ref() if refbind.available() else None
+fails = 0
+for (t, r, k, pc) in ((0, 4, 1, False), (1, 3, 2, True), (0, 3, 3, False), (1, 4, 3, False)):
+    hm = yfd.HostMesh.create(t, r)
+    mesh = yfd.Mesh(ctx, hm)
+    sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0, build_pc=pc)
+    loc = sysm.local_sizes()
+    p = yfd.CgParams(rr_tol=1e-12, rr_max=1e4, max_iter=2 * sysm.n)
+    res = sysm.solve_cg(p, use_pc=pc, history=True)
+    rhs = sysm.rhs()
+    line = "case t=%d r=%d k=%d pc=%d: n=%d local rows %d halo dofs %d iters %d" % (t, r, k, pc, sysm.n, loc["n_local"], loc["n_halo"], res["iterations"])
+    if ref is not None and rank == 0:
+        ref.mesh(t, r)
+        ref.set_cg(rr_tol=1e-12, rr_max=1e4, max_iter=-1)
+        out = ref.run_dg(k, eta=1.0, use_pc=pc)
+        e_rhs = np.abs(rhs - out["rhs"]).max() / np.abs(out["rhs"]).max()
+        e_sol = np.linalg.norm(res["x"] - out["sol"]) / np.linalg.norm(out["sol"])
+        ok = e_rhs <= 1e-12 and e_sol <= 1e-10 and abs(res["iterations"] - out["iters"]) <= max(3, 0.05 * out["iters"])
+        fails += 0 if ok else 1
+        line += " | vs reference: rhs %.1e sol %.1e ref iters %d %s" % (e_rhs, e_sol, out["iters"], "OK" if ok else "FAIL")
+    # every rank must hold the same full solution
+    xs = torch.from_numpy(res["x"]).cuda()
+    lo, hi = xs.clone(), xs.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same = bool(torch.equal(lo, hi))
+    fails += 0 if same else 1
+    if rank == 0:
+        print(line + (" | identical on all ranks" if same else " | RANKS DIFFER"), flush=True)
+    sysm.close(); mesh.close()
+t = torch.tensor([fails], device="cuda")
+dist.all_reduce(t)
+if rank == 0:
+    print("multi_gpu_check: %s (%d ranks)" % ("PASS" if t.item() == 0 else "FAIL", world), flush=True)
+ctx.close()
+dist.destroy_process_group()
+sys.exit(0 if t.item() == 0 else 1)

@@ -122,6 +122,12 @@ def lib():
         "yfd_mesh_get_cell_faces": (cint, [vp, _i64p]),
         "yfd_mesh_get_permutation": (cint, [vp, _i64p]),
         "yfd_mesh_set_points": (cint, [vp, _f64p]),
+        "yfd_mesh_get_neighbours": (cint, [vp, _i64p]),
+        "yfd_partition_create": (cint, [i64, cint, _i64p, cint, cint, P(vp)]),
+        "yfd_partition_destroy": (None, [vp]),
+        "yfd_partition_sizes": (None, [vp, P(i64), P(i64), P(i64), P(i64), P(cint)]),
+        "yfd_partition_get": (cint, [vp, vp, vp, vp, vp, vp]),
+        "yfd_system_local_sizes": (None, [vp, P(i64), P(i64), P(i64), P(i64)]),
         "yfd_csr_from_triplets": (cint, [vp, i64, i64, i64, _i64p, _i64p, _f64p, P(vp)]),
         "yfd_csr_from_arrays": (cint, [vp, i64, i64, i64, _i64p, _i64p, _f64p, P(vp)]),
         "yfd_csr_destroy": (None, [vp]),
@@ -304,10 +310,34 @@ class Mesh:
         self.ctx.check(lib().yfd_mesh_get_permutation(self._h, out))
         return out
 
+    def neighbours(self):
+        """[ncells][nf] internal ids of the cell across each local face (-1: boundary), internal cell order."""
+        out = np.empty((self.ncells, self.nv), np.int64)
+        self.ctx.check(lib().yfd_mesh_get_neighbours(self._h, out))
+        return out
+
     def set_points(self, points):
         points = np.ascontiguousarray(points, np.float64)
         assert points.shape == (self.npoints, 2)
         self.ctx.check(lib().yfd_mesh_set_points(self._h, points))
+
+
+def partition_plan(neighbours, nranks, rank):
+    """yfd_partition_create (host, no CUDA): contiguous blocks of the internal cell order + halo / send lists."""
+    nbr = np.ascontiguousarray(neighbours, np.int64)
+    h = C.c_void_p()
+    st = lib().yfd_partition_create(nbr.shape[0], nbr.shape[1], nbr, nranks, rank, C.byref(h))
+    if st != 0:
+        raise YfdError(st, lib().yfd_status_string(st).decode())
+    try:
+        b, e, nh, ns, npr = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
+        lib().yfd_partition_sizes(h, C.byref(b), C.byref(e), C.byref(nh), C.byref(ns), C.byref(npr))
+        halo = np.empty(nh.value, np.int64); send = np.empty(ns.value, np.int64)
+        peers = np.empty(npr.value, np.int32); rc = np.empty(npr.value, np.int64); sc = np.empty(npr.value, np.int64)
+        lib().yfd_partition_get(h, _ptr(halo), _ptr(send), _ptr(peers), _ptr(rc), _ptr(sc))
+    finally:
+        lib().yfd_partition_destroy(h)
+    return dict(cell_begin=b.value, cell_end=e.value, halo_cells=halo, send_cells=send, peers=peers, recv_counts=rc, send_counts=sc)
 
 
 def _solve_common(ctx, call, n, params, x0, history):
@@ -441,6 +471,11 @@ class System:
         self.ctx.check(lib().yfd_system_solve_cg_device(self.ctx._h, self._h, int(use_pc), C.byref(params),
                                                         C.c_void_p(d_x) if d_x else None, C.byref(info)))
         return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve)
+
+    def local_sizes(self):
+        a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        lib().yfd_system_local_sizes(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d))
+        return dict(n_local=a.value, nnz_local=b.value, n_halo=c.value, row_begin=d.value)
 
     def time_spmv(self, reps=20):
         ms, b1, b2 = C.c_double(), C.c_double(), C.c_double()

@@ -100,15 +100,20 @@ cg_init(const double *__restrict__ b, const double *__restrict__ y /* A x0 or nu
     }
     __shared__ double tot[2];
     const double v[2] = { rr, rz };
-    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) {
-        const double nr = sqrt(tot[0]);
-        sc->rho = tot[1];
-        sc->nr0 = nr; sc->nr = nr;
-        sc->iter = 0;
-        const double rel = nr / nr;            /* nr/nr0 with nr0 = nr: 1, or NaN when b = A x0 exactly */
-        sc->done = !(rel > sc->rr_tol && 0 < sc->max_iter && rel < sc->rr_max);
-        if (history && history_cap > 0) history[0] = rel;
-    }
+    /* raw sums; with several ranks they are all-reduced before cg_init_finish reads them */
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+    (void) history; (void) history_cap;
+}
+
+__global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap)
+{
+    const double nr = sqrt(sc->rr_new);
+    sc->rho = sc->rz_new;
+    sc->nr0 = nr; sc->nr = nr;
+    sc->iter = 0;
+    const double rel = nr / nr;                /* nr/nr0 with nr0 = nr: 1, or NaN when b = A x0 exactly */
+    sc->done = !(rel > sc->rr_tol && 0 < sc->max_iter && rel < sc->rr_max);
+    if (history && history_cap > 0) history[0] = rel;
 }
 
 /* ---- K2 ------------------------------------------------------------------------------------ */
@@ -207,6 +212,8 @@ struct spmv_op {
     /* DG block rows */
     const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
     int64_t ncells = 0;
+    /* several ranks: x carries nhalo*bs halo entries after the nrows owned ones */
+    const dist_plan *plan = nullptr;
 };
 
 static int pick_team(double avg_row)
@@ -265,7 +272,14 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns (core/solvers.hpp:88-91) is not on the symmetric hot path");
     dbuf<double> r, d, y, z, partials, hist;
     dbuf<cg_scalars> sc;
-    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(d.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    const dist_plan *pl = op.plan;
+    const int64_t nhalo_dofs = pl ? pl->nhalo * op.bs : 0;
+    dbuf<double> sendbuf;
+    if (pl) {
+        if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
+        YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));
+    }
+    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
     if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) n, 2));
     YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
     YFD_TRY(sc.alloc(ctx, 1));
@@ -284,9 +298,12 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     if (p->use_initial_guess) {
         YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));          /* r0 = b - A x (core/solvers.hpp:91) */
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
     } else {
         YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+        if (pl) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
+        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
     }
 
     /* one CUDA graph = `batch` iterations */
@@ -298,9 +315,12 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
     yfd_status cap_st = YFD_OK;
     for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
+        if (pl) { cap_st = halo_exchange(ctx, *pl, op.bs, d.p, sendbuf.p); if (cap_st != YFD_OK) break; }
         cap_st = launch_spmv<true>(ctx, op, d.p, y.p, sc.p, partials.p);
         if (cap_st != YFD_OK) break;
+        if (pl) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
         cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, d.p, y.p, d_pc, n, sc.p, partials.p);
+        if (pl) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
         cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(d.p, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
         ctx->launches += 2;
     }
@@ -360,6 +380,7 @@ static spmv_op op_of_system(const yfd_system *sys, bool allow_block_kernel)
     (void) allow_block_kernel;
     if (sys->kind == YFD_SYS_DG) {
         op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf; op.ncells = sys->ncells;
+        op.plan = sys->plan.get();
     }
     return op;
 }
@@ -423,12 +444,14 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     if (use_pc && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
     scoped_device dev(ctx->device);
     const int64_t n = sys->n;
+    const bool dg = sys->kind == YFD_SYS_DG;
+    const int64_t nloc = dg ? sys->n_local : n;
     dbuf<double> dx, tmp;
-    YFD_TRY(dx.alloc(ctx, (size_t) n, 2));
-    const bool permuted = sys->kind == YFD_SYS_DG;
+    YFD_TRY(dx.alloc(ctx, (size_t) nloc, 2));
     if (p->use_initial_guess) {
         if (!x_host) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_initial_guess needs a host x");
-        if (permuted) {
+        if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
+        if (dg) {
             YFD_TRY(tmp.alloc(ctx, (size_t) n));
             YFD_TRY(tmp.upload(ctx, x_host, (size_t) n));
             YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, tmp.p, dx.p, sys->perm.p, sys->ncells, sys->bs);
@@ -437,18 +460,21 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         }
     }
     YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
-    if (permuted) {
-        /* x_ref[rc] = x_int[iperm[rc]] */
+    const double *result = dx.p;
+    if (dg) {
+        /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */
         double *dst = d_x_out;
-        if (!dst) { if (tmp.n == 0) YFD_TRY(tmp.alloc(ctx, (size_t) n)); dst = tmp.p; }
-        YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, dx.p, dst, sys->iperm.p, sys->ncells, sys->bs);
-        if (x_host) {
-            YFD_CUDA(ctx, cudaMemcpyAsync(x_host, dst, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        if (!dst) {
+            if (!x_host) return YFD_OK;
+            if (tmp.n == 0) YFD_TRY(tmp.alloc(ctx, (size_t) n));
+            dst = tmp.p;
         }
-    } else {
-        if (d_x_out) YFD_CUDA(ctx, cudaMemcpyAsync(d_x_out, dx.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
-        if (x_host) YFD_CUDA(ctx, cudaMemcpyAsync(x_host, dx.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        YFD_TRY(system_vector_to_ref(sys, dx.p, dst));
+        result = dst;
+    } else if (d_x_out) {
+        YFD_CUDA(ctx, cudaMemcpyAsync(d_x_out, dx.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
     }
+    if (x_host) YFD_CUDA(ctx, cudaMemcpyAsync(x_host, result, (size_t) n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return YFD_OK;
 }
@@ -473,10 +499,12 @@ yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double 
 {
     if (!ctx || !sys || reps <= 0) return YFD_ERR_INVALID_ARGUMENT;
     scoped_device dev(ctx->device);
-    const int64_t n = sys->n;
+    const int64_t n = sys->kind == YFD_SYS_DG ? sys->n_local : sys->n;
+    const int64_t nh = sys->plan ? sys->plan->nhalo * sys->bs : 0;
     dbuf<double> x, y, partials;
     dbuf<cg_scalars> sc;
-    YFD_TRY(x.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(x.alloc(ctx, (size_t) (n + nh), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(x.zero(ctx));
     YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
     YFD_TRY(sc.alloc(ctx, 1)); YFD_TRY(sc.zero(ctx));
     YFD_CUDA(ctx, cudaMemcpyAsync(x.p, sys->rhs.p, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));

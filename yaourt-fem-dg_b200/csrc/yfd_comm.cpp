@@ -15,6 +15,12 @@ typedef int (*fn_get_unique_id)(nccl_unique_id *);
 typedef int (*fn_comm_init_rank)(void **, int, nccl_unique_id, int);
 typedef int (*fn_comm_destroy)(void *);
 typedef const char *(*fn_get_error_string)(int);
+typedef int (*fn_all_reduce)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*fn_send)(const void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*fn_recv)(void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*fn_group)(void);
+constexpr int NCCL_FLOAT64 = 8;     /* ncclFloat64 (nccl.h) */
+constexpr int NCCL_SUM = 0;         /* ncclSum */
 
 struct nccl_api {
     void *handle = nullptr;
@@ -22,6 +28,10 @@ struct nccl_api {
     fn_comm_init_rank comm_init_rank = nullptr;
     fn_comm_destroy comm_destroy = nullptr;
     fn_get_error_string error_string = nullptr;
+    fn_all_reduce all_reduce = nullptr;
+    fn_send send = nullptr;
+    fn_recv recv = nullptr;
+    fn_group group_start = nullptr, group_end = nullptr;
     bool ok = false;
 };
 
@@ -36,11 +46,43 @@ nccl_api &api()
     a.comm_init_rank = (fn_comm_init_rank) dlsym(a.handle, "ncclCommInitRank");
     a.comm_destroy = (fn_comm_destroy) dlsym(a.handle, "ncclCommDestroy");
     a.error_string = (fn_get_error_string) dlsym(a.handle, "ncclGetErrorString");
-    a.ok = a.get_unique_id && a.comm_init_rank && a.comm_destroy;
+    a.all_reduce = (fn_all_reduce) dlsym(a.handle, "ncclAllReduce");
+    a.send = (fn_send) dlsym(a.handle, "ncclSend");
+    a.recv = (fn_recv) dlsym(a.handle, "ncclRecv");
+    a.group_start = (fn_group) dlsym(a.handle, "ncclGroupStart");
+    a.group_end = (fn_group) dlsym(a.handle, "ncclGroupEnd");
+    a.ok = a.get_unique_id && a.comm_init_rank && a.comm_destroy && a.all_reduce && a.send && a.recv && a.group_start && a.group_end;
     return a;
 }
 
+yfd_status nccl_check(yfd_ctx *ctx, int rc, const char *what)
+{
+    if (rc == 0) return YFD_OK;
+    return yfd::fail(ctx, YFD_ERR_COMM, "%s: %s", what, api().error_string ? api().error_string(rc) : "NCCL error");
+}
+
 } // namespace
+
+namespace yfd {
+
+yfd_status comm_allreduce_sum_f64(yfd_ctx *ctx, double *d_buf, size_t count)
+{
+    if (ctx->nranks <= 1) return YFD_OK;
+    if (!ctx->comm) return fail(ctx, YFD_ERR_COMM, "no communicator attached");
+    return nccl_check(ctx, api().all_reduce(d_buf, d_buf, count, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream), "ncclAllReduce");
+}
+yfd_status comm_group_begin(yfd_ctx *ctx) { return nccl_check(ctx, api().group_start(), "ncclGroupStart"); }
+yfd_status comm_group_end(yfd_ctx *ctx) { return nccl_check(ctx, api().group_end(), "ncclGroupEnd"); }
+yfd_status comm_send_f64(yfd_ctx *ctx, const double *d_buf, size_t count, int peer)
+{
+    return nccl_check(ctx, api().send(d_buf, count, NCCL_FLOAT64, peer, ctx->comm, ctx->stream), "ncclSend");
+}
+yfd_status comm_recv_f64(yfd_ctx *ctx, double *d_buf, size_t count, int peer)
+{
+    return nccl_check(ctx, api().recv(d_buf, count, NCCL_FLOAT64, peer, ctx->comm, ctx->stream), "ncclRecv");
+}
+
+} // namespace yfd
 
 extern "C" {
 

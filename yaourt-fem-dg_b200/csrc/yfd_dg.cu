@@ -38,7 +38,9 @@ struct dg_args {
     const int2    *faces;
     const int2    *face_owners;
     const int32_t *perm, *iperm;
-    int64_t        ncells;
+    int64_t        ncells;                /* cells assembled by this launch (the rank's own block) */
+    int64_t        cell_begin;            /* first of them in the internal order (0 on one GPU)     */
+    const int32_t *g2l;                   /* distributed: internal id -> local x index; null on one GPU */
     double         eta;                   /* 3 k^2 cfg.eta (dg2d_diffusion.cpp:127) */
     int            rhs_fn, dir_fn;
     const double  *cell_rule;             /* tri: (c0,c1,c2,w)[nq] ; quad: unused */
@@ -140,7 +142,7 @@ dg_sip_cells(const dg_args a)
 
     const int64_t nwarps = (int64_t) gridDim.x * DG_WARPS;
     for (int64_t cell = (int64_t) blockIdx.x * DG_WARPS + warp; cell < a.ncells; cell += nwarps) {
-        const int32_t rc = a.perm[cell];
+        const int32_t rc = a.perm[cell + a.cell_begin];
         double2 P[NV];
 #pragma unroll
         for (int v = 0; v < NV; v++) P[v] = __ldg(&a.pts[a.cells[(int64_t) NV * rc + v]]);
@@ -326,10 +328,11 @@ __device__ __forceinline__ int cell_block_list(const dg_args &a, int64_t cell, i
 {
     /* ids: ascending internal ids of {cell} + neighbours; slots[0] = position of the diagonal,
      * slots[1+e] = position of the neighbour across local face e, or -1 */
-    const int32_t rc = a.perm[cell];
+    const int32_t gcell = (int32_t) (cell + a.cell_begin);
+    const int32_t rc = a.perm[gcell];
     int32_t nb[NV];
     int n = 1;
-    ids[0] = (int32_t) cell;
+    ids[0] = gcell;
 #pragma unroll
     for (int e = 0; e < NV; e++) {
         const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
@@ -347,7 +350,7 @@ __device__ __forceinline__ int cell_block_list(const dg_args &a, int64_t cell, i
     }
     for (int i = 1; i < n; i++)
         if (ids[i] == ids[i - 1]) atomicExch(err, 1);      /* two faces to the same neighbour: needs the fold path */
-    for (int s = 0; s < n; s++) if (ids[s] == (int32_t) cell) slots[0] = (int8_t) s;
+    for (int s = 0; s < n; s++) if (ids[s] == gcell) slots[0] = (int8_t) s;
 #pragma unroll
     for (int e = 0; e < NV; e++) {
         slots[1 + e] = -1;
@@ -376,7 +379,9 @@ __global__ void dg_fill_blocks(const dg_args a, int32_t *__restrict__ blk_cell, 
     int8_t slots[NV + 1];
     const int n = cell_block_list<NV>(a, cell, ids, slots, err);
     const int64_t cp = a.cellptr[cell];
-    for (int s = 0; s < n; s++) blk_cell[cp + s] = ids[s];
+    /* blocks stay in ascending GLOBAL id order (so a row sums in the same order on any number of GPUs);
+     * what is stored is where the block's x entries live locally */
+    for (int s = 0; s < n; s++) blk_cell[cp + s] = a.g2l ? a.g2l[ids[s]] : ids[s];
 #pragma unroll
     for (int s = 0; s < NV + 1; s++) slots_out[cell * (NV + 1) + s] = slots[s];
 }
@@ -434,6 +439,8 @@ static yfd_status fill_common_args(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_co
     a.perm = mesh->perm.p;
     a.iperm = mesh->iperm.p;
     a.ncells = mesh->ncells;
+    a.cell_begin = 0;
+    a.g2l = nullptr;
     a.eta = 3.0 * cfg->degree * cfg->degree * cfg->eta;
     a.rhs_fn = cfg->rhs_fn;
     a.dir_fn = cfg->dirichlet_fn;
@@ -454,7 +461,9 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
                                   yfd_system *sys, yfd_assembly_info *info)
 {
     const int bs = sys->bs;
-    const int64_t nc = mesh->ncells, n = sys->n;
+    const int64_t nc = sys->ncells, n = sys->n_local;        /* this rank's cells / rows */
+    a.ncells = nc;
+    if (sys->plan) { a.cell_begin = sys->plan->cell_begin; a.g2l = sys->plan->g2l.p; }
     gpu_timer t_struct, t_elem;
     dbuf<int32_t> nblk;
     dbuf<int8_t> slots;
@@ -499,13 +508,14 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
     /* keep the permutation with the system: the mesh may be destroyed first */
-    YFD_TRY(sys->perm.alloc(ctx, (size_t) nc));
-    YFD_TRY(sys->iperm.alloc(ctx, (size_t) nc));
-    YFD_CUDA(ctx, cudaMemcpyAsync(sys->perm.p, mesh->perm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-    YFD_CUDA(ctx, cudaMemcpyAsync(sys->iperm.p, mesh->iperm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    const int64_t ncg = mesh->ncells;
+    YFD_TRY(sys->perm.alloc(ctx, (size_t) ncg));
+    YFD_TRY(sys->iperm.alloc(ctx, (size_t) ncg));
+    YFD_CUDA(ctx, cudaMemcpyAsync(sys->perm.p, mesh->perm.p, (size_t) ncg * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    YFD_CUDA(ctx, cudaMemcpyAsync(sys->iperm.p, mesh->iperm.p, (size_t) ncg * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (info) {
-        info->system_size = n;
+        info->system_size = sys->n;
         info->nnz = sys->nnz;
         info->basis_size = bs;
         info->ms_elements = t_elem.ms();
@@ -530,7 +540,16 @@ yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config
     if (n >= 0x7fffffff) return fail(ctx, YFD_ERR_UNSUPPORTED, "system size %lld exceeds 32-bit column indices", (long long) n);
 
     yfd_system *sys = new yfd_system();
-    sys->ctx = ctx; sys->kind = YFD_SYS_DG; sys->bs = bs; sys->nf = mesh->nv; sys->ncells = mesh->ncells; sys->n = n;
+    sys->ctx = ctx; sys->kind = YFD_SYS_DG; sys->bs = bs; sys->nf = mesh->nv; sys->n = n;
+    sys->ncells_global = mesh->ncells; sys->ncells = mesh->ncells; sys->n_local = n;
+    if (ctx->nranks > 1) {
+        const yfd_status ps = ensure_dist_plan(ctx, mesh);
+        if (ps != YFD_OK) { delete sys; return ps; }
+        sys->plan = mesh->plan;
+        sys->ncells = sys->plan->nown;
+        sys->n_local = sys->plan->nown * bs;
+        if (sys->ncells == 0) { delete sys; return fail(ctx, YFD_ERR_UNSUPPORTED, "fewer cells than ranks"); }
+    }
     const yfd_status st = mesh->nv == 3 ? build_dg_system<3>(ctx, mesh, cfg, a, sys, info)
                                         : build_dg_system<4>(ctx, mesh, cfg, a, sys, info);
     if (st != YFD_OK) { cudaStreamSynchronize(ctx->stream); delete sys; return st; }

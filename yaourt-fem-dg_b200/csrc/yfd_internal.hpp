@@ -11,6 +11,7 @@
 #include <cstdarg>
 #include <string>
 #include <vector>
+#include <memory>
 #include "yfd.h"
 
 struct yfd_ctx {
@@ -158,6 +159,37 @@ yfd_status gauss_rule_for_degree(yfd_ctx *ctx, int degree, quad_rule *out);
 /* triangle_quadrature_dunavant(degree): rule max(degree,1) (core/quadratures.hpp:570-581) */
 yfd_status dunavant_rule_for_degree(yfd_ctx *ctx, int degree, tri_rule *out);
 
+/* ---- yfd_partition.cpp ---- */
+int64_t partition_begin(int64_t ncells, int nranks, int r);
+int     partition_owner(int64_t ncells, int nranks, int64_t cell);
+
+/* ---- yfd_comm.cpp: NCCL on the context's stream (all capturable into CUDA graphs) ---- */
+yfd_status comm_allreduce_sum_f64(yfd_ctx *ctx, double *d_buf, size_t count);          /* in place */
+yfd_status comm_group_begin(yfd_ctx *ctx);
+yfd_status comm_send_f64(yfd_ctx *ctx, const double *d_buf, size_t count, int peer);
+yfd_status comm_recv_f64(yfd_ctx *ctx, double *d_buf, size_t count, int peer);
+yfd_status comm_group_end(yfd_ctx *ctx);
+
+/* ---- yfd_dist.cu: this rank's share of a replicated mesh ---- */
+struct dist_plan {
+    int      nranks = 1, rank = 0;
+    int64_t  ncells_global = 0;
+    int64_t  cell_begin = 0, cell_end = 0;       /* owned block of the internal order */
+    int64_t  nown = 0, nhalo = 0, nsend = 0;
+    std::vector<int32_t> peers;
+    std::vector<int64_t> recv_off, send_off;     /* [npeers+1], in cells */
+    dbuf<int32_t> g2l;                           /* [ncells_global] internal id -> local index (owned: id-cell_begin, halo: nown+k), -1 elsewhere */
+    dbuf<int32_t> send_lidx;                     /* [nsend] local indices of the owned cells to pack, grouped by peer */
+};
+
+} // namespace yfd
+
+struct yfd_mesh;
+namespace yfd {
+yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh);
+/* fill the halo part of x ([ (nown+nhalo)*bs ]) from the owners; sendbuf holds nsend*bs doubles */
+yfd_status halo_exchange(yfd_ctx *ctx, const dist_plan &pl, int bs, double *x, double *sendbuf);
+yfd_status mesh_neighbours_device(yfd_ctx *ctx, yfd_mesh *m, dbuf<int32_t> &nbr);
 } // namespace yfd
 
 /* ---- objects behind the opaque handles ---- */
@@ -174,6 +206,7 @@ struct yfd_mesh {
     yfd::dbuf<int32_t>  face_owners;  /* [nfaces][2]     REFERENCE cell ids, -1 none */
     yfd::dbuf<int32_t>  perm;         /* [ncells] internal -> reference             */
     yfd::dbuf<int32_t>  iperm;        /* [ncells] reference -> internal             */
+    std::shared_ptr<yfd::dist_plan> plan;   /* built on first distributed use (yfd_dist.cu) */
 };
 
 struct yfd_csr {
@@ -197,7 +230,10 @@ struct yfd_system {
     /* DG block structure: cell c owns rows [c*bs, (c+1)*bs); its blocks are listed in
      * blk_cell[cellptr[c] .. cellptr[c+1]) in ascending internal cell id */
     int      bs = 0, nf = 0;
-    int64_t  ncells = 0;
+    int64_t  ncells = 0;              /* cells whose rows this rank holds (all of them on one GPU) */
+    int64_t  ncells_global = 0;
+    int64_t  n_local = 0;             /* rows held by this rank                     */
+    std::shared_ptr<yfd::dist_plan> plan;   /* null on one GPU                      */
     yfd::dbuf<int64_t> cellptr;       /* [ncells+1]                                 */
     yfd::dbuf<int32_t> blk_cell;      /* [nblocks]                                  */
     yfd::dbuf<int32_t> perm, iperm;   /* copies of the mesh's cell permutation      */
@@ -207,6 +243,10 @@ struct yfd_system {
 };
 
 namespace yfd {
+/* ---- yfd_system.cu ---- */
+/* DG: this rank's rows (internal order) -> the FULL vector in reference numbering, on the device (d_out_ref [n]);
+ * with several ranks the parts are combined by an all-reduce, so every rank ends up with the whole vector */
+yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *d_out_ref);
 /* ---- yfd_triplets.cu ---- */
 int key_bits_for(int64_t n);
 /* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order */

@@ -248,6 +248,7 @@ yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_sy
     *out = nullptr;
     if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
     if (mesh->nv != 3) return fail(ctx, YFD_ERR_UNSUPPORTED, "continuous FEM is P1 on triangles only (methods/cfem.hpp:31-89)");
+    if (ctx->nranks > 1) return fail(ctx, YFD_ERR_UNSUPPORTED, "the CFEM path is not partitioned: run it on a context without a communicator");
     scoped_device dev(ctx->device);
     yfd_system *sys = new yfd_system();
     sys->ctx = ctx; sys->kind = YFD_SYS_CFEM; sys->bs = 1; sys->nf = 3; sys->ncells = mesh->ncells;
@@ -289,7 +290,16 @@ void yfd_system_destroy(yfd_system *sys)
 void yfd_system_sizes(const yfd_system *sys, int64_t *n, int64_t *nnz)
 {
     if (n) *n = sys->n;
-    if (nnz) *nnz = sys->nnz;
+    if (nnz) *nnz = sys->nnz;           /* distributed: this rank's share */
+}
+
+void yfd_system_local_sizes(const yfd_system *sys, int64_t *n_local, int64_t *nnz_local, int64_t *n_halo, int64_t *row_begin)
+{
+    const bool dist = (bool) sys->plan;
+    if (n_local) *n_local = sys->kind == YFD_SYS_DG ? sys->n_local : sys->n;
+    if (nnz_local) *nnz_local = sys->nnz;
+    if (n_halo) *n_halo = dist ? sys->plan->nhalo * sys->bs : 0;
+    if (row_begin) *row_begin = dist ? sys->plan->cell_begin * sys->bs : 0;
 }
 
 yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx, double *values)
@@ -298,6 +308,7 @@ yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx,
     yfd_ctx *ctx = sys->ctx;
     scoped_device dev(ctx->device);
     if (sys->kind != YFD_SYS_DG) return yfd_csr_get(&sys->A, rowptr, colidx, values);
+    if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "distributed system: the rows live on %d ranks; assemble on one GPU to export CSR", sys->plan->nranks);
     const int64_t nc = sys->ncells, n = sys->n, nnz = sys->nnz;
     dbuf<int32_t> nblk_ref;
     dbuf<int64_t> cp_ref, d_rowptr, d_col;
@@ -319,6 +330,30 @@ yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx,
     return YFD_OK;
 }
 
+} /* extern "C" */
+
+namespace yfd {
+yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *d_out_ref)
+{
+    yfd_ctx *ctx = sys->ctx;
+    const double *full = d_local;
+    dbuf<double> tmp;
+    if (sys->plan) {
+        YFD_TRY(tmp.alloc(ctx, (size_t) sys->n));
+        YFD_TRY(tmp.zero(ctx));
+        YFD_CUDA(ctx, cudaMemcpyAsync(tmp.p + sys->plan->cell_begin * sys->bs, d_local, (size_t) sys->n_local * sizeof(double),
+                                      cudaMemcpyDeviceToDevice, ctx->stream));
+        YFD_TRY(comm_allreduce_sum_f64(ctx, tmp.p, (size_t) sys->n));
+        full = tmp.p;
+    }
+    YFD_LAUNCH(ctx, permute_rows, sgrid(ctx, sys->n), 256, 0, full, d_out_ref, sys->iperm.p, sys->ncells_global, sys->bs);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));       /* tmp goes out of scope */
+    return YFD_OK;
+}
+} // namespace yfd
+
+extern "C" {
+
 static yfd_status get_vector_ref(yfd_system *sys, const dbuf<double> &v, double *host)
 {
     yfd_ctx *ctx = sys->ctx;
@@ -326,7 +361,7 @@ static yfd_status get_vector_ref(yfd_system *sys, const dbuf<double> &v, double 
     if (sys->kind != YFD_SYS_DG) return v.download(ctx, host, (size_t) sys->n);
     dbuf<double> tmp;
     YFD_TRY(tmp.alloc(ctx, (size_t) sys->n));
-    YFD_LAUNCH(ctx, permute_rows, sgrid(ctx, sys->n), 256, 0, v.p, tmp.p, sys->iperm.p, sys->ncells, sys->bs);
+    YFD_TRY(system_vector_to_ref(sys, v.p, tmp.p));
     return tmp.download(ctx, host, (size_t) sys->n);
 }
 
