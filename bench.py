@@ -129,7 +129,7 @@ def load_reference():
         return None, 0, None
     cores = os.cpu_count() or 1
     if omp:
-        os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+        os.environ["OMP_NUM_THREADS"] = str(cores)      # torchrun pins it to 1; the reference arm uses every host core
     ref = refbind.Ref(omp=omp)
     return ref, (ref.num_threads() if omp else 1), "reference"
 
@@ -287,7 +287,7 @@ def main():
     achieved = sp["csr_bytes"] / (sp["ms"] * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
     roofline = {"bound": "hbm", "kernel": "dg_spmv_tma (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
