@@ -251,8 +251,11 @@ def main():
     info = {}
 
     def step_resident():
+        t0 = time.perf_counter()
         sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0, build_pc=wl["pc"])
+        t1 = time.perf_counter()
         res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr() if world == 1 else None)
+        info.update(host_ms_assemble=1e3 * (t1 - t0), host_ms_solve=1e3 * (time.perf_counter() - t1))
         info.update(res, nnz=sysm.nnz, n=sysm.n, ms_elements=sysm.info.ms_elements, ms_structure=sysm.info.ms_structure)
         info.update(sysm.local_sizes())
         return sysm
@@ -354,7 +357,8 @@ def main():
                            "cg": "rr_tol %.0e, rr_max 1e4, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], "Jacobi (-p)" if wl["pc"] else "no preconditioner (reference default)"),
                            "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
                            "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
-                           "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"]},
+                           "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
+                                         "host_wall_assemble_call": info["host_ms_assemble"], "host_wall_solve_call": info["host_ms_solve"]},
                            "cg_iteration_gbs": cg_gbs, "parallelism": "1 GPU" if world == 1 else "contiguous blocks of the Z-curve cell order over %d GPUs: rank 0 holds %d rows + %d halo dofs; "
                                           "per CG iteration one packed NCCL send/recv per neighbour rank and 2 scalar all-reduces" % (world, info["n_local"], info["n_halo"])},
                 "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})

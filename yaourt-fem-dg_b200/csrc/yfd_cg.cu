@@ -78,7 +78,7 @@ csr_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
     if (WITH_DOT) {
         __shared__ double tot[1];
         const double v[1] = { dot };
-        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) sc->dy = tot[0];
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) { xrank_sum<1>(sc, 0, tot); sc->dy = tot[0]; }
     }
 }
 
@@ -101,7 +101,7 @@ cg_init(const double *__restrict__ b, const double *__restrict__ y /* A x0 or nu
     __shared__ double tot[2];
     const double v[2] = { rr, rz };
     /* raw sums; with several ranks they are all-reduced before cg_init_finish reads them */
-    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { xrank_sum<2>(sc, 1, tot); sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
     (void) history; (void) history_cap;
 }
 
@@ -151,7 +151,7 @@ cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict_
     }
     __shared__ double tot[2];
     const double v[2] = { rr, pc ? rz : rr };
-    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { xrank_sum<2>(sc, 1, tot); sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
 }
 
 /* ---- K3 ------------------------------------------------------------------------------------ */
@@ -275,9 +275,12 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     const dist_plan *pl = op.plan;
     const int64_t nhalo_dofs = pl ? pl->nhalo * op.bs : 0;
     dbuf<double> sendbuf;
+    bool peer = false;                  /* peer-memory transport (yfd_peer.cu) or NCCL calls */
     if (pl) {
         if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
-        YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));
+        YFD_TRY(ensure_peer_region(ctx, (size_t) (pl->max_halo_cells * op.bs)));
+        peer = ctx->peer_enabled;
+        if (!peer) YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));
     }
     YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
     if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) n, 2));
@@ -290,6 +293,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     }
     cg_scalars h0 = {};
     h0.max_iter = p->max_iter; h0.rr_tol = p->rr_tol; h0.rr_max = p->rr_max;
+    h0.peer = peer ? ctx->d_peer_view : nullptr;
     YFD_CUDA(ctx, cudaMemcpyAsync(sc.p, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
 
     gpu_timer timer;
@@ -302,7 +306,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     } else {
         YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
-        if (pl) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
+        if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
     }
 
@@ -315,12 +319,12 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
     yfd_status cap_st = YFD_OK;
     for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
-        if (pl) { cap_st = halo_exchange(ctx, *pl, op.bs, d.p, sendbuf.p); if (cap_st != YFD_OK) break; }
+        if (pl) { cap_st = peer ? halo_put_launch(ctx, *pl, op.bs, d.p, sc.p) : halo_exchange(ctx, *pl, op.bs, d.p, sendbuf.p); if (cap_st != YFD_OK) break; }
         cap_st = launch_spmv<true>(ctx, op, d.p, y.p, sc.p, partials.p);
         if (cap_st != YFD_OK) break;
-        if (pl) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
+        if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
         cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, d.p, y.p, d_pc, n, sc.p, partials.p);
-        if (pl) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
+        if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
         cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(d.p, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
         ctx->launches += 2;
     }
@@ -341,6 +345,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         cudaError_t e = cudaMemcpyAsync(&hs, sc.p, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "CG poll: %s", cudaGetErrorString(e)); break; }
+        if (hs.comm_error) { st = fail(ctx, YFD_ERR_COMM, "peer-memory transport: a rank did not arrive within the spin bound"); break; }
         if (hs.done) break;
         e = cudaGraphLaunch(exec, ctx->stream);
         if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "graph launch: %s", cudaGetErrorString(e)); break; }

@@ -20,7 +20,44 @@ struct cg_scalars {
     double rr_tol, rr_max;
     int    done;
     unsigned int ticket[3];
+    /* several ranks on the peer-memory transport (yfd_peer.cu); null otherwise */
+    const peer_view *peer;
+    int    comm_error;
 };
+
+/* Sum tot[0..NV) over all ranks through peer memory; called by ONE thread (thread 0 of the kernel's last block).
+ * Every rank adds the same slots in rank order, so all ranks end with identical bits. */
+template <int NV>
+__device__ __forceinline__ void xrank_sum(cg_scalars *sc, int kind, double *tot)
+{
+    const peer_view *pv = sc->peer;
+    if (!pv) return;
+    peer_ctl *me = pv->ctl[pv->me];
+    const unsigned long long e = me->red_epoch[kind] + 1;
+    me->red_epoch[kind] = e;
+    const int par = (int) (e & 1);
+    for (int q = 0; q < pv->nranks; q++) {
+        volatile peer_slot *slot = &pv->ctl[q]->red[par][kind][pv->me];
+#pragma unroll
+        for (int k = 0; k < NV; k++) slot->v[k] = tot[k];
+    }
+    __threadfence_system();
+    for (int q = 0; q < pv->nranks; q++) *((volatile unsigned long long *) &pv->ctl[q]->red[par][kind][pv->me].flag) = e;
+    double s[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) s[k] = 0.0;
+    for (int q = 0; q < pv->nranks; q++) {
+        volatile peer_slot *slot = &me->red[par][kind][q];
+        long long spins = 0;
+        while (slot->flag != e)
+            if (++spins > (1ll << 28)) { sc->comm_error = 1; sc->done = 1; break; }
+        __threadfence_system();
+#pragma unroll
+        for (int k = 0; k < NV; k++) s[k] += slot->v[k];
+    }
+#pragma unroll
+    for (int k = 0; k < NV; k++) tot[k] = s[k];
+}
 
 /* ---- deterministic block + grid reduction ------------------------------------------- */
 __device__ __forceinline__ double warp_sum(double v)
@@ -87,6 +124,9 @@ __device__ __forceinline__ double team_sum(double v)
 
 
 /* yfd_spmv_tma.cu: TMA-streamed DG block-row SpMV; YFD_ERR_UNSUPPORTED if bs has no instantiation */
+/* yfd_peer.cu */
+yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d, cg_scalars *sc);
+
 template <bool WITH_DOT>
 yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellptr, const int32_t *blk_cell, const double *values,
                               int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials);

@@ -19,6 +19,8 @@ typedef int (*fn_all_reduce)(const void *, void *, size_t, int, int, void *, cud
 typedef int (*fn_send)(const void *, size_t, int, int, void *, cudaStream_t);
 typedef int (*fn_recv)(void *, size_t, int, int, void *, cudaStream_t);
 typedef int (*fn_group)(void);
+typedef int (*fn_all_gather)(const void *, void *, size_t, int, void *, cudaStream_t);
+constexpr int NCCL_INT8 = 0;        /* ncclInt8 / ncclChar */
 constexpr int NCCL_FLOAT64 = 8;     /* ncclFloat64 (nccl.h) */
 constexpr int NCCL_SUM = 0;         /* ncclSum */
 
@@ -32,6 +34,7 @@ struct nccl_api {
     fn_send send = nullptr;
     fn_recv recv = nullptr;
     fn_group group_start = nullptr, group_end = nullptr;
+    fn_all_gather all_gather = nullptr;
     bool ok = false;
 };
 
@@ -51,6 +54,7 @@ nccl_api &api()
     a.recv = (fn_recv) dlsym(a.handle, "ncclRecv");
     a.group_start = (fn_group) dlsym(a.handle, "ncclGroupStart");
     a.group_end = (fn_group) dlsym(a.handle, "ncclGroupEnd");
+    a.all_gather = (fn_all_gather) dlsym(a.handle, "ncclAllGather");
     a.ok = a.get_unique_id && a.comm_init_rank && a.comm_destroy && a.all_reduce && a.send && a.recv && a.group_start && a.group_end;
     return a;
 }
@@ -71,6 +75,11 @@ yfd_status comm_allreduce_sum_f64(yfd_ctx *ctx, double *d_buf, size_t count)
     if (!ctx->comm) return fail(ctx, YFD_ERR_COMM, "no communicator attached");
     return nccl_check(ctx, api().all_reduce(d_buf, d_buf, count, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream), "ncclAllReduce");
 }
+yfd_status comm_allgather_bytes(yfd_ctx *ctx, const void *d_send, void *d_recv, size_t bytes_per_rank)
+{
+    if (!ctx->comm || !api().all_gather) return fail(ctx, YFD_ERR_COMM, "ncclAllGather unavailable");
+    return nccl_check(ctx, api().all_gather(d_send, d_recv, bytes_per_rank, NCCL_INT8, ctx->comm, ctx->stream), "ncclAllGather");
+}
 yfd_status comm_group_begin(yfd_ctx *ctx) { return nccl_check(ctx, api().group_start(), "ncclGroupStart"); }
 yfd_status comm_group_end(yfd_ctx *ctx) { return nccl_check(ctx, api().group_end(), "ncclGroupEnd"); }
 yfd_status comm_send_f64(yfd_ctx *ctx, const double *d_buf, size_t count, int peer)
@@ -88,6 +97,7 @@ extern "C" {
 
 void yfd_comm_destroy_internal(yfd_ctx *ctx)
 {
+    if (ctx) yfd::peer_release(ctx);
     if (ctx && ctx->comm && api().ok) api().comm_destroy(ctx->comm);
     if (ctx) ctx->comm = nullptr;
 }

@@ -9,6 +9,7 @@
  * halo part of x (the receiver's halo group "owned by q" has the same order as q's send list).
  */
 #include "yfd_internal.hpp"
+#include <algorithm>
 
 namespace yfd {
 
@@ -82,6 +83,37 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
     for (int k = 0; k < npeers; k++) { pl->recv_off[k + 1] = pl->recv_off[k] + rc[k]; pl->send_off[k + 1] = pl->send_off[k] + sc[k]; }
     if (pl->nown + pl->nhalo >= 0x7fffffff) return fail(ctx, YFD_ERR_UNSUPPORTED, "local cell count exceeds 32-bit ids");
 
+    /* peer-memory transport: every rank can derive every other rank's plan from the replicated neighbour table,
+     * so "where does my block land in q's halo" needs no communication */
+    {
+        std::vector<int32_t> srank((size_t) pl->nsend), sdst((size_t) pl->nsend);
+        pl->max_halo_cells = pl->nhalo;
+        for (int q = 0; q < ctx->nranks; q++) {
+            if (q == ctx->rank) continue;
+            yfd_partition *qp = nullptr;
+            if (yfd_partition_create(nc, nf, nbr.data(), ctx->nranks, q, &qp) != YFD_OK) return fail(ctx, YFD_ERR_INVALID_STATE, "partition planner failed for rank %d", q);
+            int64_t qh = 0; int qn = 0;
+            yfd_partition_sizes(qp, nullptr, nullptr, &qh, nullptr, &qn);
+            if (qh > pl->max_halo_cells) pl->max_halo_cells = qh;
+            const size_t k = std::lower_bound(pl->peers.begin(), pl->peers.end(), q) - pl->peers.begin();
+            if (k < pl->peers.size() && pl->peers[k] == q) {
+                std::vector<int32_t> qpeers((size_t) qn);
+                std::vector<int64_t> qrc((size_t) qn);
+                yfd_partition_get(qp, nullptr, nullptr, qpeers.data(), qrc.data(), nullptr);
+                int64_t off = 0;
+                for (int j = 0; j < qn && qpeers[(size_t) j] != ctx->rank; j++) off += qrc[(size_t) j];
+                for (int64_t i = pl->send_off[k]; i < pl->send_off[k + 1]; i++) {
+                    srank[(size_t) i] = q;
+                    sdst[(size_t) i] = (int32_t) (off + (i - pl->send_off[k]));
+                }
+            }
+            yfd_partition_destroy(qp);
+        }
+        YFD_TRY(pl->send_rank.alloc(ctx, (size_t) pl->nsend)); YFD_TRY(pl->send_rank.upload(ctx, srank.data(), srank.size()));
+        YFD_TRY(pl->send_dst.alloc(ctx, (size_t) pl->nsend));   YFD_TRY(pl->send_dst.upload(ctx, sdst.data(), sdst.size()));
+        YFD_TRY(pl->d_peers.alloc(ctx, pl->peers.size()));      YFD_TRY(pl->d_peers.upload(ctx, pl->peers.data(), pl->peers.size()));
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     std::vector<int32_t> halo32(halo.begin(), halo.end()), send32((size_t) pl->nsend);
     for (int64_t i = 0; i < pl->nsend; i++) send32[(size_t) i] = (int32_t) (send[(size_t) i] - pl->cell_begin);
     dbuf<int32_t> d_halo;

@@ -14,6 +14,25 @@
 #include <memory>
 #include "yfd.h"
 
+/* ---- peer-memory (NVLink / NVSwitch) control structures: every rank allocates one region with cudaMalloc,
+ * the ranks swap CUDA IPC handles once, and from then on device code stores straight into its peers' regions
+ * (yfd_peer.cu).  Layout of a region: [ peer_ctl | landing zone for halo dofs ]. ---- */
+constexpr int YFD_MAX_RANKS = 16;
+struct peer_slot { double v[2]; unsigned long long flag, pad; };
+struct peer_ctl {
+    unsigned long long red_epoch[4];            /* local counters, one per reduction kind            */
+    unsigned long long halo_epoch;              /* local counter of halo exchanges                   */
+    unsigned int       halo_ticket, pad0;
+    unsigned long long pad1[2];
+    peer_slot          red[2][4][YFD_MAX_RANKS]; /* [epoch parity][kind][source rank], written by peers */
+    unsigned long long halo_flag[YFD_MAX_RANKS]; /* [source rank] = epoch of the halo data it has delivered */
+};
+struct peer_view {                              /* lives in device memory, one per context             */
+    peer_ctl *ctl[YFD_MAX_RANKS];               /* ctl[q]: rank q's control block as seen from here    */
+    double   *land[YFD_MAX_RANKS];              /* land[q]: rank q's landing zone                      */
+    int       me, nranks;
+};
+
 struct yfd_ctx {
     int           device = 0;
     cudaStream_t  stream = nullptr;
@@ -29,6 +48,12 @@ struct yfd_ctx {
     /* NCCL (yfd_comm.cpp) */
     void         *comm = nullptr;
     int           rank = 0, nranks = 1;
+    /* peer-memory transport (yfd_peer.cu); null -> NCCL calls are used instead */
+    void         *peer_region = nullptr;       /* this rank's region (cudaMalloc)                     */
+    size_t        peer_land_cap = 0;           /* doubles in the landing zone                         */
+    void         *peer_opened[YFD_MAX_RANKS] = {};   /* cudaIpcOpenMemHandle results, to close later  */
+    peer_view    *d_peer_view = nullptr;       /* device copy handed to the kernels                   */
+    bool          peer_enabled = false;
 };
 
 namespace yfd {
@@ -169,6 +194,13 @@ yfd_status comm_group_begin(yfd_ctx *ctx);
 yfd_status comm_send_f64(yfd_ctx *ctx, const double *d_buf, size_t count, int peer);
 yfd_status comm_recv_f64(yfd_ctx *ctx, double *d_buf, size_t count, int peer);
 yfd_status comm_group_end(yfd_ctx *ctx);
+yfd_status comm_allgather_bytes(yfd_ctx *ctx, const void *d_send, void *d_recv, size_t bytes_per_rank);
+
+/* ---- yfd_peer.cu ---- */
+/* collective: make sure every rank's landing zone holds at least `land_doubles` (same value on all ranks);
+ * on failure the context silently stays on the NCCL transport (peer_enabled = false) */
+yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles);
+void       peer_release(yfd_ctx *ctx);
 
 /* ---- yfd_dist.cu: this rank's share of a replicated mesh ---- */
 struct dist_plan {
@@ -180,6 +212,11 @@ struct dist_plan {
     std::vector<int64_t> recv_off, send_off;     /* [npeers+1], in cells */
     dbuf<int32_t> g2l;                           /* [ncells_global] internal id -> local index (owned: id-cell_begin, halo: nown+k), -1 elsewhere */
     dbuf<int32_t> send_lidx;                     /* [nsend] local indices of the owned cells to pack, grouped by peer */
+    /* peer-memory transport: where each packed cell lands on its destination rank */
+    int64_t  max_halo_cells = 0;                 /* max over ALL ranks (sizes the landing zones identically)  */
+    dbuf<int32_t> send_rank;                     /* [nsend] destination rank                                 */
+    dbuf<int32_t> send_dst;                      /* [nsend] cell slot in the destination's landing zone      */
+    dbuf<int32_t> d_peers;                       /* [npeers]                                                 */
 };
 
 } // namespace yfd
