@@ -360,7 +360,7 @@ def main():
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
                                          "host_wall_assemble_call": info["host_ms_assemble"], "host_wall_solve_call": info["host_ms_solve"]},
                            "cg_iteration_gbs": cg_gbs, "parallelism": "1 GPU" if world == 1 else "contiguous blocks of the Z-curve cell order over %d GPUs: rank 0 holds %d rows + %d halo dofs; "
-                                          "per CG iteration one packed NCCL send/recv per neighbour rank and 2 scalar all-reduces" % (world, info["n_local"], info["n_halo"])},
+                                          "transport: %s (per CG iteration one halo exchange and 2 scalar all-reduces)" % (world, info["n_local"], info["n_halo"], info.get("transport"))},
                 "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
         print(json.dumps(line))
     ctx.close()

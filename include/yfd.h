@@ -63,6 +63,9 @@ yfd_status  yfd_ctx_create(int device, void *stream, yfd_ctx **out);
 void        yfd_ctx_destroy(yfd_ctx *ctx);
 const char *yfd_last_error(const yfd_ctx *ctx);
 yfd_status  yfd_ctx_synchronize(yfd_ctx *ctx);
+/* Device buffers released by destroyed meshes / systems / solves are cached in the context and reused (cudaMalloc
+ * and cudaFree synchronise the device); this returns the cache to the driver. released_bytes may be NULL. */
+yfd_status  yfd_ctx_trim(yfd_ctx *ctx, size_t *released_bytes);
 /* kernels launched by this context so far (graph replays count their kernel nodes) */
 int64_t     yfd_ctx_launch_count(const yfd_ctx *ctx);
 /* name and SM count of the device (buf may be NULL) */
@@ -276,6 +279,7 @@ typedef struct yfd_cg_info {
                                              a separate timing pass of `spmv_timing_reps` launches;
                                              0 if not requested)                             */
     int64_t history_len;                  /* entries written to `history` (iterations+1)    */
+    int     transport;                    /* 0 = one GPU, 1 = NCCL calls, 2 = peer-memory stores over NVLink (yfd_peer.cu) */
 } yfd_cg_info;
 
 /* Solve sys.lhs x = sys.rhs on the device, no host round trip of the matrix.

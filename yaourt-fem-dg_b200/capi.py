@@ -13,6 +13,7 @@ mirror them one to one:
 import ctypes as C
 import os
 import re
+import weakref
 
 import numpy as np
 
@@ -77,7 +78,7 @@ class CgParams(C.Structure):
 
 class CgInfo(C.Structure):
     _fields_ = [("iterations", C.c_int64), ("nr0", C.c_double), ("nr", C.c_double), ("converged", C.c_int),
-                ("ms_solve", C.c_double), ("ms_spmv", C.c_double), ("history_len", C.c_int64)]
+                ("ms_solve", C.c_double), ("ms_spmv", C.c_double), ("history_len", C.c_int64), ("transport", C.c_int)]
 
 
 _lib = None
@@ -102,6 +103,7 @@ def lib():
         "yfd_last_error": (C.c_char_p, [vp]),
         "yfd_ctx_synchronize": (cint, [vp]),
         "yfd_ctx_launch_count": (i64, [vp]),
+        "yfd_ctx_trim": (cint, [vp, P(C.c_size_t)]),
         "yfd_ctx_device_info": (cint, [vp, C.c_char_p, C.c_size_t, P(cint), P(cint), P(cint)]),
         "yfd_comm_unique_id": (cint, [C.c_char_p]),
         "yfd_ctx_attach_comm": (cint, [vp, cint, cint, C.c_char_p]),
@@ -173,6 +175,7 @@ class Context:
             self._h = None
             raise YfdError(st, lib().yfd_status_string(st).decode())
         self.device = device
+        self._children = weakref.WeakSet()     # meshes / systems / matrices: closed before the context goes
 
     def check(self, st):
         if st != 0:
@@ -180,6 +183,8 @@ class Context:
 
     def close(self):
         if self._h:
+            for ch in list(self._children):
+                ch.close()
             lib().yfd_ctx_destroy(self._h)
             self._h = None
 
@@ -188,6 +193,11 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def trim(self):
+        n = C.c_size_t()
+        self.check(lib().yfd_ctx_trim(self._h, C.byref(n)))
+        return n.value
 
     def synchronize(self):
         self.check(lib().yfd_ctx_synchronize(self._h))
@@ -283,6 +293,7 @@ class Mesh:
         self.npoints, self.ncells, self.nfaces = len(host.points), len(host.cells), len(host.faces)
         ctx.check(lib().yfd_mesh_create(ctx._h, host.cell_type, self.npoints, host.points, self.ncells, host.cells,
                                         self.nfaces, host.faces, host.face_boundary, reorder, C.byref(self._h)))
+        ctx._children.add(self)
 
     def close(self):
         if self._h:
@@ -363,6 +374,7 @@ class Csr:
 
     def __init__(self, ctx, handle):
         self.ctx, self._h = ctx, handle
+        ctx._children.add(self)
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         lib().yfd_csr_sizes(handle, C.byref(a), C.byref(b), C.byref(c))
         self.nrows, self.ncols, self.nnz = a.value, b.value, c.value
@@ -421,6 +433,7 @@ class System:
 
     def __init__(self, ctx, handle, info):
         self.ctx, self._h, self.info = ctx, handle, info
+        ctx._children.add(self)
         self.n, self.nnz = info.system_size, info.nnz
 
     def close(self):

@@ -367,6 +367,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         info->converged = (hs.nr / hs.nr0 <= p->rr_tol) ? 1 : 0;
         info->ms_solve = timer.ms();
         info->ms_spmv = 0.0;
+        info->transport = pl ? (peer ? 2 : 1) : 0;
     }
     return YFD_OK;
 }

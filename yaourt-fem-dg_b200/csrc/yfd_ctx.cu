@@ -18,6 +18,41 @@ yfd_status fail(yfd_ctx *ctx, yfd_status s, const char *fmt, ...)
     return s;
 }
 
+void *pool_alloc(yfd_ctx *ctx, size_t bytes)
+{
+    /* best fit, but never hand out a block more than 25 % larger than asked (keeps big blocks for big requests) */
+    auto it = ctx->pool.lower_bound(bytes);
+    if (it != ctx->pool.end() && it->first <= bytes + bytes / 4) {
+        void *p = it->second;
+        ctx->pool_bytes -= it->first;
+        ctx->pool.erase(it);
+        return p;
+    }
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes) == cudaSuccess) return p;
+    cudaGetLastError();
+    pool_trim(ctx);                      /* out of memory: give the cache back and retry once */
+    if (cudaMalloc(&p, bytes) == cudaSuccess) return p;
+    cudaGetLastError();
+    return nullptr;
+}
+
+void pool_free(yfd_ctx *ctx, void *p, size_t bytes)
+{
+    if (!p) return;
+    /* callers that lie about the size cannot exist: dbuf remembers what pool_alloc gave it */
+    ctx->pool.emplace(bytes, p);
+    ctx->pool_bytes += bytes;
+}
+
+void pool_trim(yfd_ctx *ctx)
+{
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &kv : ctx->pool) cudaFree(kv.second);
+    ctx->pool.clear();
+    ctx->pool_bytes = 0;
+}
+
 } // namespace yfd
 
 extern "C" {
@@ -85,6 +120,7 @@ void yfd_ctx_destroy(yfd_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     yfd_comm_destroy_internal(ctx);
+    yfd::pool_trim(ctx);
     if (ctx->tab_gauss_x) cudaFree(ctx->tab_gauss_x);
     if (ctx->tab_gauss_w) cudaFree(ctx->tab_gauss_w);
     if (ctx->tab_dunavant) cudaFree(ctx->tab_dunavant);
@@ -98,6 +134,15 @@ yfd_status yfd_ctx_synchronize(yfd_ctx *ctx)
 {
     if (!ctx) return YFD_ERR_INVALID_ARGUMENT;
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+yfd_status yfd_ctx_trim(yfd_ctx *ctx, size_t *released_bytes)
+{
+    if (!ctx) return YFD_ERR_INVALID_ARGUMENT;
+    yfd::scoped_device dev(ctx->device);
+    if (released_bytes) *released_bytes = ctx->pool_bytes;
+    yfd::pool_trim(ctx);
     return YFD_OK;
 }
 

@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include <memory>
+#include <map>
 #include "yfd.h"
 
 /* ---- peer-memory (NVLink / NVSwitch) control structures: every rank allocates one region with cudaMalloc,
@@ -48,6 +49,11 @@ struct yfd_ctx {
     /* NCCL (yfd_comm.cpp) */
     void         *comm = nullptr;
     int           rank = 0, nranks = 1;
+    /* device-memory cache: blocks released by dbuf are kept and handed out again (all work of a context is ordered
+     * on its one stream, so reuse is safe); cudaMalloc / cudaFree synchronise the device and, once peer mappings
+     * exist, cost milliseconds each */
+    std::multimap<size_t, void *> pool;
+    size_t        pool_bytes = 0;
     /* peer-memory transport (yfd_peer.cu); null -> NCCL calls are used instead */
     void         *peer_region = nullptr;       /* this rank's region (cudaMalloc)                     */
     size_t        peer_land_cap = 0;           /* doubles in the landing zone                         */
@@ -59,6 +65,10 @@ struct yfd_ctx {
 namespace yfd {
 
 yfd_status fail(yfd_ctx *ctx, yfd_status s, const char *fmt, ...);
+/* yfd_ctx.cu: cached device allocations (bytes are rounded up to 512) */
+void *pool_alloc(yfd_ctx *ctx, size_t bytes);
+void  pool_free(yfd_ctx *ctx, void *p, size_t bytes);
+void  pool_trim(yfd_ctx *ctx);
 
 #define YFD_CUDA(ctx, call)                                                                   \
     do {                                                                                      \
@@ -91,18 +101,24 @@ template <typename T>
 struct dbuf {
     T     *p = nullptr;
     size_t n = 0;
+    yfd_ctx *owner = nullptr;
+    size_t bytes_held = 0;
     dbuf() = default;
     dbuf(const dbuf &) = delete;
     dbuf &operator=(const dbuf &) = delete;
-    dbuf(dbuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    dbuf(dbuf &&o) noexcept : p(o.p), n(o.n), owner(o.owner), bytes_held(o.bytes_held) { o.p = nullptr; o.n = 0; o.owner = nullptr; o.bytes_held = 0; }
     dbuf &operator=(dbuf &&o) noexcept {
-        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        if (this != &o) {
+            release();
+            p = o.p; n = o.n; owner = o.owner; bytes_held = o.bytes_held;
+            o.p = nullptr; o.n = 0; o.owner = nullptr; o.bytes_held = 0;
+        }
         return *this;
     }
     ~dbuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
-        p = nullptr; n = 0;
+        if (p) { if (owner) pool_free(owner, p, bytes_held); else cudaFree(p); }
+        p = nullptr; n = 0; owner = nullptr; bytes_held = 0;
     }
     /* `pad` extra elements are allocated (and zeroed) past n so that aligned vector
      * loads of the last quad never leave the allocation */
@@ -110,11 +126,11 @@ struct dbuf {
         release();
         size_t bytes = (count + pad) * sizeof(T);
         if (bytes == 0) bytes = sizeof(T);
-        cudaError_t e = cudaMalloc((void **) &p, bytes);
-        if (e != cudaSuccess) {
-            p = nullptr;
-            return fail(ctx, YFD_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
-        }
+        bytes = (bytes + 511) & ~(size_t) 511;
+        p = (T *) pool_alloc(ctx, bytes);
+        if (!p) return fail(ctx, YFD_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu bytes) failed", bytes);
+        owner = ctx; bytes_held = bytes;
+        cudaError_t e = cudaSuccess;
         n = count;
         if (pad) {
             e = cudaMemsetAsync(p + count, 0, pad * sizeof(T), ctx->stream);
