@@ -1,0 +1,62 @@
+"""GPU: the reference's UNMODIFIED dg2d_diffusion.cpp recompiled against include/yaourt_b200/dropin*.hpp
+(oracle/_ref/dropin_dg2d_diffusion, built by oracle/Makefile where /root/reference exists).  Its finalize() ->
+blaze::init_from_triplets and its conjugated_gradient calls run on the GPU; the driver's own printed L2 errors must
+match what the reference itself produces (golden fixture + live oracle/_ref)."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden
+
+pytestmark = pytest.mark.gpu
+EXE = os.path.join(ROOT, "oracle", "_ref", "dropin_dg2d_diffusion")
+
+
+def run(args, env=None):
+    if not os.path.exists(EXE):
+        pytest.skip("oracle/_ref/dropin_dg2d_diffusion not built (needs /root/reference at build time)")
+    e = dict(os.environ)
+    e.update(env or {})
+    res = subprocess.run([EXE] + args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=e, timeout=600, cwd="/tmp")
+    assert res.returncode == 0, res.stdout[-2000:]
+    return res.stdout
+
+
+@pytest.mark.parametrize("row", [0, 1, 2])
+def test_unmodified_driver_on_gpu_prints_the_reference_errors(row):
+    t, r, k, n, nnz, iters, l2_qp, l2_mm, h = golden("dg_driver_runs.npz")["runs"][row]
+    out = run(["-m", "tri" if t == 0 else "quad", "-r", str(int(r)), "-k", str(int(k))])
+    qp = float(re.search(r"L2-norm error \(qp\):\s+(\S+)", out).group(1))
+    mm = float(re.search(r"L2-norm error \(mm\):\s+(\S+)", out).group(1))
+    it = int(re.search(r"\[yaourt_b200\] CG on GPU: iterations (\d+)", out).group(1))
+    assert "converged 1" in out
+    # the driver prints 6 significant digits; CG stops at rr 1e-8, so errors agree to ~1e-6 relative
+    assert abs(qp - l2_qp) <= 2e-5 * l2_qp and abs(mm - l2_mm) <= 2e-5 * l2_mm
+    assert abs(it - iters) <= max(3, 0.05 * iters)
+
+
+def test_preconditioned_driver_flag(ref):
+    out = run(["-r", "3", "-k", "2", "-p"])
+    ref.mesh(0, 3)
+    ref.set_cg(rr_tol=1e-8, rr_max=1e4, max_iter=-1)
+    o = ref.run_dg(2, use_pc=True)
+    qp = float(re.search(r"L2-norm error \(qp\):\s+(\S+)", out).group(1))
+    it = int(re.search(r"iterations (\d+)", out).group(1))
+    assert abs(qp - o["l2_qp"]) <= 2e-5 * o["l2_qp"] and abs(it - o["iters"]) <= max(3, 0.05 * o["iters"])
+
+
+@pytest.mark.parametrize("spec,t,r,k,pc", [("tri 3 2 1", 0, 3, 2, True), ("quad 3 3 0", 1, 3, 3, False)])
+def test_batched_entry_from_cpp(ref, spec, t, r, k, pc):
+    out = run([], env={"YFD_DROPIN_BATCHED": spec})
+    m = re.search(r"batched: n (\d+) nnz (\d+) iterations (\d+) sol_norm (\S+) rhs_norm (\S+)", out)
+    n, nnz, it, sn, rn = int(m.group(1)), int(m.group(2)), int(m.group(3)), float(m.group(4)), float(m.group(5))
+    ref.mesh(t, r)
+    ref.set_cg(rr_tol=1e-12, rr_max=1e4, max_iter=-1)
+    o = ref.run_dg(k, use_pc=pc)
+    assert (n, nnz) == (o["n"], o["nnz"])
+    assert abs(sn - np.linalg.norm(o["sol"])) <= 1e-10 * np.linalg.norm(o["sol"])
+    assert abs(rn - np.linalg.norm(o["rhs"])) <= 1e-12 * np.linalg.norm(o["rhs"])
+    assert abs(it - o["iters"]) <= max(3, 0.05 * o["iters"])

@@ -363,7 +363,7 @@ def _solve_common(ctx, call, n, params, x0, history):
         hist = np.zeros(cap, np.float64)
     ctx.check(call(params, x, info, _ptr(hist), cap))
     out = dict(x=x, iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged),
-               ms_solve=info.ms_solve)
+               ms_solve=info.ms_solve, transport=("one GPU", "NCCL", "peer memory")[info.transport])
     if history:
         out["history"] = hist[:info.history_len].copy()
     return out
@@ -475,7 +475,8 @@ class System:
         assert x.dtype == np.float64 and x.flags.c_contiguous and x.shape == (self.n,)
         info = CgInfo()
         self.ctx.check(lib().yfd_system_solve_cg(self.ctx._h, self._h, int(use_pc), C.byref(params), x, C.byref(info), None, 0))
-        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve)
+        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
+                    transport=("one GPU", "NCCL", "peer memory")[info.transport])
 
     def solve_cg_device(self, params=None, use_pc=False, d_x=None):
         """Resident solve: x0 = 0, solution left in the device buffer `d_x` (raw pointer int or None)."""
@@ -483,7 +484,8 @@ class System:
         info = CgInfo()
         self.ctx.check(lib().yfd_system_solve_cg_device(self.ctx._h, self._h, int(use_pc), C.byref(params),
                                                         C.c_void_p(d_x) if d_x else None, C.byref(info)))
-        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve)
+        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
+                    transport=("one GPU", "NCCL", "peer memory")[info.transport])
 
     def local_sizes(self):
         a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
