@@ -278,11 +278,14 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     bool peer = false;                  /* peer-memory transport (yfd_peer.cu) or NCCL calls */
     if (pl) {
         if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
-        YFD_TRY(ensure_peer_region(ctx, (size_t) (pl->max_halo_cells * op.bs)));
+        YFD_TRY(ensure_peer_region(ctx, (size_t) (pl->max_local_cells * op.bs) + 8));
         peer = ctx->peer_enabled;
         if (!peer) YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));
     }
-    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    /* peer transport: d = [owned | halo] lives in this rank's landing zone, where the neighbours store its halo part */
+    if (!peer) YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2));
+    double *const dv = peer ? ctx->peer_land : d.p;
     if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) n, 2));
     YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
     YFD_TRY(sc.alloc(ctx, 1));
@@ -301,13 +304,43 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     const unsigned vg = vec_grid(ctx, n);
     if (p->use_initial_guess) {
         YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));          /* r0 = b - A x (core/solvers.hpp:91) */
-        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
     } else {
         YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
-        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, d.p, n, sc.p, partials.p, hist.p, hcap);
+        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
+    }
+
+    /* YFD_CG_TRACE=1: time 200 iterations kernel by kernel with CUDA events (no graph) and print the averages; the
+     * solve then continues normally.  A diagnostic for the multi-rank path, where ncu cannot be used. */
+    if (getenv("YFD_CG_TRACE") && p->max_iter > 200) {
+        const int NT = 200, NK = 4;
+        std::vector<cudaEvent_t> ev((size_t) NT * (NK + 1));
+        for (auto &e : ev) cudaEventCreate(&e);
+        for (int it = 0; it < NT; it++) {
+            cudaEvent_t *e = &ev[(size_t) it * (NK + 1)];
+            cudaEventRecord(e[0], ctx->stream);
+            if (pl) { if (peer) YFD_TRY(halo_put_launch(ctx, *pl, op.bs, dv, sc.p)); else YFD_TRY(halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p)); }
+            cudaEventRecord(e[1], ctx->stream);
+            YFD_TRY(launch_spmv<true>(ctx, op, dv, y.p, sc.p, partials.p));
+            if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->dy, 1));
+            cudaEventRecord(e[2], ctx->stream);
+            cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p);
+            if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
+            cudaEventRecord(e[3], ctx->stream);
+            cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
+            cudaEventRecord(e[4], ctx->stream);
+            ctx->launches += 2;
+        }
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        double acc[NK] = { 0, 0, 0, 0 };
+        for (int it = 20; it < NT; it++)
+            for (int k = 0; k < NK; k++) { float ms = 0; cudaEventElapsedTime(&ms, ev[(size_t) it * (NK + 1) + k], ev[(size_t) it * (NK + 1) + k + 1]); acc[k] += ms; }
+        fprintf(stderr, "[yfd trace] rank %d/%d n_local %lld: halo %.1f us | spmv(+dy sum) %.1f us | update_xr(+rr sum) %.1f us | update_d %.1f us (eager launches, avg of %d)\n",
+                ctx->rank, ctx->nranks, (long long) n, 1e3 * acc[0] / (NT - 20), 1e3 * acc[1] / (NT - 20), 1e3 * acc[2] / (NT - 20), 1e3 * acc[3] / (NT - 20), NT - 20);
+        for (auto &e : ev) cudaEventDestroy(e);
     }
 
     /* one CUDA graph = `batch` iterations */
@@ -319,13 +352,13 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
     yfd_status cap_st = YFD_OK;
     for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
-        if (pl) { cap_st = peer ? halo_put_launch(ctx, *pl, op.bs, d.p, sc.p) : halo_exchange(ctx, *pl, op.bs, d.p, sendbuf.p); if (cap_st != YFD_OK) break; }
-        cap_st = launch_spmv<true>(ctx, op, d.p, y.p, sc.p, partials.p);
+        if (pl) { cap_st = peer ? halo_put_launch(ctx, *pl, op.bs, dv, sc.p) : halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p); if (cap_st != YFD_OK) break; }
+        cap_st = launch_spmv<true>(ctx, op, dv, y.p, sc.p, partials.p);
         if (cap_st != YFD_OK) break;
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
-        cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, d.p, y.p, d_pc, n, sc.p, partials.p);
+        cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p);
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
-        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(d.p, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
+        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
         ctx->launches += 2;
     }
     {

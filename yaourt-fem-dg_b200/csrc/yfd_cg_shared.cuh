@@ -51,7 +51,10 @@ __device__ __forceinline__ void xrank_sum(cg_scalars *sc, int kind, double *tot)
         long long spins = 0;
         while (slot->flag != e)
             if (++spins > (1ll << 28)) { sc->comm_error = 1; sc->done = 1; break; }
-        __threadfence_system();
+    }
+    __threadfence_system();
+    for (int q = 0; q < pv->nranks; q++) {
+        volatile peer_slot *slot = &me->red[par][kind][q];
 #pragma unroll
         for (int k = 0; k < NV; k++) s[k] += slot->v[k];
     }

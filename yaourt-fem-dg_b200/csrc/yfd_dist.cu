@@ -88,6 +88,7 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
     {
         std::vector<int32_t> srank((size_t) pl->nsend), sdst((size_t) pl->nsend);
         pl->max_halo_cells = pl->nhalo;
+        pl->max_local_cells = pl->nown + pl->nhalo;
         for (int q = 0; q < ctx->nranks; q++) {
             if (q == ctx->rank) continue;
             yfd_partition *qp = nullptr;
@@ -95,6 +96,8 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
             int64_t qh = 0; int qn = 0;
             yfd_partition_sizes(qp, nullptr, nullptr, &qh, nullptr, &qn);
             if (qh > pl->max_halo_cells) pl->max_halo_cells = qh;
+            const int64_t q_own = partition_begin(nc, ctx->nranks, q + 1) - partition_begin(nc, ctx->nranks, q);
+            if (q_own + qh > pl->max_local_cells) pl->max_local_cells = q_own + qh;
             const size_t k = std::lower_bound(pl->peers.begin(), pl->peers.end(), q) - pl->peers.begin();
             if (k < pl->peers.size() && pl->peers[k] == q) {
                 std::vector<int32_t> qpeers((size_t) qn);
@@ -104,7 +107,8 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
                 for (int j = 0; j < qn && qpeers[(size_t) j] != ctx->rank; j++) off += qrc[(size_t) j];
                 for (int64_t i = pl->send_off[k]; i < pl->send_off[k + 1]; i++) {
                     srank[(size_t) i] = q;
-                    sdst[(size_t) i] = (int32_t) (off + (i - pl->send_off[k]));
+                    /* the landing zone of rank q IS its direction vector d = [owned | halo]: slot = its owned count + position in its halo */
+                    sdst[(size_t) i] = (int32_t) (q_own + off + (i - pl->send_off[k]));
                 }
             }
             yfd_partition_destroy(qp);

@@ -57,6 +57,7 @@ struct yfd_ctx {
     /* peer-memory transport (yfd_peer.cu); null -> NCCL calls are used instead */
     void         *peer_region = nullptr;       /* this rank's region (cudaMalloc)                     */
     size_t        peer_land_cap = 0;           /* doubles in the landing zone                         */
+    double       *peer_land = nullptr;         /* this rank's landing zone                            */
     void         *peer_opened[YFD_MAX_RANKS] = {};   /* cudaIpcOpenMemHandle results, to close later  */
     peer_view    *d_peer_view = nullptr;       /* device copy handed to the kernels                   */
     bool          peer_enabled = false;
@@ -229,7 +230,8 @@ struct dist_plan {
     dbuf<int32_t> g2l;                           /* [ncells_global] internal id -> local index (owned: id-cell_begin, halo: nown+k), -1 elsewhere */
     dbuf<int32_t> send_lidx;                     /* [nsend] local indices of the owned cells to pack, grouped by peer */
     /* peer-memory transport: where each packed cell lands on its destination rank */
-    int64_t  max_halo_cells = 0;                 /* max over ALL ranks (sizes the landing zones identically)  */
+    int64_t  max_halo_cells = 0;                 /* max over ALL ranks                                        */
+    int64_t  max_local_cells = 0;                /* max over ALL ranks of owned + halo (sizes the landing zones identically) */
     dbuf<int32_t> send_rank;                     /* [nsend] destination rank                                 */
     dbuf<int32_t> send_dst;                      /* [nsend] cell slot in the destination's landing zone      */
     dbuf<int32_t> d_peers;                       /* [npeers]                                                 */

@@ -8,8 +8,9 @@
  *   - a reduction's last block stores its partial sums into a slot on every rank, fences, raises a flag, then
  *     spins until the flags of all ranks for this epoch are up and adds the slots IN RANK ORDER -- every rank
  *     gets the same bits, so `done` flips on all ranks in the same iteration (cg_shared.cuh: xrank_sum);
- *   - halo_put stores the dofs of the cells a neighbour needs straight into that neighbour's landing zone,
- *     and its last block signals / waits / moves the landed dofs behind the owned part of d.
+ *   - the direction vector d = [owned | halo] of every rank lives IN its landing zone, and halo_put stores the
+ *     dofs of the cells a neighbour needs straight into the halo part of that neighbour's d; its last block
+ *     signals the neighbours and waits for theirs.
  * Epoch counters live on the device and advance inside the kernels, so the whole iteration stays inside one
  * CUDA graph with no host or NCCL involvement.  Every rank runs one kernel at a time on its own GPU and
  * writes before it waits, so the spins cannot deadlock; they are bounded anyway and raise comm_error.
@@ -34,6 +35,7 @@ void peer_release(yfd_ctx *ctx)
     if (ctx->peer_region) { cudaFree(ctx->peer_region); ctx->peer_region = nullptr; }
     if (ctx->d_peer_view) { cudaFree(ctx->d_peer_view); ctx->d_peer_view = nullptr; }
     ctx->peer_land_cap = 0;
+    ctx->peer_land = nullptr;
     ctx->peer_enabled = false;
 }
 
@@ -95,13 +97,14 @@ yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles)
     YFD_CUDA(ctx, cudaMalloc((void **) &ctx->d_peer_view, sizeof(peer_view)));
     YFD_CUDA(ctx, cudaMemcpy(ctx->d_peer_view, &pv, sizeof(pv), cudaMemcpyHostToDevice));
     ctx->peer_land_cap = cap;
+    ctx->peer_land = pv.land[ctx->rank];
     ctx->peer_enabled = true;
     return YFD_OK;
 }
 
 /* ---- halo exchange by direct stores ---------------------------------------------------------- */
 __global__ void __launch_bounds__(256)
-halo_put(double *__restrict__ d, int64_t nown_dofs, int64_t nhalo_dofs, const int32_t *__restrict__ send_lidx,
+halo_put(const double *d, const int32_t *__restrict__ send_lidx,
          const int32_t *__restrict__ send_rank, const int32_t *__restrict__ send_dst, int64_t nsend, int bs,
          const int32_t *__restrict__ peers, int npeers, cg_scalars *__restrict__ sc)
 {
@@ -138,10 +141,8 @@ halo_put(double *__restrict__ d, int64_t nown_dofs, int64_t nhalo_dofs, const in
     }
     __syncthreads();
     __threadfence_system();
-    if (bad) { if (threadIdx.x == 0) { sc->comm_error = 1; sc->done = 1; } return; }
-    const double *land = pv->land[pv->me];
-    for (int64_t t = threadIdx.x; t < nhalo_dofs; t += blockDim.x)
-        d[nown_dofs + t] = __ldcg(&land[t]);
+    if (bad && threadIdx.x == 0) { sc->comm_error = 1; sc->done = 1; }
+    /* nothing to move: the neighbours stored straight into the halo part of d (d lives in the landing zone) */
 }
 
 yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d, cg_scalars *sc)
@@ -150,7 +151,7 @@ yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d,
     const int64_t n = pl.nsend * bs;
     int64_t grid = ceil_div(n > 0 ? n : 1, 256);
     if (grid > ctx->sm_count) grid = ctx->sm_count;
-    YFD_LAUNCH(ctx, halo_put, (unsigned) grid, 256, 0, d, pl.nown * bs, pl.nhalo * bs, pl.send_lidx.p, pl.send_rank.p, pl.send_dst.p,
+    YFD_LAUNCH(ctx, halo_put, (unsigned) grid, 256, 0, d, pl.send_lidx.p, pl.send_rank.p, pl.send_dst.p,
                pl.nsend, bs, pl.d_peers.p, (int) pl.peers.size(), sc);
     return YFD_OK;
 }
