@@ -49,6 +49,11 @@ WORKLOADS = {
                              desc="DG-SIP diffusion, triangles k=2, -r 9: 1,048,576 cells, 6,291,456 dofs"),
     "dg_sip_tri_k2_r11": dict(cell=0, r=11, k=2, pc=True, rr_tol=1e-10, ref_r=5, base_r=6,
                               desc="DG-SIP diffusion, triangles k=2, -r 11: 16,777,216 cells, 100,663,296 dofs (BASELINE configs[4])"),
+    # configs[1] names a P2 continuous FEM the reference does not have (methods/cfem.hpp is P1 only); this is its P1 path
+    "cfem_p1_r11": dict(kind="cfem", cell=0, r=11, k=1, pc=False, rr_tol=1e-8, rr_max=1e3, ref_r=7, base_r=8,
+                        desc="continuous P1 FEM Poisson, triangles -r 11: 33,554,432 cells, 8,380,417 dofs (BASELINE configs[1] is P2; the reference is P1 only)"),
+    "cfem_p1_r10": dict(kind="cfem", cell=0, r=10, k=1, pc=False, rr_tol=1e-8, rr_max=1e3, ref_r=7, base_r=8,
+                        desc="continuous P1 FEM Poisson, triangles -r 10: 8,388,608 cells, 2,095,105 dofs"),
 }
 DEFAULT_WORKLOAD = "dg_sip_quad_k3_r9"
 
@@ -115,9 +120,12 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 def reference_step(ref, wl, r):
     """One full reference pass at refinement r: mesh (untimed) -> cell loop -> finalize -> CG."""
-    ref.mesh(wl["cell"], r)
-    ref.set_cg(rr_tol=wl["rr_tol"], rr_max=1e4, max_iter=-1)
-    out = ref.run_dg(wl["k"], eta=1.0, use_pc=wl["pc"])
+    ref.set_cg(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4), max_iter=-1)
+    if wl.get("kind") == "cfem":
+        out = ref.run_cfem(r)               # continuous_fem.cpp: builds its own mesh (counted in t_blocks)
+    else:
+        ref.mesh(wl["cell"], r)
+        out = ref.run_dg(wl["k"], eta=1.0, use_pc=wl["pc"])
     t = out["t_blocks"] + out["t_csr"] + out["t_cg"]
     return dict(n=out["n"], nnz=out["nnz"], iters=out["iters"], t=t, t_blocks=out["t_blocks"], t_csr=out["t_csr"], t_cg=out["t_cg"])
 
@@ -228,9 +236,16 @@ def main():
         dist.broadcast_object_list(ids, src=0)
         ctx.attach_comm(rank, world, ids[0])
 
-    k, bs = wl["k"], bs_of(wl["k"])
+    cfem = wl.get("kind") == "cfem"
+    if cfem and world > 1:
+        raise SystemExit("the CFEM path is not partitioned (DESIGN.md section 6): run it with --gpus 1")
+    k, bs = wl["k"], (1 if cfem else bs_of(wl["k"]))
+
+    def assemble(m):
+        return ctx.cfem_assemble_p1(m) if cfem else ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"])
     hm = yfd.HostMesh.create(wl["cell"], wl["r"])           # mesher: input generation, untimed
-    params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=1e4, max_iter=args.profile_iters or 2 * bs * len(hm.cells))
+    params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4),
+                          max_iter=args.profile_iters or 2 * (len(hm.points) if wl.get("kind") == "cfem" else bs_of(wl["k"]) * len(hm.cells)))
 
     def barrier():
         if dist is not None:
@@ -246,13 +261,13 @@ def main():
 
     # ---------------- resident leg: mesh in HBM before the clock starts ----------------
     mesh = yfd.Mesh(ctx, hm)
-    n = bs * mesh.ncells
+    n = assemble(mesh).n if cfem else bs * mesh.ncells
     d_x = torch.empty(n if world == 1 else 1, dtype=torch.float64, device="cuda")
     info = {}
 
     def step_resident():
         t0 = time.perf_counter()
-        sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0, build_pc=wl["pc"])
+        sysm = assemble(mesh)
         t1 = time.perf_counter()
         res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr() if world == 1 else None)
         info.update(host_ms_assemble=1e3 * (t1 - t0), host_ms_solve=1e3 * (time.perf_counter() - t1))
@@ -292,7 +307,7 @@ def main():
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
     if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
-    roofline = {"bound": "hbm", "kernel": "dg_spmv_tma (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": ("csr_spmv" if cfem else "dg_spmv_tma") + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": sp["csr_bytes"], "kernel_requested_bytes_per_launch": sp["kernel_bytes"],
                 "kernel_requested_gbs": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9, "ms_per_launch": sp["ms"]}
@@ -323,7 +338,7 @@ def main():
 
         def step_e2e():
             m2 = yfd.Mesh(ctx, hm_p)
-            s2 = ctx.dg_assemble_sip(m2, k, eta=1.0, build_pc=wl["pc"])
+            s2 = assemble(m2)
             s2.solve_cg_into(params, x_host, use_pc=wl["pc"])
             s2.close(); m2.close()
 
@@ -342,7 +357,7 @@ def main():
         ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
-               "path": "yfd_mesh_create -> yfd_dg_assemble_sip -> yfd_system_solve_cg (host x) through include/yfd.h"}
+               "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % ("yfd_cfem_assemble_p1" if cfem else "yfd_dg_assemble_sip")}
 
     base = None
     if rank == 0 and not args.no_cpu_baseline:
@@ -354,7 +369,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(info["n"]), "nnz": int(nnz_global),
-                           "cg": "rr_tol %.0e, rr_max 1e4, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], "Jacobi (-p)" if wl["pc"] else "no preconditioner (reference default)"),
+                           "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], "Jacobi (-p)" if wl["pc"] else "no preconditioner (reference default)"),
                            "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
                            "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],

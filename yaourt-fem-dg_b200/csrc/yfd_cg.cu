@@ -208,7 +208,7 @@ __global__ void permute_blocks(const double *__restrict__ in, double *__restrict
 struct spmv_op {
     /* generic */
     const int64_t *rowptr = nullptr; const int32_t *colidx = nullptr; const double *values = nullptr;
-    int64_t nrows = 0, nnz = 0;
+    int64_t nrows = 0, nnz = 0, max_chunk_nnz = -1;
     /* DG block rows */
     const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
     int64_t ncells = 0;
@@ -236,6 +236,12 @@ static unsigned spmv_grid(yfd_ctx *ctx, int64_t nrows, int ts)
 template <bool WITH_DOT>
 static yfd_status launch_csr_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
 {
+    {
+        const int64_t before = ctx->launches;
+        const yfd_status st = launch_csr_spmv_tma<WITH_DOT>(ctx, op.rowptr, op.colidx, op.values, op.nrows, op.max_chunk_nnz, x, y, sc, partials);
+        if (st != YFD_ERR_UNSUPPORTED || ctx->launches != before) return st;
+    }
+    /* very long rows: a team of lanes per row */
     const int ts = pick_team(op.nrows ? (double) op.nnz / (double) op.nrows : 1.0);
     const unsigned g = spmv_grid(ctx, op.nrows, ts);
     switch (ts) {
@@ -409,7 +415,7 @@ static spmv_op op_of_csr(const yfd_csr *A)
 {
     spmv_op op;
     op.rowptr = A->rowptr.p; op.colidx = A->colidx.p; op.values = A->values.p;
-    op.nrows = A->nrows; op.nnz = A->nnz;
+    op.nrows = A->nrows; op.nnz = A->nnz; op.max_chunk_nnz = A->max_chunk_nnz;
     return op;
 }
 
@@ -452,6 +458,7 @@ yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y)
 {
     if (!ctx || !A || !x || !y) return YFD_ERR_INVALID_ARGUMENT;
     scoped_device dev(ctx->device);
+    YFD_TRY(csr_prepare(ctx, A));
     dbuf<double> dx, dy;
     YFD_TRY(dx.alloc(ctx, (size_t) A->ncols, 2)); YFD_TRY(dy.alloc(ctx, (size_t) A->nrows, 2));
     YFD_TRY(dx.upload(ctx, x, (size_t) A->ncols));
@@ -465,6 +472,7 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
     if (!ctx || !A || !b || !x || !p) return YFD_ERR_INVALID_ARGUMENT;
     if (A->nrows != A->ncols) return fail(ctx, YFD_ERR_SHAPE_MISMATCH, "[CG solver] A square matrix is required");
     scoped_device dev(ctx->device);
+    YFD_TRY(csr_prepare(ctx, A));
     const int64_t n = A->nrows;
     dbuf<double> db, dx, dpc;
     YFD_TRY(db.alloc(ctx, (size_t) n, 2)); YFD_TRY(dx.alloc(ctx, (size_t) n, 2));
@@ -484,6 +492,7 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     scoped_device dev(ctx->device);
     const int64_t n = sys->n;
     const bool dg = sys->kind == YFD_SYS_DG;
+    if (!dg) YFD_TRY(csr_prepare(ctx, &sys->A));
     const int64_t nloc = dg ? sys->n_local : n;
     dbuf<double> dx, tmp;
     YFD_TRY(dx.alloc(ctx, (size_t) nloc, 2));
@@ -538,6 +547,7 @@ yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double 
 {
     if (!ctx || !sys || reps <= 0) return YFD_ERR_INVALID_ARGUMENT;
     scoped_device dev(ctx->device);
+    if (sys->kind != YFD_SYS_DG) YFD_TRY(csr_prepare(ctx, &sys->A));
     const int64_t n = sys->kind == YFD_SYS_DG ? sys->n_local : sys->n;
     const int64_t nh = sys->plan ? sys->plan->nhalo * sys->bs : 0;
     dbuf<double> x, y, partials;

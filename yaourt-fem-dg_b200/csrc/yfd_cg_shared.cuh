@@ -127,6 +127,12 @@ __device__ __forceinline__ double team_sum(double v)
 
 
 /* yfd_spmv_tma.cu: TMA-streamed DG block-row SpMV; YFD_ERR_UNSUPPORTED if bs has no instantiation */
+/* yfd_spmv_csr.cu: TMA-streamed SpMV for any CSR; YFD_ERR_UNSUPPORTED (nothing launched) if a chunk does not fit the ring */
+yfd_status csr_prepare(yfd_ctx *ctx, yfd_csr *A);
+template <bool WITH_DOT>
+yfd_status launch_csr_spmv_tma(yfd_ctx *ctx, const int64_t *rowptr, const int32_t *colidx, const double *values, int64_t nrows,
+                               int64_t max_chunk_nnz, const double *x, double *y, cg_scalars *sc, double *partials);
+
 /* yfd_peer.cu */
 yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d, cg_scalars *sc);
 

@@ -267,6 +267,7 @@ struct yfd_mesh {
 struct yfd_csr {
     yfd_ctx *ctx = nullptr;
     int64_t  nrows = 0, ncols = 0, nnz = 0;
+    int64_t  max_chunk_nnz = -1;      /* largest 32-row chunk (yfd_spmv_csr.cu), -1 = not computed yet */
     yfd::dbuf<int64_t> rowptr;        /* [nrows+1]                                  */
     yfd::dbuf<int32_t> colidx;        /* [nnz] (+4 pad)                             */
     yfd::dbuf<double>  values;        /* [nnz] (+4 pad)                             */

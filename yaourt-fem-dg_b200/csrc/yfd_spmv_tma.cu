@@ -26,6 +26,7 @@
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
+#include "yfd_tma.cuh"
 #include <cstdlib>
 
 namespace yfd {
@@ -34,49 +35,6 @@ namespace yfd {
  * of independent pipelines, not their depth (tools/spmv_sweep.py).  Small blocks fit more than 16 rings. */
 __host__ __device__ constexpr int tma_max_warps(int bs) { return bs <= 3 ? 32 : 16; }
 constexpr int TMA_XPL = 5;                 /* gathered x entries per lane: chunk blocks * bs <= 160 */
-
-/* ---- PTX wrappers (sm_100a): mbarrier + bulk async copy -------------------------------------- */
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-    const uint32_t addr = smem_u32(bar);
-    uint32_t ok;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
-    } while (!ok);
-}
-__device__ __forceinline__ void fence_proxy_async()
-{
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-__device__ __forceinline__ uint64_t policy_evict_first()
-{
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-/* bytes: multiple of 16; src and dst 16-byte aligned */
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar, uint64_t policy)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_plain(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
 
 struct tma_layout {
     int G;              /* cells per chunk (rows = G*bs <= 32) */
@@ -90,7 +48,6 @@ struct tma_layout {
     int warp_bytes;     /* per warp: stages + xs + barriers */
 };
 
-__host__ __device__ inline int round16(int b) { return (b + 15) & ~15; }
 
 template <int BS, bool WITH_DOT>
 __global__ void __launch_bounds__(tma_max_warps(BS) * 32, 1)

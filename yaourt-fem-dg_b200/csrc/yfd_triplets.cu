@@ -102,7 +102,7 @@ static yfd_status build_from_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols
                                       const int64_t *rows, const int64_t *cols, const double *vals, yfd_csr *A)
 {
     A->ctx = ctx; A->nrows = nrows; A->ncols = ncols; A->nnz = 0;
-    YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1));
+    YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1, 2));
     if (count == 0) {
         YFD_TRY(A->rowptr.zero(ctx));
         YFD_TRY(A->colidx.alloc(ctx, 0, 4));
@@ -153,7 +153,7 @@ yfd_status csr_from_device_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, 
                                     const double *d_vals, yfd_csr *A)
 {
     A->ctx = ctx; A->nrows = nrows; A->ncols = ncols; A->nnz = 0;
-    YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1));
+    YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1, 2));
     if (count == 0) {
         YFD_TRY(A->rowptr.zero(ctx));
         YFD_TRY(A->colidx.alloc(ctx, 0, 4));
@@ -227,7 +227,7 @@ yfd_status yfd_csr_from_arrays(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64
         dbuf<int> derr;
         dbuf<int64_t> tmp;
         YFD_TRY(derr.alloc(ctx, 1)); YFD_TRY(derr.zero(ctx));
-        YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1));
+        YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1, 2));
         YFD_TRY(A->rowptr.upload(ctx, rowptr, (size_t) nrows + 1));
         YFD_TRY(A->colidx.alloc(ctx, (size_t) nnz, 4));
         YFD_TRY(A->values.alloc(ctx, (size_t) nnz, 4));
