@@ -83,3 +83,32 @@ void dgetrs_(char *trans, int *n, int *nrhs, double *A, int *lda, int *ipiv,
         }
     }
 }
+
+/* dgesv_: A X = B by the two routines above (the DG Maxwell assembly's blaze::solve,
+ * methods/dg_maxwell_2D.hpp:284-285,426,441,539-541 -> blaze/math/dense/LSE.h:5763). */
+void dgesv_(int *n, int *nrhs, double *A, int *lda, int *ipiv, double *B, int *ldb, int *info)
+{
+    dgetrf_(n, n, A, lda, ipiv, info);
+    if (*info != 0) return;
+    char tr = 'N';
+    dgetrs_(&tr, n, nrhs, A, lda, ipiv, B, ldb, info, 1);
+}
+
+/* dgetri_: inverse from the LU factors (only linked because blaze::inv is instantiated by the
+ * reference-simplex variant's headers; never called on the paths the harness runs).  Column by
+ * column: solve A x = e_j. */
+void dgetri_(int *n, double *A, int *lda, int *ipiv, double *work, int *lwork, int *info)
+{
+    const int N = *n, LD = *lda;
+    *info = 0;
+    if (*lwork == -1) { work[0] = (double) (N > 0 ? N * N : 1); return; }
+    if (N <= 0) return;
+    if (*lwork < N * N) { *info = -6; return; }
+    for (int j = 0; j < N; j++)
+        for (int i = 0; i < N; i++) work[i + (size_t) j * N] = i == j ? 1.0 : 0.0;
+    char tr = 'N';
+    int nn = N, ldb = N;
+    dgetrs_(&tr, &nn, &nn, A, lda, ipiv, work, &ldb, info, 1);
+    for (int j = 0; j < N; j++)
+        for (int i = 0; i < N; i++) A[i + (size_t) j * LD] = work[i + (size_t) j * N];
+}

@@ -45,6 +45,12 @@ class Oracle:
         L.yfo_cfem_p1.argtypes = [i64, _f64p, i64, _i64p, i64, _i64p, _u8p, cint, _i64p, C.POINTER(i64), _i64p, _i64p, _f64p, _f64p]
         L.yfo_cfem_p1.restype = i64
         L.yfo_mesher.argtypes = [cint, cint, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), vp, vp, vp, vp]
+        _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+        L.yfo_maxwell_assemble.argtypes = [cint, _f64p, i64, _i64p, i64, _i64p, _i64p, _i64p, cint, cint, dbl, vp, vp,
+                                           _f64p, _f64p, _i64p, _i32p, _f64p]
+        L.yfo_maxwell_init.argtypes = [cint, _f64p, i64, _i64p, cint, _f64p, _f64p]
+        L.yfo_maxwell_step.argtypes = [cint, i64, cint, _f64p, _f64p, _i64p, _i32p, dbl, cint, i64, _f64p]
+        L.yfo_maxwell_errors.argtypes = [cint, _f64p, i64, _i64p, cint, _f64p, dbl, _f64p]
 
     # ---- mesher (core/meshers.hpp) ----
     def mesh(self, cell_type, levels):
@@ -162,3 +168,44 @@ class Oracle:
         rowptr, colidx, values = self.csr_from_triplets(n, n, ri[:cnt], rj[:cnt], rv[:cnt])
         return dict(n=n, nnz=len(values), rowptr=rowptr, colidx=colidx, values=values, rhs=rhs[:n].copy(), compress_map=cmap,
                     raw=(ri[:cnt].copy(), rj[:cnt].copy(), rv[:cnt].copy()))
+
+    # ---- DG Maxwell TM (methods/dg_maxwell_2D.hpp, maxwell_driver.cpp) ----
+    def maxwell_assemble(self, points, cells, faces, k, upwind=False, eta=1.0, mu_r=None, eps_r=None):
+        points, cells, faces = _c(points, np.float64), _c(cells, np.int64), _c(faces, np.int64)
+        nc, nv = cells.shape
+        cf, owners = self.connectivity(cells, faces)
+        bs = self.lib.yfo_basis_size(k)
+        L = 3 * bs
+        on = np.empty((nc, L, L)); off = np.empty((nc, nv, L, L))
+        nb = np.empty((nc, nv), np.int64); has = np.empty((nc, nv), np.int32); gM = np.empty((nc, bs, bs))
+        mu = None if mu_r is None else _c(mu_r, np.float64)
+        ep = None if eps_r is None else _c(eps_r, np.float64)
+        vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        rc = self.lib.yfo_maxwell_assemble(nv, points, nc, cells, len(faces), faces, _c(cf, np.int64), _c(owners, np.int64),
+                                           k, int(upwind), eta, vp(mu), vp(ep), on, off, nb, has, gM)
+        if rc != 0:
+            raise RuntimeError("yfo_maxwell_assemble rc=%d" % rc)
+        return dict(ondiag=on, offdiag=off, neigh=nb, has=has, gM=gM, bs=bs)
+
+    def maxwell_init(self, points, cells, k, gM):
+        points, cells = _c(points, np.float64), _c(cells, np.int64)
+        nc, nv = cells.shape
+        bs = self.lib.yfo_basis_size(k)
+        dofs = np.empty(nc * 3 * bs)
+        rc = self.lib.yfo_maxwell_init(nv, points, nc, cells, k, _c(gM, np.float64), dofs)
+        if rc != 0:
+            raise RuntimeError("yfo_maxwell_init rc=%d" % rc)
+        return dofs
+
+    def maxwell_step(self, op, k, dofs, dt, nsteps=1, euler=False):
+        nc, nv = op["neigh"].shape
+        d = np.array(dofs, np.float64, copy=True)
+        self.lib.yfo_maxwell_step(nv, nc, k, op["ondiag"], op["offdiag"], op["neigh"], op["has"], dt, int(euler), nsteps, d)
+        return d
+
+    def maxwell_errors(self, points, cells, k, dofs, t):
+        points, cells = _c(points, np.float64), _c(cells, np.int64)
+        nc, nv = cells.shape
+        out = np.empty(3)
+        self.lib.yfo_maxwell_errors(nv, points, nc, cells, k, _c(dofs, np.float64), t, out)
+        return out

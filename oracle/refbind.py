@@ -140,3 +140,104 @@ class Ref:
 
     def num_threads(self):
         return self.lib.yfd_ref_num_threads()
+
+
+# --------------------------------------------------------------------------------------------
+# DG Maxwell TM (methods/dg_maxwell_2D.hpp + maxwell_driver.cpp), oracle/ref_harness_maxwell.cpp
+# --------------------------------------------------------------------------------------------
+def maxwell_lib_path(omp=False):
+    return os.path.join(_HERE, "_ref", "libyfd_ref_maxwell_omp.so" if omp else "libyfd_ref_maxwell.so")
+
+
+def maxwell_available(omp=False):
+    return os.path.exists(maxwell_lib_path(omp))
+
+
+class RefMaxwell:
+    """The unmodified reference Maxwell solver; one context at a time."""
+
+    def __init__(self, omp=False):
+        self.lib = L = C.CDLL(maxwell_lib_path(omp))
+        L.yfd_refmx_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+        L.yfd_refmx_sizes.argtypes = [C.POINTER(C.c_int64)] * 5
+        L.yfd_refmx_mesh_copy.argtypes = [_f64p, _i64p, _i64p, _i32p]
+        L.yfd_refmx_set_material.argtypes = [_f64p, _f64p]
+        L.yfd_refmx_get_operator.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.yfd_refmx_get_dofs.argtypes = [_f64p]
+        L.yfd_refmx_set_dofs.argtypes = [_f64p]
+        L.yfd_refmx_step.argtypes = [C.c_int]
+        L.yfd_refmx_step.restype = C.c_double
+        L.yfd_refmx_errors.argtypes = [C.c_int64, _f64p]
+        L.yfd_refmx_time_assemble.restype = C.c_double
+        L.yfd_refmx_run_driver.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_int64, C.c_int, C.c_int, C.c_char_p]
+        L.yfd_refmx_num_threads.restype = C.c_int
+
+    def create(self, mtype, levels, degree, dt=0.1, eta=1.0, upwind=False, euler=False, shatter=False):
+        if self.lib.yfd_refmx_create(mtype, levels, degree, dt, eta, int(upwind), int(euler), int(shatter)) != 0:
+            raise RuntimeError("reference maxwell_context failed")
+        s = [C.c_int64() for _ in range(5)]
+        self.lib.yfd_refmx_sizes(*[C.byref(v) for v in s])
+        self.npoints, self.ncells, self.nfaces, self.nf, self.bs = [v.value for v in s]
+        return self
+
+    def mesh(self):
+        pts = np.empty((self.npoints, 2), np.float64)
+        cells = np.empty((self.ncells, self.nf), np.int64)
+        faces = np.empty((self.nfaces, 2), np.int64)
+        fbnd = np.empty(self.nfaces, np.int32)
+        self.lib.yfd_refmx_mesh_copy(pts, cells, faces, fbnd)
+        return dict(points=pts, cells=cells, faces=faces, face_boundary=fbnd)
+
+    def set_material(self, mu_r, eps_r):
+        self.lib.yfd_refmx_set_material(np.ascontiguousarray(mu_r, np.float64), np.ascontiguousarray(eps_r, np.float64))
+
+    def assemble(self):
+        if self.lib.yfd_refmx_assemble() != 0:
+            raise RuntimeError("reference maxwell assemble failed")
+        return self.lib.yfd_refmx_time_assemble()
+
+    def operator(self, blocks=True):
+        """gOp_ondiag [nc][3bs][3bs], gOp_offdiag [nc][nf][3bs][3bs], neighbour offsets / flags [nc][nf], gM [nc][bs][bs]"""
+        nc, nf, bs = self.ncells, self.nf, self.bs
+        L = 3 * bs
+        on = np.empty((nc, L, L), np.float64) if blocks else None
+        off = np.empty((nc, nf, L, L), np.float64) if blocks else None
+        nb = np.empty((nc, nf), np.int64)
+        has = np.empty((nc, nf), np.int32)
+        gM = np.empty((nc, bs, bs), np.float64)
+        vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        self.lib.yfd_refmx_get_operator(vp(on), vp(off), vp(nb), vp(has), vp(gM))
+        return dict(ondiag=on, offdiag=off, neigh=nb, has=has, gM=gM)
+
+    def init(self):
+        if self.lib.yfd_refmx_init() != 0:
+            raise RuntimeError("reference apply_initial_condition failed")
+
+    def dofs(self):
+        d = np.empty(3 * self.bs * self.ncells, np.float64)
+        self.lib.yfd_refmx_get_dofs(d)
+        return d
+
+    def set_dofs(self, d):
+        self.lib.yfd_refmx_set_dofs(np.ascontiguousarray(d, np.float64))
+
+    def step(self, nsteps=1):
+        return self.lib.yfd_refmx_step(nsteps)
+
+    def errors(self, cycle):
+        e = np.empty(3, np.float64)
+        self.lib.yfd_refmx_errors(cycle, e)
+        return e
+
+    def run_driver(self, mtype, levels, degree, dt, timesteps, upwind=False, euler=False):
+        """run_maxwell_solver exactly as shipped; returns the error log rows (cycle, time, Hx, Hy, Ez errors)."""
+        path = "/tmp/yfd_refmx_err_%d.txt" % os.getpid()
+        rc = self.lib.yfd_refmx_run_driver(mtype, levels, degree, dt, timesteps, int(upwind), int(euler), path.encode())
+        if rc != 0:
+            raise RuntimeError("reference maxwell driver failed")
+        rows = [list(map(float, ln.split())) for ln in open(path) if ln.strip() and not ln.startswith("#")]
+        os.remove(path)
+        return np.array(rows)
+
+    def num_threads(self):
+        return self.lib.yfd_refmx_num_threads()
