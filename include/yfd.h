@@ -306,6 +306,94 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
 yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double *ms_per_launch,
                                 double *csr_bytes, double *kernel_bytes);
 
+/* ---------------------------------------------------------------------------------- */
+/* DG Maxwell TM, explicit time domain: replaces maxwell_context's storage + assemble   */
+/* (methods/dg_maxwell_2D.hpp:75-152, :220-461), apply_initial_condition (:513-554),    */
+/* do_timestep / apply_operator (:558-675) and the driver's report_errors               */
+/* (maxwell_driver.cpp:133-191).                                                        */
+/*                                                                                      */
+/* The reference stores, per cell, a dense 3bs x 3bs on-diagonal block and one dense    */
+/* 3bs x 3bs block per face (gOp_ondiag / gOp_offdiag, :90) although only 4 (centred)   */
+/* of the 9 bs x bs sub-blocks are non-zero and all of them are scalar multiples of     */
+/* M^-1 Sx, M^-1 Sy, M^-1 tmass_f, M^-1 nmass_f.  Here exactly those 2 + 2 nf blocks    */
+/* per cell are kept (4.5x fewer bytes per operator application);  */
+/* yfd_maxwell_get_operator re-emits the reference's dense layout for parity checks.    */
+/* Unknowns at this boundary are numbered as the reference numbers gDofs:               */
+/* 3 bs cell + bs field + i, field 0 = Hx, 1 = Hy, 2 = Ez (:541-547).                   */
+/* ---------------------------------------------------------------------------------- */
+#define YFD_TI_RK4    0     /* time_integrator_type::RUNGE_KUTTA_4 (default, :66)       */
+#define YFD_TI_EULER  1     /* time_integrator_type::EXPLICIT_EULER                     */
+
+/* analytic fields: the driver's TM_mn cavity mode (maxwell_driver.cpp:202-216) */
+#define YFD_MAXWELL_FIELDS_CAVITY_11  0    /* m = n = 1                                 */
+#define YFD_MAXWELL_FIELDS_ZERO       1
+
+typedef struct yfd_maxwell_config {   /* maxwell_config<T> (methods/dg_maxwell_2D.hpp:46-72), solver-relevant fields */
+    int     degree;                   /* cfg.degree                                     */
+    double  delta_t;                  /* cfg.delta_t                                    */
+    double  eta;                      /* cfg.eta (upwind penalisation)                  */
+    int     upwind;                   /* cfg.upwind                                     */
+    int     time_integrator;          /* YFD_TI_*                                       */
+} yfd_maxwell_config;
+
+void yfd_maxwell_config_default(yfd_maxwell_config *cfg);   /* degree 1, delta_t 0.1, eta 1, centred, RK4 (:63-69) */
+
+typedef struct yfd_maxwell yfd_maxwell;
+
+typedef struct yfd_maxwell_info {
+    int64_t ncells, basis_size, faces_per_elem;
+    int64_t ndofs;                    /* 3 bs ncells                                    */
+    int64_t operator_bytes;           /* bytes of the factored operator held in HBM     */
+    int64_t reference_operator_bytes; /* (1 + nf) (3bs)^2 8 ncells: gOp_ondiag + gOp_offdiag */
+    double  ms_assemble;              /* device time of the element/face kernel incl. the M^-1 solves */
+} yfd_maxwell_info;
+
+/* maxwell_context ctor (storage) + assemble(ctx).  mu_r / eps_r: [ncells] in REFERENCE cell order, or NULL
+ * for 1.0 everywhere (the context's default, :149-150).  The mesh may be destroyed afterwards. */
+yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_config *cfg,
+                              const double *mu_r, const double *eps_r, yfd_maxwell **out, yfd_maxwell_info *info);
+void       yfd_maxwell_destroy(yfd_maxwell *m);
+void       yfd_maxwell_get_info(const yfd_maxwell *m, yfd_maxwell_info *info);
+/* change delta_t / the integrator without re-assembling (the operator does not depend on them) */
+yfd_status yfd_maxwell_set_time_integration(yfd_maxwell *m, double delta_t, int time_integrator);
+
+/* The operator in the REFERENCE's layout and numbering, for parity tests on small meshes:
+ *   ondiag  [ncells][3bs][3bs]       gOp_ondiag   (:90)
+ *   offdiag [ncells][nf][3bs][3bs]   gOp_offdiag, zero where the face is on the boundary
+ *   neigh   [ncells][nf], has [ncells][nf]   offdiag_neigh_offsets .first / .second (:106-107)
+ *   gM      [ncells][bs][bs]         elemental mass matrices (:87)
+ * Any output may be NULL. */
+yfd_status yfd_maxwell_get_operator(yfd_maxwell *m, double *ondiag, double *offdiag, int64_t *neigh,
+                                    int32_t *has, double *gM);
+
+/* apply_initial_condition: per-cell L2 projection of the analytic fields at time t into gDofs */
+yfd_status yfd_maxwell_apply_initial_condition(yfd_maxwell *m, int fields, double t);
+/* gDofs, host, reference numbering */
+yfd_status yfd_maxwell_get_dofs(yfd_maxwell *m, double *dofs);
+yfd_status yfd_maxwell_set_dofs(yfd_maxwell *m, const double *dofs);
+/* v_next = apply_operator(v) (:586-625) on host vectors in reference numbering */
+yfd_status yfd_maxwell_apply_operator(yfd_maxwell *m, const double *v, double *v_next);
+
+typedef struct yfd_maxwell_step_info {
+    int64_t steps;
+    double  ms_total;                 /* device time of all steps (CUDA events)                     */
+    double  ms_per_step;
+    int64_t operator_applications;    /* 4 per RK4 step, 1 per Euler step                           */
+} yfd_maxwell_step_info;
+
+/* nsteps x do_timestep (:558-675); gDofs stays on the device.  info may be NULL. */
+yfd_status yfd_maxwell_timesteps(yfd_maxwell *m, int64_t nsteps, yfd_maxwell_step_info *info);
+/* report_errors: L2 norms of (numerical - analytic(t)) for Hx, Hy, Ez.  The reference driver calls it with
+ * t = cycle * delta_t AFTER do_timestep of that cycle (maxwell_driver.cpp:249,266); callers wanting its
+ * numbers pass the same t. */
+yfd_status yfd_maxwell_report_errors(yfd_maxwell *m, int fields, double t, double errors[3]);
+
+/* Time `reps` operator applications with CUDA events (bench.py's roofline leg): average ms per application,
+ * the bytes the reference's dense layout would stream per application ((1+nf)(3bs)^2 8 per cell + 2 vectors)
+ * and the bytes this kernel requests. */
+yfd_status yfd_maxwell_time_apply(yfd_maxwell *m, int reps, double *ms_per_apply, double *reference_bytes,
+                                  double *kernel_bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,6 +21,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 
 TRI, QUAD = 0, 1
+TI_RK4, TI_EULER = 0, 1
+FIELDS_CAVITY_11, FIELDS_ZERO = 0, 1
 FN_ZERO, FN_SINSIN, FN_ONE = 0, 1, 2
 REORDER_NONE, REORDER_MORTON = 0, 1
 
@@ -74,6 +76,22 @@ class CgParams(C.Structure):
             if k not in dict(self._fields_):
                 raise TypeError("unknown CG parameter " + k)
             setattr(self, k, v)
+
+
+class MaxwellConfig(C.Structure):
+    """maxwell_config<T> (methods/dg_maxwell_2D.hpp:46-72), solver-relevant fields"""
+    _fields_ = [("degree", C.c_int), ("delta_t", C.c_double), ("eta", C.c_double), ("upwind", C.c_int),
+                ("time_integrator", C.c_int)]
+
+
+class MaxwellInfo(C.Structure):
+    _fields_ = [("ncells", C.c_int64), ("basis_size", C.c_int64), ("faces_per_elem", C.c_int64), ("ndofs", C.c_int64),
+                ("operator_bytes", C.c_int64), ("reference_operator_bytes", C.c_int64), ("ms_assemble", C.c_double)]
+
+
+class MaxwellStepInfo(C.Structure):
+    _fields_ = [("steps", C.c_int64), ("ms_total", C.c_double), ("ms_per_step", C.c_double),
+                ("operator_applications", C.c_int64)]
 
 
 class CgInfo(C.Structure):
@@ -151,6 +169,19 @@ def lib():
         "yfd_system_solve_cg_device": (cint, [vp, vp, cint, P(CgParams), vp, P(CgInfo)]),
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
+        "yfd_maxwell_config_default": (None, [P(MaxwellConfig)]),
+        "yfd_maxwell_create": (cint, [vp, vp, P(MaxwellConfig), vp, vp, P(vp), P(MaxwellInfo)]),
+        "yfd_maxwell_destroy": (None, [vp]),
+        "yfd_maxwell_get_info": (None, [vp, P(MaxwellInfo)]),
+        "yfd_maxwell_set_time_integration": (cint, [vp, dbl, cint]),
+        "yfd_maxwell_get_operator": (cint, [vp, vp, vp, vp, vp, vp]),
+        "yfd_maxwell_apply_initial_condition": (cint, [vp, cint, dbl]),
+        "yfd_maxwell_get_dofs": (cint, [vp, _f64p]),
+        "yfd_maxwell_set_dofs": (cint, [vp, _f64p]),
+        "yfd_maxwell_apply_operator": (cint, [vp, _f64p, _f64p]),
+        "yfd_maxwell_timesteps": (cint, [vp, i64, P(MaxwellStepInfo)]),
+        "yfd_maxwell_report_errors": (cint, [vp, cint, dbl, _f64p]),
+        "yfd_maxwell_time_apply": (cint, [vp, cint, P(dbl), P(dbl), P(dbl)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -514,3 +545,86 @@ class System:
         if not hasattr(self, "npoints"):
             raise YfdError(1, "set System.npoints (mesh.npoints) before CFEM expand/compress_map")
         return self.npoints
+
+
+class Maxwell:
+    """maxwell_context + assemble / apply_initial_condition / do_timestep / report_errors
+    (methods/dg_maxwell_2D.hpp, maxwell_driver.cpp:133-272) on the device (yfd_maxwell)."""
+
+    def __init__(self, ctx, mesh, degree, delta_t=0.1, eta=1.0, upwind=False, euler=False, mu_r=None, eps_r=None):
+        self.ctx = ctx
+        cfg = MaxwellConfig(degree, delta_t, eta, int(upwind), TI_EULER if euler else TI_RK4)
+        h = C.c_void_p()
+        self.info = MaxwellInfo()
+        mu = None if mu_r is None else np.ascontiguousarray(mu_r, np.float64)
+        ep = None if eps_r is None else np.ascontiguousarray(eps_r, np.float64)
+        self._h = None
+        ctx.check(lib().yfd_maxwell_create(ctx._h, mesh._h, C.byref(cfg), _ptr(mu), _ptr(ep), C.byref(h), C.byref(self.info)))
+        self._h = h
+        ctx._children.add(self)
+        self.ncells, self.bs, self.nf, self.ndofs = (self.info.ncells, self.info.basis_size, self.info.faces_per_elem,
+                                                      self.info.ndofs)
+        self.delta_t = delta_t
+
+    def close(self):
+        if self._h:
+            lib().yfd_maxwell_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_time_integration(self, delta_t, euler=False):
+        self.ctx.check(lib().yfd_maxwell_set_time_integration(self._h, delta_t, TI_EULER if euler else TI_RK4))
+        self.delta_t = delta_t
+
+    def operator(self, blocks=True):
+        nc, nf, bs = self.ncells, self.nf, self.bs
+        L = 3 * bs
+        on = np.empty((nc, L, L)) if blocks else None
+        off = np.empty((nc, nf, L, L)) if blocks else None
+        nb = np.empty((nc, nf), np.int64)
+        has = np.empty((nc, nf), np.int32)
+        gM = np.empty((nc, bs, bs))
+        self.ctx.check(lib().yfd_maxwell_get_operator(self._h, _ptr(on), _ptr(off), _ptr(nb), _ptr(has), _ptr(gM)))
+        return dict(ondiag=on, offdiag=off, neigh=nb, has=has, gM=gM)
+
+    def apply_initial_condition(self, fields=FIELDS_CAVITY_11, t=0.0):
+        self.ctx.check(lib().yfd_maxwell_apply_initial_condition(self._h, fields, t))
+
+    def dofs(self):
+        d = np.empty(self.ndofs)
+        self.ctx.check(lib().yfd_maxwell_get_dofs(self._h, d))
+        return d
+
+    def set_dofs(self, d):
+        d = np.ascontiguousarray(d, np.float64)
+        if d.size != self.ndofs:
+            raise YfdError(8, "wrong size of the dof vector")
+        self.ctx.check(lib().yfd_maxwell_set_dofs(self._h, d))
+
+    def apply_operator(self, v):
+        v = np.ascontiguousarray(v, np.float64)
+        if v.size != self.ndofs:
+            raise YfdError(8, "wrong size of the dof vector")
+        out = np.empty(self.ndofs)
+        self.ctx.check(lib().yfd_maxwell_apply_operator(self._h, v, out))
+        return out
+
+    def timesteps(self, nsteps=1):
+        info = MaxwellStepInfo()
+        self.ctx.check(lib().yfd_maxwell_timesteps(self._h, nsteps, C.byref(info)))
+        return info
+
+    def report_errors(self, t, fields=FIELDS_CAVITY_11):
+        e = np.empty(3)
+        self.ctx.check(lib().yfd_maxwell_report_errors(self._h, fields, t, e))
+        return e
+
+    def time_apply(self, reps=20):
+        ms, rb, kb = C.c_double(), C.c_double(), C.c_double()
+        self.ctx.check(lib().yfd_maxwell_time_apply(self._h, reps, C.byref(ms), C.byref(rb), C.byref(kb)))
+        return ms.value, rb.value, kb.value

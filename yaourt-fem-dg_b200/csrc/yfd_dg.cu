@@ -24,11 +24,11 @@
  * Small dense contractions: FP64 FMA, no tensor cores (north_star: only if ncu shows a win).
  */
 #include "yfd_internal.hpp"
+#include "yfd_elem.cuh"
 #include <cmath>
 
 namespace yfd {
 
-constexpr int DG_MAX_DEGREE = 6;          /* bs = 28, 25 accumulators per lane */
 constexpr int DG_WARPS = 4;               /* warps (cells) per CTA */
 
 struct dg_args {
@@ -64,63 +64,6 @@ __device__ __forceinline__ double eval_fn(int fn, double x, double y)
     case YFD_FN_ONE: return 1.0;
     default: return 0.0;
     }
-}
-
-__host__ __device__ constexpr int dg_nq_cell(int nv, int k)
-{
-    /* Dunavant point counts for degree 2k (degree 0 uses rule 1) */
-    return nv == 4 ? (k + 1) * (k + 1)
-                   : (k == 0 ? 1 : k == 1 ? 3 : k == 2 ? 6 : k == 3 ? 12 : k == 4 ? 16 : k == 5 ? 25 : 33);
-}
-
-template <int K>
-struct basis_eval {
-    static constexpr int BS = (K + 2) * (K + 1) / 2;
-    /* phi[i], gx[i], gy[i] for all i at physical point (x,y); frame (xb,yb,h) */
-    __device__ static __forceinline__ void run(double x, double y, double xb, double yb, double h,
-                                               double *phi, double *gx, double *gy, int stride)
-    {
-        const double half_h = 0.5 * h;
-        const double bx = (x - xb) / half_h, by = (y - yb) / half_h;
-        const double ih = 2.0 / h;
-        double px[K + 1], py[K + 1];
-        px[0] = 1.0; py[0] = 1.0;
-#pragma unroll
-        for (int p = 1; p <= K; p++) { px[p] = px[p - 1] * bx; py[p] = py[p - 1] * by; }
-        int pos = 0;
-#pragma unroll
-        for (int d = 0; d <= K; d++) {
-#pragma unroll
-            for (int i = 0; i <= d; i++) {
-                const int ex = d - i, ey = i;
-                phi[pos * stride] = px[ex] * py[ey];
-                const double dx = ex == 0 ? 0.0 : (double) ex * ih * px[ex == 0 ? 0 : ex - 1];
-                const double dy = ey == 0 ? 0.0 : (double) ey * ih * py[ey == 0 ? 0 : ey - 1];
-                gx[pos * stride] = dx * py[ey];
-                gy[pos * stride] = px[ex] * dy;
-                pos++;
-            }
-        }
-    }
-};
-
-template <int NV>
-__device__ __forceinline__ void cell_frame(const double2 *P, double &xb, double &yb, double &h)
-{
-    /* barycenter (core/mesh.hpp:424-441), diameter = max pairwise vertex distance (:474-487) */
-    double sx = P[0].x, sy = P[0].y;
-#pragma unroll
-    for (int v = 1; v < NV; v++) { sx += P[v].x; sy += P[v].y; }
-    xb = sx / (double) NV; yb = sy / (double) NV;
-    double d = 0.0;
-#pragma unroll
-    for (int a = 0; a < NV; a++)
-#pragma unroll
-        for (int b = a + 1; b < NV; b++) {
-            const double dx = P[a].x - P[b].x, dy = P[a].y - P[b].y;
-            d = fmax(sqrt(dx * dx + dy * dy), d);
-        }
-    h = d;
 }
 
 template <int NV, int K>

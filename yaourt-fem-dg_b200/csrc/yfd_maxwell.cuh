@@ -1,0 +1,62 @@
+/*
+ * yfd_maxwell.cuh -- the DG Maxwell TM solver object and the layout of its factored operator
+ * (shared by yfd_maxwell.cu: assembly / projection / errors, and yfd_maxwell_step.cu: the time loop).
+ *
+ * Operator layout in HBM ("row chunks"): consecutive cells of the internal (Z-curve) order are grouped into
+ * chunks of CPW = max(1, 32 / bs) cells, so that a warp owns one chunk with lane r = slot * bs + i holding row i
+ * of cell `slot`.  Per chunk NB = 2 + 2 nf blocks are stored one after the other,
+ *     b = 0: Gx = M^-1 Sx     b = 1: Gy = M^-1 Sy     b = 2 + f: T_f = M^-1 tmass_f     b = 2 + nf + f: N_f = M^-1 nmass_f
+ * each as [j][RWP] doubles (column j of every row of the chunk side by side; RWP = CPW * bs rounded up to even so
+ * that every [j] line starts 16-byte aligned).  For a fixed (b, j) the warp reads RWP consecutive doubles: the
+ * whole operator is streamed exactly once per application with fully coalesced loads and no staging, because
+ * every entry is used by exactly one lane.
+ */
+#pragma once
+#include "yfd_internal.hpp"
+
+namespace yfd {
+
+__host__ __device__ constexpr int mx_bs(int k) { return (k + 2) * (k + 1) / 2; }
+__host__ __device__ constexpr int mx_cpw(int bs) { return 32 / bs > 0 ? 32 / bs : 1; }
+__host__ __device__ constexpr int mx_rwp(int bs) { return (mx_cpw(bs) * bs + 1) & ~1; }
+__host__ __device__ constexpr int mx_nb(int nf) { return 2 + 2 * nf; }
+
+/* per (cell, face): everything the flux terms need besides the two blocks */
+struct mx_face_coef { double nx, ny, cE, cH, vH, vE; };
+
+} // namespace yfd
+
+struct yfd_maxwell {
+    yfd_ctx *ctx = nullptr;
+    int      cell_type = 0, nv = 3, nf = 3, degree = 1, bs = 3;
+    int      upwind = 0, time_integrator = 0;
+    double   delta_t = 0.1, eta = 1.0;
+    int64_t  ncells = 0, ndofs = 0, nchunks = 0;
+    double   ms_assemble = 0;
+    /* geometry kept for projection / error norms (the mesh handle may die first) */
+    yfd::dbuf<double>  cell_pts;      /* [ncells][nv][2] internal order                                   */
+    yfd::dbuf<int32_t> perm, iperm;   /* internal <-> reference cell ids                                  */
+    yfd::dbuf<int32_t> nbr;           /* [ncells][nf] internal id of the cell across local face f, -1 none */
+    /* operator */
+    yfd::dbuf<double>  op;            /* [nchunks][NB][bs][RWP]                                           */
+    yfd::dbuf<yfd::mx_face_coef> fc;  /* [ncells][nf]                                                     */
+    yfd::dbuf<double>  cs;            /* [ncells][2] = inv_mu, inv_eps                                    */
+    yfd::dbuf<double>  gM;            /* [ncells][bs][bs] row-major, internal order                       */
+    /* state: gDofs and the RK work vectors, internal order, [ncells][3][bs] */
+    yfd::dbuf<double>  u, s1, s2, acc, kb;
+};
+
+namespace yfd {
+/* yfd_maxwell_step.cu */
+enum mx_mode { MX_APPLY = 0, MX_RK1 = 1, MX_RK2 = 2, MX_RK3 = 3, MX_RK4 = 4, MX_EULER = 5 };
+struct mx_step_args {
+    const double *op; const mx_face_coef *fc; const double *cs; const int32_t *nbr;
+    int64_t ncells, nchunks;
+    const double *vin;      /* operand of the operator                                   */
+    double *u;              /* gDofs (RK base, updated by the last stage)                */
+    double *out;            /* MX_APPLY: L(vin); stages 1-3: next stage operand          */
+    double *acc, *kb;       /* k1 (+ 2(k2+k3)) and k2                                    */
+    double dt;
+};
+yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
+} // namespace yfd

@@ -1,0 +1,176 @@
+/*
+ * yfd_maxwell_step.cu -- the DG Maxwell time loop: one kernel per operator application, fused with the
+ * Runge-Kutta vector updates that follow it.
+ *
+ * Replaces apply_operator + the RK4 / Euler combinations of do_timestep (methods/dg_maxwell_2D.hpp:586-657).
+ * The reference multiplies, per cell, a dense 3bs x 3bs block with the cell's unknowns and one more per face
+ * with the neighbour's (HBM-bound block GEMV over (1+nf)(3bs)^2 doubles per cell).  Only 4 (centred fluxes) or
+ * 9 (upwind) of the 9 sub-blocks are non-zero and every one is a scalar multiple of Gx = M^-1 Sx, Gy = M^-1 Sy,
+ * T_f = M^-1 tmass_f or N_f = M^-1 nmass_f (:290-295, :356-381, :404-410), so this kernel streams exactly those
+ * 2 + 2 nf blocks per cell and applies the 3x3 pattern in registers:
+ *     a_f(v) = T_f v_c - N_f v_n                                   (N_f = 0, v_n = 0 on the boundary)
+ *     Hx' = 1/mu  [ -Gy Ez + sum_f  ny cE a_f(Ez) - vH ( ny ny a_f(Hx) - nx ny a_f(Hy) ) ]
+ *     Hy' = 1/mu  [ +Gx Ez + sum_f -nx cE a_f(Ez) + vH ( nx ny a_f(Hx) - nx nx a_f(Hy) ) ]
+ *     Ez' = 1/eps [ -Gy Hx + Gx Hy + sum_f cH ( ny a_f(Hx) - nx a_f(Hy) ) - vE a_f(Ez) ]
+ * with (cE, cH, vH, vE) = (kappa_E, kappa_H, nu_H, nu_E) on interior faces and (2 kappa_E, 0, 0, 2 nu_E) on
+ * boundary faces (:396-410).
+ *
+ * Kernel shape (sm_100a): one warp per chunk of CPW = 32/bs consecutive cells, lane = (cell slot, row i).
+ * The operator is laid out [chunk][block][j][row] (yfd_maxwell.cuh), so for each (block, j) the warp reads one
+ * contiguous line, every entry is used by exactly one lane, and nothing is staged: the loads are fully unrolled
+ * per block and marked evict-first (each byte is touched once per application).  The cell's own unknowns and
+ * its neighbours' are gathered once (coalesced bs-wide runs, L2 hits thanks to the Z-curve order) into a small
+ * per-warp shared-memory table [group][field][j][slot] from which every lane reads its cell's v[j] as a
+ * conflict-free broadcast.  HBM-bound fp64 FMA work, 0.7 flop/B: no tensor cores.
+ *
+ * RK4 without extra passes (the reference forms k1..k4 and four temporaries, :636-657): stage s writes the
+ * operand of stage s+1 and keeps  k1  and  k2  so that the last stage can form the reference's expression
+ * u + ((1/6) dt) (k1 + 2 (k2 + k3) + k4)  in its own order.  Per step: 4 launches.
+ */
+#include "yfd_maxwell.cuh"
+
+namespace yfd {
+
+constexpr int MX_WARPS = 8;
+
+__device__ __forceinline__ double ld_stream(const double *p)
+{
+    return __ldcs(p);          /* ld.global.cs: streamed once, evict first */
+}
+
+template <int NV, int K>
+__global__ void __launch_bounds__(MX_WARPS * 32)
+maxwell_stage(const mx_step_args a, const int mode)
+{
+    constexpr int BS = mx_bs(K), CPW = mx_cpw(BS), RWP = mx_rwp(BS), NB = mx_nb(NV), L = 3 * BS;
+    constexpr int GRP = 3 * BS * CPW;                 /* one group of the v table: [field][j][slot] */
+    extern __shared__ double sm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *VS = sm + (size_t) warp * ((1 + NV) * GRP);
+    const int64_t chunk = (int64_t) blockIdx.x * MX_WARPS + warp;
+    if (chunk >= a.nchunks) return;                   /* warps are independent: no CTA-wide barrier below */
+
+    const int slot = lane / BS, i = lane - slot * BS;
+    const bool inwarp = slot < CPW;
+    const int64_t cell = chunk * CPW + slot;
+    const bool valid = inwarp && cell < a.ncells;
+    const int r = inwarp ? lane : 0;                  /* lanes past the chunk's rows read row 0 and store nothing */
+    const int sl = inwarp ? slot : 0;
+
+    /* ---- gather: own unknowns and the neighbours' ---- */
+    double own[3] = {0.0, 0.0, 0.0};
+    if (valid) {
+        const double *v = a.vin + cell * L + i;
+        own[0] = __ldg(v); own[1] = __ldg(v + BS); own[2] = __ldg(v + 2 * BS);
+    }
+    if (inwarp) {
+#pragma unroll
+        for (int fld = 0; fld < 3; fld++) VS[(fld * BS + i) * CPW + slot] = own[fld];
+    }
+#pragma unroll
+    for (int f = 0; f < NV; f++) {
+        const int32_t nb = valid ? __ldg(&a.nbr[cell * NV + f]) : -1;
+        double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+        if (nb >= 0) {
+            const double *v = a.vin + (int64_t) nb * L + i;
+            w0 = __ldg(v); w1 = __ldg(v + BS); w2 = __ldg(v + 2 * BS);
+        }
+        if (inwarp) {
+            double *G = VS + (1 + f) * GRP;
+            G[(0 * BS + i) * CPW + slot] = w0; G[(1 * BS + i) * CPW + slot] = w1; G[(2 * BS + i) * CPW + slot] = w2;
+        }
+    }
+    __syncwarp();
+
+    /* ---- cell blocks: Gx (b = 0), Gy (b = 1) ---- */
+    const double *opc = a.op + (size_t) chunk * (NB * BS * RWP) + r;
+    const double *V0 = VS + sl;                       /* own group, this lane's slot */
+    double gxe = 0.0, gxh = 0.0, gye = 0.0, gyh = 0.0;
+    {
+        double wx[BS], wy[BS];
+#pragma unroll
+        for (int j = 0; j < BS; j++) { wx[j] = ld_stream(opc + j * RWP); wy[j] = ld_stream(opc + (BS + j) * RWP); }
+#pragma unroll
+        for (int j = 0; j < BS; j++) {
+            const double hx = V0[(0 * BS + j) * CPW], hy = V0[(1 * BS + j) * CPW], ez = V0[(2 * BS + j) * CPW];
+            gxe += wx[j] * ez; gxh += wx[j] * hy;
+            gye += wy[j] * ez; gyh += wy[j] * hx;
+        }
+    }
+    double Hx = -gye, Hy = gxe, Ez = gxh - gyh;
+
+    /* ---- faces: a_f = T_f v_c - N_f v_n ---- */
+#pragma unroll
+    for (int f = 0; f < NV; f++) {
+        const double *Tf = opc + (size_t) (2 + f) * BS * RWP, *Nf = opc + (size_t) (2 + NV + f) * BS * RWP;
+        const double *VN = VS + (1 + f) * GRP + sl;
+        double wt[BS], wn[BS];
+#pragma unroll
+        for (int j = 0; j < BS; j++) { wt[j] = ld_stream(Tf + j * RWP); wn[j] = ld_stream(Nf + j * RWP); }
+        double p = 0.0, q = 0.0, s = 0.0;
+#pragma unroll
+        for (int j = 0; j < BS; j++) {
+            p += wt[j] * V0[(0 * BS + j) * CPW]; q += wt[j] * V0[(1 * BS + j) * CPW]; s += wt[j] * V0[(2 * BS + j) * CPW];
+            p -= wn[j] * VN[(0 * BS + j) * CPW]; q -= wn[j] * VN[(1 * BS + j) * CPW]; s -= wn[j] * VN[(2 * BS + j) * CPW];
+        }
+        mx_face_coef c = {0, 0, 0, 0, 0, 0};
+        if (valid) c = a.fc[cell * NV + f];
+        Hx += c.ny * c.cE * s - c.vH * (c.ny * c.ny * p - c.nx * c.ny * q);
+        Hy += -c.nx * c.cE * s + c.vH * (c.nx * c.ny * p - c.nx * c.nx * q);
+        Ez += c.cH * (c.ny * p - c.nx * q) - c.vE * s;
+    }
+    if (!valid) return;
+    const double inv_mu = __ldg(&a.cs[2 * cell]), inv_eps = __ldg(&a.cs[2 * cell + 1]);
+    const double kv[3] = {inv_mu * Hx, inv_mu * Hy, inv_eps * Ez};
+
+    /* ---- sink: plain application or one Runge-Kutta stage (methods/dg_maxwell_2D.hpp:630-657), no FMA
+     * contraction so the combinations round as the reference's separate multiply and add ---- */
+    const int64_t base = cell * L + i;
+#pragma unroll
+    for (int fld = 0; fld < 3; fld++) {
+        const int64_t idx = base + fld * BS;
+        const double k = kv[fld];
+        switch (mode) {
+        case MX_APPLY: a.out[idx] = k; break;
+        case MX_RK1:   a.acc[idx] = k; a.out[idx] = __dadd_rn(own[fld], __dmul_rn(a.dt / 2., k)); break;
+        case MX_RK2:   a.kb[idx] = k;  a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt / 2., k)); break;
+        case MX_RK3:   a.acc[idx] = __dadd_rn(a.acc[idx], __dmul_rn(__dadd_rn(a.kb[idx], k), 2.0));
+                       a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt, k)); break;
+        case MX_RK4:   a.u[idx] = __dadd_rn(a.u[idx], __dmul_rn(__dadd_rn(a.acc[idx], k), (1. / 6.) * a.dt)); break;
+        case MX_EULER: a.out[idx] = __dadd_rn(own[fld], __dmul_rn(a.dt, k)); break;
+        }
+    }
+}
+
+template <int NV, int K>
+static yfd_status launch_stage(yfd_ctx *ctx, int mode, const mx_step_args &a)
+{
+    constexpr int BS = mx_bs(K), CPW = mx_cpw(BS);
+    const size_t smem = (size_t) MX_WARPS * (1 + NV) * 3 * BS * CPW * sizeof(double);
+    const unsigned grid = (unsigned) ceil_div(a.nchunks, MX_WARPS);
+    YFD_LAUNCH(ctx, (maxwell_stage<NV, K>), grid, MX_WARPS * 32, smem, a, mode);
+    return YFD_OK;
+}
+
+template <int NV>
+static yfd_status dispatch_stage(yfd_ctx *ctx, int degree, int mode, const mx_step_args &a)
+{
+    switch (degree) {
+    case 0: return launch_stage<NV, 0>(ctx, mode, a);
+    case 1: return launch_stage<NV, 1>(ctx, mode, a);
+    case 2: return launch_stage<NV, 2>(ctx, mode, a);
+    case 3: return launch_stage<NV, 3>(ctx, mode, a);
+    case 4: return launch_stage<NV, 4>(ctx, mode, a);
+    case 5: return launch_stage<NV, 5>(ctx, mode, a);
+    case 6: return launch_stage<NV, 6>(ctx, mode, a);
+    }
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "Maxwell degree %d: kernels are instantiated for 0..6", degree);
+}
+
+yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a)
+{
+    if (a.nchunks <= 0) return YFD_OK;
+    return nv == 3 ? dispatch_stage<3>(ctx, degree, mode, a) : dispatch_stage<4>(ctx, degree, mode, a);
+}
+
+} // namespace yfd
