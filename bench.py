@@ -54,6 +54,13 @@ WORKLOADS = {
                         desc="continuous P1 FEM Poisson, triangles -r 11: 33,554,432 cells, 8,380,417 dofs (BASELINE configs[1] is P2; the reference is P1 only)"),
     "cfem_p1_r10": dict(kind="cfem", cell=0, r=10, k=1, pc=False, rr_tol=1e-8, rr_max=1e3, ref_r=7, base_r=8,
                         desc="continuous P1 FEM Poisson, triangles -r 10: 8,388,608 cells, 2,095,105 dofs"),
+    # configs[3]: "dg_maxwell_2D time-domain explicit run, degree 4 triangles, matrix-free element+face operator"
+    "maxwell_tri_k4_r9": dict(kind="maxwell", cell=0, r=9, k=4, upwind=False, dt=2e-5, timesteps=50, ref_r=5, base_r=6,
+                              desc="DG Maxwell TM, triangles k=4, -r 9, centred fluxes, RK4: 1,048,576 cells, 47,185,920 unknowns (BASELINE configs[3])"),
+    "maxwell_tri_k4_r8_upwind": dict(kind="maxwell", cell=0, r=8, k=4, upwind=True, dt=4e-5, timesteps=50, ref_r=5, base_r=6,
+                                     desc="DG Maxwell TM, triangles k=4, -r 8, upwind fluxes, RK4: 262,144 cells, 11,796,480 unknowns"),
+    "maxwell_quad_k3_r9": dict(kind="maxwell", cell=1, r=9, k=3, upwind=False, dt=2e-5, timesteps=50, ref_r=5, base_r=6,
+                               desc="DG Maxwell TM, quadrangles k=3, -r 9, centred fluxes, RK4: 1,048,576 cells, 31,457,280 unknowns"),
 }
 DEFAULT_WORKLOAD = "dg_sip_quad_k3_r9"
 
@@ -187,6 +194,189 @@ def run_reference_arm(args, wl, rank):
 
 
 # ------------------------------------------------------------------------------------------------
+# DG Maxwell workloads (BASELINE configs[3]): one step = assemble + initial condition + T RK4 timesteps + error norms
+# ------------------------------------------------------------------------------------------------
+MAXWELL_METRIC, MAXWELL_UNIT = "assembled+time-stepped DOF updates/sec", "DOF-steps/s"
+
+
+def maxwell_reference_step(R, wl, r):
+    """The unmodified reference (oracle/_ref/libyfd_ref_maxwell*.so): maxwell_context (mesh: untimed) -> assemble ->
+    apply_initial_condition -> T x do_timestep -> report_errors."""
+    R.create(wl["cell"], r, wl["k"], dt=wl["dt"], upwind=wl["upwind"])
+    t0 = time.perf_counter()
+    R.assemble()
+    R.init()
+    t1 = time.perf_counter()
+    R.step(wl["timesteps"])
+    t2 = time.perf_counter()
+    R.errors(wl["timesteps"] - 1)
+    t3 = time.perf_counter()
+    return dict(n=3 * R.bs * R.ncells, t=t3 - t0, t_assemble=t1 - t0, t_steps=t2 - t1, t_errors=t3 - t2, cells=R.ncells)
+
+
+def load_maxwell_reference():
+    import refbind
+    omp = refbind.maxwell_available(omp=True)
+    if not refbind.maxwell_available(omp=omp):
+        return None, 0
+    cores = os.cpu_count() or 1
+    if omp:
+        os.environ["OMP_NUM_THREADS"] = str(cores)
+    R = refbind.RefMaxwell(omp=omp)
+    return R, (R.num_threads() if omp else 1)
+
+
+def maxwell_sample_text(wl, r, s):
+    return ("unmodified reference (Blaze dense blocks, -O3 -fopenmp; its cell loops are serial), same discretisation at -r %d: "
+            "%d cells, %d unknowns, %d RK4 timesteps; assemble+IC %.2fs, timesteps %.2fs (%.1f ns per unknown per step), errors %.2fs"
+            % (r, s["cells"], s["n"], wl["timesteps"], s["t_assemble"], s["t_steps"], 1e9 * s["t_steps"] / (s["n"] * wl["timesteps"]), s["t_errors"]))
+
+
+def run_maxwell_reference_arm(args, wl, rank):
+    if rank != 0:
+        return 0
+    R, cores = load_maxwell_reference()
+    if R is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libyfd_ref_maxwell.so not built (needs /root/reference at build time)"}))
+        return 0
+    r = wl["ref_r"]
+    for _ in range(args.warmup):
+        maxwell_reference_step(R, wl, r)
+    tot, last = 0.0, None
+    for _ in range(args.steps):
+        last = maxwell_reference_step(R, wl, r)
+        tot += last["t"]
+    value = last["n"] * wl["timesteps"] / (tot / args.steps)
+    sample = maxwell_sample_text(wl, r, last)
+    print(json.dumps({"impl": "reference", "metric": MAXWELL_METRIC, "value": value, "unit": MAXWELL_UNIT, "n_gpus": args.gpus,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True,
+                      "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": args.workload, "description": wl["desc"], "sample": sample},
+                      "cpu_baseline": {"value": value, "unit": MAXWELL_UNIT, "cores": cores, "kind": "reference", "sample": sample},
+                      "e2e": {"value": value, "unit": MAXWELL_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+    return 0
+
+
+def run_maxwell(args, wl, rank, world, local_rank):
+    import torch
+    import yaourt_fem_dg_b200 as yfd
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path is CUDA only (no CPU fallback)")
+    if world > 1:
+        raise SystemExit("the Maxwell time loop is not partitioned yet (DESIGN.md): run it with --gpus 1")
+    torch.cuda.set_device(local_rank)
+    stream = torch.cuda.current_stream()
+    ctx = yfd.Context(local_rank, stream=stream.cuda_stream)
+    T = args.profile_iters or wl["timesteps"]
+    hm = yfd.HostMesh.create(wl["cell"], wl["r"])            # mesher: input generation, untimed
+    info = {}
+
+    def one_pass(mesh, x_host=None):
+        mx = yfd.Maxwell(ctx, mesh, wl["k"], delta_t=wl["dt"], upwind=wl["upwind"])
+        mx.apply_initial_condition()
+        st = mx.timesteps(T)
+        err = mx.report_errors((T - 1) * wl["dt"])
+        if x_host is not None:
+            ctx.check(yfd.lib().yfd_maxwell_get_dofs(mx._h, x_host))
+        info.update(n=mx.ndofs, cells=mx.ncells, ms_assemble=mx.info.ms_assemble, ms_timesteps=st.ms_total, errors=[float(e) for e in err],
+                    operator_bytes=mx.info.operator_bytes, reference_operator_bytes=mx.info.reference_operator_bytes)
+        return mx
+
+    mesh = yfd.Mesh(ctx, hm)
+    for _ in range(args.warmup):
+        one_pass(mesh).close()
+    sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", ""))
+    torch.cuda.synchronize()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = ctx.launches
+    e0.record(stream)
+    for _ in range(args.steps):
+        one_pass(mesh).close()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    launches = ctx.launches - l0
+    ms_step = e0.elapsed_time(e1) / args.steps
+    n = info["n"]
+    value = n * T / (ms_step * 1e-3)
+
+    # roofline leg: the operator application alone, CUDA events on the launching stream
+    mx = one_pass(mesh)
+    ms_apply, ref_bytes, kern_bytes = mx.time_apply(30)
+    mx.close()
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(args.workload)
+    achieved = ref_bytes / (ms_apply * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "maxwell_stage (operator application, factored blocks)", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": ref_bytes, "kernel_requested_bytes_per_launch": kern_bytes,
+                "kernel_requested_gbs": kern_bytes / (ms_apply * 1e-3) / 1e9, "ms_per_launch": ms_apply,
+                "note": "algorithmic = the reference's dense layout, (1+nf)(3bs)^2 8 B per cell + 2 vectors (SURVEY.md 8, cfg 4); "
+                        "the kernel streams 2+2nf blocks of bs^2 per cell instead, hence frac > 1; kernel_requested_gbs / peak is the honest HBM fraction"}
+
+    e2e = None
+    if not args.no_e2e:
+        keep, arrs = [], {}
+        for nme in ("points", "cells", "faces", "face_boundary"):
+            t, a = pinned_like(torch, getattr(hm, nme))
+            keep.append(t); arrs[nme] = a
+        xt = torch.empty(n, dtype=torch.float64).pin_memory()
+        x_host = xt.numpy()
+        hm_p = yfd.HostMesh(hm.cell_type, arrs["points"], arrs["cells"], arrs["faces"], arrs["face_boundary"])
+
+        def step_e2e():
+            m2 = yfd.Mesh(ctx, hm_p)
+            one_pass(m2, x_host).close()
+            m2.close()
+        mesh.close()
+        step_e2e()
+        torch.cuda.synchronize()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        f0.record(stream)
+        for _ in range(args.steps):
+            step_e2e()
+        f1.record(stream)
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / args.steps
+        ms_e2e = f0.elapsed_time(f1) / args.steps
+        e2e = {"value": n * T / (ms_e2e * 1e-3), "unit": MAXWELL_UNIT, "h2d_bytes_per_step": int(sum(a.nbytes for a in arrs.values())),
+               "d2h_bytes_per_step": int(x_host.nbytes), "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
+               "path": "yfd_mesh_create -> yfd_maxwell_create -> apply_initial_condition -> timesteps -> report_errors -> get_dofs (host) through include/yfd.h"}
+
+    base = None
+    if not args.no_cpu_baseline:
+        R, cores = load_maxwell_reference()
+        if R is not None:
+            sres = maxwell_reference_step(R, wl, wl["base_r"])
+            base = dict(value=sres["n"] * wl["timesteps"] / sres["t"], unit=MAXWELL_UNIT, cores=cores, kind="reference",
+                        sample=maxwell_sample_text(wl, wl["base_r"], sres))
+    line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else {}
+    line.update({"metric": MAXWELL_METRIC, "value": value, "unit": MAXWELL_UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                 "data": "synthetic",
+                 "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(n), "cells": int(info["cells"]),
+                            "timesteps_per_step": T, "delta_t": wl["dt"], "time_integrator": "RK4 (4 operator applications per timestep)",
+                            "l2_policy": "inputs larger than L2: the factored operator is %.1f GB vs 126 MB L2" % (1e-9 * info["operator_bytes"]),
+                            "operator_bytes": int(info["operator_bytes"]), "reference_operator_bytes": int(info["reference_operator_bytes"]),
+                            "phases_ms": {"assemble": info["ms_assemble"], "timesteps": info["ms_timesteps"]},
+                            "l2_errors_vs_analytic": info["errors"], "parallelism": "1 GPU"},
+                 "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
+    print(json.dumps(line))
+    ctx.close()
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
 def pinned_like(torch, a):
@@ -211,12 +401,14 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        return run_reference_arm(args, wl, rank)
+        return run_maxwell_reference_arm(args, wl, rank) if wl.get("kind") == "maxwell" else run_reference_arm(args, wl, rank)
     if args.profile_iters > 0:
         args.warmup, args.steps, args.no_e2e, args.no_cpu_baseline = 0, 1, True, True
     elif args.warmup < 3:
         args.warmup = 3
 
+    if wl.get("kind") == "maxwell":
+        return run_maxwell(args, wl, rank, world, local_rank)
     import torch
     import yaourt_fem_dg_b200 as yfd
     if not torch.cuda.is_available():

@@ -140,12 +140,13 @@ def test_centred_scheme_conserves_energy_at_scale(yfd, ctx):
     # a rough (random) state has jumps everywhere: the centred scheme still conserves, upwinding must dissipate
     rng = np.random.default_rng(5)
     rough = rng.standard_normal(mx.ndofs)
+    mx.set_time_integration(dt / 10)          # RK4 itself damps modes with lambda dt ~ 1: keep the rough state well resolved in time
     mx.set_dofs(rough)
     r0 = energy(rough)
     mx.timesteps(20)
     r1 = energy(mx.dofs())
-    assert abs(r1 - r0) <= 1e-6 * r0
-    up = yfd.Maxwell(ctx, mesh, 3, delta_t=dt, upwind=True)
+    assert abs(r1 - r0) <= 1e-7 * r0
+    up = yfd.Maxwell(ctx, mesh, 3, delta_t=dt / 10, upwind=True)
     up.set_dofs(rough)
     up.timesteps(20)
     r2 = energy(up.dofs())

@@ -18,7 +18,8 @@
  * Kernel shape (sm_100a): one warp per chunk of CPW = 32/bs consecutive cells, lane = (cell slot, row i).
  * The operator is laid out [chunk][block][j][row] (yfd_maxwell.cuh), so for each (block, j) the warp reads one
  * contiguous line, every entry is used by exactly one lane, and nothing is staged: the loads are fully unrolled
- * per block and marked evict-first (each byte is touched once per application).  The cell's own unknowns and
+ * per block and marked evict-first (each byte is touched once per application).  Lane 0 opens with one
+ * cp.async.bulk.prefetch.L2 of the whole chunk slab, so DRAM works on all of it while the first blocks are consumed.  The cell's own unknowns and
  * its neighbours' are gathered once (coalesced bs-wide runs, L2 hits thanks to the Z-curve order) into a small
  * per-warp shared-memory table [group][field][j][slot] from which every lane reads its cell's v[j] as a
  * conflict-free broadcast.  HBM-bound fp64 FMA work, 0.7 flop/B: no tensor cores.
@@ -28,6 +29,7 @@
  * u + ((1/6) dt) (k1 + 2 (k2 + k3) + k4)  in its own order.  Per step: 4 launches.
  */
 #include "yfd_maxwell.cuh"
+#include <cstdlib>
 
 namespace yfd {
 
@@ -38,9 +40,15 @@ __device__ __forceinline__ double ld_stream(const double *p)
     return __ldcs(p);          /* ld.global.cs: streamed once, evict first */
 }
 
-template <int NV, int K>
-__global__ void __launch_bounds__(MX_WARPS * 32)
-maxwell_stage(const mx_step_args a, const int mode)
+/* one lane asks the L2 to start fetching `bytes` (multiple of 16) at p: no registers, no shared memory */
+__device__ __forceinline__ void l2_prefetch_bulk(const void *p, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
+template <int NV, int K, int MINB>
+__global__ void __launch_bounds__(MX_WARPS * 32, MINB)
+maxwell_stage(const mx_step_args a, const int mode, const int prefetch)
 {
     constexpr int BS = mx_bs(K), CPW = mx_cpw(BS), RWP = mx_rwp(BS), NB = mx_nb(NV), L = 3 * BS;
     constexpr int GRP = 3 * BS * CPW;                 /* one group of the v table: [field][j][slot] */
@@ -56,6 +64,8 @@ maxwell_stage(const mx_step_args a, const int mode)
     const bool valid = inwarp && cell < a.ncells;
     const int r = inwarp ? lane : 0;                  /* lanes past the chunk's rows read row 0 and store nothing */
     const int sl = inwarp ? slot : 0;
+    if (prefetch && lane == 0)                        /* the whole chunk's operator slab: DRAM starts on all of it now */
+        l2_prefetch_bulk(a.op + (size_t) chunk * (NB * BS * RWP), (uint32_t) (NB * BS * RWP * sizeof(double)));
 
     /* ---- gather: own unknowns and the neighbours' ---- */
     double own[3] = {0.0, 0.0, 0.0};
@@ -142,13 +152,24 @@ maxwell_stage(const mx_step_args a, const int mode)
     }
 }
 
+/* Measured on B200 (profiles/README.md, r01 Maxwell sweep): the L2 bulk prefetch is worth +8-10 % at every degree;
+ * 2 CTAs per SM (128 registers: all loads of a face in flight at once) is best for bs >= 6, 4 CTAs for bs <= 3. */
+template <int K>
+struct mx_tune { static constexpr int MINB = K <= 1 ? 4 : 2; };
+
+static int mx_prefetch()
+{
+    static const int on = [] { const char *e = getenv("YFD_MX_PREFETCH"); return e ? atoi(e) : 1; }();
+    return on;
+}
+
 template <int NV, int K>
 static yfd_status launch_stage(yfd_ctx *ctx, int mode, const mx_step_args &a)
 {
     constexpr int BS = mx_bs(K), CPW = mx_cpw(BS);
     const size_t smem = (size_t) MX_WARPS * (1 + NV) * 3 * BS * CPW * sizeof(double);
     const unsigned grid = (unsigned) ceil_div(a.nchunks, MX_WARPS);
-    YFD_LAUNCH(ctx, (maxwell_stage<NV, K>), grid, MX_WARPS * 32, smem, a, mode);
+    YFD_LAUNCH(ctx, (maxwell_stage<NV, K, mx_tune<K>::MINB>), grid, MX_WARPS * 32, smem, a, mode, mx_prefetch());
     return YFD_OK;
 }
 
