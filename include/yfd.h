@@ -191,6 +191,7 @@ yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y);
 #define YFD_FN_ZERO    0   /* data::dirichlet (dg2d_diffusion.cpp:61-66)                  */
 #define YFD_FN_SINSIN  1   /* data::rhs = 2 pi^2 sin(pi x) sin(pi y) (dg2d_diffusion.cpp:53-59) */
 #define YFD_FN_ONE     2
+#define YFD_FN_SINSIN_SOL 3 /* data::diffusion_ref_sol = sin(pi x) sin(pi y) (dg2d_diffusion.cpp:68-76); post-processing only */
 
 typedef struct yfd_dg_config {
     int     degree;             /* cfg.degree, k >= 0; basis size (k+2)(k+1)/2 (core/bases.hpp:63-74) */
@@ -224,6 +225,17 @@ yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config
  * all indexed by REFERENCE cell id.  Any output may be NULL. */
 yfd_status yfd_dg_local_blocks(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
                                double *K, double *Att, double *Atn, double *rhs);
+
+/* Post-processing of a DG solution (dg2d_diffusion.cpp:225-268): sol [ncells * bs] in REFERENCE numbering,
+ *   *l2_errsq_qp = sum_cells sum_q w (ref(x_q) - u_h(x_q))^2          status.L2_errsq_qp (:261-262)
+ *   *l2_errsq_mm = sum_cells (proj - u_c)^T M (proj - u_c)            status.L2_errsq_mm (:258-259,:265-266; the
+ *                  reference's solve_LU -> LAPACK is an in-kernel pivoted LU here)
+ * ref_fn: YFD_FN_SINSIN_SOL for the driver's manufactured solution.  Either output may be NULL.  The _device variant
+ * takes sol as a DEVICE pointer (e.g. the d_x of yfd_system_solve_cg_device). */
+yfd_status yfd_dg_postprocess(yfd_ctx *ctx, yfd_mesh *mesh, int degree, int ref_fn, const double *sol,
+                              double *l2_errsq_qp, double *l2_errsq_mm);
+yfd_status yfd_dg_postprocess_device(yfd_ctx *ctx, yfd_mesh *mesh, int degree, int ref_fn, const double *d_sol,
+                                     double *l2_errsq_qp, double *l2_errsq_mm);
 
 /* ---------------------------------------------------------------------------------- */
 /* Continuous P1 FEM: replaces cfem::stiffness_matrix / eval_basis_grad                 */

@@ -60,3 +60,28 @@ def test_batched_entry_from_cpp(ref, spec, t, r, k, pc):
     assert abs(sn - np.linalg.norm(o["sol"])) <= 1e-10 * np.linalg.norm(o["sol"])
     assert abs(rn - np.linalg.norm(o["rhs"])) <= 1e-12 * np.linalg.norm(o["rhs"])
     assert abs(it - o["iters"]) <= max(3, 0.05 * o["iters"])
+
+
+# ---- the reference's UNMODIFIED maxwell_driver.cpp against include/yaourt_b200/maxwell.hpp ----
+MX_EXE = os.path.join(ROOT, "oracle", "_ref", "dropin_maxwell")
+
+
+@pytest.mark.parametrize("name,extra", [("tri_r2_k2", []), ("quad_r2_k1_up", ["-u"]), ("tri_r3_k3_up", ["-u"])])
+def test_unmodified_maxwell_driver_on_gpu_writes_the_reference_error_log(name, extra, tmp_path):
+    """run_maxwell_solver as shipped (maxwell_driver.cpp:194-272): assemble(ctx) and do_timestep(ctx) bind to the GPU
+    overloads, everything else is the reference's own code; its error log must equal the log of the reference's own run."""
+    if not os.path.exists(MX_EXE):
+        pytest.skip("oracle/_ref/dropin_maxwell not built (needs /root/reference at build time)")
+    logs = golden("maxwell_driver_logs.npz")
+    t, r, k, up, dt, steps = logs[name + "_cfg"]
+    errfile = str(tmp_path / "err.txt")
+    res = subprocess.run([MX_EXE, "-m", "tri" if t == 0 else "quad", "-r", str(int(r)), "-k", str(int(k)), "-d", repr(float(dt)),
+                          "-t", str(int(steps)), "-E", errfile] + extra,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, cwd="/tmp")
+    assert res.returncode == 0, res.stdout[-2000:]
+    assert "[yaourt_b200] maxwell contexts on the GPU: 1" in res.stdout
+    rows = np.array([list(map(float, ln.split())) for ln in open(errfile) if ln.strip() and not ln.startswith("#")])
+    want = logs[name]
+    assert rows.shape == want.shape
+    assert np.array_equal(rows[:, 0], want[:, 0])
+    assert np.allclose(rows[:, 2:5], want[:, 2:5], rtol=2e-5, atol=0)          # 6 printed digits

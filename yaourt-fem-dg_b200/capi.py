@@ -23,7 +23,7 @@ _ROOT = os.path.dirname(_HERE)
 TRI, QUAD = 0, 1
 TI_RK4, TI_EULER = 0, 1
 FIELDS_CAVITY_11, FIELDS_ZERO = 0, 1
-FN_ZERO, FN_SINSIN, FN_ONE = 0, 1, 2
+FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL = 0, 1, 2, 3
 REORDER_NONE, REORDER_MORTON = 0, 1
 
 
@@ -169,6 +169,8 @@ def lib():
         "yfd_system_solve_cg_device": (cint, [vp, vp, cint, P(CgParams), vp, P(CgInfo)]),
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
+        "yfd_dg_postprocess": (cint, [vp, vp, cint, cint, _f64p, P(dbl), P(dbl)]),
+        "yfd_dg_postprocess_device": (cint, [vp, vp, cint, cint, vp, P(dbl), P(dbl)]),
         "yfd_maxwell_config_default": (None, [P(MaxwellConfig)]),
         "yfd_maxwell_create": (cint, [vp, vp, P(MaxwellConfig), vp, vp, P(vp), P(MaxwellInfo)]),
         "yfd_maxwell_destroy": (None, [vp]),
@@ -270,6 +272,16 @@ class Context:
         K = np.empty((nc, bs, bs)); Att = np.empty((nc, nf, bs, bs)); Atn = np.empty((nc, nf, bs, bs)); rhs = np.empty((nc, bs))
         self.check(lib().yfd_dg_local_blocks(self._h, mesh._h, C.byref(cfg), _ptr(K), _ptr(Att), _ptr(Atn), _ptr(rhs)))
         return K, Att, Atn, rhs
+
+    def dg_postprocess(self, mesh, degree, sol, ref_fn=FN_SINSIN_SOL, device_ptr=None):
+        """(L2_errsq_qp, L2_errsq_mm) of run_diffusion_solver's post-process (dg2d_diffusion.cpp:225-268)."""
+        qp, mm = C.c_double(), C.c_double()
+        if device_ptr is not None:
+            self.check(lib().yfd_dg_postprocess_device(self._h, mesh._h, degree, ref_fn, C.c_void_p(device_ptr), C.byref(qp), C.byref(mm)))
+        else:
+            sol = np.ascontiguousarray(sol, np.float64)
+            self.check(lib().yfd_dg_postprocess(self._h, mesh._h, degree, ref_fn, sol, C.byref(qp), C.byref(mm)))
+        return qp.value, mm.value
 
     def cfem_assemble_p1(self, mesh, rhs_fn=FN_SINSIN):
         h = C.c_void_p()
