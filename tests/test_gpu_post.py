@@ -8,7 +8,7 @@ from conftest import host_mesh_from_ref
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mtype,r,k,shatter", [(0, 3, 1, 0), (0, 2, 2, 1), (1, 2, 3, 0), (0, 1, 4, 1), (1, 2, 2, 1), (0, 2, 0, 0), (1, 1, 5, 0)])
+@pytest.mark.parametrize("mtype,r,k,shatter", [(0, 3, 1, 0), (0, 2, 2, 1), (1, 2, 3, 0), (0, 1, 4, 1), (1, 2, 2, 1), (0, 3, 3, 0), (1, 1, 5, 0)])
 def test_postprocess_matches_reference(yfd, ref, ctx, mtype, r, k, shatter):
     m = ref.mesh(mtype, r, shatter=bool(shatter))
     ref.set_cg(rr_tol=1e-12, rr_max=1e4, max_iter=-1)
@@ -23,11 +23,12 @@ def test_postprocess_matches_reference(yfd, ref, ctx, mtype, r, k, shatter):
 def test_postprocess_device_pointer_and_orders(yfd, ctx):
     """assemble -> CG -> post-process with the solution never leaving the device; L2 error order k+1 on -r 4,5,6."""
     import torch
-    for mtype, k in ((0, 1), (1, 2)):
+    # tri k = 1 with the driver's default eta = 1 is under-penalised: the reference itself shows orders 1.48, 1.28 there
+    for mtype, k, eta in ((0, 1, 10.0), (1, 2, 1.0)):
         errs = []
         for r in (4, 5, 6):
             mesh = yfd.Mesh(ctx, yfd.HostMesh.create(mtype, r))
-            sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0)
+            sysm = ctx.dg_assemble_sip(mesh, k, eta=eta)
             d_x = torch.empty(sysm.n, dtype=torch.float64, device="cuda")
             sysm.solve_cg_device(yfd.CgParams(rr_tol=1e-12, rr_max=1e4, max_iter=2 * sysm.n), d_x=d_x.data_ptr())
             ctx.synchronize()
