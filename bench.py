@@ -263,11 +263,31 @@ def run_maxwell(args, wl, rank, world, local_rank):
     import yaourt_fem_dg_b200 as yfd
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path is CUDA only (no CPU fallback)")
-    if world > 1:
-        raise SystemExit("the Maxwell time loop is not partitioned yet (DESIGN.md): run it with --gpus 1")
     torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torch.distributed.run --nproc-per-node %d" % (args.gpus, world, args.gpus))
     stream = torch.cuda.current_stream()
     ctx = yfd.Context(local_rank, stream=stream.cuda_stream)
+    if world > 1:
+        ids = [yfd.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.attach_comm(rank, world, ids[0])
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
     T = args.profile_iters or wl["timesteps"]
     hm = yfd.HostMesh.create(wl["cell"], wl["r"])            # mesher: input generation, untimed
     info = {}
@@ -287,7 +307,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
     for _ in range(args.warmup):
         one_pass(mesh).close()
     sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", ""))
-    torch.cuda.synchronize()
+    barrier()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = ctx.launches
@@ -295,10 +315,10 @@ def run_maxwell(args, wl, rank, world, local_rank):
     for _ in range(args.steps):
         one_pass(mesh).close()
     e1.record(stream)
-    torch.cuda.synchronize()
+    barrier()
     clocks = sampler.stop()
     launches = ctx.launches - l0
-    ms_step = e0.elapsed_time(e1) / args.steps
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     n = info["n"]
     value = n * T / (ms_step * 1e-3)
 
@@ -316,7 +336,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
     if os.path.exists(tpath):
         traffic = json.load(open(tpath)).get(args.workload)
     achieved = ref_bytes / (ms_apply * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "maxwell_stage (operator application, factored blocks)", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "maxwell_stage (operator application, factored blocks)%s" % ("" if world == 1 else ", rank 0's share of the cells"), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ref_bytes, "kernel_requested_bytes_per_launch": kern_bytes,
                 "kernel_requested_gbs": kern_bytes / (ms_apply * 1e-3) / 1e9, "ms_per_launch": ms_apply,
@@ -339,29 +359,29 @@ def run_maxwell(args, wl, rank, world, local_rank):
             m2.close()
         mesh.close()
         step_e2e()
-        torch.cuda.synchronize()
+        barrier()
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         f0.record(stream)
         for _ in range(args.steps):
             step_e2e()
         f1.record(stream)
-        torch.cuda.synchronize()
+        barrier()
         wall = (time.perf_counter() - t0) / args.steps
-        ms_e2e = f0.elapsed_time(f1) / args.steps
+        ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
         e2e = {"value": n * T / (ms_e2e * 1e-3), "unit": MAXWELL_UNIT, "h2d_bytes_per_step": int(sum(a.nbytes for a in arrs.values())),
                "d2h_bytes_per_step": int(x_host.nbytes), "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
                "path": "yfd_mesh_create -> yfd_maxwell_create -> apply_initial_condition -> timesteps -> report_errors -> get_dofs (host) through include/yfd.h"}
 
     base = None
-    if not args.no_cpu_baseline:
+    if rank == 0 and not args.no_cpu_baseline:
         R, cores = load_maxwell_reference()
         if R is not None:
             sres = maxwell_reference_step(R, wl, wl["base_r"])
             base = dict(value=sres["n"] * wl["timesteps"] / sres["t"], unit=MAXWELL_UNIT, cores=cores, kind="reference",
                         sample=maxwell_sample_text(wl, wl["base_r"], sres))
     line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else {}
-    line.update({"metric": MAXWELL_METRIC, "value": value, "unit": MAXWELL_UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+    line.update({"metric": MAXWELL_METRIC, "value": value, "unit": MAXWELL_UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                  "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                  "data": "synthetic",
                  "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(n), "cells": int(info["cells"]),
@@ -369,10 +389,14 @@ def run_maxwell(args, wl, rank, world, local_rank):
                             "l2_policy": "inputs larger than L2: the factored operator is %.1f GB vs 126 MB L2" % (1e-9 * info["operator_bytes"]),
                             "operator_bytes": int(info["operator_bytes"]), "reference_operator_bytes": int(info["reference_operator_bytes"]),
                             "phases_ms": {"assemble": info["ms_assemble"], "timesteps": info["ms_timesteps"]},
-                            "l2_errors_vs_analytic": info["errors"], "parallelism": "1 GPU"},
+                            "l2_errors_vs_analytic": info["errors"], "parallelism": "1 GPU" if world == 1 else "contiguous blocks of the Z-curve cell order over %d GPUs; one NCCL halo exchange "
+                                           "(3 bs doubles per cut-face cell) before each of the 4 operator applications of a timestep" % world},
                  "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
-    print(json.dumps(line))
+    if rank == 0:
+        print(json.dumps(line))
     ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
     return 0
 
 

@@ -55,6 +55,37 @@ for (t, r, k, pc) in ((0, 4, 1, False), (1, 3, 2, True), (0, 3, 3, False), (1, 4
     if rank == 0:
         print(line + (" | identical on all ranks" if same else " | RANKS DIFFER"), flush=True)
     sysm.close(); mesh.close()
+# ---- DG Maxwell: every rank advances its block, one halo exchange per operator application ----
+mref = refbind.RefMaxwell() if refbind.maxwell_available() else None
+for (t, r, k, up) in ((0, 3, 2, False), (1, 3, 3, True), (0, 2, 4, True), (0, 4, 1, False)):
+    dt, steps = 0.002, 10
+    mesh = yfd.Mesh(ctx, yfd.HostMesh.create(t, r))
+    mx = yfd.Maxwell(ctx, mesh, k, delta_t=dt, upwind=up)
+    mx.apply_initial_condition()
+    d0 = mx.dofs()
+    mx.timesteps(steps)
+    d = mx.dofs()
+    err = mx.report_errors((steps - 1) * dt)
+    line = "maxwell t=%d r=%d k=%d upwind=%d: %d unknowns, %d steps" % (t, r, k, up, mx.ndofs, steps)
+    if mref is not None and rank == 0:
+        mref.create(t, r, k, dt=dt, upwind=up)
+        mref.assemble(); mref.init()
+        e0 = np.linalg.norm(d0 - mref.dofs()) / np.linalg.norm(d0)
+        mref.step(steps)
+        want = mref.dofs()
+        e1 = np.linalg.norm(d - want) / np.linalg.norm(want)
+        e2 = np.abs(err - mref.errors(steps - 1)).max()
+        ok = e0 <= 1e-10 and e1 <= 1e-10 and e2 <= 1e-10
+        fails += 0 if ok else 1
+        line += " | vs reference: init %.1e dofs %.1e error norms %.1e %s" % (e0, e1, e2, "OK" if ok else "FAIL")
+    xs = torch.from_numpy(d).cuda()
+    lo, hi = xs.clone(), xs.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    same = bool(torch.equal(lo, hi))
+    fails += 0 if same else 1
+    if rank == 0:
+        print(line + (" | identical on all ranks" if same else " | RANKS DIFFER"), flush=True)
+    mx.close(); mesh.close()
 t = torch.tensor([fails], device="cuda")
 dist.all_reduce(t)
 if rank == 0:

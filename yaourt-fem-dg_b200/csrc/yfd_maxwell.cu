@@ -31,7 +31,8 @@ struct mx_asm_args {
     const int32_t *cells, *cell_faces;
     const int2    *faces, *face_owners;
     const int32_t *perm, *iperm;
-    int64_t        ncells;
+    int64_t        ncells;                /* cells assembled by this launch (the rank's own block) */
+    int64_t        cell_begin;            /* first of them in the internal order (0 on one GPU)     */
     const double  *cell_rule, *gx, *gw;
     const double  *mu_r, *eps_r;          /* reference cell order, or null = 1 */
     int            upwind;
@@ -82,7 +83,7 @@ maxwell_assemble(const mx_asm_args a)
 
     const int64_t nwarps = (int64_t) gridDim.x * S::WARPS;
     for (int64_t cell = (int64_t) blockIdx.x * S::WARPS + warp; cell < a.ncells; cell += nwarps) {
-        const int32_t rc = a.perm[cell];
+        const int32_t rc = a.perm[cell + a.cell_begin];
         double2 P[NV];
 #pragma unroll
         for (int v = 0; v < NV; v++) P[v] = __ldg(&a.pts[a.cells[(int64_t) NV * rc + v]]);
@@ -366,14 +367,23 @@ __global__ void maxwell_dense_operator(int64_t ncells, int nv, int bs, const dou
             for (int q = 0; q < 3; q++) ondiag[((size_t) rc * L + p * bs + i) * L + q * bs + j] = D[p][q];
 }
 
-/* internal <-> reference order of the unknowns: whole cells of 3bs doubles move */
-__global__ void maxwell_permute_dofs(int64_t ncells, int L, const int32_t *perm, const double *in, double *out, int to_ref)
+/* nbr_local[c][f] = g2l[nbr_global[c + cell_begin][f]] */
+__global__ void maxwell_localize_nbr(int64_t ncells, int64_t cell_begin, int nv, const int32_t *nbr_global, const int32_t *g2l, int32_t *out)
+{
+    const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ncells * nv) return;
+    const int32_t g = nbr_global[cell_begin * nv + t];
+    out[t] = g >= 0 ? g2l[g] : -1;
+}
+
+/* internal <-> reference order of the unknowns: whole cells of 3bs doubles move; this rank's own cells only */
+__global__ void maxwell_permute_dofs(int64_t ncells, int64_t cell_begin, int L, const int32_t *perm, const double *in, double *out, int to_ref)
 {
     const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ncells * L) return;
     const int64_t cell = t / L;
     const int k = (int) (t - cell * L);
-    const int64_t rc = perm[cell];
+    const int64_t rc = perm[cell + cell_begin];
     if (to_ref) out[rc * L + k] = in[t]; else out[t] = in[rc * L + k];
 }
 
@@ -483,12 +493,17 @@ mx_step_args step_args(yfd_maxwell *m)
     return s;
 }
 
+yfd_status exchange(yfd_maxwell *m, double *v)
+{
+    return m->plan ? halo_exchange(m->ctx, *m->plan, 3 * m->bs, v, m->sendbuf.p) : YFD_OK;
+}
+
 yfd_status permute_dofs(yfd_maxwell *m, const double *d_in, double *d_out, int to_ref)
 {
     const int L = 3 * m->bs;
     const int64_t n = m->ncells * L;
     if (n == 0) return YFD_OK;
-    YFD_LAUNCH(m->ctx, maxwell_permute_dofs, (unsigned) ceil_div(n, 256), 256, 0, m->ncells, L, m->perm.p, d_in, d_out, to_ref);
+    YFD_LAUNCH(m->ctx, maxwell_permute_dofs, (unsigned) ceil_div(n, 256), 256, 0, m->ncells, m->cell_begin, L, m->perm.p, d_in, d_out, to_ref);
     return YFD_OK;
 }
 
@@ -522,11 +537,20 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     m->degree = cfg->degree; m->bs = basis_size_2d(cfg->degree);
     m->upwind = cfg->upwind != 0; m->time_integrator = cfg->time_integrator;
     m->delta_t = cfg->delta_t; m->eta = cfg->eta;
-    m->ncells = mesh->ncells; m->ndofs = 3 * (int64_t) m->bs * m->ncells;
+    m->ncells_global = mesh->ncells; m->ncells = mesh->ncells; m->nlocal = mesh->ncells; m->cell_begin = 0;
+    m->ndofs = 3 * (int64_t) m->bs * m->ncells_global;
+    if (mesh->ncells >= 0x7fffffff / 4) return fail(ctx, YFD_ERR_UNSUPPORTED, "cell count exceeds 32-bit ids");
+    if (ctx->nranks > 1) {
+        /* every rank holds the replicated mesh and assembles / advances only its contiguous block of the internal
+         * cell order; each operator application is preceded by one halo exchange of its operand */
+        YFD_TRY(ensure_dist_plan(ctx, mesh));
+        m->plan = mesh->plan;
+        m->ncells = m->plan->nown; m->cell_begin = m->plan->cell_begin; m->nlocal = m->plan->nown + m->plan->nhalo;
+        if (m->ncells == 0) return fail(ctx, YFD_ERR_UNSUPPORTED, "fewer cells than ranks");
+    }
     const int bs = m->bs, nv = m->nv, cpw = mx_cpw(bs), rwp = mx_rwp(bs), nb = mx_nb(nv);
-    const int64_t nc = m->ncells;
+    const int64_t nc = m->ncells, ncg = m->ncells_global, L = 3 * bs;
     m->nchunks = ceil_div(nc, cpw);
-    if (nc >= 0x7fffffff / 4) return fail(ctx, YFD_ERR_UNSUPPORTED, "cell count exceeds 32-bit ids");
 
     quad_rule g;
     YFD_TRY(gauss_rule_for_degree(ctx, 2 * cfg->degree, &g));
@@ -535,12 +559,22 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     if (nv == 3 && t.n != dg_nq_cell(3, cfg->degree))
         return fail(ctx, YFD_ERR_INVALID_STATE, "internal: Dunavant rule size mismatch");
 
-    YFD_TRY(mesh_neighbours_device(ctx, mesh, m->nbr));
-    YFD_TRY(m->perm.alloc(ctx, (size_t) nc));
-    YFD_TRY(m->iperm.alloc(ctx, (size_t) nc));
-    if (nc) {
-        YFD_CUDA(ctx, cudaMemcpyAsync(m->perm.p, mesh->perm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        YFD_CUDA(ctx, cudaMemcpyAsync(m->iperm.p, mesh->iperm.p, (size_t) nc * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (m->plan) {
+        dbuf<int32_t> nbr_global;
+        YFD_TRY(mesh_neighbours_device(ctx, mesh, nbr_global));
+        YFD_TRY(m->nbr.alloc(ctx, (size_t) nc * nv));
+        YFD_LAUNCH(ctx, maxwell_localize_nbr, (unsigned) ceil_div(nc * nv, 256), 256, 0, nc, m->cell_begin, nv, nbr_global.p,
+                   m->plan->g2l.p, m->nbr.p);
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));          /* nbr_global goes out of scope */
+        YFD_TRY(m->sendbuf.alloc(ctx, (size_t) (m->plan->nsend * L)));
+    } else {
+        YFD_TRY(mesh_neighbours_device(ctx, mesh, m->nbr));
+    }
+    YFD_TRY(m->perm.alloc(ctx, (size_t) ncg));
+    YFD_TRY(m->iperm.alloc(ctx, (size_t) ncg));
+    if (ncg) {
+        YFD_CUDA(ctx, cudaMemcpyAsync(m->perm.p, mesh->perm.p, (size_t) ncg * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        YFD_CUDA(ctx, cudaMemcpyAsync(m->iperm.p, mesh->iperm.p, (size_t) ncg * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     }
     const size_t opn = (size_t) m->nchunks * nb * bs * rwp;
     YFD_TRY(m->op.alloc(ctx, opn, 32));
@@ -550,12 +584,15 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     YFD_TRY(m->gM.alloc(ctx, (size_t) nc * bs * bs));
     YFD_TRY(m->cell_pts.alloc(ctx, (size_t) nc * nv * 2));
     dbuf<double> *vecs[5] = {&m->u, &m->s1, &m->s2, &m->acc, &m->kb};
-    for (auto *v : vecs) { YFD_TRY(v->alloc(ctx, (size_t) m->ndofs)); YFD_TRY(v->zero(ctx)); }   /* reset(gDofs), :138-139 */
+    for (int v = 0; v < 5; v++) {                 /* reset(gDofs), :138-139 */
+        YFD_TRY(vecs[v]->alloc(ctx, (size_t) ((v < 3 ? m->nlocal : nc) * L)));
+        YFD_TRY(vecs[v]->zero(ctx));
+    }
 
     dbuf<double> d_mu, d_eps;
     if (mu_r) {
-        YFD_TRY(d_mu.alloc(ctx, (size_t) nc)); YFD_TRY(d_eps.alloc(ctx, (size_t) nc));
-        YFD_TRY(d_mu.upload(ctx, mu_r, (size_t) nc)); YFD_TRY(d_eps.upload(ctx, eps_r, (size_t) nc));
+        YFD_TRY(d_mu.alloc(ctx, (size_t) ncg)); YFD_TRY(d_eps.alloc(ctx, (size_t) ncg));
+        YFD_TRY(d_mu.upload(ctx, mu_r, (size_t) ncg)); YFD_TRY(d_eps.upload(ctx, eps_r, (size_t) ncg));
     }
     dbuf<int> derr;
     YFD_TRY(derr.alloc(ctx, 1));
@@ -564,7 +601,7 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     mx_asm_args a;
     a.pts = (const double2 *) mesh->points.p; a.cells = mesh->cells.p; a.cell_faces = mesh->cell_faces.p;
     a.faces = (const int2 *) mesh->faces.p; a.face_owners = (const int2 *) mesh->face_owners.p;
-    a.perm = mesh->perm.p; a.iperm = mesh->iperm.p; a.ncells = nc;
+    a.perm = mesh->perm.p; a.iperm = mesh->iperm.p; a.ncells = nc; a.cell_begin = m->cell_begin;
     a.cell_rule = t.cw; a.gx = g.x; a.gw = g.w;
     a.mu_r = mu_r ? d_mu.p : nullptr; a.eps_r = mu_r ? d_eps.p : nullptr;
     a.upwind = m->upwind; a.eta = cfg->eta;
@@ -594,10 +631,10 @@ void yfd_maxwell_get_info(const yfd_maxwell *m, yfd_maxwell_info *info)
 {
     if (!m || !info) return;
     const int bs = m->bs, L = 3 * bs;
-    info->ncells = m->ncells; info->basis_size = bs; info->faces_per_elem = m->nf; info->ndofs = m->ndofs;
+    info->ncells = m->ncells_global; info->basis_size = bs; info->faces_per_elem = m->nf; info->ndofs = m->ndofs;
     info->operator_bytes = (int64_t) (m->op.n * sizeof(double) + m->fc.n * sizeof(mx_face_coef) + m->cs.n * sizeof(double)
                                       + m->nbr.n * sizeof(int32_t));
-    info->reference_operator_bytes = (int64_t) (1 + m->nf) * L * L * 8 * m->ncells;
+    info->reference_operator_bytes = (int64_t) (1 + m->nf) * L * L * 8 * m->ncells_global;
     info->ms_assemble = m->ms_assemble;
 }
 
@@ -617,6 +654,7 @@ yfd_status yfd_maxwell_get_operator(yfd_maxwell *m, double *ondiag, double *offd
     scoped_device dev(ctx->device);
     const int bs = m->bs, nv = m->nv, L = 3 * bs;
     const int64_t nc = m->ncells;
+    if (m->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "yfd_maxwell_get_operator: a parity aid for one GPU (the operator is partitioned here)");
     if (nc == 0) return YFD_OK;
     if (ondiag || offdiag) {
         dbuf<double> d_on, d_off;
@@ -669,11 +707,14 @@ yfd_status yfd_maxwell_apply_initial_condition(yfd_maxwell *m, int fields, doubl
 yfd_status yfd_maxwell_get_dofs(yfd_maxwell *m, double *dofs)
 {
     if (!m || !dofs) return YFD_ERR_INVALID_ARGUMENT;
-    scoped_device dev(m->ctx->device);
+    yfd_ctx *ctx = m->ctx;
+    scoped_device dev(ctx->device);
     dbuf<double> tmp;
-    YFD_TRY(tmp.alloc(m->ctx, (size_t) m->ndofs));
+    YFD_TRY(tmp.alloc(ctx, (size_t) m->ndofs));
+    if (m->plan) YFD_TRY(tmp.zero(ctx));                           /* every rank contributes its own cells, then a sum */
     YFD_TRY(permute_dofs(m, m->u.p, tmp.p, 1));
-    return tmp.download(m->ctx, dofs, (size_t) m->ndofs);
+    if (m->plan) YFD_TRY(comm_allreduce_sum_f64(ctx, tmp.p, (size_t) m->ndofs));
+    return tmp.download(ctx, dofs, (size_t) m->ndofs);
 }
 
 yfd_status yfd_maxwell_set_dofs(yfd_maxwell *m, const double *dofs)
@@ -682,7 +723,7 @@ yfd_status yfd_maxwell_set_dofs(yfd_maxwell *m, const double *dofs)
     scoped_device dev(m->ctx->device);
     dbuf<double> tmp;
     YFD_TRY(tmp.alloc(m->ctx, (size_t) m->ndofs));
-    YFD_TRY(tmp.upload(m->ctx, dofs, (size_t) m->ndofs));
+    YFD_TRY(tmp.upload(m->ctx, dofs, (size_t) m->ndofs));          /* the full vector on every rank; each keeps its own cells */
     YFD_TRY(permute_dofs(m, tmp.p, m->u.p, 0));
     YFD_CUDA(m->ctx, cudaStreamSynchronize(m->ctx->stream));      /* the caller's buffer is free again */
     return YFD_OK;
@@ -699,8 +740,11 @@ yfd_status yfd_maxwell_apply_operator(yfd_maxwell *m, const double *v, double *v
     YFD_TRY(permute_dofs(m, tmp.p, m->s1.p, 0));
     mx_step_args s = step_args(m);
     s.vin = m->s1.p; s.out = m->s2.p;
+    if (m->plan) YFD_TRY(halo_exchange(ctx, *m->plan, 3 * m->bs, m->s1.p, m->sendbuf.p));
     YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+    if (m->plan) YFD_TRY(tmp.zero(ctx));
     YFD_TRY(permute_dofs(m, m->s2.p, tmp.p, 1));
+    if (m->plan) YFD_TRY(comm_allreduce_sum_f64(ctx, tmp.p, (size_t) m->ndofs));
     return tmp.download(ctx, v_next, (size_t) m->ndofs);
 }
 
@@ -715,14 +759,16 @@ yfd_status yfd_maxwell_timesteps(yfd_maxwell *m, int64_t nsteps, yfd_maxwell_ste
         mx_step_args s = step_args(m);
         if (m->time_integrator == YFD_TI_EULER) {                 /* :630-634 + swap (:672) */
             s.vin = m->u.p; s.out = m->s1.p;
+            YFD_TRY(exchange(m, m->u.p));
             YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_EULER, s));
             std::swap(m->u, m->s1);
             continue;
         }
-        s.vin = m->u.p;  s.out = m->s1.p; YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK1, s));   /* :643-645 */
-        s.vin = m->s1.p; s.out = m->s2.p; YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK2, s));   /* :646-648 */
-        s.vin = m->s2.p; s.out = m->s1.p; YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK3, s));   /* :649-651 */
-        s.vin = m->s1.p; s.out = nullptr; YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK4, s));   /* :652-656 */
+        /* distributed: the operand's halo cells are refreshed from their owners before every application */
+        s.vin = m->u.p;  s.out = m->s1.p; YFD_TRY(exchange(m, m->u.p));  YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK1, s));   /* :643-645 */
+        s.vin = m->s1.p; s.out = m->s2.p; YFD_TRY(exchange(m, m->s1.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK2, s));   /* :646-648 */
+        s.vin = m->s2.p; s.out = m->s1.p; YFD_TRY(exchange(m, m->s2.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK3, s));   /* :649-651 */
+        s.vin = m->s1.p; s.out = nullptr; YFD_TRY(exchange(m, m->s1.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_RK4, s));   /* :652-656 */
     }
     tm.stop(ctx->stream);
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -750,6 +796,7 @@ yfd_status yfd_maxwell_report_errors(yfd_maxwell *m, int fields, double t, doubl
     a.fields = fields; a.t = t; a.partial = partial.p;
     YFD_TRY(dispatch_cellwise(ctx, m->nv, m->degree, 1, a));
     YFD_LAUNCH(ctx, sum_columns_fixed, 1, 1024, 0, partial.p, m->ncells, 3, total.p);
+    if (m->plan) YFD_TRY(comm_allreduce_sum_f64(ctx, total.p, 3));
     double h[3];
     YFD_TRY(total.download(ctx, h, 3));
     for (int k = 0; k < 3; k++) errors[k] = std::sqrt(h[k]);      /* maxwell_driver.cpp:186-188 */
@@ -763,6 +810,7 @@ yfd_status yfd_maxwell_time_apply(yfd_maxwell *m, int reps, double *ms_per_apply
     scoped_device dev(ctx->device);
     mx_step_args s = step_args(m);
     s.vin = m->u.p; s.out = m->s2.p;
+    YFD_TRY(exchange(m, m->u.p));
     for (int w = 0; w < 3; w++) YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
     gpu_timer tm;
     tm.start(ctx->stream);

@@ -31,18 +31,22 @@ struct yfd_maxwell {
     int      cell_type = 0, nv = 3, nf = 3, degree = 1, bs = 3;
     int      upwind = 0, time_integrator = 0;
     double   delta_t = 0.1, eta = 1.0;
-    int64_t  ncells = 0, ndofs = 0, nchunks = 0;
+    int64_t  ncells = 0, ndofs = 0, nchunks = 0;   /* cells whose rows this rank holds / GLOBAL unknowns / local chunks */
+    int64_t  ncells_global = 0, cell_begin = 0, nlocal = 0;   /* nlocal = owned + halo cells (vector length / 3bs) */
+    std::shared_ptr<yfd::dist_plan> plan;          /* null on one GPU */
+    yfd::dbuf<double>  sendbuf;                    /* packed boundary cells for the halo exchange */
     double   ms_assemble = 0;
     /* geometry kept for projection / error norms (the mesh handle may die first) */
     yfd::dbuf<double>  cell_pts;      /* [ncells][nv][2] internal order                                   */
-    yfd::dbuf<int32_t> perm, iperm;   /* internal <-> reference cell ids                                  */
-    yfd::dbuf<int32_t> nbr;           /* [ncells][nf] internal id of the cell across local face f, -1 none */
+    yfd::dbuf<int32_t> perm, iperm;   /* internal <-> reference cell ids (GLOBAL)                          */
+    yfd::dbuf<int32_t> nbr;           /* [ncells][nf] LOCAL index of the cell across local face f (owned: id - cell_begin,
+                                         halo: ncells + k), -1 none                                        */
     /* operator */
     yfd::dbuf<double>  op;            /* [nchunks][NB][bs][RWP]                                           */
     yfd::dbuf<yfd::mx_face_coef> fc;  /* [ncells][nf]                                                     */
     yfd::dbuf<double>  cs;            /* [ncells][2] = inv_mu, inv_eps                                    */
     yfd::dbuf<double>  gM;            /* [ncells][bs][bs] row-major, internal order                       */
-    /* state: gDofs and the RK work vectors, internal order, [ncells][3][bs] */
+    /* state: gDofs and the RK stage operands [nlocal][3][bs] (owned | halo), k1 / k2 [ncells][3][bs]; internal order */
     yfd::dbuf<double>  u, s1, s2, acc, kb;
 };
 
