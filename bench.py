@@ -333,7 +333,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
     achieved = ref_bytes / (ms_apply * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "maxwell_stage (operator application, factored blocks)%s" % ("" if world == 1 else ", rank 0's share of the cells"), "achieved": achieved, "peak": peak,
