@@ -78,12 +78,12 @@ class ClockSampler:
               "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_id):
-        self.gpu_id, self.rows, self.proc, self.thr = gpu_id, [], None, None
+        self.gpu_id, self.rows, self.proc, self.thr, self.t0 = gpu_id, [], None, None, None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_id), "--query-gpu=" + self.FIELDS,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -93,7 +93,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([c.strip() for c in line.split(",")] + [time.time()])
+
+    def mark(self):
+        """The timed region starts now: nvidia-smi was started earlier (before the warm-up) so that even a region of a
+        few hundred ms is sampled; only rows that arrive from here on count."""
+        self.t0 = time.time()
 
     def stop(self):
         if not self.proc:
@@ -106,7 +111,11 @@ class ClockSampler:
         self.thr.join(timeout=2)
         sm, smax, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = self.rows
+        if self.t0 is not None:
+            inside = [r for r in rows if r[-1] >= self.t0]
+            rows = inside if inside else rows[-1:]          # region shorter than one period: the sample nearest to it
+        for r in rows:
             if len(r) < 7:
                 continue
             try:
@@ -304,11 +313,12 @@ def run_maxwell(args, wl, rank, world, local_rank):
         return mx
 
     mesh = yfd.Mesh(ctx, hm)
+    sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", ""))
+    sampler.start()                                     # nvidia-smi is up before the warm-up; rows count from mark()
     for _ in range(args.warmup):
         one_pass(mesh).close()
-    sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", ""))
     barrier()
-    sampler.start()
+    sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = ctx.launches
     e0.record(stream)
@@ -491,12 +501,13 @@ def main():
         info.update(sysm.local_sizes())
         return sysm
 
-    for _ in range(args.warmup):
-        step_resident().close()
     gpu_uuid = "GPU-" + str(torch.cuda.get_device_properties(local_rank).uuid).replace("GPU-", "")
     sampler = ClockSampler(gpu_uuid)
+    sampler.start()                                     # nvidia-smi is up before the warm-up; rows count from mark()
+    for _ in range(args.warmup):
+        step_resident().close()
     barrier()
-    sampler.start()
+    sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = ctx.launches
     e0.record(stream)
