@@ -191,6 +191,8 @@ yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y);
 #define YFD_FN_ZERO    0   /* data::dirichlet (dg2d_diffusion.cpp:61-66)                  */
 #define YFD_FN_SINSIN  1   /* data::rhs = 2 pi^2 sin(pi x) sin(pi y) (dg2d_diffusion.cpp:53-59) */
 #define YFD_FN_ONE     2
+#define YFD_FN_ADVECTION_RHS 4 /* data::rhs of dg2d_advection.cpp:62-73: beta . grad u + mu u with u = sin(pi x), beta = (1,0), mu = 1 */
+#define YFD_FN_SIN_X_SOL 5   /* data::advection_ref_sol = sin(pi x) (dg2d_advection.cpp:75-80); post-processing only */
 #define YFD_FN_SINSIN_SOL 3 /* data::diffusion_ref_sol = sin(pi x) sin(pi y) (dg2d_diffusion.cpp:68-76); post-processing only */
 
 typedef struct yfd_dg_config {
@@ -216,6 +218,13 @@ typedef struct yfd_assembly_info {
  * entry points then exchange halos and reduce scalars over NCCL.  system_size stays the global size. */
 yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg,
                                yfd_system **out, yfd_assembly_info *info);
+
+/* Advection-reaction (dg2d_advection.cpp:137-213: K = int mu phi phi^T + phi (beta . grad phi)^T, face terms with
+ * fi_coeff = beta.n [- eta |beta.n| with use_upwinding], inflow boundary term; beta = (1,0), mu = 1 as params:: there).
+ * cfg->eta is used unscaled (:133), cfg->rhs_fn should be YFD_FN_ADVECTION_RHS, dirichlet_fn is ignored.  The system is
+ * NOT symmetric: solve it as the driver does, yfd_cg_params.use_normal_eqns = 1 (:225).  One GPU. */
+yfd_status yfd_dg_assemble_advection(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, int use_upwinding,
+                                     yfd_system **out, yfd_assembly_info *info);
 
 /* Per-cell local blocks BEFORE the scatter, for unit-level parity with the reference loop:
  *   K   [ncells][bs][bs]      cell stiffness            (dg2d_diffusion.cpp:141-149)
@@ -271,7 +280,7 @@ typedef struct yfd_cg_params {            /* conjugated_gradient_params<T> (core
     double  rr_max;                       /* 20    */
     int64_t max_iter;                     /* 100   */
     int     use_initial_guess;            /* false */
-    int     use_normal_eqns;              /* false; true -> YFD_ERR_UNSUPPORTED */
+    int     use_normal_eqns;              /* false; true: CG on A^T A x = A^T b (core/solvers.hpp:88-91,112-113), x0 = 0, one GPU */
     int     save_iteration_history;       /* false */
     int     check_every;                  /* extension: iterations per device-side batch between
                                              host polls of the stop flag (0 = default 64).  The

@@ -46,6 +46,9 @@ class Oracle:
         L.yfo_cfem_p1.restype = i64
         L.yfo_mesher.argtypes = [cint, cint, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), vp, vp, vp, vp]
         _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+        L.yfo_set_physics.argtypes = [cint, cint]
+        L.yfo_cg_normal.argtypes = [i64, _i64p, _i64p, _f64p, _f64p, _f64p, dbl, dbl, i64, vp, i64]
+        L.yfo_cg_normal.restype = i64
         L.yfo_maxwell_assemble.argtypes = [cint, _f64p, i64, _i64p, i64, _i64p, _i64p, _i64p, cint, cint, dbl, vp, vp,
                                            _f64p, _f64p, _i64p, _i32p, _f64p]
         L.yfo_maxwell_init.argtypes = [cint, _f64p, i64, _i64p, cint, _f64p, _f64p]
@@ -209,3 +212,19 @@ class Oracle:
         out = np.empty(3)
         self.lib.yfo_maxwell_errors(nv, points, nc, cells, k, _c(dofs, np.float64), t, out)
         return out
+
+    # ---- advection-reaction (dg2d_advection.cpp) ----
+    def advection(self, cell_type, points, cells, faces, k, eta=1.0, upwinding=False):
+        """The advection driver's cell loop + finalize: same shapes as dg_sip()."""
+        self.lib.yfo_set_physics(1, int(upwinding))
+        try:
+            return self.dg_sip(cell_type, points, cells, faces, k, eta=eta, rhs_fn=4, dir_fn=0)
+        finally:
+            self.lib.yfo_set_physics(0, 0)
+
+    def cg_normal(self, rowptr, colidx, values, b, rr_tol=1e-8, rr_max=1e4, max_iter=100):
+        n = len(b)
+        x = np.zeros(n); hist = np.empty(max_iter + 2)
+        it = self.lib.yfo_cg_normal(n, _c(rowptr, np.int64), _c(colidx, np.int64), _c(values, np.float64), _c(b, np.float64), x,
+                                    rr_tol, rr_max, max_iter, hist.ctypes.data_as(C.c_void_p), len(hist))
+        return dict(x=x, iterations=it, history=hist[:it + 1])

@@ -35,15 +35,27 @@
 #define YFD_CG_NAME yfd_dg_cg
 YFD_DECLARE_CG_HOOKS(yfd_dg_cg)
 
+/* -DYFD_REF_ADVECTION builds the same harness around dg2d_advection.cpp instead (libyfd_ref_adv.so): the two drivers
+ * define the same global names (params::, data::rhs, dg_config, solver_status), so they cannot share a library. */
 #define conjugated_gradient yfd_dg_cg
+#ifdef YFD_REF_ADVECTION
+#define main yfd_ref_dg2d_advection_main
+#include "dg2d_advection.cpp"
+#else
 #define main yfd_ref_dg2d_diffusion_main
 #include "dg2d_diffusion.cpp"
+#endif
 #undef main
 #undef conjugated_gradient
 
 #include "ref_cg_hooks.inl"
 
+#ifdef YFD_REF_ADVECTION
+extern "C" int yfd_ref_cfem_driver(int) { return 1; }            /* not in this library */
+static int yfd_adv_upwinding = 0;
+#else
 extern "C" int yfd_ref_cfem_driver(int levels);   /* ref_harness_cfem.cpp */
+#endif
 
 /* ======================================================================= */
 /*                                C ABI                                    */
@@ -119,7 +131,12 @@ static void run_dg_on(Mesh& msh, int degree, double eta, int use_pc)
     cfg.use_preconditioner = use_pc != 0;
     G.ift_calls = 0;
     G.t_enter = now_s();
+#ifdef YFD_REF_ADVECTION
+    cfg.use_upwinding = yfd_adv_upwinding != 0;
+    auto st = run_advection_reaction_solver(msh, cfg);     /* dg2d_advection.cpp:120, unmodified */
+#else
     auto st = run_diffusion_solver(msh, cfg);     /* dg2d_diffusion.cpp:114, unmodified */
+#endif
     G.l2_qp = std::sqrt(st.L2_errsq_qp);
     G.l2_mm = std::sqrt(st.L2_errsq_mm);
     G.mesh_h = st.mesh_h;
@@ -160,6 +177,9 @@ void yfd_ref_set_cg(double rr_tol, double rr_max, long max_iter, int skip_solve)
     yfd_ref::G.max_iter = max_iter; yfd_ref::G.skip_solve = skip_solve != 0;
 }
 void yfd_ref_keep_raw_triplets(int on) { yfd_ref::G.keep_raw_triplets = on != 0; }
+#ifdef YFD_REF_ADVECTION
+void yfd_ref_set_upwinding(int on) { yfd_adv_upwinding = on; }          /* dg_config::use_upwinding, dg2d_advection.cpp:104 */
+#endif
 
 /* ---- run the unmodified DG-SIP driver body on the current mesh ---- */
 int yfd_ref_run_dg(int degree, double eta, int use_pc)

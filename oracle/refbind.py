@@ -18,19 +18,26 @@ _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 
 
-def lib_path(omp=False):
+def lib_path(omp=False, advection=False):
+    if advection:
+        return os.path.join(_HERE, "_ref", "libyfd_ref_adv.so")
     return os.path.join(_HERE, "_ref", "libyfd_ref_omp.so" if omp else "libyfd_ref.so")
 
 
-def available(omp=False):
-    return os.path.exists(lib_path(omp))
+def available(omp=False, advection=False):
+    return os.path.exists(lib_path(omp, advection))
 
 
 class Ref:
     """One loaded copy of the reference library (it keeps one mesh + one result)."""
 
-    def __init__(self, omp=False):
-        self.lib = L = C.CDLL(lib_path(omp))
+    def __init__(self, omp=False, advection=False):
+        """advection=True loads the same harness built around dg2d_advection.cpp (run_dg then runs
+        run_advection_reaction_solver, dg2d_advection.cpp:120; CG on the normal equations as that driver sets it)."""
+        self.lib = L = C.CDLL(lib_path(omp, advection))
+        self.advection = advection
+        if advection:
+            L.yfd_ref_set_upwinding.argtypes = [C.c_int]
         L.yfd_ref_mesh_create.argtypes = [C.c_int, C.c_int, C.c_int]
         L.yfd_ref_mesh_sizes.argtypes = [C.POINTER(C.c_int64)] * 4
         L.yfd_ref_mesh_copy.argtypes = [_f64p, _i64p, _i64p, _i32p, _i64p]
@@ -68,9 +75,11 @@ class Ref:
     def set_cg(self, rr_tol=1e-8, rr_max=1e4, max_iter=-1, skip_solve=False):
         self.lib.yfd_ref_set_cg(rr_tol, rr_max, max_iter, int(skip_solve))
 
-    def run_dg(self, degree, eta=1.0, use_pc=False, raw_triplets=False):
+    def run_dg(self, degree, eta=1.0, use_pc=False, raw_triplets=False, upwinding=False):
         """run_diffusion_solver (dg2d_diffusion.cpp:114) on the current mesh."""
         self.lib.yfd_ref_keep_raw_triplets(int(raw_triplets))
+        if self.advection:
+            self.lib.yfd_ref_set_upwinding(int(upwinding))
         rc = self.lib.yfd_ref_run_dg(degree, eta, int(use_pc))
         if rc != 0:
             raise RuntimeError("reference DG driver failed")

@@ -23,7 +23,7 @@ _ROOT = os.path.dirname(_HERE)
 TRI, QUAD = 0, 1
 TI_RK4, TI_EULER = 0, 1
 FIELDS_CAVITY_11, FIELDS_ZERO = 0, 1
-FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL = 0, 1, 2, 3
+FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL, FN_ADVECTION_RHS, FN_SIN_X_SOL = 0, 1, 2, 3, 4, 5
 REORDER_NONE, REORDER_MORTON = 0, 1
 
 
@@ -156,6 +156,7 @@ def lib():
         "yfd_csr_spmv": (cint, [vp, vp, _f64p, _f64p]),
         "yfd_dg_assemble_sip": (cint, [vp, vp, P(DgConfig), P(vp), P(AssemblyInfo)]),
         "yfd_dg_local_blocks": (cint, [vp, vp, P(DgConfig), vp, vp, vp, vp]),
+        "yfd_dg_assemble_advection": (cint, [vp, vp, P(DgConfig), cint, P(vp), P(AssemblyInfo)]),
         "yfd_cfem_assemble_p1": (cint, [vp, vp, cint, P(vp), P(AssemblyInfo)]),
         "yfd_cfem_expand": (cint, [vp, _f64p, _f64p]),
         "yfd_cfem_get_compress_map": (cint, [vp, _i64p]),
@@ -263,6 +264,14 @@ class Context:
         h = C.c_void_p()
         info = AssemblyInfo()
         self.check(lib().yfd_dg_assemble_sip(self._h, mesh._h, C.byref(cfg), C.byref(h), C.byref(info)))
+        return System(self, h, info)
+
+    def dg_assemble_advection(self, mesh, degree, eta=1.0, upwinding=False, build_pc=False):
+        """run_advection_reaction_solver's cell loop + finalize (dg2d_advection.cpp:137-215); solve with
+        CgParams(use_normal_eqns=1) as that driver does."""
+        cfg = DgConfig(degree, eta, FN_ADVECTION_RHS, FN_ZERO, int(build_pc))
+        h, info = C.c_void_p(), AssemblyInfo()
+        self.check(lib().yfd_dg_assemble_advection(self._h, mesh._h, C.byref(cfg), int(upwinding), C.byref(h), C.byref(info)))
         return System(self, h, info)
 
     def dg_local_blocks(self, mesh, degree, eta=1.0, rhs_fn=FN_SINSIN, dirichlet_fn=FN_ZERO):

@@ -205,6 +205,50 @@ __global__ void permute_blocks(const double *__restrict__ in, double *__restrict
 /* -------------------------------------------------------------------------------------------- */
 /* host side                                                                                    */
 /* -------------------------------------------------------------------------------------------- */
+/* ---- normal equations (core/solvers.hpp:88-91,112-113): d.y = d.A^T A d = |A d|^2 ------------------- */
+__global__ void __launch_bounds__(CG_THREADS)
+cg_dot_self(const double *__restrict__ t, int64_t n, cg_scalars *__restrict__ sc, double *__restrict__ partials)
+{
+    if (sc->done) return;
+    double s = 0.0;
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) s += t[i] * t[i];
+    __shared__ double tot[1];
+    const double v[1] = { s };
+    if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) sc->dy = tot[0];
+}
+
+/* DG block rows: the blocks of A^T in the layout of A.  Block (c, slot s -> column cell nb) of A^T is the transpose
+ * of block (nb, slot s' -> column cell c) of A; the face-neighbour pattern is symmetric, so s' always exists. */
+__global__ void dg_transpose_blocks(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell,
+                                    const double *__restrict__ values, double *__restrict__ values_t, int64_t ncells, int bs)
+{
+    const int bs2 = bs * bs;
+    const int64_t nblocks = cellptr[ncells];
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < nblocks * bs2; t += stride) {
+        const int64_t blk = t / bs2;
+        const int m = (int) (t - blk * bs2), j = m / bs, i = m - j * bs;
+        /* which cell owns block `blk`: binary search in cellptr */
+        int64_t lo = 0, hi = ncells;
+        while (hi - lo > 1) { const int64_t mid = (lo + hi) >> 1; if (cellptr[mid] <= blk) lo = mid; else hi = mid; }
+        const int64_t c = lo, nb = blk_cell[blk];
+        int64_t sp = -1;
+        for (int64_t q = cellptr[nb]; q < cellptr[nb + 1]; q++) if (blk_cell[q] == c) { sp = q; break; }
+        /* A^T(c bs + i, nb bs + j) = A(nb bs + j, c bs + i) */
+        values_t[blk * bs2 + j * bs + i] = sp >= 0 ? values[sp * bs2 + i * bs + j] : 0.0;
+    }
+}
+
+/* generic CSR: (col, row) keys for the sort-based build of A^T */
+__global__ void csr_transpose_keys(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx, int64_t nrows,
+                                   int row_bits, uint64_t *__restrict__ keys)
+{
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; r < nrows; r += stride)
+        for (int64_t q = rowptr[r]; q < rowptr[r + 1]; q++) keys[q] = ((uint64_t) colidx[q] << row_bits) | (uint64_t) r;
+}
+
 struct spmv_op {
     /* generic */
     const int64_t *rowptr = nullptr; const int32_t *colidx = nullptr; const double *values = nullptr;
@@ -271,12 +315,20 @@ static unsigned vec_grid(yfd_ctx *ctx, int64_t n)
 
 /* The solver proper: all vectors on the device, in the operator's numbering. */
 static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, double *d_x, const double *d_pc,
-                            const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap)
+                            const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap,
+                            const spmv_op *opT = nullptr)
 {
     const int64_t n = op.nrows;
-    if (p->use_normal_eqns)
-        return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns (core/solvers.hpp:88-91) is not on the symmetric hot path");
-    dbuf<double> r, d, y, z, partials, hist;
+    const bool normal = p->use_normal_eqns != 0;
+    if (normal) {
+        /* CG on A^T A x = A^T b as the advection driver runs it (dg2d_advection.cpp:225): r0 = A^T b, y = A^T (A d).
+         * d.y is formed as |A d|^2 (equal in exact arithmetic, one reduction pass over A d instead of a fused one) */
+        if (!opT) return fail(ctx, YFD_ERR_INVALID_STATE, "internal: normal equations without the transposed operator");
+        if (op.plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a distributed system");
+        if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with use_initial_guess");
+        if (d_pc) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner (the reference's 5-argument overload ignores the flag, core/solvers.hpp:141-243)");
+    }
+    dbuf<double> r, d, y, z, partials, hist, t_ad, atb;
     dbuf<cg_scalars> sc;
     const dist_plan *pl = op.plan;
     const int64_t nhalo_dofs = pl ? pl->nhalo * op.bs : 0;
@@ -314,6 +366,11 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
     } else {
         YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
+        if (normal) {                                                                        /* r0 = A^T (b - A 0) (:88-89) */
+            YFD_TRY(t_ad.alloc(ctx, (size_t) n, 2)); YFD_TRY(atb.alloc(ctx, (size_t) n, 2));
+            YFD_TRY(launch_spmv<false>(ctx, *opT, d_b, atb.p, sc.p, partials.p));
+            d_b = atb.p;
+        }
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
@@ -321,7 +378,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
 
     /* YFD_CG_TRACE=1: time 200 iterations kernel by kernel with CUDA events (no graph) and print the averages; the
      * solve then continues normally.  A diagnostic for the multi-rank path, where ncu cannot be used. */
-    if (getenv("YFD_CG_TRACE") && p->max_iter > 200) {
+    if (getenv("YFD_CG_TRACE") && p->max_iter > 200 && !normal) {
         const int NT = 200, NK = 4;
         std::vector<cudaEvent_t> ev((size_t) NT * (NK + 1));
         for (auto &e : ev) cudaEventCreate(&e);
@@ -359,7 +416,15 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     yfd_status cap_st = YFD_OK;
     for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
         if (pl) { cap_st = peer ? halo_put_launch(ctx, *pl, op.bs, dv, sc.p) : halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p); if (cap_st != YFD_OK) break; }
-        cap_st = launch_spmv<true>(ctx, op, dv, y.p, sc.p, partials.p);
+        if (normal) {                                   /* y = trans(A)*A*d (core/solvers.hpp:112-113) */
+            cap_st = launch_spmv<false>(ctx, op, dv, t_ad.p, sc.p, partials.p);
+            if (cap_st != YFD_OK) break;
+            cg_dot_self<<<vg, CG_THREADS, 0, ctx->stream>>>(t_ad.p, n, sc.p, partials.p);
+            ctx->launches += 1;
+            cap_st = launch_spmv<false>(ctx, *opT, t_ad.p, y.p, sc.p, partials.p);
+        } else {
+            cap_st = launch_spmv<true>(ctx, op, dv, y.p, sc.p, partials.p);
+        }
         if (cap_st != YFD_OK) break;
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
         cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p);
@@ -479,6 +544,20 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
     YFD_TRY(db.upload(ctx, b, (size_t) n));
     if (p->use_initial_guess) YFD_TRY(dx.upload(ctx, x, (size_t) n));
     if (pc_diag) { YFD_TRY(dpc.alloc(ctx, (size_t) n, 2)); YFD_TRY(dpc.upload(ctx, pc_diag, (size_t) n)); }
+    if (p->use_normal_eqns) {
+        /* A^T by the same sort-based build as init_from_triplets: keys (col, row), stable, values carried along */
+        yfd_csr AT;
+        AT.ctx = ctx;
+        dbuf<uint64_t> keys;
+        YFD_TRY(keys.alloc(ctx, (size_t) A->nnz));
+        const int rb = key_bits_for(A->nrows), cb = key_bits_for(A->ncols);
+        if (A->nnz) YFD_LAUNCH(ctx, csr_transpose_keys, stream_grid(ctx, A->nrows), 256, 0, A->rowptr.p, A->colidx.p, A->nrows, rb, keys.p);
+        YFD_TRY(csr_from_device_triplets(ctx, A->ncols, A->nrows, A->nnz, keys.p, rb, cb, A->values.p, &AT));
+        YFD_TRY(csr_prepare(ctx, &AT));
+        const spmv_op opT = op_of_csr(&AT);
+        YFD_TRY(cg_device(ctx, op_of_csr(A), db.p, dx.p, pc_diag ? dpc.p : nullptr, p, info, history, history_cap, &opT));
+        return dx.download(ctx, x, (size_t) n);
+    }
     YFD_TRY(cg_device(ctx, op_of_csr(A), db.p, dx.p, pc_diag ? dpc.p : nullptr, p, info, history, history_cap));
     return dx.download(ctx, x, (size_t) n);
 }
@@ -507,7 +586,20 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
             YFD_TRY(dx.upload(ctx, x_host, (size_t) n));
         }
     }
-    YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
+    spmv_op opT;
+    if (p->use_normal_eqns) {
+        if (!dg) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a CFEM system (symmetric): use yfd_cg_solve for a general CSR");
+        if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a distributed system");
+        if (sys->values_t.n == 0) {                /* built once, kept with the system */
+            YFD_TRY(sys->values_t.alloc(ctx, (size_t) sys->nnz, 4));
+            YFD_LAUNCH(ctx, dg_transpose_blocks, stream_grid(ctx, sys->nnz), 256, 0, sys->cellptr.p, sys->blk_cell.p, sys->A.values.p,
+                       sys->values_t.p, sys->ncells, sys->bs);
+        }
+        opT = op_of_system(sys, true);
+        opT.values = sys->values_t.p;
+    }
+    YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
+                      p->use_normal_eqns ? &opT : nullptr));
     const double *result = dx.p;
     if (dg) {
         /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */

@@ -52,6 +52,8 @@ struct dg_args {
     /* per-cell block sink (reference numbering), yfd_dg_local_blocks */
     double        *oK, *oAtt, *oAtn, *orhs;
     int            blocks_mode;
+    int            physics;               /* 0 = SIP diffusion, 1 = advection-reaction */
+    int            adv_upwind;            /* advection-reaction only: cfg.use_upwinding (dg2d_advection.cpp:104); eta is then cfg.eta itself */
 };
 
 __device__ __forceinline__ double eval_fn(int fn, double x, double y)
@@ -62,11 +64,19 @@ __device__ __forceinline__ double eval_fn(int fn, double x, double y)
         return 2.0 * M_PI * M_PI * sx * sy;         /* data::rhs, dg2d_diffusion.cpp:53-59 */
     }
     case YFD_FN_ONE: return 1.0;
+    case YFD_FN_ADVECTION_RHS:                      /* data::rhs = beta . grad u + mu u, u = sin(pi x) (dg2d_advection.cpp:62-73) */
+        return M_PI * cos(M_PI * x) + sin(M_PI * x);
     default: return 0.0;
     }
 }
 
-template <int NV, int K>
+/* advection-reaction coefficients of the reference driver: constants there too (params::mu, params::beta,
+ * dg2d_advection.cpp:41-57) */
+constexpr double ADV_MU = 1.0, ADV_BX = 1.0, ADV_BY = 0.0;
+
+/* ADV = false: SIP diffusion (dg2d_diffusion.cpp:133-201); ADV = true: advection-reaction (dg2d_advection.cpp:137-213),
+ * same tables, same sinks, different contractions */
+template <int NV, int K, bool ADV>
 __global__ void __launch_bounds__(DG_WARPS * 32)
 dg_sip_cells(const dg_args a)
 {
@@ -135,8 +145,12 @@ dg_sip_cells(const dg_args a)
             double s = 0.0;
             if (m < BS2) {
                 const int j = m / BS, i = m - j * BS;
-                for (int q = 0; q < NQ; q++)
-                    s += W[q] * (DX[i * NQ + q] * DX[j * NQ + q] + DY[i * NQ + q] * DY[j * NQ + q]);
+                for (int q = 0; q < NQ; q++) {
+                    if (ADV)        /* K += mu w phi phi^T + w phi (dphi beta)^T, dg2d_advection.cpp:151-154 */
+                        s += W[q] * PHI[i * NQ + q] * (ADV_MU * PHI[j * NQ + q] + ADV_BX * DX[j * NQ + q] + ADV_BY * DY[j * NQ + q]);
+                    else
+                        s += W[q] * (DX[i * NQ + q] * DX[j * NQ + q] + DY[i * NQ + q] * DY[j * NQ + q]);
+                }
             }
             accD[t] = s;
         }
@@ -209,6 +223,10 @@ dg_sip_cells(const dg_args a)
             __syncwarp();
 
             const double c = has_nb ? 0.5 : 1.0;         /* dg2d_diffusion.cpp:171-173 vs :186-188 */
+            /* advection-reaction flux coefficients (dg2d_advection.cpp:180-199) */
+            const double beta_nf = ADV_BX * nx + ADV_BY * ny;
+            const double fi_coeff = a.adv_upwind ? beta_nf - a.eta * fabs(beta_nf) : beta_nf;
+            const double att_c = has_nb ? -0.5 * fi_coeff : (beta_nf < 0.0 ? 0.5 * (fabs(beta_nf) - beta_nf) : 0.0);
             const int slot = a.blocks_mode ? -1 : (int) a.slots[cell * (NV + 1) + 1 + e];
 #pragma unroll
             for (int t = 0; t < NACC; t++) {
@@ -219,11 +237,16 @@ dg_sip_cells(const dg_args a)
                     for (int q = 0; q < NFQ; q++) {
                         const double w = FW[q];
                         const double ti = TPHI[i * NFQ + q], tj = TPHI[j * NFQ + q];
-                        const double gi = TGN[i * NFQ + q], gj = TGN[j * NFQ + q];
-                        att += w * (eta_l * ti * tj - c * ti * gj - c * gi * tj);
-                        if (has_nb) {
-                            const double pj = NPHI[j * NFQ + q], hj = NGN[j * NFQ + q];
-                            atn += w * (-eta_l * ti * pj - 0.5 * ti * hj + 0.5 * gi * pj);    /* :178-180 */
+                        if (ADV) {
+                            att += w * att_c * ti * tj;
+                            if (has_nb) atn += w * fi_coeff * 0.5 * ti * NPHI[j * NFQ + q];      /* dg2d_advection.cpp:206 */
+                        } else {
+                            const double gi = TGN[i * NFQ + q], gj = TGN[j * NFQ + q];
+                            att += w * (eta_l * ti * tj - c * ti * gj - c * gi * tj);
+                            if (has_nb) {
+                                const double pj = NPHI[j * NFQ + q], hj = NGN[j * NFQ + q];
+                                atn += w * (-eta_l * ti * pj - 0.5 * ti * hj + 0.5 * gi * pj);    /* :178-180 */
+                            }
                         }
                     }
                     accD[t] += att;
@@ -236,7 +259,7 @@ dg_sip_cells(const dg_args a)
                     }
                 }
             }
-            if (!has_nb && lane < BS) {
+            if (!ADV && !has_nb && lane < BS) {
                 /* loc_rhs -= w g (grad phi . n) ; loc_rhs += w eta_l g phi   (:190-191) */
                 for (int q = 0; q < NFQ; q++)
                     rhs_i += FG[q] * (eta_l * TPHI[lane * NFQ + q] - TGN[lane * NFQ + q]);
@@ -329,7 +352,7 @@ __global__ void dg_fill_blocks(const dg_args a, int32_t *__restrict__ blk_cell, 
     for (int s = 0; s < NV + 1; s++) slots_out[cell * (NV + 1) + s] = slots[s];
 }
 
-template <int NV, int K>
+template <int NV, int K, bool ADV>
 static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
 {
     constexpr int BS = (K + 2) * (K + 1) / 2;
@@ -340,27 +363,35 @@ static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
     constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
     const size_t smem = (size_t) DG_WARPS * WARP_DBL * sizeof(double);
     if (smem > 48 * 1024)
-        YFD_CUDA(ctx, cudaFuncSetAttribute(dg_sip_cells<NV, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        YFD_CUDA(ctx, cudaFuncSetAttribute(dg_sip_cells<NV, K, ADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const int64_t want = ceil_div(a.ncells, DG_WARPS);
     const int64_t cap = (int64_t) ctx->sm_count * 32;        /* grid-stride beyond 32 CTAs per SM */
     const unsigned grid = (unsigned) (want < cap ? (want > 0 ? want : 1) : cap);
-    YFD_LAUNCH(ctx, (dg_sip_cells<NV, K>), grid, DG_WARPS * 32, smem, a);
+    YFD_LAUNCH(ctx, (dg_sip_cells<NV, K, ADV>), grid, DG_WARPS * 32, smem, a);
     return YFD_OK;
+}
+
+template <int NV, bool ADV>
+static yfd_status dispatch_cells_phys(yfd_ctx *ctx, int degree, const dg_args &a)
+{
+    switch (degree) {
+    case 0: return launch_cells<NV, 0, ADV>(ctx, a);
+    case 1: return launch_cells<NV, 1, ADV>(ctx, a);
+    case 2: return launch_cells<NV, 2, ADV>(ctx, a);
+    case 3: return launch_cells<NV, 3, ADV>(ctx, a);
+    case 4: return launch_cells<NV, 4, ADV>(ctx, a);
+    case 5: return launch_cells<NV, 5, ADV>(ctx, a);
+    case 6: return launch_cells<NV, 6, ADV>(ctx, a);
+    }
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "DG degree %d: the element kernel is instantiated for 0..%d", degree, DG_MAX_DEGREE);
 }
 
 template <int NV>
 static yfd_status dispatch_cells(yfd_ctx *ctx, int degree, const dg_args &a)
 {
-    switch (degree) {
-    case 0: return launch_cells<NV, 0>(ctx, a);
-    case 1: return launch_cells<NV, 1>(ctx, a);
-    case 2: return launch_cells<NV, 2>(ctx, a);
-    case 3: return launch_cells<NV, 3>(ctx, a);
-    case 4: return launch_cells<NV, 4>(ctx, a);
-    case 5: return launch_cells<NV, 5>(ctx, a);
-    case 6: return launch_cells<NV, 6>(ctx, a);
-    }
-    return fail(ctx, YFD_ERR_UNSUPPORTED, "DG degree %d: the element kernel is instantiated for 0..%d", degree, DG_MAX_DEGREE);
+    if (a.physics == 1) return dispatch_cells_phys<NV, true>(ctx, degree, a);
+    if (a.physics == 0) return dispatch_cells_phys<NV, false>(ctx, degree, a);
+    return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "unknown physics %d", a.physics);
 }
 
 static yfd_status fill_common_args(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, dg_args &a)
@@ -392,6 +423,7 @@ static yfd_status fill_common_args(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_co
     a.cellptr = nullptr; a.slots = nullptr; a.values = a.rhs = a.pc = nullptr;
     a.oK = a.oAtt = a.oAtn = a.orhs = nullptr;
     a.blocks_mode = 0;
+    a.physics = 0; a.adv_upwind = 0;
     return YFD_OK;
 }
 
@@ -469,7 +501,22 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
 
 extern "C" {
 
+static yfd_status dg_assemble(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, int physics, int upwinding,
+                              yfd_system **out, yfd_assembly_info *info);
+
 yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, yfd_system **out, yfd_assembly_info *info)
+{
+    return dg_assemble(ctx, mesh, cfg, 0, 0, out, info);
+}
+
+yfd_status yfd_dg_assemble_advection(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, int use_upwinding,
+                                     yfd_system **out, yfd_assembly_info *info)
+{
+    return dg_assemble(ctx, mesh, cfg, 1, use_upwinding, out, info);
+}
+
+static yfd_status dg_assemble(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config *cfg, int physics, int upwinding,
+                              yfd_system **out, yfd_assembly_info *info)
 {
     if (!ctx || !mesh || !cfg || !out) return YFD_ERR_INVALID_ARGUMENT;
     *out = nullptr;
@@ -478,12 +525,15 @@ yfd_status yfd_dg_assemble_sip(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_config
     scoped_device dev(ctx->device);
     dg_args a;
     YFD_TRY(fill_common_args(ctx, mesh, cfg, a));
+    a.physics = physics;
+    if (physics == 1) { a.eta = cfg->eta; a.adv_upwind = upwinding != 0; }       /* eta unscaled: dg2d_advection.cpp:133,187 */
     const int bs = basis_size_2d(cfg->degree);
     const int64_t n = mesh->ncells * bs;
     if (n >= 0x7fffffff) return fail(ctx, YFD_ERR_UNSUPPORTED, "system size %lld exceeds 32-bit column indices", (long long) n);
 
     yfd_system *sys = new yfd_system();
     sys->ctx = ctx; sys->kind = YFD_SYS_DG; sys->bs = bs; sys->nf = mesh->nv; sys->n = n;
+    sys->symmetric = physics == 0;
     sys->ncells_global = mesh->ncells; sys->ncells = mesh->ncells; sys->n_local = n;
     if (ctx->nranks > 1) {
         const yfd_status ps = ensure_dist_plan(ctx, mesh);

@@ -35,6 +35,7 @@ __device__ __forceinline__ double post_ref_fn(int fn, double x, double y)
     switch (fn) {
     case YFD_FN_SINSIN_SOL: return sin(M_PI * x) * sin(M_PI * y);        /* data::diffusion_ref_sol, dg2d_diffusion.cpp:68-76 */
     case YFD_FN_SINSIN:     return 2.0 * M_PI * M_PI * sin(M_PI * x) * sin(M_PI * y);
+    case YFD_FN_SIN_X_SOL:  return sin(M_PI * x);                        /* data::advection_ref_sol, dg2d_advection.cpp:75-80 */
     case YFD_FN_ONE:        return 1.0;
     default:                return 0.0;
     }
