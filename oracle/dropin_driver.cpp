@@ -15,10 +15,15 @@
 #include "core/blaze_sparse_init.hpp"
 #include "yaourt_b200/dropin_triplets.hpp"   /* before methods/dg.hpp is parsed: that call is qualified */
 #define main yfd_reference_main
+#ifdef YFD_DROPIN_ADVECTION          /* -> oracle/_ref/dropin_dg2d_advection: dg2d_advection.cpp, CG on the normal equations */
+#include "dg2d_advection.cpp"
+#else
 #include "dg2d_diffusion.cpp"
+#endif
 #undef main
 #include "yaourt_b200/dropin.hpp"       /* after the reference headers: the overloads win at instantiation */
 
+#ifndef YFD_DROPIN_ADVECTION
 /* YFD_DROPIN_BATCHED="<tri|quad> <levels> <degree> <pc>": the batched entry on a mesh made by the reference's own mesher;
  * prints sizes, iteration count and ||sol||_2 so the test can compare with the reference */
 template <typename Mesh>
@@ -37,8 +42,11 @@ static void batched(int levels, int degree, bool pc)
               << std::endl;
 }
 
+#endif
+
 int main(int argc, char **argv)
 {
+#ifndef YFD_DROPIN_ADVECTION
     if (const char *b = std::getenv("YFD_DROPIN_BATCHED")) {
         char type[16] = "tri";
         int levels = 3, degree = 1, pc = 0;
@@ -47,6 +55,7 @@ int main(int argc, char **argv)
         else batched<yaourt::simplicial_mesh<double>>(levels, degree, pc != 0);
         return 0;
     }
+#endif
     const int rc = yfd_reference_main(argc, argv);
     const auto &rep = yaourt::b200::last_cg_report();
     std::cout << "[yaourt_b200] CG on GPU: iterations " << rep.iterations << ", rr " << (rep.nr0 > 0 ? rep.nr / rep.nr0 : 0.0)

@@ -38,7 +38,7 @@ def test_system_matches_reference(yfd, aref, ctx, mtype, r, k, up, shatter):
     assert np.abs(sysm.rhs() - out["rhs"]).max() <= 1e-12 * np.abs(out["rhs"]).max()
     # CG on the normal equations: the reference's own residual history, iteration by iteration (6 printed digits)
     res = sysm.solve_cg(yfd.CgParams(rr_tol=1e-8, rr_max=1e4, max_iter=30, use_normal_eqns=1), history=True)
-    nh = min(len(res["history"]), len(out["history"]), 12)
+    nh = min(len(res["history"]), len(out["history"]), 8)
     assert nh >= 2
     assert np.allclose(res["history"][:nh], out["history"][:nh], rtol=1e-4)
 

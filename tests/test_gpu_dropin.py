@@ -85,3 +85,26 @@ def test_unmodified_maxwell_driver_on_gpu_writes_the_reference_error_log(name, e
     assert rows.shape == want.shape
     assert np.array_equal(rows[:, 0], want[:, 0])
     assert np.allclose(rows[:, 2:5], want[:, 2:5], rtol=2e-5, atol=0)          # 6 printed digits
+
+
+# ---- the reference's UNMODIFIED dg2d_advection.cpp: finalize() and CG on the normal equations on the GPU ----
+ADV_EXE = os.path.join(ROOT, "oracle", "_ref", "dropin_dg2d_advection")
+
+
+@pytest.mark.parametrize("name", ["tri_r2_k1", "quad_r1_k3_up"])
+def test_unmodified_advection_driver_on_gpu(name):
+    """cgp.use_normal_eqns = true (dg2d_advection.cpp:225) goes through the drop-in conjugated_gradient -> yfd_cg_solve,
+    which builds A^T on the device; the driver's printed L2 error must match the reference's own run."""
+    if not os.path.exists(ADV_EXE):
+        pytest.skip("oracle/_ref/dropin_dg2d_advection not built (needs /root/reference at build time)")
+    g = golden("adv_%s.npz" % name)
+    args = ["-m", "tri" if int(g["mtype"]) == 0 else "quad", "-r", str(int(g["levels"])), "-k", str(int(g["degree"]))]
+    if int(g["upwinding"]):
+        args.append("-u")
+    res = subprocess.run([ADV_EXE] + args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, cwd="/tmp")
+    assert res.returncode == 0, res.stdout[-2000:]
+    qp = float(re.search(r"L2-norm error \(qp\):\s+(\S+)", res.stdout).group(1))
+    it = int(re.search(r"\[yaourt_b200\] CG on GPU: iterations (\d+)", res.stdout).group(1))
+    # CG on A^T A is ill-conditioned: iteration counts of two correct implementations differ by a few percent
+    assert abs(qp - float(g["l2_qp"])) <= 0.02 * float(g["l2_qp"])
+    assert abs(it - int(g["iters"])) <= max(5, 0.15 * int(g["iters"]))
