@@ -35,6 +35,14 @@ import numpy as np
 # name -> (cell type, refinement, degree, use_pc, rr_tol, cpu sample refinement for one reference step,
 #          cpu sample refinement for the in-run cpu_baseline)
 WORKLOADS = {
+    # BASELINE.json configs[2] at its stated size: "DG diffusion on quadrilaterals degree 3, ~20M dofs".  The reference mesher
+    # only offers 10.49M (-r 9) or 41.9M (-r 10) dofs, so the mesh is the nx x nx structured one (yfd_mesher_create_structured,
+    # same conventions; the reference consumes it unchanged, tests/test_gpu_structured.py)
+    "dg_sip_quad_k3_20m": dict(cell=1, nx=1448, k=3, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
+                               desc="DG-SIP diffusion, quadrangles k=3, 1448 x 1448 structured: 2,096,704 cells, 20,967,040 dofs, nnz 1,047,772,800 (BASELINE configs[2], ~20M dofs)"),
+    # configs[0] as written: "64x64 structured triangle mesh, degree 1" = 2 * 64^2 triangles
+    "dg_sip_tri_k1_64x64": dict(cell=0, nx=64, k=1, pc=False, rr_tol=1e-8, ref_r=6, base_r=6,
+                                desc="DG-SIP diffusion, triangles k=1, 64 x 64 structured (8,192 cells, 24,576 dofs; BASELINE configs[0])"),
     # BASELINE.json configs[2]: "DG diffusion on quadrilaterals degree 3, ~20M dofs" -- the reference
     # mesher only offers 10.49M (r=9) or 41.9M (r=10) dofs (size table)
     "dg_sip_quad_k3_r9": dict(cell=1, r=9, k=3, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
@@ -62,7 +70,13 @@ WORKLOADS = {
     "maxwell_quad_k3_r9": dict(kind="maxwell", cell=1, r=9, k=3, upwind=False, dt=2e-5, timesteps=50, ref_r=5, base_r=6,
                                desc="DG Maxwell TM, quadrangles k=3, -r 9, centred fluxes, RK4: 1,048,576 cells, 31,457,280 unknowns"),
 }
-DEFAULT_WORKLOAD = "dg_sip_quad_k3_r9"
+DEFAULT_WORKLOAD = "dg_sip_quad_k3_20m"
+
+
+def make_host_mesh(yfd, wl):
+    if "nx" in wl:
+        return yfd.HostMesh.structured(wl["cell"], wl["nx"])
+    return yfd.HostMesh.create(wl["cell"], wl["r"])
 
 
 def bs_of(k):
@@ -298,7 +312,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
     T = args.profile_iters or wl["timesteps"]
-    hm = yfd.HostMesh.create(wl["cell"], wl["r"])            # mesher: input generation, untimed
+    hm = make_host_mesh(yfd, wl)                             # mesher: input generation, untimed
     info = {}
 
     def one_pass(mesh, x_host=None):
@@ -469,7 +483,7 @@ def main():
 
     def assemble(m):
         return ctx.cfem_assemble_p1(m) if cfem else ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"])
-    hm = yfd.HostMesh.create(wl["cell"], wl["r"])           # mesher: input generation, untimed
+    hm = make_host_mesh(yfd, wl)                            # mesher: input generation, untimed
     params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4),
                           max_iter=args.profile_iters or 2 * (len(hm.points) if wl.get("kind") == "cfem" else bs_of(wl["k"]) * len(hm.cells)))
 

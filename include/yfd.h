@@ -92,6 +92,11 @@ int         yfd_ctx_nranks(const yfd_ctx *ctx);
 typedef struct yfd_host_mesh yfd_host_mesh;
 
 yfd_status yfd_mesher_create(int cell_type, int refinement_levels, yfd_host_mesh **out);
+/* New (the reference mesher only offers 4^(r+1) cells): nx x ny structured mesh of the unit square in the reference's
+ * conventions -- cells (p00, p10, p11, p01) or the two triangles (p00, p10, p11), (p00, p11, p01), sorted cells and faces,
+ * boundary ids 0 bottom / 1 right / 2 top / 3 left.  The reference consumes such a mesh unchanged (its public
+ * points / faces / cells vectors, core/mesh.hpp:239-243), which is how parity on these meshes is checked. */
+yfd_status yfd_mesher_create_structured(int cell_type, int64_t nx, int64_t ny, yfd_host_mesh **out);
 void       yfd_host_mesh_destroy(yfd_host_mesh *m);
 void       yfd_host_mesh_sizes(const yfd_host_mesh *m, int64_t *npoints, int64_t *ncells,
                                int64_t *nfaces, int *verts_per_cell);

@@ -156,6 +156,44 @@ int yfd_ref_mesh_create(int type, int levels, int shatter)
     return 0;
 }
 
+/* Inject a mesh made elsewhere (e.g. yfd_mesher_create_structured) into the reference's own mesh type through its public
+ * vectors (core/mesh.hpp:239-243), with the reference's own element constructors; compute_connectivity is the reference's. */
+extern "C++" {
+template<typename Mesh, typename Cell>
+static void set_mesh(Mesh& msh, int64_t np, const double *pts, int64_t nc, const int64_t *cells, int64_t nf,
+                     const int64_t *faces, const uint8_t *fbnd, const int64_t *fbid)
+{
+    using point_type = typename Mesh::point_type;
+    using face_type = typename Mesh::face_type;
+    msh = Mesh();
+    for (int64_t i = 0; i < np; i++) msh.points.push_back(point_type(pts[2*i], pts[2*i+1]));
+    for (int64_t i = 0; i < nf; i++)
+        msh.faces.push_back(fbnd[i] ? face_type((size_t) faces[2*i], (size_t) faces[2*i+1], (size_t) (fbid ? fbid[i] : 0), true)
+                                    : face_type((size_t) faces[2*i], (size_t) faces[2*i+1]));
+    for (int64_t i = 0; i < nc; i++) {
+        Cell c;
+        for (size_t v = 0; v < c.p.size(); v++) c.p[v] = (size_t) cells[c.p.size()*i + v];
+        msh.cells.push_back(c);
+    }
+    msh.compute_connectivity();
+}
+} /* extern "C++" */
+
+int yfd_ref_mesh_set(int type, int64_t np, const double *pts, int64_t nc, const int64_t *cells, int64_t nf,
+                     const int64_t *faces, const uint8_t *fbnd, const int64_t *fbid)
+{
+    using namespace yfd_ref;
+    M.type = type;
+    try {
+        if (type == 0) set_mesh<tri_mesh, yaourt::triangle>(M.tri, np, pts, nc, cells, nf, faces, fbnd, fbid);
+        else           set_mesh<quad_mesh, yaourt::quadrangle>(M.quad, np, pts, nc, cells, nf, faces, fbnd, fbid);
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "[yfd_ref] exception: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}
+
 void yfd_ref_mesh_sizes(int64_t *npoints, int64_t *ncells, int64_t *nfaces, int64_t *nverts)
 {
     using namespace yfd_ref;

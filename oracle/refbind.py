@@ -41,6 +41,8 @@ class Ref:
         L.yfd_ref_mesh_create.argtypes = [C.c_int, C.c_int, C.c_int]
         L.yfd_ref_mesh_sizes.argtypes = [C.POINTER(C.c_int64)] * 4
         L.yfd_ref_mesh_copy.argtypes = [_f64p, _i64p, _i64p, _i32p, _i64p]
+        L.yfd_ref_mesh_set.argtypes = [C.c_int, C.c_int64, _f64p, C.c_int64, _i64p, C.c_int64, _i64p,
+                                       np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS"), C.c_void_p]
         L.yfd_ref_set_cg.argtypes = [C.c_double, C.c_double, C.c_long, C.c_int]
         L.yfd_ref_keep_raw_triplets.argtypes = [C.c_int]
         L.yfd_ref_run_dg.argtypes = [C.c_int, C.c_double, C.c_int]
@@ -60,6 +62,9 @@ class Ref:
     # ---- mesh -----------------------------------------------------------
     def mesh(self, mtype, levels, shatter=False):
         self.lib.yfd_ref_mesh_create(mtype, levels, int(shatter))
+        return self.mesh_arrays(mtype)
+
+    def mesh_arrays(self, mtype):
         s = [C.c_int64() for _ in range(4)]
         self.lib.yfd_ref_mesh_sizes(*[C.byref(v) for v in s])
         npts, ncells, nfaces, nv = [v.value for v in s]
@@ -70,6 +75,17 @@ class Ref:
         owners = np.empty((nfaces, 2), np.int64)
         self.lib.yfd_ref_mesh_copy(pts, cells, faces, fbnd, owners)
         return dict(type=mtype, points=pts, cells=cells, faces=faces, face_boundary=fbnd, face_owners=owners)
+
+    def set_mesh(self, mtype, points, cells, faces, face_boundary, face_boundary_id=None):
+        """Hand the reference a mesh made elsewhere (its public points / faces / cells vectors + its own compute_connectivity)."""
+        points = np.ascontiguousarray(points, np.float64); cells = np.ascontiguousarray(cells, np.int64)
+        faces = np.ascontiguousarray(faces, np.int64); fb = np.ascontiguousarray(face_boundary, np.uint8)
+        fid = None if face_boundary_id is None else np.ascontiguousarray(face_boundary_id, np.int64)
+        rc = self.lib.yfd_ref_mesh_set(mtype, len(points), points, len(cells), cells, len(faces), faces, fb,
+                                       None if fid is None else fid.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise RuntimeError("reference rejected the mesh")
+        return self.mesh_arrays(mtype)
 
     # ---- drivers --------------------------------------------------------
     def set_cg(self, rr_tol=1e-8, rr_max=1e4, max_iter=-1, skip_solve=False):

@@ -93,3 +93,30 @@ def test_mesher_rejects_bad_arguments(yfd):
         yfd.HostMesh.create(7, 1)
     with pytest.raises(yfd.YfdError):
         yfd.HostMesh.create(0, -1)
+
+
+def test_structured_mesher_follows_the_reference_conventions():
+    """yfd_mesher_create_structured (host only): sorted cells / faces, boundary flags, and -- where oracle/_ref is present --
+    the reference's own compute_connectivity accepts the mesh and reproduces the same owners as the C restatement."""
+    import yaourt_fem_dg_b200 as yfd
+    import oraclebind
+    for t, nx, ny in ((0, 5, 7), (1, 6, 4), (0, 1, 1), (1, 1, 3)):
+        hm = yfd.HostMesh.structured(t, nx, ny)
+        nv = 3 if t == 0 else 4
+        assert hm.cells.shape == ((2 if t == 0 else 1) * nx * ny, nv)
+        assert len(hm.points) == (nx + 1) * (ny + 1)
+        assert (np.lexsort(hm.cells.T[::-1]) == np.arange(len(hm.cells))).all()
+        assert (np.lexsort(hm.faces.T[::-1]) == np.arange(len(hm.faces))).all() and (hm.faces[:, 0] < hm.faces[:, 1]).all()
+        assert hm.face_boundary.sum() == 2 * (nx + ny)
+        cf, owners = oraclebind.Oracle().connectivity(hm.cells, hm.faces)
+        assert ((owners[:, 1] < 0) == (hm.face_boundary == 1)).all()          # boundary faces are exactly the one-owner faces
+        # positive orientation of every cell (counter-clockwise like the reference's base cells)
+        p = hm.points[hm.cells]
+        area2 = (p[:, 1, 0] - p[:, 0, 0]) * (p[:, 2, 1] - p[:, 0, 1]) - (p[:, 2, 0] - p[:, 0, 0]) * (p[:, 1, 1] - p[:, 0, 1])
+        assert (area2 > 0).all()
+        import refbind
+        if refbind.available():
+            m = refbind.Ref().set_mesh(t, hm.points, hm.cells, hm.faces, hm.face_boundary, hm.face_boundary_id)
+            assert np.array_equal(m["face_owners"], owners) and np.array_equal(m["cells"], hm.cells)
+    with pytest.raises(yfd.YfdError):
+        yfd.HostMesh.structured(0, 0, 3)

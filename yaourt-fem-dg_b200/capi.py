@@ -128,6 +128,7 @@ def lib():
         "yfd_ctx_rank": (cint, [vp]),
         "yfd_ctx_nranks": (cint, [vp]),
         "yfd_mesher_create": (cint, [cint, cint, P(vp)]),
+        "yfd_mesher_create_structured": (cint, [cint, i64, i64, P(vp)]),
         "yfd_host_mesh_destroy": (None, [vp]),
         "yfd_host_mesh_sizes": (None, [vp, P(i64), P(i64), P(i64), P(cint)]),
         "yfd_host_mesh_points": (P(dbl), [vp]),
@@ -316,6 +317,20 @@ class HostMesh:
         L = lib()
         h = C.c_void_p()
         st = L.yfd_mesher_create(cell_type, levels, C.byref(h))
+        return cls._adopt(cell_type, h, st)
+
+    @classmethod
+    def structured(cls, cell_type, nx, ny=None):
+        """nx x ny structured mesh of the unit square in the reference's conventions (yfd_mesher_create_structured;
+        new: the reference mesher only offers 4^(r+1) cells)."""
+        L = lib()
+        h = C.c_void_p()
+        st = L.yfd_mesher_create_structured(cell_type, nx, nx if ny is None else ny, C.byref(h))
+        return cls._adopt(cell_type, h, st)
+
+    @classmethod
+    def _adopt(cls, cell_type, h, st):
+        L = lib()
         if st != 0:
             raise YfdError(st, L.yfd_status_string(st).decode())
         try:

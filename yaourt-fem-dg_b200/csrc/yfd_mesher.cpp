@@ -211,6 +211,83 @@ yfd_status yfd_mesher_create(int cell_type, int levels, yfd_host_mesh **out)
     return YFD_OK;
 }
 
+/* nx x ny structured mesh of the unit square in the reference's conventions (new: the reference mesher only offers
+ * 4^(r+1) cells; BASELINE's "64x64 triangles", "~20M dofs", "~4M dofs" sizes fall between its levels).
+ * Points: id = j (nx+1) + i at (i/nx, j/ny).  Quadrangles: (p00, p10, p11, p01), counter-clockwise like the reference's
+ * base cells (core/meshers.hpp:327-330).  Triangles: every quadrangle split along p00-p11 into (p00, p10, p11) and
+ * (p00, p11, p01), 2 nx ny cells.  Cells sorted lexicographically on the vertex tuple (core/meshers.hpp:178,:360), faces
+ * sorted by (p0 < p1) (core/mesh.hpp:77-81), boundary ids 0 bottom, 1 right, 2 top, 3 left (core/meshers.hpp:139-144). */
+yfd_status yfd_mesher_create_structured(int cell_type, int64_t nx, int64_t ny, yfd_host_mesh **out)
+{
+    if (!out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if ((cell_type != YFD_CELL_TRIANGLE && cell_type != YFD_CELL_QUADRANGLE) || nx < 1 || ny < 1 ||
+        (nx + 1) * (ny + 1) >= 0x7fffffffLL)
+        return YFD_ERR_INVALID_ARGUMENT;
+    try {
+        yfd_host_mesh *m = new yfd_host_mesh();
+        m->cell_type = cell_type;
+        const int nv = m->nv = cell_type == YFD_CELL_TRIANGLE ? 3 : 4;
+        const int64_t npx = nx + 1, np = npx * (ny + 1);
+        m->points.resize((size_t) np * 2);
+#pragma omp parallel for
+        for (int64_t j = 0; j <= ny; j++)
+            for (int64_t i = 0; i <= nx; i++) {
+                m->points[(size_t) (j * npx + i) * 2] = (double) i / (double) nx;
+                m->points[(size_t) (j * npx + i) * 2 + 1] = (double) j / (double) ny;
+            }
+        const bool tri = nv == 3;
+        const int64_t nc = (tri ? 2 : 1) * nx * ny;
+        m->cells.resize((size_t) nc * nv);
+        /* generation order (j, i[, half]) is already lexicographic on the first vertex p00 = j npx + i, and for the two
+         * triangles of a quadrangle (p00, p10, ..) < (p00, p11, ..) since p10 < p11: no sort needed */
+#pragma omp parallel for
+        for (int64_t j = 0; j < ny; j++)
+            for (int64_t i = 0; i < nx; i++) {
+                const int64_t p00 = j * npx + i, p10 = p00 + 1, p01 = p00 + npx, p11 = p01 + 1;
+                if (tri) {
+                    int64_t *c = &m->cells[(size_t) (2 * (j * nx + i)) * 3];
+                    c[0] = p00; c[1] = p10; c[2] = p11; c[3] = p00; c[4] = p11; c[5] = p01;
+                } else {
+                    int64_t *c = &m->cells[(size_t) (j * nx + i) * 4];
+                    c[0] = p00; c[1] = p10; c[2] = p11; c[3] = p01;
+                }
+            }
+        /* faces in (p0, p1) order: from point p = (i, j) the edges with p as the smaller end are, by increasing p1,
+         * p -> p+1 (horizontal), p -> p+npx (vertical), p -> p+npx+1 (diagonal, triangles only) */
+        const int64_t nf = nx * (ny + 1) + ny * (nx + 1) + (tri ? nx * ny : 0);
+        m->faces.resize((size_t) nf * 2);
+        m->fbnd.assign((size_t) nf, 0);
+        m->fbid.assign((size_t) nf, 0);
+        int64_t f = 0;
+        for (int64_t j = 0; j <= ny; j++)
+            for (int64_t i = 0; i <= nx; i++) {
+                const int64_t p = j * npx + i;
+                if (i < nx) {
+                    m->faces[(size_t) f * 2] = p; m->faces[(size_t) f * 2 + 1] = p + 1;
+                    if (j == 0) { m->fbnd[(size_t) f] = 1; m->fbid[(size_t) f] = 0; }
+                    if (j == ny) { m->fbnd[(size_t) f] = 1; m->fbid[(size_t) f] = 2; }
+                    f++;
+                }
+                if (j < ny) {
+                    m->faces[(size_t) f * 2] = p; m->faces[(size_t) f * 2 + 1] = p + npx;
+                    if (i == 0) { m->fbnd[(size_t) f] = 1; m->fbid[(size_t) f] = 3; }
+                    if (i == nx) { m->fbnd[(size_t) f] = 1; m->fbid[(size_t) f] = 1; }
+                    f++;
+                }
+                if (tri && i < nx && j < ny) {
+                    m->faces[(size_t) f * 2] = p; m->faces[(size_t) f * 2 + 1] = p + npx + 1;
+                    f++;
+                }
+            }
+        if (f != nf) { delete m; return YFD_ERR_INVALID_STATE; }
+        *out = m;
+    } catch (const std::bad_alloc &) {
+        return YFD_ERR_OUT_OF_MEMORY;
+    }
+    return YFD_OK;
+}
+
 void yfd_host_mesh_destroy(yfd_host_mesh *m) { delete m; }
 
 void yfd_host_mesh_sizes(const yfd_host_mesh *m, int64_t *npoints, int64_t *ncells, int64_t *nfaces, int *nv)
