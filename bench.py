@@ -62,6 +62,11 @@ WORKLOADS = {
                         desc="continuous P1 FEM Poisson, triangles -r 11: 33,554,432 cells, 8,380,417 dofs (BASELINE configs[1] is P2; the reference is P1 only)"),
     "cfem_p1_r10": dict(kind="cfem", cell=0, r=10, k=1, pc=False, rr_tol=1e-8, rr_max=1e3, ref_r=7, base_r=8,
                         desc="continuous P1 FEM Poisson, triangles -r 10: 8,388,608 cells, 2,095,105 dofs"),
+    # configs[1] as written: "continuous_fem P2 Poisson on triangles, ~4M dofs" -- an extension (parity unpinned): P2 on the
+    # structured mesher, (2 nx - 1)^2 unknowns.  CPU baseline = the oracle's P2 statement + its CG (a scalar port)
+    "cfem_p2_4m": dict(kind="cfem", order=2, cell=0, nx=1000, k=2, pc=False, rr_tol=1e-8, rr_max=1e3, ref_r=7, base_r=8,
+                       desc="continuous P2 FEM Poisson, triangles, 1000 x 1000 structured: 2,000,000 cells, 3,996,001 dofs (BASELINE configs[1]; "
+                            "extension, the reference is P1 only: parity unpinned)"),
     # configs[3]: "dg_maxwell_2D time-domain explicit run, degree 4 triangles, matrix-free element+face operator"
     "maxwell_tri_k4_r9": dict(kind="maxwell", cell=0, r=9, k=4, upwind=False, dt=2e-5, timesteps=50, ref_r=5, base_r=6,
                               desc="DG Maxwell TM, triangles k=4, -r 9, centred fluxes, RK4: 1,048,576 cells, 47,185,920 unknowns (BASELINE configs[3])"),
@@ -150,6 +155,8 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 def reference_step(ref, wl, r):
     """One full reference pass at refinement r: mesh (untimed) -> cell loop -> finalize -> CG."""
+    if wl.get("order") == 2:
+        return port_step_p2(wl, r)
     ref.set_cg(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4), max_iter=-1)
     if wl.get("kind") == "cfem":
         out = ref.run_cfem(r)               # continuous_fem.cpp: builds its own mesh (counted in t_blocks)
@@ -158,6 +165,20 @@ def reference_step(ref, wl, r):
         out = ref.run_dg(wl["k"], eta=1.0, use_pc=wl["pc"])
     t = out["t_blocks"] + out["t_csr"] + out["t_cg"]
     return dict(n=out["n"], nnz=out["nnz"], iters=out["iters"], t=t, t_blocks=out["t_blocks"], t_csr=out["t_csr"], t_cg=out["t_cg"])
+
+
+def port_step_p2(wl, r):
+    """P2 has no reference implementation: time the oracle's C statement of it (scalar port), mesh untimed."""
+    import oraclebind
+    o = oraclebind.Oracle()
+    m = o.mesh(0, r)
+    t0 = time.perf_counter()
+    s = o.cfem_p2(m["points"], m["cells"], m["faces"], m["face_boundary"])
+    t1 = time.perf_counter()
+    res = o.cg(s["rowptr"], s["colidx"], s["values"], s["rhs"], rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4),
+               max_iter=4 * s["n"], history=False)
+    t2 = time.perf_counter()
+    return dict(n=s["n"], nnz=s["nnz"], iters=res["iterations"], t=t2 - t0, t_blocks=t1 - t0, t_csr=0.0, t_cg=t2 - t1)
 
 
 def load_reference():
@@ -172,13 +193,24 @@ def load_reference():
     return ref, (ref.num_threads() if omp else 1), "reference"
 
 
-def cpu_baseline(wl, r):
+PORT_P2_LABEL = "oracle/ C statement of the P2 extension + its scalar CG (the reference has no P2: port)"
+
+
+def load_arm(wl):
+    """(handle, cores, kind, label) of the CPU implementation timed for this workload."""
+    if wl.get("order") == 2:
+        return object(), 1, "port", PORT_P2_LABEL
     ref, cores, kind = load_reference()
+    return ref, cores, kind, "unmodified reference (Blaze, -O3 -fopenmp: only its CG is threaded)"
+
+
+def cpu_baseline(wl, r):
+    ref, cores, kind, label = load_arm(wl)
     if ref is None:
         return None
     s = reference_step(ref, wl, r)
     return dict(value=s["n"] / s["t"], unit="DOFs/s", cores=cores, kind=kind,
-                sample="unmodified reference (Blaze, -O3 -fopenmp: only its CG is threaded), same discretisation at -r %d: "
+                sample=label + ", same discretisation at -r %d: "
                        "%d dofs, nnz %d, %d CG iterations to rr %.0e; blocks %.2fs + finalize %.2fs + CG %.2fs; "
                        "%.2f ns per dof per CG iteration" % (r, s["n"], s["nnz"], s["iters"], wl["rr_tol"], s["t_blocks"],
                                                               s["t_csr"], s["t_cg"], 1e9 * s["t_cg"] / max(1, s["n"] * s["iters"])))
@@ -187,7 +219,7 @@ def cpu_baseline(wl, r):
 def run_reference_arm(args, wl, rank):
     if rank != 0:
         return 0
-    ref, cores, kind = load_reference()
+    ref, cores, kind, label = load_arm(wl)
     if ref is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libyfd_ref.so not built (needs /root/reference at build time)"}))
         return 0
@@ -203,8 +235,8 @@ def run_reference_arm(args, wl, rank):
     wall = time.perf_counter() - t0
     ms = 1e3 * tot / args.steps
     value = last["n"] / (tot / args.steps)
-    sample = ("each step = the unmodified reference's cell loop + finalize + CG at -r %d (%d dofs, nnz %d, %d iterations, rr_tol %.0e) "
-              "of the workload's discretisation; mesh creation untimed; wall %.1fs" % (r, last["n"], last["nnz"], last["iters"], wl["rr_tol"], wall))
+    sample = ("each step = cell loop + finalize + CG of the %s at -r %d (%d dofs, nnz %d, %d iterations, rr_tol %.0e) "
+              "of the workload's discretisation; mesh creation untimed; wall %.1fs" % (label, r, last["n"], last["nnz"], last["iters"], wl["rr_tol"], wall))
     line = {"impl": "reference", "metric": "assembled+solved DOFs/sec", "value": value, "unit": "DOFs/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -482,10 +514,12 @@ def main():
     k, bs = wl["k"], (1 if cfem else bs_of(wl["k"]))
 
     def assemble(m):
-        return ctx.cfem_assemble_p1(m) if cfem else ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"])
+        if cfem:
+            return ctx.cfem_assemble_p2(m) if wl.get("order") == 2 else ctx.cfem_assemble_p1(m)
+        return ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"])
     hm = make_host_mesh(yfd, wl)                            # mesher: input generation, untimed
     params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4),
-                          max_iter=args.profile_iters or 2 * (len(hm.points) if wl.get("kind") == "cfem" else bs_of(wl["k"]) * len(hm.cells)))
+                          max_iter=args.profile_iters or 2 * ((len(hm.points) + len(hm.faces)) if wl.get("kind") == "cfem" else bs_of(wl["k"]) * len(hm.cells)))
 
     def barrier():
         if dist is not None:
@@ -598,7 +632,7 @@ def main():
         ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
-               "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % ("yfd_cfem_assemble_p1" if cfem else "yfd_dg_assemble_sip")}
+               "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % (("yfd_cfem_assemble_p2" if wl.get("order") == 2 else "yfd_cfem_assemble_p1") if cfem else "yfd_dg_assemble_sip")}
 
     base = None
     if rank == 0 and not args.no_cpu_baseline:

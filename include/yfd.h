@@ -258,9 +258,25 @@ yfd_status yfd_dg_postprocess_device(yfd_ctx *ctx, yfd_mesh *mesh, int degree, i
 /* ---------------------------------------------------------------------------------- */
 yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn,
                                 yfd_system **out, yfd_assembly_info *info);
-/* cfem::assembler::expand (methods/cfem.hpp:190-197): sol[system_size] -> expanded[npoints] */
+/* Continuous P2 on triangles -- an EXTENSION (BASELINE configs[1]); the reference is P1-only (StaticMatrix<T,3,3>,  */
+/* methods/cfem.hpp:77-89; get_assembler ignores `degree`, :200-204), so results are "parity unpinned".  Written in   */
+/* the reference's conventions: nodes = mesh points followed by edge midpoints (node id = point id | npoints + face    */
+/* id, faces in the reference's sorted order), local order (v0,v1,v2,e(p0p1),e(p1p2),e(p0p2)) (core/mesh.hpp:299-312), */
+/* Dirichlet nodes = endpoints and midpoints of boundary faces with the compress map of methods/cfem.hpp:134-148 over  */
+/* the larger node set, triplets pushed in (cell,i,j) order and folded in that order.  Quadrature: the reference's     */
+/* Dunavant rules of degree 2 (stiffness, exact) and 4 (load vector).  expand / get_compress_map work on               */
+/* yfd_cfem_node_count() nodes.                                                                                        */
+yfd_status yfd_cfem_assemble_p2(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn,
+                                yfd_system **out, yfd_assembly_info *info);
+/* nodes behind the compress map: npoints (P1), npoints + nfaces (P2) */
+yfd_status yfd_cfem_node_count(const yfd_system *sys, int64_t *nnodes);
+/* sum over cells of int (u_h - u)^2 with the Dunavant rule of degree 6 (fixed summation order); order = 1 | 2,        */
+/* expanded [node count], ref_fn = YFD_FN_SINSIN_SOL for the driver's problem.  The reference's continuous_fem.cpp     */
+/* reports no error norm; this is the validation hook of the P2 extension.                                             */
+yfd_status yfd_cfem_l2_error(yfd_ctx *ctx, yfd_mesh *mesh, int order, int ref_fn, const double *expanded, double *l2_errsq);
+/* cfem::assembler::expand (methods/cfem.hpp:190-197): sol[system_size] -> expanded[node count] */
 yfd_status yfd_cfem_expand(yfd_system *sys, const double *sol, double *expanded);
-/* compress_map [npoints] (i64; -1 on Dirichlet nodes) */
+/* compress_map[node count]: system row of each node, -1 on Dirichlet nodes */
 yfd_status yfd_cfem_get_compress_map(yfd_system *sys, int64_t *compress_map);
 
 /* ---------------------------------------------------------------------------------- */

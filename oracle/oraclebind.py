@@ -44,6 +44,12 @@ class Oracle:
         L.yfo_cg.restype = i64
         L.yfo_cfem_p1.argtypes = [i64, _f64p, i64, _i64p, i64, _i64p, _u8p, cint, _i64p, C.POINTER(i64), _i64p, _i64p, _f64p, _f64p]
         L.yfo_cfem_p1.restype = i64
+        L.yfo_cfem_p2.argtypes = L.yfo_cfem_p1.argtypes
+        L.yfo_cfem_p2.restype = i64
+        L.yfo_cfem_p2_element.argtypes = [_f64p, cint, _f64p, _f64p]
+        L.yfo_cfem_p2_element.restype = None
+        L.yfo_cfem_p2_errsq.argtypes = [i64, _f64p, i64, _i64p, i64, _i64p, _f64p, cint]
+        L.yfo_cfem_p2_errsq.restype = C.c_double
         L.yfo_mesher.argtypes = [cint, cint, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), vp, vp, vp, vp]
         _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
         L.yfo_set_physics.argtypes = [cint, cint]
@@ -171,6 +177,30 @@ class Oracle:
         rowptr, colidx, values = self.csr_from_triplets(n, n, ri[:cnt], rj[:cnt], rv[:cnt])
         return dict(n=n, nnz=len(values), rowptr=rowptr, colidx=colidx, values=values, rhs=rhs[:n].copy(), compress_map=cmap,
                     raw=(ri[:cnt].copy(), rj[:cnt].copy(), rv[:cnt].copy()))
+
+    # ---- continuous P2 (extension: the reference is P1-only, parity unpinned) ----
+    def cfem_p2_element(self, verts, rhs_fn=1):
+        v = _c(verts, np.float64).reshape(6)
+        K = np.empty((6, 6)); b = np.empty(6)
+        self.lib.yfo_cfem_p2_element(v, rhs_fn, K, b)
+        return K, b
+
+    def cfem_p2(self, points, cells, faces, face_boundary, rhs_fn=1):
+        points = _c(points, np.float64); cells = _c(cells, np.int64); faces = _c(faces, np.int64)
+        fb = _c(face_boundary, np.uint8)
+        nn, nc = len(points) + len(faces), len(cells)
+        cmap = np.empty(nn, np.int64); n = C.c_int64()
+        ri = np.empty(36 * nc, np.int64); rj = np.empty(36 * nc, np.int64); rv = np.empty(36 * nc); rhs = np.empty(nn)
+        cnt = self.lib.yfo_cfem_p2(len(points), points, nc, cells, len(faces), faces, fb, rhs_fn, cmap, C.byref(n), ri, rj, rv, rhs)
+        if cnt < 0:
+            raise ValueError("a cell face is missing from the face list")
+        n = n.value
+        rowptr, colidx, values = self.csr_from_triplets(n, n, ri[:cnt], rj[:cnt], rv[:cnt])
+        return dict(n=n, nnz=len(values), rowptr=rowptr, colidx=colidx, values=values, rhs=rhs[:n].copy(), compress_map=cmap)
+
+    def cfem_p2_errsq(self, points, cells, faces, expanded, ref_fn=3):
+        points = _c(points, np.float64); cells = _c(cells, np.int64); faces = _c(faces, np.int64)
+        return self.lib.yfo_cfem_p2_errsq(len(points), points, len(cells), cells, len(faces), faces, _c(expanded, np.float64), ref_fn)
 
     # ---- DG Maxwell TM (methods/dg_maxwell_2D.hpp, maxwell_driver.cpp) ----
     def maxwell_assemble(self, points, cells, faces, k, upwind=False, eta=1.0, mu_r=None, eps_r=None):

@@ -159,6 +159,9 @@ def lib():
         "yfd_dg_local_blocks": (cint, [vp, vp, P(DgConfig), vp, vp, vp, vp]),
         "yfd_dg_assemble_advection": (cint, [vp, vp, P(DgConfig), cint, P(vp), P(AssemblyInfo)]),
         "yfd_cfem_assemble_p1": (cint, [vp, vp, cint, P(vp), P(AssemblyInfo)]),
+        "yfd_cfem_assemble_p2": (cint, [vp, vp, cint, P(vp), P(AssemblyInfo)]),
+        "yfd_cfem_node_count": (cint, [vp, P(i64)]),
+        "yfd_cfem_l2_error": (cint, [vp, vp, cint, cint, _f64p, P(C.c_double)]),
         "yfd_cfem_expand": (cint, [vp, _f64p, _f64p]),
         "yfd_cfem_get_compress_map": (cint, [vp, _i64p]),
         "yfd_system_destroy": (None, [vp]),
@@ -298,6 +301,19 @@ class Context:
         info = AssemblyInfo()
         self.check(lib().yfd_cfem_assemble_p1(self._h, mesh._h, rhs_fn, C.byref(h), C.byref(info)))
         return System(self, h, info)
+
+    def cfem_assemble_p2(self, mesh, rhs_fn=FN_SINSIN):
+        """Continuous P2 (extension; the reference is P1-only, methods/cfem.hpp:200-204)."""
+        h = C.c_void_p()
+        info = AssemblyInfo()
+        self.check(lib().yfd_cfem_assemble_p2(self._h, mesh._h, rhs_fn, C.byref(h), C.byref(info)))
+        return System(self, h, info)
+
+    def cfem_l2_error(self, mesh, order, expanded, ref_fn=FN_SINSIN_SOL):
+        """sqrt of the summed cell integrals of (u_h - u)^2."""
+        e = C.c_double()
+        self.check(lib().yfd_cfem_l2_error(self._h, mesh._h, order, ref_fn, np.ascontiguousarray(expanded, np.float64), C.byref(e)))
+        return float(np.sqrt(e.value))
 
 
 class HostMesh:
@@ -578,9 +594,9 @@ class System:
         return out
 
     def _npoints(self):
-        if not hasattr(self, "npoints"):
-            raise YfdError(1, "set System.npoints (mesh.npoints) before CFEM expand/compress_map")
-        return self.npoints
+        n = C.c_int64()
+        self.ctx.check(lib().yfd_cfem_node_count(self._h, C.byref(n)))
+        return n.value
 
 
 class Maxwell:

@@ -88,14 +88,17 @@ __global__ void invert_diag(const double *__restrict__ in, double *__restrict__ 
 }
 
 /* ---- CFEM ------------------------------------------------------------------------------------ */
-__global__ void mark_dirichlet(const int2 *__restrict__ faces, const uint8_t *__restrict__ fbnd, int64_t nfaces, int32_t *__restrict__ free_node)
+__global__ void mark_dirichlet(const int2 *__restrict__ faces, const uint8_t *__restrict__ fbnd, int64_t nfaces, int32_t *__restrict__ free_node,
+                               int64_t edge_node_base)
 {
-    /* dirichlet_nodes from boundary faces (methods/cfem.hpp:119-132); free_node = !dirichlet */
+    /* dirichlet_nodes from boundary faces (methods/cfem.hpp:119-132); free_node = !dirichlet.
+     * P2 (edge_node_base >= 0): the midpoint node of a boundary face is a Dirichlet node too */
     const int64_t f = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= nfaces || !fbnd[f]) return;
     const int2 p = faces[f];
     free_node[p.x] = 0;
     free_node[p.y] = 0;
+    if (edge_node_base >= 0) free_node[edge_node_base + f] = 0;
 }
 
 __global__ void fill_i32(int32_t *p, int64_t n, int32_t v)
@@ -159,6 +162,158 @@ __global__ void cfem_p1_cells(const double2 *__restrict__ pts, const int32_t *__
     if (nr) atomicAdd(&counts[1], (unsigned long long) nr);
 }
 
+/* ---- continuous P2 (extension: the reference is P1-only, methods/cfem.hpp:200-204) ------------------------------
+ * Local order (v0, v1, v2, e(p0p1), e(p1p2), e(p0p2)) = vertices, then the reference's local face order
+ * (core/mesh.hpp:299-312); global node = point id | npoints + face id. */
+__device__ __forceinline__ void p2_basis(const double *l, double *phi)
+{
+    phi[0] = l[0] * (2.0 * l[0] - 1.0);
+    phi[1] = l[1] * (2.0 * l[1] - 1.0);
+    phi[2] = l[2] * (2.0 * l[2] - 1.0);
+    phi[3] = 4.0 * l[0] * l[1];
+    phi[4] = 4.0 * l[1] * l[2];
+    phi[5] = 4.0 * l[0] * l[2];
+}
+
+__device__ __forceinline__ double cfem_fn(int fn, double x, double y)
+{
+    switch (fn) {
+    case YFD_FN_SINSIN: { const double sx = sin(M_PI * x), sy = sin(M_PI * y); return 2.0 * M_PI * M_PI * sx * sy; }
+    case YFD_FN_SINSIN_SOL: return sin(M_PI * x) * sin(M_PI * y);
+    case YFD_FN_SIN_X_SOL:  return sin(M_PI * x);
+    case YFD_FN_ONE: return 1.0;
+    default: return 0.0;
+    }
+}
+
+/* one thread per cell: 36 matrix triplets + 6 rhs triplets in (cell, i, j) push order.  ruleK / ruleF are the
+ * reference's Dunavant rules of degree 2 (exact for the products of the linear P2 gradients) and 4 */
+__global__ void __launch_bounds__(128)
+cfem_p2_cells(const double2 *__restrict__ pts, const int32_t *__restrict__ cells, const int32_t *__restrict__ cell_faces,
+              int64_t ncells, int64_t npoints, const int32_t *__restrict__ cmap, int64_t n, int col_bits, int rhs_fn,
+              const double *__restrict__ ruleK, int nqK, const double *__restrict__ ruleF, int nqF,
+              uint64_t *__restrict__ mkeys, double *__restrict__ mvals, uint64_t *__restrict__ rkeys,
+              double *__restrict__ rvals, unsigned long long *__restrict__ counts)
+{
+    const int64_t c = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const int32_t id[3] = { cells[3 * c], cells[3 * c + 1], cells[3 * c + 2] };
+    const double2 p0 = pts[id[0]], p1 = pts[id[1]], p2 = pts[id[2]];
+    const double x0 = p0.x, y0 = p0.y, x1 = p1.x, y1 = p1.y, x2 = p2.x, y2 = p2.y;
+    const double m = (x1 * y2 - y1 * x2 - x0 * (y2 - y1) + y0 * (x2 - x1));     /* eval_basis_grad, methods/cfem.hpp:53-75 */
+    const double g[3][2] = { { (y1 - y2) / m, (x2 - x1) / m }, { (y2 - y0) / m, (x0 - x2) / m }, { (y0 - y1) / m, (x1 - x0) / m } };
+    const double d0x = x1 - x0, d0y = y1 - y0, d1x = x2 - x0, d1y = y2 - y0;
+    const double area = fabs(d0x * d1y - d1x * d0y) / 2.0;                       /* measure, core/mesh.hpp:444-460 */
+
+    double K[6][6], b[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+        b[i] = 0.0;
+#pragma unroll
+        for (int j = 0; j < 6; j++) K[i][j] = 0.0;
+    }
+    for (int q = 0; q < nqK; q++) {
+        const double l[3] = { __ldg(&ruleK[4 * q]), __ldg(&ruleK[4 * q + 1]), __ldg(&ruleK[4 * q + 2]) };
+        const double w = __ldg(&ruleK[4 * q + 3]) * area;
+        double dphi[6][2];
+#pragma unroll
+        for (int d = 0; d < 2; d++) {
+            dphi[0][d] = (4.0 * l[0] - 1.0) * g[0][d];
+            dphi[1][d] = (4.0 * l[1] - 1.0) * g[1][d];
+            dphi[2][d] = (4.0 * l[2] - 1.0) * g[2][d];
+            dphi[3][d] = 4.0 * (l[0] * g[1][d] + l[1] * g[0][d]);
+            dphi[4][d] = 4.0 * (l[1] * g[2][d] + l[2] * g[1][d]);
+            dphi[5][d] = 4.0 * (l[0] * g[2][d] + l[2] * g[0][d]);
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int j = 0; j < 6; j++) K[i][j] += w * (dphi[i][0] * dphi[j][0] + dphi[i][1] * dphi[j][1]);
+    }
+    for (int q = 0; q < nqF; q++) {
+        const double l[3] = { __ldg(&ruleF[4 * q]), __ldg(&ruleF[4 * q + 1]), __ldg(&ruleF[4 * q + 2]) };
+        const double w = __ldg(&ruleF[4 * q + 3]) * area;
+        const double x = x0 * l[0] + x1 * l[1] + x2 * l[2], y = y0 * l[0] + y1 * l[1] + y2 * l[2];
+        const double f = cfem_fn(rhs_fn, x, y);
+        double phi[6];
+        p2_basis(l, phi);
+#pragma unroll
+        for (int i = 0; i < 6; i++) b[i] += w * f * phi[i];
+    }
+
+    int32_t dof[6];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        dof[i] = cmap[id[i]];
+        dof[3 + i] = cmap[npoints + cell_faces[3 * c + i]];
+    }
+    const uint64_t sentinel = (uint64_t) n << col_bits;
+    unsigned nm = 0, nr = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            const bool keep = dof[i] >= 0 && dof[j] >= 0;
+            mkeys[36 * c + 6 * i + j] = keep ? (((uint64_t) dof[i] << col_bits) | (uint64_t) dof[j]) : sentinel;
+            mvals[36 * c + 6 * i + j] = K[i][j];
+            nm += keep;
+        }
+        const bool keep = dof[i] >= 0;
+        rkeys[6 * c + i] = keep ? ((uint64_t) dof[i] << 1) : ((uint64_t) n << 1);
+        rvals[6 * c + i] = b[i];
+        nr += keep;
+    }
+    if (nm) atomicAdd(&counts[0], (unsigned long long) nm);
+    if (nr) atomicAdd(&counts[1], (unsigned long long) nr);
+}
+
+/* per cell: sum over the quadrature points of w (u_h - u)^2, u_h from the expanded nodal vector (order 1 or 2) */
+__global__ void cfem_cell_errsq(const double2 *__restrict__ pts, const int32_t *__restrict__ cells, const int32_t *__restrict__ cell_faces,
+                                int64_t ncells, int64_t npoints, int order, const double *__restrict__ expanded, int ref_fn,
+                                const double *__restrict__ rule, int nq, double *__restrict__ partial)
+{
+    const int64_t c = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const int32_t id[3] = { cells[3 * c], cells[3 * c + 1], cells[3 * c + 2] };
+    const double2 p0 = pts[id[0]], p1 = pts[id[1]], p2 = pts[id[2]];
+    const double area = fabs((p1.x - p0.x) * (p2.y - p0.y) - (p2.x - p0.x) * (p1.y - p0.y)) / 2.0;
+    double u[6] = { expanded[id[0]], expanded[id[1]], expanded[id[2]], 0.0, 0.0, 0.0 };
+    if (order == 2)
+        for (int e = 0; e < 3; e++) u[3 + e] = expanded[npoints + cell_faces[3 * c + e]];
+    double err = 0.0;
+    for (int q = 0; q < nq; q++) {
+        const double l[3] = { __ldg(&rule[4 * q]), __ldg(&rule[4 * q + 1]), __ldg(&rule[4 * q + 2]) };
+        const double x = p0.x * l[0] + p1.x * l[1] + p2.x * l[2], y = p0.y * l[0] + p1.y * l[1] + p2.y * l[2];
+        double uh;
+        if (order == 2) {
+            double phi[6];
+            p2_basis(l, phi);
+            uh = 0.0;
+            for (int i = 0; i < 6; i++) uh += u[i] * phi[i];
+        } else {
+            uh = u[0] * l[0] + u[1] * l[1] + u[2] * l[2];
+        }
+        const double d = uh - cfem_fn(ref_fn, x, y);
+        err += __ldg(&rule[4 * q + 3]) * area * d * d;
+    }
+    partial[c] = err;
+}
+
+/* fixed-order sum: thread t adds its strided elements, then a tree over the 1024 partials */
+__global__ void __launch_bounds__(1024) cfem_sum_fixed(const double *__restrict__ in, int64_t n, double *__restrict__ out)
+{
+    __shared__ double sh[1024];
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += 1024) s += in[i];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if ((int) threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = sh[0];
+}
+
 __global__ void rhs_from_fold(const int64_t *__restrict__ rowptr, const double *__restrict__ values, int64_t n, double *__restrict__ rhs)
 {
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -174,9 +329,13 @@ __global__ void cfem_expand(const double *__restrict__ sol, const int32_t *__res
     out[i] = d >= 0 ? sol[d] : 0.0;          /* expand (methods/cfem.hpp:190-197) */
 }
 
-static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system *sys, yfd_assembly_info *info)
+/* order 1: the reference's P1 path; order 2: the P2 extension (nodes = points | edge midpoints) */
+static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int order, int rhs_fn, yfd_system *sys, yfd_assembly_info *info)
 {
-    const int64_t np = mesh->npoints, nc = mesh->ncells, nfc = mesh->nfaces;
+    const int64_t npts = mesh->npoints, nc = mesh->ncells, nfc = mesh->nfaces;
+    const int64_t np = order == 2 ? npts + nfc : npts;            /* nodes */
+    const int ldofs = order == 2 ? 6 : 3;
+    const int64_t ntrip = nc * ldofs * ldofs, nrtrip = nc * ldofs;
     gpu_timer t_struct, t_elem;
     dbuf<int32_t> free_node;
     dbuf<int64_t> scan;
@@ -184,7 +343,8 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_syste
     YFD_TRY(free_node.alloc(ctx, (size_t) np));
     YFD_TRY(scan.alloc(ctx, (size_t) np + 1));
     YFD_LAUNCH(ctx, fill_i32, sgrid(ctx, np), 256, 0, free_node.p, np, 1);
-    YFD_LAUNCH(ctx, mark_dirichlet, (unsigned) ceil_div(std::max<int64_t>(nfc, 1), 256), 256, 0, (const int2 *) mesh->faces.p, mesh->face_bnd.p, nfc, free_node.p);
+    YFD_LAUNCH(ctx, mark_dirichlet, (unsigned) ceil_div(std::max<int64_t>(nfc, 1), 256), 256, 0, (const int2 *) mesh->faces.p, mesh->face_bnd.p, nfc, free_node.p,
+               order == 2 ? npts : (int64_t) -1);
     YFD_TRY(exclusive_scan_i32_to_i64(ctx, free_node.p, scan.p, np));
     int64_t n = 0;
     YFD_CUDA(ctx, cudaMemcpyAsync(&n, scan.p + np, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
@@ -198,19 +358,29 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_syste
     dbuf<uint64_t> mkeys, rkeys;
     dbuf<double> mvals, rvals;
     dbuf<unsigned long long> counts;
-    YFD_TRY(mkeys.alloc(ctx, (size_t) nc * 9)); YFD_TRY(mvals.alloc(ctx, (size_t) nc * 9));
-    YFD_TRY(rkeys.alloc(ctx, (size_t) nc * 3)); YFD_TRY(rvals.alloc(ctx, (size_t) nc * 3));
+    YFD_TRY(mkeys.alloc(ctx, (size_t) ntrip)); YFD_TRY(mvals.alloc(ctx, (size_t) ntrip));
+    YFD_TRY(rkeys.alloc(ctx, (size_t) nrtrip)); YFD_TRY(rvals.alloc(ctx, (size_t) nrtrip));
     YFD_TRY(counts.alloc(ctx, 2)); YFD_TRY(counts.zero(ctx));
+    tri_rule ruleK, ruleF;
+    if (order == 2) {
+        YFD_TRY(dunavant_rule_for_degree(ctx, 2, &ruleK));
+        YFD_TRY(dunavant_rule_for_degree(ctx, 4, &ruleF));
+    }
     t_elem.start(ctx->stream);
-    YFD_LAUNCH(ctx, cfem_p1_cells, (unsigned) ceil_div(std::max<int64_t>(nc, 1), 256), 256, 0, (const double2 *) mesh->points.p, mesh->cells.p, nc,
-               sys->compress_map.p, n, col_bits, rhs_fn, mkeys.p, mvals.p, rkeys.p, rvals.p, counts.p);
+    if (order == 2)
+        YFD_LAUNCH(ctx, cfem_p2_cells, (unsigned) ceil_div(std::max<int64_t>(nc, 1), 128), 128, 0, (const double2 *) mesh->points.p, mesh->cells.p,
+                   mesh->cell_faces.p, nc, npts, sys->compress_map.p, n, col_bits, rhs_fn, ruleK.cw, ruleK.n, ruleF.cw, ruleF.n,
+                   mkeys.p, mvals.p, rkeys.p, rvals.p, counts.p);
+    else
+        YFD_LAUNCH(ctx, cfem_p1_cells, (unsigned) ceil_div(std::max<int64_t>(nc, 1), 256), 256, 0, (const double2 *) mesh->points.p, mesh->cells.p, nc,
+                   sys->compress_map.p, n, col_bits, rhs_fn, mkeys.p, mvals.p, rkeys.p, rvals.p, counts.p);
     t_elem.stop(ctx->stream);
     unsigned long long hc[2] = { 0, 0 };
     YFD_TRY(counts.download(ctx, hc, 2));
     /* the fold ignores the sentinel tail: sort everything, then build from the first hc[] records.
      * A sentinel has row n, so give the builder n+1 rows and drop the last one afterwards. */
     yfd_csr full;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, nc * 9, mkeys.p, col_bits, row_bits, mvals.p, &full));
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, ntrip, mkeys.p, col_bits, row_bits, mvals.p, &full));
     /* rows 0..n-1 of `full` are the matrix; row n holds the folded sentinel (one entry) */
     sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n;
     int64_t nnz = 0;
@@ -224,13 +394,13 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_syste
     sys->A.colidx.n = (size_t) nnz; sys->A.values.n = (size_t) nnz;
 
     yfd_csr rf;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nc * 3, rkeys.p, 1, row_bits, rvals.p, &rf));
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nrtrip, rkeys.p, 1, row_bits, rvals.p, &rf));
     YFD_TRY(sys->rhs.alloc(ctx, (size_t) n, 2));
     YFD_LAUNCH(ctx, rhs_from_fold, (unsigned) ceil_div(std::max<int64_t>(n, 1), 256), 256, 0, rf.rowptr.p, rf.values.p, n, sys->rhs.p);
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     (void) hc;
     if (info) {
-        info->system_size = n; info->nnz = nnz; info->basis_size = 3;
+        info->system_size = n; info->nnz = nnz; info->basis_size = ldofs;
         info->ms_elements = t_elem.ms(); info->ms_structure = t_struct.ms();
     }
     return YFD_OK;
@@ -242,20 +412,63 @@ using namespace yfd;
 
 extern "C" {
 
-yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system **out, yfd_assembly_info *info)
+static yfd_status cfem_assemble(yfd_ctx *ctx, yfd_mesh *mesh, int order, int rhs_fn, yfd_system **out, yfd_assembly_info *info)
 {
     if (!ctx || !mesh || !out) return YFD_ERR_INVALID_ARGUMENT;
     *out = nullptr;
     if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
-    if (mesh->nv != 3) return fail(ctx, YFD_ERR_UNSUPPORTED, "continuous FEM is P1 on triangles only (methods/cfem.hpp:31-89)");
+    if (mesh->nv != 3) return fail(ctx, YFD_ERR_UNSUPPORTED, "continuous FEM is defined on triangles only (methods/cfem.hpp:31-89)");
     if (ctx->nranks > 1) return fail(ctx, YFD_ERR_UNSUPPORTED, "the CFEM path is not partitioned: run it on a context without a communicator");
+    if (order == 2 && mesh->npoints + mesh->nfaces > (int64_t) INT32_MAX)
+        return fail(ctx, YFD_ERR_UNSUPPORTED, "P2: points + faces exceed the 32-bit node index");
     scoped_device dev(ctx->device);
     yfd_system *sys = new yfd_system();
     sys->ctx = ctx; sys->kind = YFD_SYS_CFEM; sys->bs = 1; sys->nf = 3; sys->ncells = mesh->ncells;
-    const yfd_status st = build_cfem(ctx, mesh, rhs_fn, sys, info);
+    const yfd_status st = build_cfem(ctx, mesh, order, rhs_fn, sys, info);
     if (st != YFD_OK) { cudaStreamSynchronize(ctx->stream); delete sys; return st; }
     *out = sys;
     return YFD_OK;
+}
+
+yfd_status yfd_cfem_assemble_p1(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system **out, yfd_assembly_info *info)
+{
+    return cfem_assemble(ctx, mesh, 1, rhs_fn, out, info);
+}
+
+yfd_status yfd_cfem_assemble_p2(yfd_ctx *ctx, yfd_mesh *mesh, int rhs_fn, yfd_system **out, yfd_assembly_info *info)
+{
+    return cfem_assemble(ctx, mesh, 2, rhs_fn, out, info);
+}
+
+yfd_status yfd_cfem_node_count(const yfd_system *sys, int64_t *nnodes)
+{
+    if (!sys || !nnodes) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->kind != YFD_SYS_CFEM) return fail(sys->ctx, YFD_ERR_INVALID_ARGUMENT, "not a CFEM system");
+    *nnodes = sys->npoints;
+    return YFD_OK;
+}
+
+yfd_status yfd_cfem_l2_error(yfd_ctx *ctx, yfd_mesh *mesh, int order, int ref_fn, const double *expanded, double *l2_errsq)
+{
+    if (!ctx || !mesh || !expanded || !l2_errsq) return YFD_ERR_INVALID_ARGUMENT;
+    if (mesh->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "mesh belongs to another context");
+    if (mesh->nv != 3) return fail(ctx, YFD_ERR_UNSUPPORTED, "continuous FEM is defined on triangles only (methods/cfem.hpp:31-89)");
+    if (order != 1 && order != 2) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "order must be 1 or 2");
+    scoped_device dev(ctx->device);
+    const int64_t nn = order == 2 ? mesh->npoints + mesh->nfaces : mesh->npoints, nc = mesh->ncells;
+    *l2_errsq = 0.0;
+    if (nc == 0) return YFD_OK;
+    dbuf<double> d_ex, partial, total;
+    YFD_TRY(d_ex.alloc(ctx, (size_t) nn));
+    YFD_TRY(partial.alloc(ctx, (size_t) nc));
+    YFD_TRY(total.alloc(ctx, 1));
+    YFD_TRY(d_ex.upload(ctx, expanded, (size_t) nn));
+    tri_rule rule;
+    YFD_TRY(dunavant_rule_for_degree(ctx, 6, &rule));
+    YFD_LAUNCH(ctx, cfem_cell_errsq, (unsigned) ceil_div(nc, 128), 128, 0, (const double2 *) mesh->points.p, mesh->cells.p, mesh->cell_faces.p,
+               nc, mesh->npoints, order, d_ex.p, ref_fn, rule.cw, rule.n, partial.p);
+    YFD_LAUNCH(ctx, cfem_sum_fixed, 1, 1024, 0, partial.p, nc, total.p);
+    return total.download(ctx, l2_errsq, 1);
 }
 
 yfd_status yfd_cfem_expand(yfd_system *sys, const double *sol, double *expanded)
