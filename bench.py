@@ -585,7 +585,12 @@ def main():
     roofline = {"bound": "hbm", "kernel": ("csr_spmv" if cfem else "dg_spmv_tma") + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": sp["csr_bytes"], "kernel_requested_bytes_per_launch": sp["kernel_bytes"],
-                "kernel_requested_gbs": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9, "ms_per_launch": sp["ms"]}
+                "kernel_requested_gbs": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9, "ms_per_launch": sp["ms"],
+                "hw_frac": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9 / peak,
+                "note": "achieved = the CSR SpMV's algorithmic bytes (12 B per nonzero + vectors, SURVEY.md 8d) per launch / measured launch time; "
+                        "the kernel itself requests kernel_requested_bytes_per_launch (DG: 8 B per nonzero, the block layout stores no "
+                        "column indices), so hw_frac = kernel_requested_gbs / peak is the fraction of the HBM peak the hardware sustains "
+                        "and frac can exceed 1"}
     # whole CG iteration (SpMV + 2 fused vector kernels) over the timed solve: B_cg = B_spmv + 72 n,
     # summed over ranks
     it = max(1, info["iterations"])
@@ -650,7 +655,10 @@ def main():
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
                                          "host_wall_assemble_call": info["host_ms_assemble"], "host_wall_solve_call": info["host_ms_solve"]},
                            "cg_iteration_gbs": cg_gbs, "parallelism": "1 GPU" if world == 1 else "contiguous blocks of the Z-curve cell order over %d GPUs: rank 0 holds %d rows + %d halo dofs; "
-                                          "transport: %s (per CG iteration one halo exchange and 2 scalar all-reduces)" % (world, info["n_local"], info["n_halo"], info.get("transport"))},
+                                          "transport: %s (%s)" % (world, info["n_local"], info["n_halo"], info.get("transport"),
+                                                                  "per CG iteration 2 cross-rank scalar sums through NVLink peer memory; no exchange of d: every rank advances its halo "
+                                                                  "copies of r and d from the neighbours' y = A d, stored into its landing zone ahead of the r.r sum"
+                                                                  if info.get("transport") == "peer memory" else "per CG iteration one halo exchange and 2 scalar all-reduces")},
                 "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
         print(json.dumps(line))
     ctx.close()

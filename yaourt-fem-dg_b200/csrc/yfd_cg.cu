@@ -105,6 +105,17 @@ cg_init(const double *__restrict__ b, const double *__restrict__ y /* A x0 or nu
     (void) history; (void) history_cap;
 }
 
+/* start-up of the halo copies: r_halo has been fetched from the owners; z = iM r, d = z as in cg_init */
+__global__ void cg_init_halo(const double *__restrict__ r, double *__restrict__ z, double *__restrict__ d,
+                             const double *__restrict__ pc, int64_t n, int64_t nh)
+{
+    for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + nh; i += (int64_t) gridDim.x * blockDim.x) {
+        const double zi = pc ? pc[i] * r[i] : r[i];
+        if (pc) z[i] = zi;
+        d[i] = zi;
+    }
+}
+
 __global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap)
 {
     const double nr = sqrt(sc->rr_new);
@@ -117,21 +128,42 @@ __global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__
 }
 
 /* ---- K2 ------------------------------------------------------------------------------------ */
+/* Peer-memory transport (several ranks, yfd_peer.cu): what the neighbours need each iteration is not d but y = A d on
+ * the cells they hold as halo -- with it they advance their own halo copies of r, z and d by the same recurrences
+ * (cg_update_d), bit for bit what the owner computes.  The stores go out here, BEFORE this kernel's cross-rank sum of
+ * r.r, whose flags (raised after a system fence) therefore also announce the halo data: the iteration needs no
+ * separate halo exchange and no third synchronisation. */
+struct halo_send {
+    const int32_t *lidx, *rank, *dst;       /* per packed cell: local index, destination rank, cell slot there */
+    int64_t nsend;
+    int bs;
+};
+
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict__ z,
              const double *__restrict__ d, const double *__restrict__ y, const double *__restrict__ pc, int64_t n,
-             cg_scalars *__restrict__ sc, double *__restrict__ partials)
+             cg_scalars *__restrict__ sc, double *__restrict__ partials, halo_send hs)
 {
     if (sc->done) return;
     const double alpha = sc->rho / sc->dy;                 /* core/solvers.hpp:117-118 */
     double rr = 0.0, rz = 0.0;
     const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    if (hs.nsend > 0) {
+        const peer_view *pv = sc->peer;
+        const int64_t ns = hs.nsend * hs.bs;
+        for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < ns; t += stride) {
+            const int64_t c = t / hs.bs;
+            const int j = (int) (t - c * hs.bs);
+            pv->land[hs.rank[c]][(int64_t) hs.dst[c] * hs.bs + j] = y[(int64_t) hs.lidx[c] * hs.bs + j];
+        }
+        __threadfence_system();                            /* ordered before this block's ticket in grid_sum */
+    }
     const int64_t n2 = n >> 1;
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
         double2 xv = reinterpret_cast<double2 *>(x)[i], rv = reinterpret_cast<double2 *>(r)[i];
         const double2 dv = reinterpret_cast<const double2 *>(d)[i], yv = reinterpret_cast<const double2 *>(y)[i];
         xv.x += alpha * dv.x; xv.y += alpha * dv.y;
-        rv.x -= alpha * yv.x; rv.y -= alpha * yv.y;
+        rv.x = fma(-alpha, yv.x, rv.x); rv.y = fma(-alpha, yv.y, rv.y);
         reinterpret_cast<double2 *>(x)[i] = xv;
         reinterpret_cast<double2 *>(r)[i] = rv;
         rr += rv.x * rv.x + rv.y * rv.y;
@@ -144,7 +176,7 @@ cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict_
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
         const int64_t i = n - 1;
-        const double xi = x[i] + alpha * d[i], ri = r[i] - alpha * y[i];
+        const double xi = x[i] + alpha * d[i], ri = fma(-alpha, y[i], r[i]);
         x[i] = xi; r[i] = ri;
         rr += ri * ri;
         if (pc) { const double zi = pc[i] * ri; z[i] = zi; rz += ri * zi; }
@@ -155,21 +187,39 @@ cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict_
 }
 
 /* ---- K3 ------------------------------------------------------------------------------------ */
+/* halo rows (peer-memory transport): rows [n, n + nh) of r / z / d / pc are this rank's copies of the neighbours'
+ * boundary cells; y_halo is where the neighbours stored y = A d for them (cg_update_xr) */
+struct halo_rows {
+    double *r, *z;              /* full vectors [owned | halo]; z null without preconditioner */
+    const double *pc;           /* [owned | halo] or null */
+    const double *y_halo;       /* landing zone, indexed like the vectors */
+    int64_t nh;
+};
+
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, else r */, int64_t n,
-            cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap)
+            cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap, halo_rows hr)
 {
     if (sc->done) return;
     const double beta = sc->rz_new / sc->rho;              /* core/solvers.hpp:121 / :226 */
+    const double alpha = sc->rho / sc->dy;                 /* the alpha cg_update_xr used this iteration */
     const int64_t stride = (int64_t) gridDim.x * blockDim.x;
     const int64_t n2 = n >> 1;
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
         const double2 zv = reinterpret_cast<const double2 *>(zr)[i];
         double2 dv = reinterpret_cast<double2 *>(d)[i];
-        dv.x = zv.x + beta * dv.x; dv.y = zv.y + beta * dv.y;
+        dv.x = fma(beta, dv.x, zv.x); dv.y = fma(beta, dv.y, zv.y);
         reinterpret_cast<double2 *>(d)[i] = dv;
     }
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) d[n - 1] = zr[n - 1] + beta * d[n - 1];
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) d[n - 1] = fma(beta, d[n - 1], zr[n - 1]);
+    /* the same two recurrences on the halo copies, from the neighbours' y */
+    for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + hr.nh; i += stride) {
+        const double ri = fma(-alpha, __ldcg(&hr.y_halo[i]), hr.r[i]);
+        hr.r[i] = ri;
+        double zi = ri;
+        if (hr.pc) { zi = hr.pc[i] * ri; hr.z[i] = zi; }
+        d[i] = fma(beta, d[i], zi);
+    }
     /* bookkeeping by the last block: every other block has already read rho / rz_new */
     __shared__ bool last;
     __syncthreads();
@@ -338,13 +388,28 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
         YFD_TRY(ensure_peer_region(ctx, (size_t) (pl->max_local_cells * op.bs) + 8));
         peer = ctx->peer_enabled;
-        if (!peer) YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));
+        YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));     /* NCCL: every iteration; peer: start-up only */
     }
-    YFD_TRY(r.alloc(ctx, (size_t) n, 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
-    /* peer transport: d = [owned | halo] lives in this rank's landing zone, where the neighbours store its halo part */
-    if (!peer) YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2));
-    double *const dv = peer ? ctx->peer_land : d.p;
-    if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) n, 2));
+    /* peer transport: r, z, d and the Jacobi diagonal carry halo copies that each rank advances itself from the
+     * neighbours' y (cg_update_xr / cg_update_d); this rank's landing zone receives that y */
+    const int64_t nh = peer ? nhalo_dofs : 0;
+    dbuf<double> pc_ext;
+    YFD_TRY(r.alloc(ctx, (size_t) (n + nh), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2));
+    double *const dv = d.p;
+    if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) (n + nh), 2));
+    if (d_pc && peer) {                                    /* Jacobi diagonal of the halo cells, fetched once */
+        YFD_TRY(pc_ext.alloc(ctx, (size_t) (n + nh), 2));
+        YFD_CUDA(ctx, cudaMemcpyAsync(pc_ext.p, d_pc, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+        YFD_TRY(halo_exchange(ctx, *pl, op.bs, pc_ext.p, sendbuf.p));
+        d_pc = pc_ext.p;
+    }
+    halo_send hsend = { nullptr, nullptr, nullptr, 0, op.bs };
+    halo_rows hrows = { nullptr, nullptr, nullptr, nullptr, 0 };
+    if (peer) {
+        hsend.lidx = pl->send_lidx.p; hsend.rank = pl->send_rank.p; hsend.dst = pl->send_dst.p; hsend.nsend = pl->nsend;
+        hrows.r = r.p; hrows.z = d_pc ? z.p : nullptr; hrows.pc = d_pc; hrows.y_halo = ctx->peer_land; hrows.nh = nh;
+    }
     YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
     YFD_TRY(sc.alloc(ctx, 1));
     int64_t hcap = 0;
@@ -374,6 +439,11 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
         YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
+        if (peer) {                                       /* halo copies of r0 (fetched once), then z0 and d0 from them */
+            YFD_TRY(halo_exchange(ctx, *pl, op.bs, r.p, sendbuf.p));
+            if (nh > 0) YFD_LAUNCH(ctx, cg_init_halo, (unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0,
+                                   (const double *) r.p, z.p, dv, d_pc, n, nh);
+        }
     }
 
     /* YFD_CG_TRACE=1: time 200 iterations kernel by kernel with CUDA events (no graph) and print the averages; the
@@ -385,15 +455,15 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         for (int it = 0; it < NT; it++) {
             cudaEvent_t *e = &ev[(size_t) it * (NK + 1)];
             cudaEventRecord(e[0], ctx->stream);
-            if (pl) { if (peer) YFD_TRY(halo_put_launch(ctx, *pl, op.bs, dv, sc.p)); else YFD_TRY(halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p)); }
+            if (pl && !peer) YFD_TRY(halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p));
             cudaEventRecord(e[1], ctx->stream);
             YFD_TRY(launch_spmv<true>(ctx, op, dv, y.p, sc.p, partials.p));
             if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->dy, 1));
             cudaEventRecord(e[2], ctx->stream);
-            cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p);
+            cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p, hsend);
             if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
             cudaEventRecord(e[3], ctx->stream);
-            cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
+            cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap, hrows);
             cudaEventRecord(e[4], ctx->stream);
             ctx->launches += 2;
         }
@@ -415,7 +485,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
     yfd_status cap_st = YFD_OK;
     for (int it = 0; it < batch && cap_st == YFD_OK; it++) {
-        if (pl) { cap_st = peer ? halo_put_launch(ctx, *pl, op.bs, dv, sc.p) : halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p); if (cap_st != YFD_OK) break; }
+        if (pl && !peer) { cap_st = halo_exchange(ctx, *pl, op.bs, dv, sendbuf.p); if (cap_st != YFD_OK) break; }
         if (normal) {                                   /* y = trans(A)*A*d (core/solvers.hpp:112-113) */
             cap_st = launch_spmv<false>(ctx, op, dv, t_ad.p, sc.p, partials.p);
             if (cap_st != YFD_OK) break;
@@ -427,9 +497,9 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         }
         if (cap_st != YFD_OK) break;
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
-        cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p);
+        cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p, hsend);
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
-        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap);
+        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap, hrows);
         ctx->launches += 2;
     }
     {

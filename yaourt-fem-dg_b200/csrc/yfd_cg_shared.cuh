@@ -133,9 +133,6 @@ template <bool WITH_DOT>
 yfd_status launch_csr_spmv_tma(yfd_ctx *ctx, const int64_t *rowptr, const int32_t *colidx, const double *values, int64_t nrows,
                                int64_t max_chunk_nnz, const double *x, double *y, cg_scalars *sc, double *partials);
 
-/* yfd_peer.cu */
-yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d, cg_scalars *sc);
-
 template <bool WITH_DOT>
 yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellptr, const int32_t *blk_cell, const double *values,
                               int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials);

@@ -17,16 +17,13 @@
 
 /* ---- peer-memory (NVLink / NVSwitch) control structures: every rank allocates one region with cudaMalloc,
  * the ranks swap CUDA IPC handles once, and from then on device code stores straight into its peers' regions
- * (yfd_peer.cu).  Layout of a region: [ peer_ctl | landing zone for halo dofs ]. ---- */
+ * (yfd_peer.cu).  Layout of a region: [ peer_ctl | landing zone for the neighbours' y = A d on this rank's halo cells ]. ---- */
 constexpr int YFD_MAX_RANKS = 16;
 struct peer_slot { double v[2]; unsigned long long flag, pad; };
 struct peer_ctl {
     unsigned long long red_epoch[4];            /* local counters, one per reduction kind            */
-    unsigned long long halo_epoch;              /* local counter of halo exchanges                   */
-    unsigned int       halo_ticket, pad0;
-    unsigned long long pad1[2];
+    unsigned long long pad1[4];
     peer_slot          red[2][4][YFD_MAX_RANKS]; /* [epoch parity][kind][source rank], written by peers */
-    unsigned long long halo_flag[YFD_MAX_RANKS]; /* [source rank] = epoch of the halo data it has delivered */
 };
 struct peer_view {                              /* lives in device memory, one per context             */
     peer_ctl *ctl[YFD_MAX_RANKS];               /* ctl[q]: rank q's control block as seen from here    */

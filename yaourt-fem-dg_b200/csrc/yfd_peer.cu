@@ -8,12 +8,17 @@
  *   - a reduction's last block stores its partial sums into a slot on every rank, fences, raises a flag, then
  *     spins until the flags of all ranks for this epoch are up and adds the slots IN RANK ORDER -- every rank
  *     gets the same bits, so `done` flips on all ranks in the same iteration (cg_shared.cuh: xrank_sum);
- *   - the direction vector d = [owned | halo] of every rank lives IN its landing zone, and halo_put stores the
- *     dofs of the cells a neighbour needs straight into the halo part of that neighbour's d; its last block
- *     signals the neighbours and waits for theirs.
+ *   - there is no per-iteration halo exchange of the direction vector at all: every rank keeps halo copies of r, z
+ *     and d and advances them itself with the recurrences the owner uses (same operands, same FMAs, same bits).
+ *     What it needs for that is y = A d on its halo cells, which the owner stores straight into this rank's landing
+ *     zone from cg_update_xr (yfd_cg.cu) BEFORE that kernel's cross-rank sum of r.r -- the sum's flags, raised after
+ *     a system fence, announce the halo data too.  One iteration = 3 kernels and 2 synchronisations (the two dot
+ *     products CG cannot do without), against 4 kernels and 3 synchronisations with an explicit exchange.
  * Epoch counters live on the device and advance inside the kernels, so the whole iteration stays inside one
  * CUDA graph with no host or NCCL involvement.  Every rank runs one kernel at a time on its own GPU and
  * writes before it waits, so the spins cannot deadlock; they are bounded anyway and raise comm_error.
+ * The landing zone is single-buffered: a neighbour's next store into it follows that neighbour's next d.y sum, which
+ * needs this rank's SpMV of the next iteration to have finished, i.e. comes after this rank has consumed the zone.
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
@@ -99,60 +104,6 @@ yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles)
     ctx->peer_land_cap = cap;
     ctx->peer_land = pv.land[ctx->rank];
     ctx->peer_enabled = true;
-    return YFD_OK;
-}
-
-/* ---- halo exchange by direct stores ---------------------------------------------------------- */
-__global__ void __launch_bounds__(256)
-halo_put(const double *d, const int32_t *__restrict__ send_lidx,
-         const int32_t *__restrict__ send_rank, const int32_t *__restrict__ send_dst, int64_t nsend, int bs,
-         const int32_t *__restrict__ peers, int npeers, cg_scalars *__restrict__ sc)
-{
-    if (sc->done) return;
-    const peer_view *pv = sc->peer;
-    const int64_t n = nsend * bs;
-    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t) gridDim.x * blockDim.x) {
-        const int64_t s = t / bs;
-        const int j = (int) (t - s * bs);
-        pv->land[send_rank[s]][(int64_t) send_dst[s] * bs + j] = d[(int64_t) send_lidx[s] * bs + j];
-    }
-    /* last block: all stores of this rank are out -> signal the neighbours, wait for theirs, move the landed dofs */
-    __shared__ bool last;
-    __shared__ int bad;
-    __threadfence_system();
-    __syncthreads();
-    peer_ctl *me = pv->ctl[pv->me];
-    if (threadIdx.x == 0) {
-        last = atomicInc(&me->halo_ticket, gridDim.x - 1) == gridDim.x - 1;
-        bad = 0;
-    }
-    __syncthreads();
-    if (!last) return;
-    __shared__ unsigned long long epoch;
-    if (threadIdx.x == 0) { epoch = me->halo_epoch + 1; me->halo_epoch = epoch; }
-    __syncthreads();
-    __threadfence_system();
-    if ((int) threadIdx.x < npeers) {
-        const int q = peers[threadIdx.x];
-        *((volatile unsigned long long *) &pv->ctl[q]->halo_flag[pv->me]) = epoch;
-        long long spins = 0;
-        while (*((volatile unsigned long long *) &me->halo_flag[q]) < epoch)
-            if (++spins > (1ll << 28)) { bad = 1; break; }
-    }
-    __syncthreads();
-    __threadfence_system();
-    if (bad && threadIdx.x == 0) { sc->comm_error = 1; sc->done = 1; }
-    /* nothing to move: the neighbours stored straight into the halo part of d (d lives in the landing zone) */
-}
-
-yfd_status halo_put_launch(yfd_ctx *ctx, const dist_plan &pl, int bs, double *d, cg_scalars *sc)
-{
-    if (pl.nranks <= 1 || pl.peers.empty()) return YFD_OK;
-    const int64_t n = pl.nsend * bs;
-    int64_t grid = ceil_div(n > 0 ? n : 1, 256);
-    if (grid > ctx->sm_count) grid = ctx->sm_count;
-    YFD_LAUNCH(ctx, halo_put, (unsigned) grid, 256, 0, d, pl.send_lidx.p, pl.send_rank.p, pl.send_dst.p,
-               pl.nsend, bs, pl.d_peers.p, (int) pl.peers.size(), sc);
     return YFD_OK;
 }
 
