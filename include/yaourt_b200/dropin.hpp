@@ -9,6 +9,7 @@
  *                                                        replaces core/blaze_sparse_init.hpp:125-155 (+ reduce_triplets :101-122)
  *   conjugated_gradient(cgp, A, b, x)                    replaces core/solvers.hpp:46-138
  *   conjugated_gradient(cgp, A, b, x, iM)                replaces core/solvers.hpp:141-243 (iM diagonal, methods/dg.hpp:133-142)
+ *   bicgstab(cgp, A, b, x[, iM])                         replaces core/solvers.hpp:246-354 / :356-467
  *
  * with exactly the reference's signatures.  A non-template function beats a template of equal conversion rank,
  * and the reference's call sites (methods/dg.hpp:130,141; methods/cfem.hpp:184; dg2d_diffusion.cpp:217-219;
@@ -41,7 +42,7 @@ inline cg_report &last_cg_report()
 
 inline bool cg_impl(const conjugated_gradient_params<double> &cgp, const blaze::CompressedMatrix<double> &A,
                     const blaze::DynamicVector<double> &b, blaze::DynamicVector<double> &x,
-                    const blaze::CompressedMatrix<double> *iM)
+                    const blaze::CompressedMatrix<double> *iM, bool use_bicgstab = false)
 {
     /* the reference's shape checks and messages (core/solvers.hpp:53-77) */
     if (A.rows() != A.columns()) { if (cgp.verbose) std::cout << "[CG solver] A square matrix is required" << std::endl; return false; }
@@ -74,8 +75,8 @@ inline bool cg_impl(const conjugated_gradient_params<double> &cgp, const blaze::
     std::vector<double> hist(cgp.save_iteration_history ? cgp.max_iter + 1 : 0);
     yfd_cg_info info;
     std::vector<double> xs(x.data(), x.data() + N);
-    const yfd_status st = yfd_cg_solve(ctx.get(), dA, b.data(), xs.data(), iM ? pc.data() : nullptr, &p, &info,
-                                       hist.empty() ? nullptr : hist.data(), (int64_t) hist.size());
+    const yfd_status st = (use_bicgstab ? yfd_bicgstab_solve : yfd_cg_solve)(ctx.get(), dA, b.data(), xs.data(), iM ? pc.data() : nullptr, &p, &info,
+                                                                           hist.empty() ? nullptr : hist.data(), (int64_t) hist.size());
     yfd_csr_destroy(dA);
     check(ctx.get(), st);
     for (size_t i = 0; i < N; i++) x[i] = xs[i];
@@ -149,4 +150,18 @@ inline bool conjugated_gradient(const conjugated_gradient_params<double> &cgp, c
                                 const blaze::CompressedMatrix<double> &iM)
 {
     return yaourt::b200::cg_impl(cgp, A, b, x, &iM);
+}
+
+/* bicgstab (core/solvers.hpp:246-354 and :356-467): same parameter struct, shape checks and return convention */
+inline bool bicgstab(const conjugated_gradient_params<double> &cgp, const blaze::CompressedMatrix<double> &A,
+                     const blaze::DynamicVector<double> &b, blaze::DynamicVector<double> &x)
+{
+    return yaourt::b200::cg_impl(cgp, A, b, x, nullptr, true);
+}
+
+inline bool bicgstab(const conjugated_gradient_params<double> &cgp, const blaze::CompressedMatrix<double> &A,
+                     const blaze::DynamicVector<double> &b, blaze::DynamicVector<double> &x,
+                     const blaze::CompressedMatrix<double> &iM)
+{
+    return yaourt::b200::cg_impl(cgp, A, b, x, &iM, true);
 }

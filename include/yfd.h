@@ -341,6 +341,16 @@ yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc,
 yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
                         const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
 
+/* BiCGStab: replaces yaourt::bicgstab, both overloads (core/solvers.hpp:246-354 without, :356-467 with iM), for   */
+/* non-symmetric systems (yfd_dg_assemble_advection).  Same parameter struct and stopping rule as the CG            */
+/* (conjugated_gradient_params, :311), same history convention, and the reference's restart r = b - A x; r0 = r     */
+/* whenever |r.r0| < 1e-9 (:327-335, an ABSOLUTE threshold: the common path once the residual is small), decided     */
+/* and executed on the device.  iM is a diagonal.  YFD_ERR_UNSUPPORTED: use_normal_eqns, distributed systems.        */
+yfd_status yfd_system_solve_bicgstab(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                     double *x, yfd_cg_info *info, double *history, int64_t history_cap);
+yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                              const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
+
 /* Time `reps` launches of y = A d for this system with CUDA events on the context's stream
  * (bench.py's roofline leg).  Returns average ms per launch and the algorithmic CSR bytes of one
  * launch (12 nnz + 8 (n+1) + 16 n) plus the bytes the kernel actually

@@ -165,6 +165,23 @@ class Oracle:
             raise ValueError("shape mismatch")
         return dict(x=x, iterations=it, nr0=nr0.value, nr=nr.value, history=hist[:it + 1].copy() if history else None)
 
+    def bicgstab(self, rowptr, colidx, values, b, pc_diag=None, rr_tol=1e-8, rr_max=20.0, max_iter=100, x0=None, history=True):
+        """bicgstab, both overloads (core/solvers.hpp:246-467)."""
+        rowptr = _c(rowptr, np.int64); colidx = _c(colidx, np.int64); values = _c(values, np.float64); b = _c(b, np.float64)
+        n = len(b)
+        x = np.zeros(n) if x0 is None else _c(x0, np.float64).copy()
+        pc = None if pc_diag is None else _c(pc_diag, np.float64)
+        cap = int(max_iter) + 2 if history else 0
+        hist = np.empty(max(cap, 1))
+        nr0, nr = C.c_double(), C.c_double()
+        f = self.lib.yfo_bicgstab
+        f.restype = C.c_int64
+        f.argtypes = [C.c_int64, _i64p, _i64p, _f64p, _f64p, _f64p, C.c_void_p, C.c_double, C.c_double, C.c_int64, C.c_int,
+                      C.c_void_p, C.c_int64, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        it = f(n, rowptr, colidx, values, b, x, None if pc is None else pc.ctypes.data_as(C.c_void_p), rr_tol, rr_max,
+               int(max_iter), int(x0 is not None), hist.ctypes.data_as(C.c_void_p) if history else None, cap, C.byref(nr0), C.byref(nr))
+        return dict(x=x, iterations=it, nr0=nr0.value, nr=nr.value, history=hist[:it + 1].copy() if history else None)
+
     # ---- CFEM P1 (methods/cfem.hpp, continuous_fem.cpp) ----
     def cfem_p1(self, points, cells, faces, face_boundary, rhs_fn=1):
         points = _c(points, np.float64); cells = _c(cells, np.int64); faces = _c(faces, np.int64)

@@ -354,6 +354,54 @@ void yfd_ref_face_geometry(int64_t cell, int local_face, double *nxy, double *di
     if (M.type == 0) doit(M.tri); else doit(M.quad);
 }
 
+/* bicgstab as shipped (core/solvers.hpp:246-354 without iM, :356-467 with iM), called on a matrix given in CSR.
+ * No reference driver calls it, so the harness does: A is rebuilt as a blaze::CompressedMatrix entry by entry, iM as the
+ * diagonal matrix the drivers build for the CG (dg2d_diffusion.cpp:200-212).  The iteration count and nr/nr0 per
+ * iteration come from the reference's own history file (6 significant digits, :320-321,:349-353).  Returns the
+ * number of history entries (iterations + 1), -1 on a shape error. */
+int64_t yfd_ref_bicgstab(int64_t n, const int64_t *rowptr, const int64_t *colidx, const double *values, const double *b,
+                         double *x, const double *pc_diag, double rr_tol, double rr_max, int64_t max_iter,
+                         int use_initial_guess, double *history, int64_t history_cap)
+{
+    using namespace yfd_ref;
+    if (n < 0) return -1;
+    blaze::CompressedMatrix<double> A((size_t) n, (size_t) n);
+    A.reserve((size_t) rowptr[n]);
+    for (int64_t i = 0; i < n; i++) {
+        for (int64_t q = rowptr[i]; q < rowptr[i + 1]; q++) A.append((size_t) i, (size_t) colidx[q], values[q]);
+        A.finalize((size_t) i);
+    }
+    blaze::DynamicVector<double> bv((size_t) n), xv((size_t) n);
+    for (int64_t i = 0; i < n; i++) { bv[i] = b[i]; xv[i] = use_initial_guess ? x[i] : 0.0; }
+    conjugated_gradient_params<double> cgp;
+    cgp.rr_tol = rr_tol; cgp.rr_max = rr_max; cgp.max_iter = (size_t) max_iter;
+    cgp.verbose = false;
+    cgp.use_initial_guess = use_initial_guess != 0;
+    cgp.save_iteration_history = true;
+    char path[256];
+    snprintf(path, sizeof(path), "/tmp/yfd_ref_bicgstab_%ld.txt", (long) getpid());
+    cgp.history_filename = path;
+    {
+        quiet q;
+        if (pc_diag) {
+            blaze::CompressedMatrix<double> iM((size_t) n, (size_t) n);
+            iM.reserve((size_t) n);
+            for (int64_t i = 0; i < n; i++) { iM.append((size_t) i, (size_t) i, pc_diag[i]); iM.finalize((size_t) i); }
+            ::bicgstab(cgp, A, bv, xv, iM);
+        } else {
+            ::bicgstab(cgp, A, bv, xv);
+        }
+    }
+    for (int64_t i = 0; i < n; i++) x[i] = xv[i];
+    int64_t cnt = 0;
+    std::ifstream ifs(path);
+    double h;
+    while (ifs >> h) { if (history && cnt < history_cap) history[cnt] = h; cnt++; }
+    ifs.close();
+    unlink(path);
+    return cnt;
+}
+
 int yfd_ref_num_threads(void)
 {
 #ifdef _OPENMP

@@ -58,6 +58,23 @@ class Ref:
         L.yfd_ref_basis_eval.argtypes = [C.c_int64, C.c_int, C.c_double, C.c_double, _f64p, _f64p]
         L.yfd_ref_face_geometry.argtypes = [C.c_int64, C.c_int, _f64p, C.POINTER(C.c_double)]
         L.yfd_ref_num_threads.restype = C.c_int
+        L.yfd_ref_bicgstab.restype = C.c_int64
+        L.yfd_ref_bicgstab.argtypes = [C.c_int64, _i64p, _i64p, _f64p, _f64p, _f64p, C.c_void_p, C.c_double, C.c_double, C.c_int64,
+                                       C.c_int, _f64p, C.c_int64]
+
+    def bicgstab(self, rowptr, colidx, values, b, pc_diag=None, rr_tol=1e-8, rr_max=20.0, max_iter=100, x0=None):
+        """The reference's own bicgstab (core/solvers.hpp:246-467) on a CSR matrix; history = its history file (6 digits)."""
+        rowptr = np.ascontiguousarray(rowptr, np.int64); colidx = np.ascontiguousarray(colidx, np.int64)
+        values = np.ascontiguousarray(values, np.float64); b = np.ascontiguousarray(b, np.float64)
+        n = len(b)
+        x = np.zeros(n) if x0 is None else np.ascontiguousarray(x0, np.float64).copy()
+        pc = None if pc_diag is None else np.ascontiguousarray(pc_diag, np.float64)
+        hist = np.empty(int(max_iter) + 2)
+        cnt = self.lib.yfd_ref_bicgstab(n, rowptr, colidx, values, b, x, None if pc is None else pc.ctypes.data_as(C.c_void_p),
+                                        rr_tol, rr_max, int(max_iter), int(x0 is not None), hist, len(hist))
+        if cnt < 0:
+            raise ValueError("shape mismatch")
+        return dict(x=x, iterations=int(cnt) - 1, history=hist[:cnt].copy())
 
     # ---- mesh -----------------------------------------------------------
     def mesh(self, mtype, levels, shatter=False):

@@ -173,6 +173,8 @@ def lib():
         "yfd_system_solve_cg": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
         "yfd_system_solve_cg_device": (cint, [vp, vp, cint, P(CgParams), vp, P(CgInfo)]),
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
+        "yfd_bicgstab_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
+        "yfd_system_solve_bicgstab": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
         "yfd_dg_postprocess": (cint, [vp, vp, cint, cint, _f64p, P(dbl), P(dbl)]),
         "yfd_dg_postprocess_device": (cint, [vp, vp, cint, cint, vp, P(dbl), P(dbl)]),
@@ -510,6 +512,18 @@ class Csr:
         call = lambda p, x, info, h, cap: lib().yfd_cg_solve(self.ctx._h, self._h, b, x, _ptr(pc), C.byref(p), C.byref(info), h, cap)
         return _solve_common(self.ctx, call, self.nrows, params, x0, history)
 
+    def solve_bicgstab(self, b, params=None, pc_diag=None, x0=None, history=False):
+        """bicgstab(cgp, A, b, x[, iM]) (core/solvers.hpp:246,356); iM diagonal."""
+        b = np.ascontiguousarray(b, np.float64)
+        if b.shape != (self.nrows,):
+            raise YfdError(8, "[CG solver] Wrong size of RHS vector")
+        pc = None if pc_diag is None else np.ascontiguousarray(pc_diag, np.float64)
+        call = lambda p, x, info, h, cap: lib().yfd_bicgstab_solve(self.ctx._h, self._h, b, x, _ptr(pc), C.byref(p), C.byref(info), h, cap)
+        if x0 is not None:
+            params = params or CgParams()
+            params.use_initial_guess = 1
+        return _solve_common(self.ctx, call, self.nrows, params, x0, history)
+
 
 class System:
     """An assembled problem on the device: assm.lhs / assm.rhs / assm.pc (yfd_system)."""
@@ -548,6 +562,14 @@ class System:
 
     def solve_cg(self, params=None, use_pc=False, x0=None, history=False):
         call = lambda p, x, info, h, cap: lib().yfd_system_solve_cg(self.ctx._h, self._h, int(use_pc), C.byref(p), x, C.byref(info), h, cap)
+        if x0 is not None:
+            params = params or CgParams()
+            params.use_initial_guess = 1
+        return _solve_common(self.ctx, call, self.n, params, x0, history)
+
+    def solve_bicgstab(self, params=None, use_pc=False, x0=None, history=False):
+        """bicgstab on the assembled system, matrix resident on the device (core/solvers.hpp:246-467)."""
+        call = lambda p, x, info, h, cap: lib().yfd_system_solve_bicgstab(self.ctx._h, self._h, int(use_pc), C.byref(p), x, C.byref(info), h, cap)
         if x0 is not None:
             params = params or CgParams()
             params.use_initial_guess = 1

@@ -546,6 +546,10 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     return YFD_OK;
 }
 
+#include "yfd_bicgstab.cuh"
+
+enum solver_method { SOLVER_CG = 0, SOLVER_BICGSTAB = 1 };
+
 static spmv_op op_of_csr(const yfd_csr *A)
 {
     spmv_op op;
@@ -601,8 +605,8 @@ yfd_status yfd_csr_spmv(yfd_ctx *ctx, yfd_csr *A, const double *x, double *y)
     return dy.download(ctx, y, (size_t) A->nrows);
 }
 
-yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
-                        const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap)
+static yfd_status csr_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                            const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap, int method)
 {
     if (!ctx || !A || !b || !x || !p) return YFD_ERR_INVALID_ARGUMENT;
     if (A->nrows != A->ncols) return fail(ctx, YFD_ERR_SHAPE_MISMATCH, "[CG solver] A square matrix is required");
@@ -614,6 +618,10 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
     YFD_TRY(db.upload(ctx, b, (size_t) n));
     if (p->use_initial_guess) YFD_TRY(dx.upload(ctx, x, (size_t) n));
     if (pc_diag) { YFD_TRY(dpc.alloc(ctx, (size_t) n, 2)); YFD_TRY(dpc.upload(ctx, pc_diag, (size_t) n)); }
+    if (method == SOLVER_BICGSTAB) {
+        YFD_TRY(bicgstab_device(ctx, op_of_csr(A), db.p, dx.p, pc_diag ? dpc.p : nullptr, p, info, history, history_cap));
+        return dx.download(ctx, x, (size_t) n);
+    }
     if (p->use_normal_eqns) {
         /* A^T by the same sort-based build as init_from_triplets: keys (col, row), stable, values carried along */
         yfd_csr AT;
@@ -632,9 +640,22 @@ yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, co
     return dx.download(ctx, x, (size_t) n);
 }
 
+yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                        const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    return csr_solve(ctx, A, b, x, pc_diag, p, info, history, history_cap, SOLVER_CG);
+}
+
+yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
+                              const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    return csr_solve(ctx, A, b, x, pc_diag, p, info, history, history_cap, SOLVER_BICGSTAB);
+}
+
 /* shared by the host- and device-resident entry points: x_host in/out (may be null), d_x_out device out (may be null) */
 static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
-                               double *x_host, double *d_x_out, yfd_cg_info *info, double *history, int64_t history_cap)
+                               double *x_host, double *d_x_out, yfd_cg_info *info, double *history, int64_t history_cap,
+                               int method = SOLVER_CG)
 {
     if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
     if (use_pc && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
@@ -657,7 +678,9 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         }
     }
     spmv_op opT;
-    if (p->use_normal_eqns) {
+    if (method == SOLVER_BICGSTAB) {
+        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab with use_normal_eqns");
+    } else if (p->use_normal_eqns) {
         if (!dg) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a CFEM system (symmetric): use yfd_cg_solve for a general CSR");
         if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a distributed system");
         if (sys->values_t.n == 0) {                /* built once, kept with the system */
@@ -668,8 +691,11 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         opT = op_of_system(sys, true);
         opT.values = sys->values_t.p;
     }
-    YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
-                      p->use_normal_eqns ? &opT : nullptr));
+    if (method == SOLVER_BICGSTAB)
+        YFD_TRY(bicgstab_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
+    else
+        YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
+                          p->use_normal_eqns ? &opT : nullptr));
     const double *result = dx.p;
     if (dg) {
         /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */
@@ -694,6 +720,13 @@ yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
 {
     if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
     return system_solve(ctx, sys, use_pc, p, x, nullptr, info, history, history_cap);
+}
+
+yfd_status yfd_system_solve_bicgstab(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                     double *x, yfd_cg_info *info, double *history, int64_t history_cap)
+{
+    if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
+    return system_solve(ctx, sys, use_pc, p, x, nullptr, info, history, history_cap, SOLVER_BICGSTAB);
 }
 
 yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
