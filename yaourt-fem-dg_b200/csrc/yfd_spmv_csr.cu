@@ -101,12 +101,17 @@ csr_spmv_tma(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ col
         if (lane < nr) {
             const int b = (int) (RP[lane] - lo), e = (int) (RP[lane + 1] - lo);
             double acc = 0.0;
-            int j = b;
-            for (; j + 3 < e; j += 4) {                 /* gathers issued together, sum kept left to right */
-                const double x0 = __ldg(&x[C[j]]), x1 = __ldg(&x[C[j + 1]]), x2 = __ldg(&x[C[j + 2]]), x3 = __ldg(&x[C[j + 3]]);
-                acc += V[j] * x0; acc += V[j + 1] * x1; acc += V[j + 2] * x2; acc += V[j + 3] * x3;
+            /* 8 gathers in flight per trip, the tail predicated instead of looped one by one (a 7-entry P1 row is ONE
+             * round trip to L2 instead of four: the ring leaves almost no L1 for x, and ncu shows the kernel waiting on
+             * exactly these gathers); out-of-row slots re-read the row's first column.  Sum kept left to right. */
+            for (int j = b; j < e; j += 8) {
+                double xv[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) xv[u] = __ldg(&x[C[j + u < e ? j + u : b]]);
+#pragma unroll
+                for (int u = 0; u < 8; u++)
+                    if (j + u < e) acc += V[j + u] * xv[u];
             }
-            for (; j < e; j++) acc += V[j] * __ldg(&x[C[j]]);
             y[r0 + lane] = acc;
             if (WITH_DOT) dot += acc * __ldg(&x[r0 + lane]);
         }
