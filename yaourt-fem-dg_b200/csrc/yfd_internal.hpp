@@ -304,7 +304,9 @@ namespace yfd {
 yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *d_out_ref);
 /* ---- yfd_triplets.cu ---- */
 int key_bits_for(int64_t n);
-/* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order */
+/* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order.  Entries of
+ * `discard_row` (-1: none) keep their slot but are not summed (the CFEM assemblers' sentinel row) */
 yfd_status csr_from_device_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t count,
-                                    uint64_t *d_keys, int col_bits, int row_bits, const double *d_vals, yfd_csr *A);
+                                    uint64_t *d_keys, int col_bits, int row_bits, const double *d_vals, yfd_csr *A,
+                                    int64_t discard_row = -1);
 } // namespace yfd

@@ -380,7 +380,7 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int order, int rhs_fn
     /* the fold ignores the sentinel tail: sort everything, then build from the first hc[] records.
      * A sentinel has row n, so give the builder n+1 rows and drop the last one afterwards. */
     yfd_csr full;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, ntrip, mkeys.p, col_bits, row_bits, mvals.p, &full));
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, ntrip, mkeys.p, col_bits, row_bits, mvals.p, &full, n));
     /* rows 0..n-1 of `full` are the matrix; row n holds the folded sentinel (one entry) */
     sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n;
     int64_t nnz = 0;
@@ -394,7 +394,7 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int order, int rhs_fn
     sys->A.colidx.n = (size_t) nnz; sys->A.values.n = (size_t) nnz;
 
     yfd_csr rf;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nrtrip, rkeys.p, 1, row_bits, rvals.p, &rf));
+    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nrtrip, rkeys.p, 1, row_bits, rvals.p, &rf, n));
     YFD_TRY(sys->rhs.alloc(ctx, (size_t) n, 2));
     YFD_LAUNCH(ctx, rhs_from_fold, (unsigned) ceil_div(std::max<int64_t>(n, 1), 256), 256, 0, rf.rowptr.p, rf.values.p, n, sys->rhs.p);
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
