@@ -324,8 +324,16 @@ typedef struct yfd_cg_info {
     int     transport;                    /* 0 = one GPU, 1 = NCCL calls, 2 = peer-memory stores over NVLink (yfd_peer.cu) */
 } yfd_cg_info;
 
+/* values of `use_pc` below */
+#define YFD_PC_NONE         0   /* conjugated_gradient(cgp, A, b, x)                 (core/solvers.hpp:46-138)            */
+#define YFD_PC_JACOBI       1   /* conjugated_gradient(cgp, A, b, x, assm.pc)        (:141-243; needs build_preconditioner) */
+#define YFD_PC_BLOCK_JACOBI 2   /* EXTENSION, DG systems: iM = blockdiag(A_cc)^-1, one bs x bs block */
+                                /* per cell, inverted once on the device (in-warp pivoted LU) and applied by the block     */
+                                /* SpMV; about half the iterations of the point-Jacobi CG.  Same recurrences (:196-227),   */
+                                /* same stopping rule, same solution to the solver tolerance; works on several GPUs.       */
+
 /* Solve sys.lhs x = sys.rhs on the device, no host round trip of the matrix.
- * use_pc != 0 -> the 5-argument overload with assm.pc.  x [n] in REFERENCE numbering, in/out
+ * use_pc = YFD_PC_JACOBI -> the 5-argument overload with assm.pc.  x [n] in REFERENCE numbering, in/out
  * (input read only if use_initial_guess).  history may be NULL, else cap >= max_iter+1 is not
  * required: writing stops at history_cap. */
 yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,

@@ -8,5 +8,5 @@ from .capi import (  # noqa: F401
     TRI, QUAD, FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL, FN_ADVECTION_RHS, FN_SIN_X_SOL, REORDER_NONE, REORDER_MORTON,
     YfdError, lib, lib_path, Context, HostMesh, Mesh, Csr, System, CgParams, CgInfo, AssemblyInfo,
     declared_symbols, partition_plan, Maxwell, MaxwellConfig, MaxwellInfo, MaxwellStepInfo,
-    TI_RK4, TI_EULER, FIELDS_CAVITY_11, FIELDS_ZERO,
+    TI_RK4, TI_EULER, FIELDS_CAVITY_11, FIELDS_ZERO, PC_NONE, PC_JACOBI, PC_BLOCK_JACOBI,
 )

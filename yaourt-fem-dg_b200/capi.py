@@ -21,6 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 
 TRI, QUAD = 0, 1
+PC_NONE, PC_JACOBI, PC_BLOCK_JACOBI = 0, 1, 2     # use_pc of System.solve_cg (include/yfd.h YFD_PC_*)
 TI_RK4, TI_EULER = 0, 1
 FIELDS_CAVITY_11, FIELDS_ZERO = 0, 1
 FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL, FN_ADVECTION_RHS, FN_SIN_X_SOL = 0, 1, 2, 3, 4, 5

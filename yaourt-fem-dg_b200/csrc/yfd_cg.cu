@@ -28,6 +28,7 @@
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
+#include "yfd_lu.cuh"
 #include <cmath>
 #include <algorithm>
 #include <cstdlib>
@@ -116,7 +117,8 @@ __global__ void cg_init_halo(const double *__restrict__ r, double *__restrict__ 
     }
 }
 
-__global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap)
+__global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap,
+                               cg_scalars *__restrict__ sc2 /* block-Jacobi: gate of the preconditioner launches, else null */)
 {
     const double nr = sqrt(sc->rr_new);
     sc->rho = sc->rz_new;
@@ -124,7 +126,25 @@ __global__ void cg_init_finish(cg_scalars *__restrict__ sc, double *__restrict__
     sc->iter = 0;
     const double rel = nr / nr;                /* nr/nr0 with nr0 = nr: 1, or NaN when b = A x0 exactly */
     sc->done = !(rel > sc->rr_tol && 0 < sc->max_iter && rel < sc->rr_max);
+    if (sc2) sc2->done = sc->done;
     if (history && history_cap > 0) history[0] = rel;
+}
+
+/* block-Jacobi start-up: z0 = iM r0 has been formed by the block SpMV (its fused dot r0.z0 sits in sc2->dy); d0 = z0 */
+__global__ void cg_block_init(double *__restrict__ d, const double *__restrict__ z, int64_t n, cg_scalars *__restrict__ sc,
+                              const cg_scalars *__restrict__ sc2)
+{
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) d[i] = z[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) sc->rho = sc2->dy;
+}
+
+/* peer transport + block-Jacobi: the halo copies of r must be advanced BEFORE the block preconditioner runs on them */
+__global__ void cg_halo_r(double *__restrict__ r, const double *__restrict__ y_halo, int64_t n, int64_t nh, const cg_scalars *__restrict__ sc)
+{
+    if (sc->done) return;
+    const double alpha = sc->rho / sc->dy;
+    for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + nh; i += (int64_t) gridDim.x * blockDim.x)
+        r[i] = fma(-alpha, __ldcg(&y_halo[i]), r[i]);
 }
 
 /* ---- K2 ------------------------------------------------------------------------------------ */
@@ -194,14 +214,17 @@ struct halo_rows {
     const double *pc;           /* [owned | halo] or null */
     const double *y_halo;       /* landing zone, indexed like the vectors */
     int64_t nh;
+    int z_ready;                /* block-Jacobi: r and z of the halo rows were already advanced (cg_halo_r + block SpMV) */
 };
 
 __global__ void __launch_bounds__(CG_THREADS)
 cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, else r */, int64_t n,
-            cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap, halo_rows hr)
+            cg_scalars *__restrict__ sc, double *__restrict__ history, int64_t history_cap, halo_rows hr,
+            cg_scalars *__restrict__ sc2 /* block-Jacobi: r.z is the fused dot of the preconditioner launch, in sc2->dy */)
 {
     if (sc->done) return;
-    const double beta = sc->rz_new / sc->rho;              /* core/solvers.hpp:121 / :226 */
+    const double rz_new = sc2 ? sc2->dy : sc->rz_new;
+    const double beta = rz_new / sc->rho;                  /* core/solvers.hpp:121 / :226 */
     const double alpha = sc->rho / sc->dy;                 /* the alpha cg_update_xr used this iteration */
     const int64_t stride = (int64_t) gridDim.x * blockDim.x;
     const int64_t n2 = n >> 1;
@@ -213,12 +236,16 @@ cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, 
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) d[n - 1] = fma(beta, d[n - 1], zr[n - 1]);
     /* the same two recurrences on the halo copies, from the neighbours' y */
-    for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + hr.nh; i += stride) {
-        const double ri = fma(-alpha, __ldcg(&hr.y_halo[i]), hr.r[i]);
-        hr.r[i] = ri;
-        double zi = ri;
-        if (hr.pc) { zi = hr.pc[i] * ri; hr.z[i] = zi; }
-        d[i] = fma(beta, d[i], zi);
+    if (hr.z_ready) {
+        for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + hr.nh; i += stride) d[i] = fma(beta, d[i], zr[i]);
+    } else {
+        for (int64_t i = n + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n + hr.nh; i += stride) {
+            const double ri = fma(-alpha, __ldcg(&hr.y_halo[i]), hr.r[i]);
+            hr.r[i] = ri;
+            double zi = ri;
+            if (hr.pc) { zi = hr.pc[i] * ri; hr.z[i] = zi; }
+            d[i] = fma(beta, d[i], zi);
+        }
     }
     /* bookkeeping by the last block: every other block has already read rho / rz_new */
     __shared__ bool last;
@@ -227,7 +254,7 @@ cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, 
         __threadfence();
         last = atomicInc(&sc->ticket[2], gridDim.x - 1) == gridDim.x - 1;
         if (last) {
-            sc->rho = sc->rz_new;
+            sc->rho = rz_new;
             const double nr = sqrt(sc->rr_new);            /* nr = norm(r), core/solvers.hpp:124 */
             sc->nr = nr;
             const long long it = sc->iter + 1;
@@ -235,6 +262,7 @@ cg_update_d(double *__restrict__ d, const double *__restrict__ zr /* z with pc, 
             const double rel = nr / sc->nr0;
             if (history && it < history_cap) history[it] = rel;
             sc->done = !(rel > sc->rr_tol && it < sc->max_iter && rel < sc->rr_max);
+            if (sc2) sc2->done = sc->done;
         }
     }
 }
@@ -366,10 +394,12 @@ static unsigned vec_grid(yfd_ctx *ctx, int64_t n)
 /* The solver proper: all vectors on the device, in the operator's numbering. */
 static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, double *d_x, const double *d_pc,
                             const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap,
-                            const spmv_op *opT = nullptr)
+                            const spmv_op *opT = nullptr, const spmv_op *opD = nullptr)
 {
     const int64_t n = op.nrows;
     const bool normal = p->use_normal_eqns != 0;
+    const bool block = opD != nullptr;          /* block-Jacobi: iM is a block SpMV (yfd_block_jacobi.cuh), d_pc is null */
+    if (block && (d_pc || normal || !op.cellptr)) return fail(ctx, YFD_ERR_INVALID_STATE, "internal: block preconditioner misuse");
     if (normal) {
         /* CG on A^T A x = A^T b as the advection driver runs it (dg2d_advection.cpp:225): r0 = A^T b, y = A^T (A d).
          * d.y is formed as |A d|^2 (equal in exact arithmetic, one reduction pass over A d instead of a fused one) */
@@ -397,7 +427,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_TRY(r.alloc(ctx, (size_t) (n + nh), 2)); YFD_TRY(y.alloc(ctx, (size_t) n, 2));
     YFD_TRY(d.alloc(ctx, (size_t) (n + nhalo_dofs), 2));
     double *const dv = d.p;
-    if (d_pc) YFD_TRY(z.alloc(ctx, (size_t) (n + nh), 2));
+    if (d_pc || block) YFD_TRY(z.alloc(ctx, (size_t) (n + nh), 2));
     if (d_pc && peer) {                                    /* Jacobi diagonal of the halo cells, fetched once */
         YFD_TRY(pc_ext.alloc(ctx, (size_t) (n + nh), 2));
         YFD_CUDA(ctx, cudaMemcpyAsync(pc_ext.p, d_pc, (size_t) n * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
@@ -405,13 +435,25 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         d_pc = pc_ext.p;
     }
     halo_send hsend = { nullptr, nullptr, nullptr, 0, op.bs };
-    halo_rows hrows = { nullptr, nullptr, nullptr, nullptr, 0 };
+    halo_rows hrows = { nullptr, nullptr, nullptr, nullptr, 0, 0 };
     if (peer) {
         hsend.lidx = pl->send_lidx.p; hsend.rank = pl->send_rank.p; hsend.dst = pl->send_dst.p; hsend.nsend = pl->nsend;
         hrows.r = r.p; hrows.z = d_pc ? z.p : nullptr; hrows.pc = d_pc; hrows.y_halo = ctx->peer_land; hrows.nh = nh;
+        hrows.z_ready = block ? 1 : 0;
     }
     YFD_TRY(partials.alloc(ctx, (size_t) 2 * CG_MAX_PARTIALS));
-    YFD_TRY(sc.alloc(ctx, 1));
+    YFD_TRY(sc.alloc(ctx, 2));
+    cg_scalars *const sc2 = block ? sc.p + 1 : nullptr;     /* gate + fused r.z of the block preconditioner launches */
+    const double *const zr = (d_pc || block) ? z.p : r.p;
+    /* z = iM r on the owned cells (fused dot r.z -> sc2->dy, summed over the ranks) and, on the peer transport, on the halo copies */
+    auto apply_block = [&]() -> yfd_status {
+        YFD_TRY(launch_dg_spmv_tma<true>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values, op.ncells, r.p, z.p, sc2, partials.p));
+        if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc2->dy, 1));
+        if (nh > 0)
+            YFD_TRY(launch_dg_spmv_tma<false>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values + op.ncells * (int64_t) (op.bs * op.bs),
+                                              pl->nhalo, r.p + n, z.p + n, nullptr, nullptr));
+        return YFD_OK;
+    };
     int64_t hcap = 0;
     if (p->save_iteration_history && host_history && history_cap > 0) {
         hcap = std::min<int64_t>(history_cap, p->max_iter + 1);
@@ -421,6 +463,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     h0.max_iter = p->max_iter; h0.rr_tol = p->rr_tol; h0.rr_max = p->rr_max;
     h0.peer = peer ? ctx->d_peer_view : nullptr;
     YFD_CUDA(ctx, cudaMemcpyAsync(sc.p, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
+    YFD_CUDA(ctx, cudaMemcpyAsync(sc.p + 1, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
 
     gpu_timer timer;
     timer.start(ctx->stream);
@@ -428,7 +471,11 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     if (p->use_initial_guess) {
         YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));          /* r0 = b - A x (core/solvers.hpp:91) */
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
-        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
+        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap, sc2);
+        if (block) {
+            YFD_TRY(apply_block());
+            YFD_LAUNCH(ctx, cg_block_init, vg, CG_THREADS, 0, dv, (const double *) z.p, n, sc.p, (const cg_scalars *) sc2);
+        }
     } else {
         YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
         if (normal) {                                                                        /* r0 = A^T (b - A 0) (:88-89) */
@@ -438,17 +485,20 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         }
         YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
-        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap);
-        if (peer) {                                       /* halo copies of r0 (fetched once), then z0 and d0 from them */
-            YFD_TRY(halo_exchange(ctx, *pl, op.bs, r.p, sendbuf.p));
-            if (nh > 0) YFD_LAUNCH(ctx, cg_init_halo, (unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0,
-                                   (const double *) r.p, z.p, dv, d_pc, n, nh);
+        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap, sc2);
+        if (peer) YFD_TRY(halo_exchange(ctx, *pl, op.bs, r.p, sendbuf.p));      /* halo copies of r0, fetched once */
+        if (block) {                                      /* z0 = iM r0 (owned + halo copies), d0 = z0, rho = r0.z0 */
+            YFD_TRY(apply_block());
+            YFD_LAUNCH(ctx, cg_block_init, vec_grid(ctx, n + nh), CG_THREADS, 0, dv, (const double *) z.p, n + nh, sc.p, (const cg_scalars *) sc2);
+        } else if (peer && nh > 0) {                      /* z0 and d0 of the halo copies */
+            YFD_LAUNCH(ctx, cg_init_halo, (unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0,
+                       (const double *) r.p, z.p, dv, d_pc, n, nh);
         }
     }
 
     /* YFD_CG_TRACE=1: time 200 iterations kernel by kernel with CUDA events (no graph) and print the averages; the
      * solve then continues normally.  A diagnostic for the multi-rank path, where ncu cannot be used. */
-    if (getenv("YFD_CG_TRACE") && p->max_iter > 200 && !normal) {
+    if (getenv("YFD_CG_TRACE") && p->max_iter > 200 && !normal && !block) {
         const int NT = 200, NK = 4;
         std::vector<cudaEvent_t> ev((size_t) NT * (NK + 1));
         for (auto &e : ev) cudaEventCreate(&e);
@@ -463,7 +513,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
             cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p, hsend);
             if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
             cudaEventRecord(e[3], ctx->stream);
-            cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap, hrows);
+            cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, zr, n, sc.p, hist.p, hcap, hrows, sc2);
             cudaEventRecord(e[4], ctx->stream);
             ctx->launches += 2;
         }
@@ -499,7 +549,15 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->dy, 1); if (cap_st != YFD_OK) break; }
         cg_update_xr<<<vg, CG_THREADS, 0, ctx->stream>>>(d_x, r.p, z.p, dv, y.p, d_pc, n, sc.p, partials.p, hsend);
         if (pl && !peer) { cap_st = comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2); if (cap_st != YFD_OK) break; }
-        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, d_pc ? z.p : r.p, n, sc.p, hist.p, hcap, hrows);
+        if (block) {
+            if (nh > 0) {
+                cg_halo_r<<<(unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0, ctx->stream>>>(r.p, ctx->peer_land, n, nh, sc.p);
+                ctx->launches += 1;
+            }
+            cap_st = apply_block();
+            if (cap_st != YFD_OK) break;
+        }
+        cg_update_d<<<vg, CG_THREADS, 0, ctx->stream>>>(dv, zr, n, sc.p, hist.p, hcap, hrows, sc2);
         ctx->launches += 2;
     }
     {
@@ -547,6 +605,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
 }
 
 #include "yfd_bicgstab.cuh"
+#include "yfd_block_jacobi.cuh"
 
 enum solver_method { SOLVER_CG = 0, SOLVER_BICGSTAB = 1 };
 
@@ -658,8 +717,16 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
                                int method = SOLVER_CG)
 {
     if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
-    if (use_pc && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
+    if (use_pc != YFD_PC_NONE && use_pc != YFD_PC_JACOBI && use_pc != YFD_PC_BLOCK_JACOBI) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_pc must be YFD_PC_NONE, YFD_PC_JACOBI or YFD_PC_BLOCK_JACOBI");
+    if (use_pc == YFD_PC_JACOBI && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
     scoped_device dev(ctx->device);
+    const bool block_pc = use_pc == YFD_PC_BLOCK_JACOBI;
+    if (block_pc) {
+        if (method == SOLVER_BICGSTAB) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab takes the diagonal preconditioner only");
+        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner");
+        YFD_TRY(ensure_block_jacobi(ctx, sys));
+        use_pc = 0;
+    }
     const int64_t n = sys->n;
     const bool dg = sys->kind == YFD_SYS_DG;
     if (!dg) YFD_TRY(csr_prepare(ctx, &sys->A));
@@ -691,11 +758,13 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         opT = op_of_system(sys, true);
         opT.values = sys->values_t.p;
     }
+    spmv_op opD;
+    if (block_pc) { opD.cellptr = sys->pcb_cellptr.p; opD.blk_cell = sys->pcb_cell.p; opD.values = sys->pc_block.p; opD.bs = sys->bs; opD.ncells = sys->ncells; }
     if (method == SOLVER_BICGSTAB)
         YFD_TRY(bicgstab_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
     else
         YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
-                          p->use_normal_eqns ? &opT : nullptr));
+                          p->use_normal_eqns ? &opT : nullptr, block_pc ? &opD : nullptr));
     const double *result = dx.p;
     if (dg) {
         /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */

@@ -282,6 +282,11 @@ struct yfd_system {
     yfd::dbuf<double>  pc;            /* 1/diag, empty if not built                 */
     bool     symmetric = true;        /* false: advection-reaction; CG then needs use_normal_eqns and the transposed blocks */
     yfd::dbuf<double>  values_t;      /* DG: the blocks of A^T in the same layout, built on first use (yfd_cg.cu)            */
+    /* DG block-Jacobi preconditioner, built on first use (yfd_block_jacobi.cuh): inverse diagonal blocks of the owned
+     * (+ halo) cells as a one-block-per-cell matrix in the layout of A */
+    yfd::dbuf<double>  pc_block;
+    yfd::dbuf<int64_t> pcb_cellptr;
+    yfd::dbuf<int32_t> pcb_cell;
     /* DG block structure: cell c owns rows [c*bs, (c+1)*bs); its blocks are listed in
      * blk_cell[cellptr[c] .. cellptr[c+1]) in ascending internal cell id */
     int      bs = 0, nf = 0;
