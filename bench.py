@@ -55,6 +55,11 @@ WORKLOADS = {
     # configs[4] mesh one level down (r=11 is the 1e8-dof point)
     "dg_sip_tri_k2_r9": dict(cell=0, r=9, k=2, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
                              desc="DG-SIP diffusion, triangles k=2, -r 9: 1,048,576 cells, 6,291,456 dofs"),
+    # the same two configurations with the block-Jacobi preconditioner (extension: SURVEY.md 8f rank 3)
+    "dg_sip_quad_k3_20m_bj": dict(cell=1, nx=1448, k=3, pc=2, rr_tol=1e-10, ref_r=5, base_r=6,
+                                  desc="DG-SIP diffusion, quadrangles k=3, 1448 x 1448 structured, 20,967,040 dofs, block-Jacobi CG (extension)"),
+    "dg_sip_tri_k2_r9_bj": dict(cell=0, r=9, k=2, pc=2, rr_tol=1e-10, ref_r=5, base_r=6,
+                                desc="DG-SIP diffusion, triangles k=2, -r 9: 6,291,456 dofs, block-Jacobi CG (extension)"),
     "dg_sip_tri_k2_r11": dict(cell=0, r=11, k=2, pc=True, rr_tol=1e-10, ref_r=5, base_r=6,
                               desc="DG-SIP diffusion, triangles k=2, -r 11: 16,777,216 cells, 100,663,296 dofs (BASELINE configs[4])"),
     # configs[1] names a P2 continuous FEM the reference does not have (methods/cfem.hpp is P1 only); this is its P1 path
@@ -162,7 +167,7 @@ def reference_step(ref, wl, r):
         out = ref.run_cfem(r)               # continuous_fem.cpp: builds its own mesh (counted in t_blocks)
     else:
         ref.mesh(wl["cell"], r)
-        out = ref.run_dg(wl["k"], eta=1.0, use_pc=wl["pc"])
+        out = ref.run_dg(wl["k"], eta=1.0, use_pc=bool(wl["pc"]))     # pc = 2 (block-Jacobi) has no reference: its best, Jacobi (-p)
     t = out["t_blocks"] + out["t_csr"] + out["t_cg"]
     return dict(n=out["n"], nnz=out["nnz"], iters=out["iters"], t=t, t_blocks=out["t_blocks"], t_csr=out["t_csr"], t_cg=out["t_cg"])
 
@@ -516,7 +521,7 @@ def main():
     def assemble(m):
         if cfem:
             return ctx.cfem_assemble_p2(m) if wl.get("order") == 2 else ctx.cfem_assemble_p1(m)
-        return ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"])
+        return ctx.dg_assemble_sip(m, k, eta=1.0, build_pc=wl["pc"] == 1)
     hm = make_host_mesh(yfd, wl)                            # mesher: input generation, untimed
     params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4),
                           max_iter=args.profile_iters or 2 * ((len(hm.points) + len(hm.faces)) if wl.get("kind") == "cfem" else bs_of(wl["k"]) * len(hm.cells)))
@@ -649,7 +654,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(info["n"]), "nnz": int(nnz_global),
-                           "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], "Jacobi (-p)" if wl["pc"] else "no preconditioner (reference default)"),
+                           "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], ("no preconditioner (reference default)", "Jacobi (-p)", "block-Jacobi (extension, YFD_PC_BLOCK_JACOBI; reference arm: Jacobi)")[int(wl["pc"])]),
                            "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
                            "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
