@@ -38,7 +38,7 @@ WORKLOADS = {
     # BASELINE.json configs[2] at its stated size: "DG diffusion on quadrilaterals degree 3, ~20M dofs".  The reference mesher
     # only offers 10.49M (-r 9) or 41.9M (-r 10) dofs, so the mesh is the nx x nx structured one (yfd_mesher_create_structured,
     # same conventions; the reference consumes it unchanged, tests/test_gpu_structured.py)
-    "dg_sip_quad_k3_20m": dict(cell=1, nx=1448, k=3, pc=False, rr_tol=1e-10, ref_r=5, base_r=6,
+    "dg_sip_quad_k3_20m": dict(cell=1, nx=1448, k=3, pc=False, rr_tol=1e-10, ref_r=6, base_r=7,
                                desc="DG-SIP diffusion, quadrangles k=3, 1448 x 1448 structured: 2,096,704 cells, 20,967,040 dofs, nnz 1,047,772,800 (BASELINE configs[2], ~20M dofs)"),
     # configs[0] as written: "64x64 structured triangle mesh, degree 1" = 2 * 64^2 triangles
     "dg_sip_tri_k1_64x64": dict(cell=0, nx=64, k=1, pc=False, rr_tol=1e-8, ref_r=6, base_r=6,
