@@ -79,7 +79,7 @@ csr_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ colidx,
     if (WITH_DOT) {
         __shared__ double tot[1];
         const double v[1] = { dot };
-        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) { xrank_sum<1>(sc, 0, tot); sc->dy = tot[0]; }
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot)) { xrank_sum<1>(sc, 0, tot); if (threadIdx.x == 0) sc->dy = tot[0]; }
     }
 }
 
@@ -102,7 +102,7 @@ cg_init(const double *__restrict__ b, const double *__restrict__ y /* A x0 or nu
     __shared__ double tot[2];
     const double v[2] = { rr, rz };
     /* raw sums; with several ranks they are all-reduced before cg_init_finish reads them */
-    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { xrank_sum<2>(sc, 1, tot); sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot)) { xrank_sum<2>(sc, 1, tot); if (threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; } }
     (void) history; (void) history_cap;
 }
 
@@ -203,7 +203,7 @@ cg_update_xr(double *__restrict__ x, double *__restrict__ r, double *__restrict_
     }
     __shared__ double tot[2];
     const double v[2] = { rr, pc ? rz : rr };
-    if (grid_sum<2>(v, partials, &sc->ticket[1], tot) && threadIdx.x == 0) { xrank_sum<2>(sc, 1, tot); sc->rr_new = tot[0]; sc->rz_new = tot[1]; }
+    if (grid_sum<2>(v, partials, &sc->ticket[1], tot)) { xrank_sum<2>(sc, 1, tot); if (threadIdx.x == 0) { sc->rr_new = tot[0]; sc->rz_new = tot[1]; } }
 }
 
 /* ---- K3 ------------------------------------------------------------------------------------ */

@@ -25,41 +25,56 @@ struct cg_scalars {
     int    comm_error;
 };
 
-/* Sum tot[0..NV) over all ranks through peer memory; called by ONE thread (thread 0 of the kernel's last block).
- * Every rank adds the same slots in rank order, so all ranks end with identical bits. */
+/* Sum tot[0..NV) (shared memory) over all ranks through peer memory.  Called by ALL threads of the kernel's last block
+ * (grid_sum returns true in all of them); warp 0 does the exchange with lane q talking to rank q -- the stores to the
+ * peers and the polls of their flags run side by side instead of one after the other, which at 8 ranks took most of
+ * the ~10 us a synchronisation cost -- and lane 0 then adds the slots IN RANK ORDER, so every rank ends with identical
+ * bits.  Result in tot[], valid for thread 0. */
 template <int NV>
 __device__ __forceinline__ void xrank_sum(cg_scalars *sc, int kind, double *tot)
 {
     const peer_view *pv = sc->peer;
-    if (!pv) return;
+    if (!pv || threadIdx.x >= 32) return;
+    const int lane = (int) threadIdx.x;
     peer_ctl *me = pv->ctl[pv->me];
-    const unsigned long long e = me->red_epoch[kind] + 1;
-    me->red_epoch[kind] = e;
+    unsigned long long e = 0;
+    if (lane == 0) { e = me->red_epoch[kind] + 1; me->red_epoch[kind] = e; }
+    e = __shfl_sync(0xffffffffu, e, 0);
     const int par = (int) (e & 1);
-    for (int q = 0; q < pv->nranks; q++) {
-        volatile peer_slot *slot = &pv->ctl[q]->red[par][kind][pv->me];
+    const bool act = lane < pv->nranks;
+    if (act) {
+        volatile peer_slot *slot = &pv->ctl[lane]->red[par][kind][pv->me];
 #pragma unroll
         for (int k = 0; k < NV; k++) slot->v[k] = tot[k];
     }
-    __threadfence_system();
-    for (int q = 0; q < pv->nranks; q++) *((volatile unsigned long long *) &pv->ctl[q]->red[par][kind][pv->me].flag) = e;
+    __threadfence_system();             /* the values (and, cumulatively, every store this kernel made to a peer) before the flag */
     double s[NV];
 #pragma unroll
     for (int k = 0; k < NV; k++) s[k] = 0.0;
-    for (int q = 0; q < pv->nranks; q++) {
-        volatile peer_slot *slot = &me->red[par][kind][q];
+    if (act) {
+        *((volatile unsigned long long *) &pv->ctl[lane]->red[par][kind][pv->me].flag) = e;
+        volatile peer_slot *slot = &me->red[par][kind][lane];
         long long spins = 0;
         while (slot->flag != e)
             if (++spins > (1ll << 28)) { sc->comm_error = 1; sc->done = 1; break; }
     }
     __threadfence_system();
-    for (int q = 0; q < pv->nranks; q++) {
-        volatile peer_slot *slot = &me->red[par][kind][q];
+    if (act) {
+        volatile peer_slot *slot = &me->red[par][kind][lane];
 #pragma unroll
-        for (int k = 0; k < NV; k++) s[k] += slot->v[k];
+        for (int k = 0; k < NV; k++) s[k] = slot->v[k];
     }
+    double acc[NV];
 #pragma unroll
-    for (int k = 0; k < NV; k++) tot[k] = s[k];
+    for (int k = 0; k < NV; k++) acc[k] = 0.0;
+    for (int q = 0; q < pv->nranks; q++) {
+#pragma unroll
+        for (int k = 0; k < NV; k++) acc[k] += __shfl_sync(0xffffffffu, s[k], q);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; k++) tot[k] = acc[k];
+    }
 }
 
 /* ---- deterministic block + grid reduction ------------------------------------------- */

@@ -124,7 +124,7 @@ csr_spmv_tma(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ col
     if (WITH_DOT) {
         __shared__ double tot[1];
         const double v[1] = { dot };
-        if (grid_sum<1>(v, partials, &sc->ticket[0], tot) && threadIdx.x == 0) { xrank_sum<1>(sc, 0, tot); sc->dy = tot[0]; }
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot)) { xrank_sum<1>(sc, 0, tot); if (threadIdx.x == 0) sc->dy = tot[0]; }
     }
 }
 
