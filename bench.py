@@ -435,7 +435,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
                "path": "yfd_mesh_create -> yfd_maxwell_create -> apply_initial_condition -> timesteps -> report_errors -> get_dofs (host) through include/yfd.h"}
 
     base = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:      # the CPU baseline is an N=1 figure (torchrun pins ranks to one thread)
         R, cores = load_maxwell_reference()
         if R is not None:
             sres = maxwell_reference_step(R, wl, wl["base_r"])
@@ -645,7 +645,7 @@ def main():
                "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % (("yfd_cfem_assemble_p2" if wl.get("order") == 2 else "yfd_cfem_assemble_p1") if cfem else "yfd_dg_assemble_sip")}
 
     base = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:      # the CPU baseline is an N=1 figure (torchrun pins ranks to one thread)
         base = cpu_baseline(wl, wl["base_r"])
 
     if rank == 0:
