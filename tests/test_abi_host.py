@@ -1,6 +1,5 @@
 """CPU: the C-ABI library loads and exports every symbol include/yfd.h declares; host-side logic (the mesher,
 parameter defaults, error mapping) against the reference's golden vectors.  No compute calls: no GPU here."""
-import ctypes as C
 import hashlib
 import os
 import re

@@ -6,7 +6,7 @@ import pytest
 import scipy.sparse as sp
 import scipy.sparse.linalg as spla
 
-from conftest import golden, host_mesh_from_ref
+from conftest import golden
 from test_oracle_bicgstab import SYSTEMS, check_against_reference, load
 
 pytestmark = pytest.mark.gpu
