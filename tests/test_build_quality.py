@@ -1,0 +1,61 @@
+"""CPU (no GPU needed): what the sm_100a build of the hot kernels looks like -- read from the shared library itself with
+cuobjdump, so a change that starts spilling registers or loses the TMA path in a benchmarked instantiation fails here,
+before any GPU time is spent (B200_PROFILING.md: check -res-usage and the SASS first)."""
+import os
+import re
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "yaourt-fem-dg_b200", "lib", "libyfd_b200.so")
+CUOBJDUMP = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+
+pytestmark = pytest.mark.skipif(not (os.path.exists(LIB) and os.path.exists(CUOBJDUMP)), reason="needs the built library and cuobjdump")
+
+
+@pytest.fixture(scope="module")
+def usage():
+    out = subprocess.run([CUOBJDUMP, "-res-usage", LIB], capture_output=True, text=True, check=True).stdout
+    res = {}
+    for m in re.finditer(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", out):
+        res[m.group(1)] = dict(reg=int(m.group(2)), stack=int(m.group(3)), shared=int(m.group(4)), local=int(m.group(5)))
+    assert res, "cuobjdump -res-usage printed nothing"
+    return res
+
+
+def find(usage, *parts):
+    hits = {k: v for k, v in usage.items() if all(p in k for p in parts)}
+    assert hits, parts
+    return hits
+
+
+def test_arch_is_sm_100a():
+    out = subprocess.run([CUOBJDUMP, "-lelf", LIB], capture_output=True, text=True, check=True).stdout
+    assert "sm_100a" in out and "sm_90" not in out and "sm_80" not in out
+
+
+def test_hot_kernels_do_not_spill(usage):
+    # the instantiations bench.py measures: DG block SpMV bs = 10 (quad k=3) and 6 / 15 (tri k=2 / k=4), the CSR SpMV of the
+    # continuous-FEM systems, the Maxwell stage kernel tri k=4 / quad k=3, and the CG vector kernels
+    for parts in (("dg_spmv_tma", "ILi10E"), ("dg_spmv_tma", "ILi6E"), ("dg_spmv_tma", "ILi15E"), ("csr_spmv_tma",),
+                  ("maxwell_stage", "ILi3ELi4E"), ("maxwell_stage", "ILi4ELi3E"), ("cg_update_xr",), ("cg_update_d",)):
+        for name, u in find(usage, *parts).items():
+            assert u["stack"] == 0 and u["local"] == 0, (name, u)
+    # two CTAs per SM for the Maxwell stage kernel at the benchmarked degrees need <= 128 registers (256 threads)
+    for name, u in find(usage, "maxwell_stage", "ILi3ELi4E").items():
+        assert u["reg"] <= 128, (name, u)
+
+
+def test_spmv_kernels_use_the_tma_engine():
+    """UBLKCP = cp.async.bulk global->shared; SYNCS = mbarrier (the mnemonics B200_PROFILING.md lists)"""
+    out = subprocess.run([CUOBJDUMP, "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    for fun in ("dg_spmv_tma", "csr_spmv_tma"):
+        blocks = [b for b in out.split("Function : ")[1:] if fun in b.split("\n", 1)[0]]
+        assert blocks, fun
+        for b in blocks:
+            assert "UBLKCP" in b and "SYNCS" in b, b.split("\n", 1)[0]
+    # the Maxwell stage kernel prefetches its operator slab into L2 with one bulk request per chunk
+    blocks = [b for b in out.split("Function : ")[1:] if "maxwell_stage" in b.split("\n", 1)[0]]
+    assert blocks and all("UBLKPF.L2" in b for b in blocks)          # cp.async.bulk.prefetch.L2
