@@ -141,3 +141,110 @@ def test_world_size_2_gloo_halo_exchange_and_spmv(tmp_path, t, r, k):
     for rank in range(2):
         ok_spmv, ok_dot, nhalo, nsend = map(int, open(tmp_path / ("rank%d.txt" % rank)).read().split())
         assert ok_spmv and ok_dot and nhalo > 0 and nsend > 0
+
+
+def _exchange(dist, torch, pl, bs, vec, c0, nown):
+    """fill the halo part of `vec` ([owned | halo], local numbering) from the owners: the explicit exchange"""
+    so = np.concatenate([[0], np.cumsum(pl["send_counts"])]); ro = np.concatenate([[0], np.cumsum(pl["recv_counts"])])
+    reqs, recvs = [], []
+    for kk, peer in enumerate(pl["peers"]):
+        cells = pl["send_cells"][so[kk]:so[kk + 1]]
+        buf = torch.from_numpy(np.concatenate([vec[(c - c0) * bs:(c - c0 + 1) * bs] for c in cells]))
+        reqs.append(dist.isend(buf, int(peer)))
+        rb = torch.empty(int(pl["recv_counts"][kk]) * bs, dtype=torch.float64)
+        recvs.append((rb, ro[kk]))
+        reqs.append(dist.irecv(rb, int(peer)))
+    for q in reqs:
+        q.wait()
+    for rb, off in recvs:
+        vec[(nown + off) * bs:(nown + off) * bs + len(rb)] = rb.numpy()
+
+
+def _worker_cg(rank, world, port, t, r, k, use_pc, out_dir):
+    """The multi-GPU CG of yfd_cg.cu on the peer transport, restated in numpy over gloo: per iteration the owners hand out
+    y = A d on the cells their neighbours hold as halo, and every rank advances its OWN halo copies of r, z, d with the
+    owner's recurrences -- no exchange of d.  Checked: the halo copies equal the owners' values bit for bit at every
+    iteration, and the iterates are those of the same CG run with an explicit exchange of d."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import torch.distributed as dist
+    import scipy.sparse as sp
+    import oraclebind
+    import yaourt_fem_dg_b200 as yfd
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    oracle = oraclebind.Oracle()
+    m, nbr = neighbours_from_oracle(oracle, t, r)
+    bs = (k + 2) * (k + 1) // 2
+    sysd = oracle.dg_sip(t, m["points"], m["cells"], m["faces"], k, 1.0)
+    A = sp.csr_matrix((sysd["values"], sysd["colidx"], sysd["rowptr"]), shape=(sysd["n"], sysd["n"]))
+    pl = yfd.partition_plan(nbr, world, rank)
+    c0, c1 = pl["cell_begin"], pl["cell_end"]
+    nown, nhalo = c1 - c0, len(pl["halo_cells"])
+    g2l = {c: c - c0 for c in range(c0, c1)}
+    g2l.update({int(c): nown + i for i, c in enumerate(pl["halo_cells"])})
+    rows = np.arange(c0 * bs, c1 * bs)
+    Aloc = A[rows].tocoo()
+    lcol = np.array([g2l[int(c) // bs] * bs + int(c) % bs for c in Aloc.col], np.int64)
+    Aloc = sp.csr_matrix((Aloc.data, (Aloc.row, lcol)), shape=(nown * bs, (nown + nhalo) * bs))
+    n, nl = nown * bs, (nown + nhalo) * bs
+    pc = np.ones(nl)
+    if use_pc:
+        pc[:n] = 1.0 / A.diagonal()[rows]
+        _exchange(dist, torch, pl, bs, pc, c0, nown)            # the Jacobi diagonal of the halo cells, once
+
+    def allsum(v):
+        tt = torch.tensor([float(v)], dtype=torch.float64)
+        dist.all_reduce(tt)
+        return tt.item()
+
+    def run(exchange_free):
+        x = np.zeros(n); rv = np.zeros(nl); dv = np.zeros(nl); yh = np.zeros(nl)
+        rv[:n] = sysd["rhs"][rows]
+        _exchange(dist, torch, pl, bs, rv, c0, nown)             # halo copies of r0, once
+        z = pc * rv
+        dv[:] = z
+        rho = allsum(rv[:n] @ z[:n])
+        same = True
+        hist = []
+        for it in range(25):
+            if not exchange_free:
+                _exchange(dist, torch, pl, bs, dv, c0, nown)
+            y = Aloc @ dv
+            alpha = rho / allsum(dv[:n] @ y)
+            x += alpha * dv[:n]
+            rv[:n] -= alpha * y
+            z[:n] = pc[:n] * rv[:n]
+            rr, rz = allsum(rv[:n] @ rv[:n]), allsum(rv[:n] @ z[:n])
+            beta = rz / rho
+            dv[:n] = z[:n] + beta * dv[:n]
+            if exchange_free:
+                yh[:n] = y
+                _exchange(dist, torch, pl, bs, yh, c0, nown)     # the owners' y lands in the neighbours' zones
+                rv[n:] -= alpha * yh[n:]
+                z[n:] = pc[n:] * rv[n:]
+                dv[n:] = z[n:] + beta * dv[n:]
+                chk = dv.copy()
+                _exchange(dist, torch, pl, bs, chk, c0, nown)    # what an explicit exchange of d would deliver
+                same = same and np.array_equal(chk[n:], dv[n:])
+            rho = rz
+            hist.append(np.sqrt(rr))
+        return x, np.array(hist), same
+
+    xa, ha, same = run(True)
+    xb, hb, _ = run(False)
+    ok = same and np.array_equal(ha, hb) and np.array_equal(xa, xb) and nhalo > 0
+    with open(os.path.join(out_dir, "cg_rank%d.txt" % rank), "w") as f:
+        f.write("%d %d %.3e\n" % (ok, same, ha[-1] / ha[0]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,t,r,k,use_pc", [(2, 0, 3, 1, False), (2, 1, 2, 2, True), (3, 0, 3, 2, True)])
+def test_gloo_exchange_free_cg_keeps_halo_copies_bit_identical(tmp_path, world, t, r, k, use_pc):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_worker_cg, args=(world, port, t, r, k, use_pc, str(tmp_path)), nprocs=world, join=True)
+    for rank in range(world):
+        ok, same, rel = open(tmp_path / ("cg_rank%d.txt" % rank)).read().split()
+        assert int(same) == 1 and int(ok) == 1 and float(rel) < 1.0
