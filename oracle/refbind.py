@@ -18,23 +18,27 @@ _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 
 
-def lib_path(omp=False, advection=False):
+def lib_path(omp=False, advection=False, lapack=False):
+    """lapack=True: the same harness linked against a real LAPACK (the OpenBLAS bundled with the opencv wheel) instead of
+    oracle/lu_shim.c; built by `make -C oracle lapack_pin` where that wheel exists, used only to pin the shim."""
+    if lapack:
+        return os.path.join(_HERE, "_ref", "libyfd_ref_lapack.so")
     if advection:
         return os.path.join(_HERE, "_ref", "libyfd_ref_adv.so")
     return os.path.join(_HERE, "_ref", "libyfd_ref_omp.so" if omp else "libyfd_ref.so")
 
 
-def available(omp=False, advection=False):
-    return os.path.exists(lib_path(omp, advection))
+def available(omp=False, advection=False, lapack=False):
+    return os.path.exists(lib_path(omp, advection, lapack))
 
 
 class Ref:
     """One loaded copy of the reference library (it keeps one mesh + one result)."""
 
-    def __init__(self, omp=False, advection=False):
+    def __init__(self, omp=False, advection=False, lapack=False):
         """advection=True loads the same harness built around dg2d_advection.cpp (run_dg then runs
         run_advection_reaction_solver, dg2d_advection.cpp:120; CG on the normal equations as that driver sets it)."""
-        self.lib = L = C.CDLL(lib_path(omp, advection))
+        self.lib = L = C.CDLL(lib_path(omp, advection, lapack))
         self.advection = advection
         if advection:
             L.yfd_ref_set_upwinding.argtypes = [C.c_int]
@@ -187,19 +191,21 @@ class Ref:
 # --------------------------------------------------------------------------------------------
 # DG Maxwell TM (methods/dg_maxwell_2D.hpp + maxwell_driver.cpp), oracle/ref_harness_maxwell.cpp
 # --------------------------------------------------------------------------------------------
-def maxwell_lib_path(omp=False):
+def maxwell_lib_path(omp=False, lapack=False):
+    if lapack:
+        return os.path.join(_HERE, "_ref", "libyfd_ref_maxwell_lapack.so")
     return os.path.join(_HERE, "_ref", "libyfd_ref_maxwell_omp.so" if omp else "libyfd_ref_maxwell.so")
 
 
-def maxwell_available(omp=False):
-    return os.path.exists(maxwell_lib_path(omp))
+def maxwell_available(omp=False, lapack=False):
+    return os.path.exists(maxwell_lib_path(omp, lapack))
 
 
 class RefMaxwell:
     """The unmodified reference Maxwell solver; one context at a time."""
 
-    def __init__(self, omp=False):
-        self.lib = L = C.CDLL(maxwell_lib_path(omp))
+    def __init__(self, omp=False, lapack=False):
+        self.lib = L = C.CDLL(maxwell_lib_path(omp, lapack))
         L.yfd_refmx_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
         L.yfd_refmx_sizes.argtypes = [C.POINTER(C.c_int64)] * 5
         L.yfd_refmx_mesh_copy.argtypes = [_f64p, _i64p, _i64p, _i32p]

@@ -5,7 +5,8 @@ oracle/Makefile).  Dev-time tool: needs /root/reference at build time, the commi
 an output of the reference's own code: maxwell_context (mesh, shatter), assemble (gM, gOp_ondiag, gOp_offdiag,
 offdiag_neigh_offsets), apply_initial_condition (gDofs), do_timestep, report_errors, and run_maxwell_solver's error
 log.  LAPACK dgesv comes from oracle/lu_shim.c (no system LAPACK in this image): the fixtures pin the reference's
-algorithm, "parity unpinned" against a real LAPACK build.
+algorithm; tests/test_oracle_lapack.py re-derives them with the same sources linked against a real LAPACK (OpenBLAS 0.3.15,
+`make -C oracle lapack_pin`) and finds them reproduced to <= 1.6e-14, which closes SURVEY.md 8c's "parity unpinned".
 
     python tools/make_golden_maxwell.py
 """
