@@ -195,6 +195,19 @@ class Oracle:
         return dict(n=n, nnz=len(values), rowptr=rowptr, colidx=colidx, values=values, rhs=rhs[:n].copy(), compress_map=cmap,
                     raw=(ri[:cnt].copy(), rj[:cnt].copy(), rv[:cnt].copy()))
 
+    # ---- the drivers' post-process (dg2d_diffusion.cpp:225-268) ----
+    def dg_postprocess(self, points, cells, k, sol, ref_fn=3):
+        """(L2_errsq_qp, L2_errsq_mm) of a DG solution vector in the reference's numbering."""
+        points = _c(points, np.float64); cells = _c(cells, np.int64); sol = _c(sol, np.float64)
+        f = self.lib.yfo_dg_postprocess
+        f.restype = C.c_int64
+        f.argtypes = [C.c_int, _f64p, C.c_int64, _i64p, C.c_int, _f64p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        qp, mm = C.c_double(), C.c_double()
+        bad = f(cells.shape[1], points, len(cells), cells, k, sol, ref_fn, C.byref(qp), C.byref(mm))
+        if bad:
+            raise ValueError("singular elemental mass matrix in cell %d" % (bad - 1))
+        return qp.value, mm.value
+
     # ---- continuous P2 (extension: the reference is P1-only, parity unpinned) ----
     def cfem_p2_element(self, verts, rhs_fn=1):
         v = _c(verts, np.float64).reshape(6)

@@ -157,3 +157,18 @@ def test_oracle_vs_live_reference(oracle, ref):
         res = oracle.cg(d["rowptr"], d["colidx"], d["values"], d["rhs"], pc_diag=d["pc_diag"] if pc else None,
                         rr_tol=1e-12, rr_max=1e4, max_iter=2 * d["n"], history=False)
         assert np.linalg.norm(res["x"] - out["sol"]) <= 1e-10 * np.linalg.norm(out["sol"])
+
+
+@pytest.mark.parametrize("name", sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLDEN, "dg_*_*.npz")) + glob.glob(os.path.join(GOLDEN, "struct_*.npz"))
+                                        if "driver" not in p))
+def test_postprocess_vs_golden(oracle, name):
+    """dg2d_diffusion.cpp:225-268 restated (oracle/yfd_oracle_post.inc) against the L2 errors the unmodified driver computed
+    from its own solution vector: quadrature-point error, and the projection error that goes through solve_LU"""
+    g = golden(name)
+    qp, mm = oracle.dg_postprocess(g["points"], g["cells"], int(g["degree"]), g["sol"])
+    assert abs(np.sqrt(qp) - float(g["l2_qp"])) <= 1e-12 * float(g["l2_qp"])
+    if "l2_mm" in g.files:
+        assert abs(np.sqrt(mm) - float(g["l2_mm"])) <= 1e-11 * float(g["l2_mm"])
+    # a perturbed solution vector moves both measures, the two stay consistent with each other
+    qp2, mm2 = oracle.dg_postprocess(g["points"], g["cells"], int(g["degree"]), g["sol"] * 1.01)
+    assert qp2 != qp and mm2 != mm
