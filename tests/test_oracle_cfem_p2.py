@@ -93,3 +93,29 @@ def test_broken_mesh_is_reported(oracle):
     m = oracle.mesh(0, 1)
     with pytest.raises(ValueError):
         oracle.cfem_p2(m["points"], m["cells"], m["faces"][:-1], m["face_boundary"][:-1])
+
+
+def test_element_matrix_and_load_against_exact_symbolic_integrals(oracle):
+    """An independent derivation: the P2 Lagrange functions written in x, y for the physical triangle, their gradients
+    and the integrals over the triangle done EXACTLY by sympy (rational vertex coordinates), against the oracle's
+    quadrature-based element matrix and (for a polynomial right-hand side) load vector."""
+    sympy = pytest.importorskip("sympy")
+    x, y, s, t = sympy.symbols("x y s t")
+    V = [(sympy.Rational(1, 10), sympy.Rational(1, 5)), (sympy.Rational(9, 10), sympy.Rational(3, 20)), (sympy.Rational(7, 20), sympy.Rational(4, 5))]
+    (x0, y0), (x1, y1), (x2, y2) = V
+    det = (x1 - x0) * (y2 - y0) - (x2 - x0) * (y1 - y0)
+    l1 = ((x - x0) * (y2 - y0) - (x2 - x0) * (y - y0)) / det
+    l2 = ((x1 - x0) * (y - y0) - (x - x0) * (y1 - y0)) / det
+    l0 = 1 - l1 - l2
+    phi = [l0 * (2 * l0 - 1), l1 * (2 * l1 - 1), l2 * (2 * l2 - 1), 4 * l0 * l1, 4 * l1 * l2, 4 * l0 * l2]
+
+    def integrate(f):        # map the reference triangle (s, t) -> physical, |det| constant
+        fx = f.subs({x: x0 + (x1 - x0) * s + (x2 - x0) * t, y: y0 + (y1 - y0) * s + (y2 - y0) * t}, simultaneous=True)
+        return sympy.integrate(sympy.integrate(fx, (t, 0, 1 - s)), (s, 0, 1)) * abs(det)
+
+    Kex = np.array([[float(integrate(sympy.diff(a, x) * sympy.diff(b, x) + sympy.diff(a, y) * sympy.diff(b, y))) for b in phi] for a in phi])
+    verts = np.array([[float(a), float(b)] for a, b in V])
+    K, b1 = oracle.cfem_p2_element(verts, rhs_fn=2)
+    assert np.abs(K - Kex).max() <= 1e-13 * np.abs(Kex).max()
+    bex = np.array([float(integrate(p)) for p in phi])                   # f = 1
+    assert np.abs(b1 - bex).max() <= 1e-14
