@@ -214,7 +214,7 @@ def cpu_baseline(wl, r):
     if ref is None:
         return None
     s = reference_step(ref, wl, r)
-    return dict(value=s["n"] / s["t"], unit="DOFs/s", cores=cores, kind=kind,
+    return dict(value=s["n"] / s["t"], unit="DOFs/s", cores=cores, kind=kind, dofs=int(s["n"]), nnz=int(s["nnz"]), cg_iterations=int(s["iters"]),
                 sample=label + ", same discretisation at -r %d: "
                        "%d dofs, nnz %d, %d CG iterations to rr %.0e; blocks %.2fs + finalize %.2fs + CG %.2fs; "
                        "%.2f ns per dof per CG iteration" % (r, s["n"], s["nnz"], s["iters"], wl["rr_tol"], s["t_blocks"],
@@ -245,7 +245,11 @@ def run_reference_arm(args, wl, rank):
     line = {"impl": "reference", "metric": "assembled+solved DOFs/sec", "value": value, "unit": "DOFs/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "description": wl["desc"], "sample": sample},
+            # `description` names the workload's discretisation; dofs / nnz / cg_iterations are what THIS arm ran (a bounded
+            # sample of it: the GPU line's same_size leg times the GPU path on exactly this system)
+            "config": {"workload": args.workload, "description": wl["desc"], "sample": sample, "sample_refinement": r,
+                       "dofs": int(last["n"]), "nnz": int(last["nnz"]), "cg_iterations": int(last["iters"]),
+                       "phases_s": {"blocks": last["t_blocks"], "finalize": last["t_csr"], "cg": last["t_cg"]}},
             "cpu_baseline": {"value": value, "unit": "DOFs/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "DOFs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -469,6 +473,63 @@ def pinned_like(torch, a):
     return t, t.numpy()
 
 
+def same_size_leg(torch, yfd, ctx, stream, wl, r, cpu, assemble, cfem, reps=3):
+    """The GPU path on the reference mesher's -r `r` mesh of the workload's discretisation -- exactly the system the CPU
+    reference was timed on (`cpu` = cpu_baseline(wl, r)) -- resident and end to end."""
+    hm = yfd.HostMesh.create(wl["cell"], r)
+    nd = (len(hm.points) + len(hm.faces)) if cfem else bs_of(wl["k"]) * len(hm.cells)
+    params = yfd.CgParams(rr_tol=wl["rr_tol"], rr_max=wl.get("rr_max", 1e4), max_iter=2 * nd)
+    mesh = yfd.Mesh(ctx, hm)
+    out = {}
+
+    def resident():
+        sysm = assemble(mesh)
+        d_x = torch.empty(sysm.n, dtype=torch.float64, device="cuda")
+        res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr())
+        out.update(n=sysm.n, nnz=sysm.nnz, iters=res["iterations"], converged=res["converged"])
+        return sysm, d_x
+    sysm, d_x = resident()
+    out["true_residual"] = sysm.true_residual(d_x=d_x.data_ptr())
+    if not cfem:
+        out["l2_error"] = float(np.sqrt(ctx.dg_postprocess(mesh, wl["k"], None, device_ptr=d_x.data_ptr())[0]))
+    sysm.close()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        resident()[0].close()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms_res = e0.elapsed_time(e1) / reps
+    mesh.close()
+    arrs, keep = {}, []
+    for nme in ("points", "cells", "faces", "face_boundary"):
+        t, a = pinned_like(torch, getattr(hm, nme))
+        keep.append(t); arrs[nme] = a
+    xt = torch.empty(out["n"], dtype=torch.float64).pin_memory()
+    hm_p = yfd.HostMesh(hm.cell_type, arrs["points"], arrs["cells"], arrs["faces"], arrs["face_boundary"])
+
+    def e2e():
+        m2 = yfd.Mesh(ctx, hm_p)
+        s2 = assemble(m2)
+        s2.solve_cg_into(params, xt.numpy(), use_pc=wl["pc"])
+        s2.close(); m2.close()
+    e2e()
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(reps):
+        e2e()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1) / reps
+    n = out["n"]
+    assert n == cpu["dofs"] and out["nnz"] == cpu["nnz"], "same_size: the two arms assembled different systems"
+    return {"refinement": r, "dofs": int(n), "nnz": int(out["nnz"]), "gpu_dofs_per_s": n / (ms_res * 1e-3), "gpu_e2e_dofs_per_s": n / (ms_e2e * 1e-3),
+            "cpu_dofs_per_s": cpu["value"], "cpu_cores": cpu["cores"], "cpu_kind": cpu["kind"], "gpu_iters": int(out["iters"]), "cpu_iters": int(cpu["cg_iterations"]),
+            "gpu_converged": bool(out["converged"]), "gpu_true_residual": out["true_residual"], "gpu_l2_error": out.get("l2_error"),
+            "ratio_resident": n / (ms_res * 1e-3) / cpu["value"], "ratio_e2e": n / (ms_e2e * 1e-3) / cpu["value"]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -476,12 +537,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=os.environ.get("YFD_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
+    ap.add_argument("--pc", type=int, default=None, choices=[0, 1, 2], help="override the workload's preconditioner: 0 none, 1 Jacobi (-p), 2 block-Jacobi")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile-iters", type=int, default=0,
                     help="ncu helper: cap CG at this many iterations, one step, no warm-up; the printed line is NOT a bench value")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.pc is not None:
+        wl["pc"] = args.pc
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -576,26 +640,38 @@ def main():
 
     # ---------------- roofline leg: the CG SpMV, CUDA events on the launching stream ----------------
     sysm = step_resident()
+    # correctness anchors of the solution just produced (after the timed region, never inside it): the TRUE residual
+    # ||b - A x|| / ||b|| through an independent one-thread-per-row kernel (yfd_system_true_residual; the solver itself
+    # stops on the recurrence residual, core/solvers.hpp:99,124) and the driver's L2 error against the analytic
+    # solution (dg2d_diffusion.cpp:225-268, yfd_dg_postprocess)
+    anchors = {}
+    if world == 1:
+        anchors["true_residual"] = sysm.true_residual(d_x=d_x.data_ptr())
+        if not cfem:
+            qp, mm = ctx.dg_postprocess(mesh, k, None, device_ptr=d_x.data_ptr())
+            anchors["l2_error"], anchors["l2_error_projection"] = float(np.sqrt(qp)), float(np.sqrt(mm))
     sp = sysm.time_spmv(reps=50)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = sp["csr_bytes"] / (sp["ms"] * 1e-3) / 1e9
+    csr_gbs = sp["csr_bytes"] / (sp["ms"] * 1e-3) / 1e9
+    achieved = sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
     if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
-    roofline = {"bound": "hbm", "kernel": ("csr_spmv" if cfem else "dg_spmv_tma") + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": sp["csr_bytes"], "kernel_requested_bytes_per_launch": sp["kernel_bytes"],
-                "kernel_requested_gbs": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9, "ms_per_launch": sp["ms"],
-                "hw_frac": sp["kernel_bytes"] / (sp["ms"] * 1e-3) / 1e9 / peak,
-                "note": "achieved = the CSR SpMV's algorithmic bytes (12 B per nonzero + vectors, SURVEY.md 8d) per launch / measured launch time; "
-                        "the kernel itself requests kernel_requested_bytes_per_launch (DG: 8 B per nonzero, the block layout stores no "
-                        "column indices), so hw_frac = kernel_requested_gbs / peak is the fraction of the HBM peak the hardware sustains "
-                        "and frac can exceed 1"}
+    roofline = {"bound": "hbm", "kernel": ("csr_spmv_tma" if cfem else "dg_spmv_tma") + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "hw_frac": achieved / peak, "traffic": traffic,
+                "traffic_source": None if traffic is None else "static: profiles/spmv_traffic.json (one ncu --set full capture of this kernel on this workload, dram__bytes_read.sum + dram__bytes_write.sum; not a live counter)",
+                "peak_source": peak_src,
+                "kernel_requested_bytes_per_launch": sp["kernel_bytes"], "ms_per_launch": sp["ms"],
+                "csr_equivalent": {"bytes_per_launch": sp["csr_bytes"], "gbs": csr_gbs, "frac": csr_gbs / peak},
+                "note": "achieved / frac = the bytes the kernel requests per launch (DG: 8 B per nonzero -- the block layout stores no "
+                        "column indices -- + block lists + x + y) / CUDA-event launch time, against the measured HBM peak: the fraction "
+                        "the hardware sustains.  csr_equivalent = SURVEY.md 8d's CSR figure (12 B per nonzero + vectors) over the same "
+                        "time: what a CSR kernel would have to sustain to be as fast (can exceed the peak)"}
     # whole CG iteration (SpMV + 2 fused vector kernels) over the timed solve: B_cg = B_spmv + 72 n,
     # summed over ranks
     it = max(1, info["iterations"])
@@ -604,7 +680,9 @@ def main():
         tn = torch.tensor([info["nnz"]], device="cuda", dtype=torch.int64)
         dist.all_reduce(tn)
         nnz_global = int(tn.item())
-    cg_gbs = (12.0 * nnz_global + 8.0 * (info["n"] + 1) + 16.0 * info["n"] + 72.0 * info["n"]) * it / (info["ms_solve"] * 1e-3) / 1e9
+    # bytes the three kernels of an iteration request: matrix (DG: 8 B/nnz + block lists; CSR: 12 B/nnz + offsets) + x, y + 72 n
+    mat_bytes = (12.0 * nnz_global + 8.0 * (info["n"] + 1)) if cfem else (8.0 * nnz_global + 12.0 * nnz_global / (bs * bs) + 8.0 * info["n"] / bs)
+    cg_gbs = (mat_bytes + 16.0 * info["n"] + 72.0 * info["n"]) * it / (info["ms_solve"] * 1e-3) / 1e9
     sysm.close()
 
     # ---------------- end-to-end leg: host buffers in, host solution out ----------------
@@ -640,13 +718,32 @@ def main():
         wall = (time.perf_counter() - t0) / args.steps
         # the events are recorded before the first / after the last call, so they span the host-side work too
         ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
+        if world > 1:                       # several ranks: the anchors come from the gathered host solution (untimed extra pass)
+            m2 = yfd.Mesh(ctx, hm_p)
+            s2 = assemble(m2)
+            s2.solve_cg_into(params, x_host, use_pc=wl["pc"])
+            anchors["true_residual"] = s2.true_residual(x=x_host)
+            if not cfem:
+                qp, mm = ctx.dg_postprocess(m2, k, x_host)
+                anchors["l2_error"], anchors["l2_error_projection"] = float(np.sqrt(qp)), float(np.sqrt(mm))
+            s2.close(); m2.close()
         e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
                "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % (("yfd_cfem_assemble_p2" if wl.get("order") == 2 else "yfd_cfem_assemble_p1") if cfem else "yfd_dg_assemble_sip")}
 
     base = None
+    same_size = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:      # the CPU baseline is an N=1 figure (torchrun pins ranks to one thread)
         base = cpu_baseline(wl, wl["base_r"])
+        # like-for-like: the GPU path on EXACTLY the systems the CPU reference runs (the reference arm's -r ref_r sample and
+        # this line's cpu_baseline at -r base_r), resident and end to end, with both sides' iteration counts
+        if base is not None:
+            same_size = []
+            for rr in sorted({wl["ref_r"], wl["base_r"]}):
+                cpu = base if rr == wl["base_r"] else cpu_baseline(wl, rr)
+                if cpu is None or wl.get("order") == 2:
+                    continue
+                same_size.append(same_size_leg(torch, yfd, ctx, stream, wl, rr, cpu, assemble, cfem))
 
     if rank == 0:
         line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else {}
@@ -656,6 +753,11 @@ def main():
                 "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(info["n"]), "nnz": int(nnz_global),
                            "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], ("no preconditioner (reference default)", "Jacobi (-p)", "block-Jacobi (extension, YFD_PC_BLOCK_JACOBI; reference arm: Jacobi)")[int(wl["pc"])]),
                            "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
+                           "true_residual": anchors.get("true_residual"), "l2_error": anchors.get("l2_error"),
+                           "l2_error_projection": anchors.get("l2_error_projection"),
+                           "anchors_note": "true_residual = ||b - A x|| / ||b|| of the returned solution by an independent one-thread-per-row kernel "
+                                           "(yfd_system_true_residual); l2_error = the driver's L2 error against sin(pi x) sin(pi y) at the quadrature "
+                                           "points (dg2d_diffusion.cpp:225-268), expected O(h^(k+1))",
                            "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
                                          "host_wall_assemble_call": info["host_ms_assemble"], "host_wall_solve_call": info["host_ms_solve"]},
@@ -664,7 +766,7 @@ def main():
                                                                   "per CG iteration 2 cross-rank scalar sums through NVLink peer memory; no exchange of d: every rank advances its halo "
                                                                   "copies of r and d from the neighbours' y = A d, stored into its landing zone ahead of the r.r sum"
                                                                   if info.get("transport") == "peer memory" else "per CG iteration one halo exchange and 2 scalar all-reduces")},
-                "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
+                "roofline": roofline, "cpu_baseline": base, "same_size": same_size, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
         print(json.dumps(line))
     ctx.close()
     if dist is not None:

@@ -359,6 +359,20 @@ yfd_status yfd_system_solve_bicgstab(yfd_ctx *ctx, yfd_system *sys, int use_pc, 
 yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
                               const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
 
+/* y = A x for the assembled system as conjugated_gradient forms it (`y = A*d`, core/solvers.hpp:115), host vectors
+ * in REFERENCE numbering, one GPU.  kernel = YFD_APPLY_SOLVER: the kernel the solvers launch (the TMA-streamed
+ * SpMV); YFD_APPLY_PLAIN: an independent one-thread-per-row kernel that reads the matrix straight from global
+ * memory and sums each row left to right (SMatDVecMultExpr.h:204-207) -- the device-side cross-check of the former. */
+#define YFD_APPLY_SOLVER 0
+#define YFD_APPLY_PLAIN  1
+yfd_status yfd_system_apply(yfd_ctx *ctx, yfd_system *sys, int kernel, const double *x, double *y);
+
+/* ||b - A x||_2 / ||b||_2 of a candidate solution (the TRUE residual; the solvers stop on the recurrence residual,
+ * core/solvers.hpp:99,124), formed with the YFD_APPLY_PLAIN kernel.  x [n] in REFERENCE numbering: x_host, or the
+ * device vector d_x when x_host is NULL.  Works on several ranks (every rank passes the full vector, as
+ * yfd_system_solve_cg returns it; the sums are combined over the ranks). */
+yfd_status yfd_system_true_residual(yfd_ctx *ctx, yfd_system *sys, const double *x_host, const double *d_x, double *rel_residual);
+
 /* Time `reps` launches of y = A d for this system with CUDA events on the context's stream
  * (bench.py's roofline leg).  Returns average ms per launch and the algorithmic CSR bytes of one
  * launch (12 nnz + 8 (n+1) + 16 n) plus the bytes the kernel actually

@@ -176,6 +176,8 @@ def lib():
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_bicgstab_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_solve_bicgstab": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
+        "yfd_system_apply": (cint, [vp, vp, cint, _f64p, _f64p]),
+        "yfd_system_true_residual": (cint, [vp, vp, vp, vp, P(dbl)]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
         "yfd_dg_postprocess": (cint, [vp, vp, cint, cint, _f64p, P(dbl), P(dbl)]),
         "yfd_dg_postprocess_device": (cint, [vp, vp, cint, cint, vp, P(dbl), P(dbl)]),
@@ -592,6 +594,23 @@ class System:
                                                         C.c_void_p(d_x) if d_x else None, C.byref(info)))
         return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
                     transport=("one GPU", "NCCL", "peer memory")[info.transport])
+
+    def apply(self, x, plain=False):
+        """y = A x (reference numbering); plain=True: the independent one-thread-per-row kernel."""
+        x = np.ascontiguousarray(x, np.float64)
+        assert x.shape == (self.n,)
+        y = np.empty(self.n, np.float64)
+        self.ctx.check(lib().yfd_system_apply(self.ctx._h, self._h, 1 if plain else 0, x, y))
+        return y
+
+    def true_residual(self, x=None, d_x=None):
+        """||b - A x|| / ||b|| with the independent kernel; x = host array or d_x = raw device pointer (reference numbering)."""
+        r = C.c_double()
+        if x is not None:
+            x = np.ascontiguousarray(x, np.float64)
+            assert x.shape == (self.n,)
+        self.ctx.check(lib().yfd_system_true_residual(self.ctx._h, self._h, _ptr(x), C.c_void_p(d_x) if d_x else None, C.byref(r)))
+        return r.value
 
     def local_sizes(self):
         a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()

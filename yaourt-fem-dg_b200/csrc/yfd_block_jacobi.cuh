@@ -102,11 +102,20 @@ static yfd_status ensure_block_jacobi(yfd_ctx *ctx, yfd_system *sys)
         dbuf<double> sendbuf;
         st = sendbuf.alloc(ctx, (size_t) (sys->plan->nsend * bs * bs), 2);
         if (st == YFD_OK) st = halo_exchange(ctx, *sys->plan, bs * bs, sys->pc_block.p, sendbuf.p);
+        /* the halo cells' blocks are applied by a launch of their own (cg_device): that launch needs a 16-byte aligned
+         * value array for its bulk copies, and pc_block + ncells bs^2 is only 8-byte aligned when ncells bs^2 is odd
+         * (odd block size and odd owned count, e.g. k = 1 on 3 ranks) -> a separate copy starting at its own allocation */
+        if (st == YFD_OK && nhalo > 0) st = sys->pc_block_halo.alloc(ctx, (size_t) (nhalo * bs * bs), 4);
+        if (st == YFD_OK && nhalo > 0) {
+            cudaError_t e = cudaMemcpyAsync(sys->pc_block_halo.p, sys->pc_block.p + sys->ncells * (int64_t) (bs * bs),
+                                            (size_t) (nhalo * bs * bs) * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+            if (e != cudaSuccess) st = fail(ctx, YFD_ERR_CUDA, "%s", cudaGetErrorString(e));
+        }
         if (st == YFD_OK) { cudaError_t e = cudaStreamSynchronize(ctx->stream); if (e != cudaSuccess) st = fail(ctx, YFD_ERR_CUDA, "%s", cudaGetErrorString(e)); }
     }
     int herr = 0;
     if (st == YFD_OK) st = derr.download(ctx, &herr, 1);
     if (st == YFD_OK && herr) st = fail(ctx, YFD_ERR_INVALID_STATE, herr == 1 ? "internal: a cell has no diagonal block" : "singular diagonal block");
-    if (st != YFD_OK) { sys->pc_block.release(); sys->pcb_cellptr.release(); sys->pcb_cell.release(); }
+    if (st != YFD_OK) { sys->pc_block.release(); sys->pc_block_halo.release(); sys->pcb_cellptr.release(); sys->pcb_cell.release(); }
     return st;
 }

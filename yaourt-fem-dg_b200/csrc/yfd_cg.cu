@@ -334,6 +334,7 @@ struct spmv_op {
     /* DG block rows */
     const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
     int64_t ncells = 0;
+    const double *values_halo = nullptr;     /* block-Jacobi on several ranks: the halo cells' blocks (own allocation) */
     /* several ranks: x carries nhalo*bs halo entries after the nrows owned ones */
     const dist_plan *plan = nullptr;
 };
@@ -450,7 +451,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         YFD_TRY(launch_dg_spmv_tma<true>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values, op.ncells, r.p, z.p, sc2, partials.p));
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc2->dy, 1));
         if (nh > 0)
-            YFD_TRY(launch_dg_spmv_tma<false>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values + op.ncells * (int64_t) (op.bs * op.bs),
+            YFD_TRY(launch_dg_spmv_tma<false>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values_halo,
                                               pl->nhalo, r.p + n, z.p + n, nullptr, nullptr));
         return YFD_OK;
     };
@@ -606,6 +607,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
 
 #include "yfd_bicgstab.cuh"
 #include "yfd_block_jacobi.cuh"
+#include "yfd_verify.cuh"
 
 enum solver_method { SOLVER_CG = 0, SOLVER_BICGSTAB = 1 };
 
@@ -759,7 +761,7 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         opT.values = sys->values_t.p;
     }
     spmv_op opD;
-    if (block_pc) { opD.cellptr = sys->pcb_cellptr.p; opD.blk_cell = sys->pcb_cell.p; opD.values = sys->pc_block.p; opD.bs = sys->bs; opD.ncells = sys->ncells; }
+    if (block_pc) { opD.cellptr = sys->pcb_cellptr.p; opD.blk_cell = sys->pcb_cell.p; opD.values = sys->pc_block.p; opD.values_halo = sys->pc_block_halo.p; opD.bs = sys->bs; opD.ncells = sys->ncells; }
     if (method == SOLVER_BICGSTAB)
         YFD_TRY(bicgstab_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
     else
@@ -804,6 +806,57 @@ yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc,
     if (!ctx || !sys || !p) return YFD_ERR_INVALID_ARGUMENT;
     if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "device-resident solve starts from x = 0");
     return system_solve(ctx, sys, use_pc, p, nullptr, d_x, info, nullptr, 0);
+}
+
+yfd_status yfd_system_apply(yfd_ctx *ctx, yfd_system *sys, int kernel, const double *x, double *y)
+{
+    if (!ctx || !sys || !x || !y) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
+    if (kernel != YFD_APPLY_SOLVER && kernel != YFD_APPLY_PLAIN) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "kernel must be YFD_APPLY_SOLVER or YFD_APPLY_PLAIN");
+    if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "yfd_system_apply on a distributed system: use yfd_system_true_residual");
+    scoped_device dev(ctx->device);
+    const bool dg = sys->kind == YFD_SYS_DG;
+    if (!dg) YFD_TRY(csr_prepare(ctx, &sys->A));
+    const int64_t n = sys->n;
+    dbuf<double> xr, xi, yi, yr;
+    YFD_TRY(xr.alloc(ctx, (size_t) n)); YFD_TRY(yi.alloc(ctx, (size_t) n, 2));
+    YFD_TRY(xr.upload(ctx, x, (size_t) n));
+    YFD_TRY(operand_from_ref(ctx, sys, xr.p, xi));
+    const spmv_op op = op_of_system(sys, true);
+    if (kernel == YFD_APPLY_PLAIN) YFD_TRY(launch_apply_plain(ctx, op, xi.p, yi.p));
+    else YFD_TRY(launch_spmv<false>(ctx, op, xi.p, yi.p, nullptr, nullptr));
+    if (!dg) return yi.download(ctx, y, (size_t) n);
+    YFD_TRY(yr.alloc(ctx, (size_t) n));
+    YFD_TRY(system_vector_to_ref(sys, yi.p, yr.p));
+    return yr.download(ctx, y, (size_t) n);
+}
+
+yfd_status yfd_system_true_residual(yfd_ctx *ctx, yfd_system *sys, const double *x_host, const double *d_x, double *rel_residual)
+{
+    if (!ctx || !sys || !rel_residual || (!x_host && !d_x)) return YFD_ERR_INVALID_ARGUMENT;
+    if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
+    scoped_device dev(ctx->device);
+    const bool dg = sys->kind == YFD_SYS_DG;
+    const int64_t n = sys->n, nloc = dg ? sys->n_local : n;
+    dbuf<double> xr, xi, yi, part, tot;
+    if (!d_x) {
+        YFD_TRY(xr.alloc(ctx, (size_t) n));
+        YFD_TRY(xr.upload(ctx, x_host, (size_t) n));
+        d_x = xr.p;
+    }
+    YFD_TRY(operand_from_ref(ctx, sys, d_x, xi));
+    YFD_TRY(yi.alloc(ctx, (size_t) nloc, 2));
+    const spmv_op op = op_of_system(sys, true);
+    YFD_TRY(launch_apply_plain(ctx, op, xi.p, yi.p));
+    const int nb = (int) std::max<int64_t>(1, std::min<int64_t>(ceil_div(nloc, 256), 1024));
+    YFD_TRY(part.alloc(ctx, (size_t) 2 * nb)); YFD_TRY(tot.alloc(ctx, 2));
+    YFD_LAUNCH(ctx, residual_partials, (unsigned) nb, 256, 0, (const double *) sys->rhs.p, (const double *) yi.p, nloc, part.p);
+    YFD_LAUNCH(ctx, residual_total, 1, 256, 0, (const double *) part.p, nb, tot.p);
+    if (sys->plan) YFD_TRY(comm_allreduce_sum_f64(ctx, tot.p, 2));
+    double h[2] = { 0, 0 };
+    YFD_TRY(tot.download(ctx, h, 2));
+    *rel_residual = h[1] > 0.0 ? std::sqrt(h[0] / h[1]) : std::sqrt(h[0]);
+    return YFD_OK;
 }
 
 yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double *ms_per_launch,

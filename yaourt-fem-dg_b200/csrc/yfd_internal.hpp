@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdarg>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include <memory>
@@ -174,6 +175,12 @@ struct gpu_timer {
 };
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+/* diagnostic switches: read on every launch, so a test can change them between calls */
+inline int env_int(const char *name, int dflt)
+{
+    const char *e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
+}
 inline int basis_size_2d(int k) { return (k + 2) * (k + 1) / 2; }
 
 /* ---- yfd_sort.cu: scans, radix sort, small device utilities ---- */
@@ -285,6 +292,7 @@ struct yfd_system {
     /* DG block-Jacobi preconditioner, built on first use (yfd_block_jacobi.cuh): inverse diagonal blocks of the owned
      * (+ halo) cells as a one-block-per-cell matrix in the layout of A */
     yfd::dbuf<double>  pc_block;
+    yfd::dbuf<double>  pc_block_halo; /* several ranks: the halo cells' blocks again, in an allocation of their own (16-byte aligned) */
     yfd::dbuf<int64_t> pcb_cellptr;
     yfd::dbuf<int32_t> pcb_cell;
     /* DG block structure: cell c owns rows [c*bs, (c+1)*bs); its blocks are listed in

@@ -156,6 +156,14 @@ static bool make_csr_layout(yfd_ctx *ctx, int64_t max_chunk_nnz, csr_layout &l)
     if (w > CSR_MAX_WARPS) w = CSR_MAX_WARPS;
     if (w < 2) return false;
     while (ns < 4 && budget / ((ns + 1) * l.stage_bytes + 128) >= w) ns++;
+    /* diagnostic switches shared with the DG kernel (yfd_spmv_tma.cu): ring depth and warps per CTA */
+    const int ens = env_int("YFD_SPMV_STAGES", 0);
+    if (ens >= 2 && ens <= 8 && budget / (ens * l.stage_bytes + 128) >= 1) {
+        ns = ens;
+        if (w > budget / (ns * l.stage_bytes + 128)) w = budget / (ns * l.stage_bytes + 128);
+    }
+    const int wcap = env_int("YFD_SPMV_WARPS", 0);
+    if (wcap >= 1 && wcap < w) w = wcap;
     l.nstages = ns;
     l.warp_bytes = (ns * l.stage_bytes + 128 + 127) & ~127;
     l.nwarps = w;
@@ -175,6 +183,8 @@ yfd_status launch_csr_spmv_tma(yfd_ctx *ctx, const int64_t *rowptr, const int32_
     const int64_t nchunks = ceil_div(nrows, CSR_CHUNK_ROWS);
     int64_t grid = ceil_div(nchunks, l.nwarps);
     if (grid > ctx->sm_count) grid = ctx->sm_count;
+    const int gcap = env_int("YFD_SPMV_CTAS", 0);
+    if (gcap >= 1 && gcap < grid) grid = gcap;
     if (grid < 1) grid = 1;
     YFD_LAUNCH(ctx, kern, (unsigned) grid, l.nwarps * 32, (size_t) smem, rowptr, colidx, values, x, y, nrows, nchunks, l, sc, partials);
     return YFD_OK;

@@ -192,12 +192,6 @@ dg_spmv_tma(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk
 }
 
 /* ---- host side ------------------------------------------------------------------------------- */
-static int env_int(const char *name, int dflt)
-{
-    const char *e = getenv(name);
-    return e && *e ? atoi(e) : dflt;
-}
-
 static tma_layout make_layout(yfd_ctx *ctx, int bs, int nf)
 {
     tma_layout l;
@@ -242,6 +236,8 @@ static yfd_status launch_tma_bs(yfd_ctx *ctx, int nf, const int64_t *cellptr, co
     const int64_t nchunks = ceil_div(ncells, l.G);
     int64_t grid = ceil_div(nchunks, l.nwarps);
     if (grid > ctx->sm_count) grid = ctx->sm_count;
+    const int gcap = env_int("YFD_SPMV_CTAS", 0);           /* tests: few CTAs = many chunks per warp on a small mesh */
+    if (gcap >= 1 && gcap < grid) grid = gcap;
     if (grid < 1) grid = 1;
     YFD_LAUNCH(ctx, kern, (unsigned) grid, l.nwarps * 32, (size_t) smem, cellptr, blk_cell, values, x, y, ncells, nchunks, l, sc, partials);
     return YFD_OK;
