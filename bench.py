@@ -651,6 +651,13 @@ def main():
             qp, mm = ctx.dg_postprocess(mesh, k, None, device_ptr=d_x.data_ptr())
             anchors["l2_error"], anchors["l2_error_projection"] = float(np.sqrt(qp)), float(np.sqrt(mm))
     sp = sysm.time_spmv(reps=50)
+    oi = None if cfem else sysm.operator_info()
+    sp_streamed = None
+    if oi and oi["uses_classes"]:            # the general (streamed) kernel on the same system, timed beside the class kernel
+        sysm.set_operator_mode(yfd.OPERATOR_STREAMED)
+        sp_streamed = sysm.time_spmv(reps=20)
+        sysm.set_operator_mode(yfd.OPERATOR_AUTO)
+    fp64_peak = ctx.measure_fp64()
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
@@ -662,7 +669,8 @@ def main():
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
     if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
-    roofline = {"bound": "hbm", "kernel": ("csr_spmv_tma" if cfem else "dg_spmv_tma") + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
+    kname = "csr_spmv_tma" if cfem else ("dg_spmv_class" if oi["uses_classes"] else "dg_spmv_tma")
+    roofline = {"bound": "hbm", "kernel": kname + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "hw_frac": achieved / peak, "traffic": traffic,
                 "traffic_source": None if traffic is None else "static: profiles/spmv_traffic.json (one ncu --set full capture of this kernel on this workload, dram__bytes_read.sum + dram__bytes_write.sum; not a live counter)",
                 "peak_source": peak_src,
@@ -672,6 +680,21 @@ def main():
                         "column indices -- + block lists + x + y) / CUDA-event launch time, against the measured HBM peak: the fraction "
                         "the hardware sustains.  csr_equivalent = SURVEY.md 8d's CSR figure (12 B per nonzero + vectors) over the same "
                         "time: what a CSR kernel would have to sustain to be as fast (can exceed the peak)"}
+    flops_spmv = 2.0 * info["nnz"]
+    roofline["fp64"] = {"achieved_tflops": flops_spmv / (sp["ms"] * 1e-3) / 1e12, "peak_tflops": fp64_peak,
+                        "frac": flops_spmv / (sp["ms"] * 1e-3) / 1e12 / fp64_peak,
+                        "peak_source": "DFMA microbenchmark run just now on this device (yfd_ctx_measure_fp64)"}
+    if oi is not None:
+        roofline["operator"] = oi
+    if sp_streamed is not None:
+        sg = sp_streamed["kernel_bytes"] / (sp_streamed["ms"] * 1e-3) / 1e9
+        roofline["streamed_kernel"] = {"kernel": "dg_spmv_tma (the general path: per-cell values streamed by TMA; what this system would run without congruent cells)",
+                                       "ms_per_launch": sp_streamed["ms"], "kernel_requested_bytes_per_launch": sp_streamed["kernel_bytes"],
+                                       "achieved": sg, "frac": sg / peak, "speedup_of_class_kernel": sp_streamed["ms"] / sp["ms"]}
+        roofline["note"] += ("; this mesh consists of %d congruence classes of cells, so the solver multiplies by one block row per class held in "
+                             "shared memory (dg_spmv_class): the matrix stream is gone, the kernel is bound by FP64 issue / shared-memory broadcasts "
+                             "(see fp64) and by the x / y vectors, and its HBM fraction is low BY DESIGN; streamed_kernel is the HBM-bound general path "
+                             "on the same system" % oi["nclasses"])
     # whole CG iteration (SpMV + 2 fused vector kernels) over the timed solve: B_cg = B_spmv + 72 n,
     # summed over ranks
     it = max(1, info["iterations"])
@@ -682,6 +705,8 @@ def main():
         nnz_global = int(tn.item())
     # bytes the three kernels of an iteration request: matrix (DG: 8 B/nnz + block lists; CSR: 12 B/nnz + offsets) + x, y + 72 n
     mat_bytes = (12.0 * nnz_global + 8.0 * (info["n"] + 1)) if cfem else (8.0 * nnz_global + 12.0 * nnz_global / (bs * bs) + 8.0 * info["n"] / bs)
+    if oi is not None and oi["uses_classes"]:
+        mat_bytes = (sp["kernel_bytes"] - 16.0 * info["n_local"]) * world       # index lists only
     cg_gbs = (mat_bytes + 16.0 * info["n"] + 72.0 * info["n"]) * it / (info["ms_solve"] * 1e-3) / 1e9
     sysm.close()
 

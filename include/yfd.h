@@ -71,6 +71,10 @@ int64_t     yfd_ctx_launch_count(const yfd_ctx *ctx);
 /* name and SM count of the device (buf may be NULL) */
 yfd_status  yfd_ctx_device_info(const yfd_ctx *ctx, char *name, size_t cap, int *sm_count, int *cc_major, int *cc_minor);
 
+/* FP64 FMA throughput of the device, measured now (16 independent DFMA chains per thread, 8 x 256 threads per SM, best of
+ * 5 launches, CUDA events): the denominator for the compute fraction of the element kernels and of the class SpMV */
+yfd_status  yfd_ctx_measure_fp64(yfd_ctx *ctx, double *tflops);
+
 /* Multi-GPU: attach an NCCL communicator (one rank per context).  `unique_id` is the
  * 128-byte ncclUniqueId made by rank 0 (yfd_comm_unique_id) and shipped by the host
  * program (torch.distributed broadcast in bench.py).  The reference has no
@@ -358,6 +362,30 @@ yfd_status yfd_system_solve_bicgstab(yfd_ctx *ctx, yfd_system *sys, int use_pc, 
                                      double *x, yfd_cg_info *info, double *history, int64_t history_cap);
 yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
                               const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
+
+/* Operator storage of a DG system.  The reference assembles each cell's blocks from the cell's physical frame
+ * (core/bases.hpp:96-155), so on refinement / structured meshes most cells hold the same (1+nf) blocks up to coordinate
+ * rounding.  yfd_dg_assemble_sip detects such congruence classes (hash of the quantised shape signature, then an
+ * entry-by-entry comparison of every cell's assembled block row with its class representative against a tolerance of
+ * 16 eps |x|/h, floor 2e-13 of the block row's max-norm; YFD_CLASS_TOL overrides) and, when the classes fit in shared
+ * memory, the solvers multiply by ONE block row per class (yfd_spmv_class.cu) instead of streaming 8 B per non-zero.
+ * Otherwise (shattered meshes, advection-reaction) the streamed kernel is used.  AUTO = classes when available. */
+#define YFD_OPERATOR_AUTO     0
+#define YFD_OPERATOR_STREAMED 1    /* always the per-cell values (yfd_spmv_tma.cu) */
+#define YFD_OPERATOR_CLASSES  2    /* YFD_ERR_INVALID_STATE if the system has no usable cache */
+typedef struct yfd_operator_info {
+    int     uses_classes;         /* what the next solve / apply will do                              */
+    int     classes_available;
+    int     reject_reason;        /* 0 none; 1 too many classes for shared memory; 2 too many small classes; 3 deviation > tolerance */
+    int64_t nclasses;
+    double  max_deviation;        /* max over cells of |W_cell - W_class|_max / |W_class|_max          */
+    double  tolerance;
+    int64_t table_bytes;          /* all class block rows                                              */
+    int64_t list_entries;         /* class-sorted cell list incl. padding to 32 per class              */
+} yfd_operator_info;
+yfd_status yfd_system_set_operator_mode(yfd_system *sys, int mode);
+yfd_status yfd_system_operator_info(const yfd_system *sys, yfd_operator_info *info);
+/* yfd_system_get_csr exports the values the solvers APPLY (class representatives when the cache is in use). */
 
 /* y = A x for the assembled system as conjugated_gradient forms it (`y = A*d`, core/solvers.hpp:115), host vectors
  * in REFERENCE numbering, one GPU.  kernel = YFD_APPLY_SOLVER: the kernel the solvers launch (the TMA-streamed

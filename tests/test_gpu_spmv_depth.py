@@ -61,6 +61,7 @@ def test_dg_spmv_deep_ring_matches_reference(yfd, ref, ctx, mtype, r, k, shatter
     A = sp.csr_matrix((out["values"], out["colidx"], out["rowptr"]), shape=(out["n"], out["n"]))
     mesh = yfd.Mesh(ctx, host_mesh_from_ref(yfd, m))
     sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0)
+    sysm.set_operator_mode(yfd.OPERATOR_STREAMED)                    # this file pins the STREAMED kernels (classes: test_gpu_classes.py)
     bs, ncells = bs_of(k), len(m["cells"])
     cells_per_chunk = max(1, 32 // bs)
     chunks_per_warp = -(-ncells // cells_per_chunk) / 2.0
@@ -93,6 +94,7 @@ def test_dg_deep_ring_jacobi_and_block_jacobi(yfd, ref, ctx, stages):
     out = ref.run_dg(3, eta=1.0, use_pc=True)
     mesh = yfd.Mesh(ctx, host_mesh_from_ref(yfd, m))
     sysm = ctx.dg_assemble_sip(mesh, 3, eta=1.0, build_pc=True)
+    sysm.set_operator_mode(yfd.OPERATOR_STREAMED)
     p = yfd.CgParams(rr_tol=1e-12, rr_max=1e4, max_iter=2 * sysm.n)
     with squeezed(stages):
         a = sysm.solve_cg(p, use_pc=yfd.PC_JACOBI)
@@ -158,6 +160,7 @@ def test_large_mesh_spmv_vs_scipy_and_plain_kernel(yfd, ctx, name, cell, how, k)
     hm = yfd.HostMesh.structured(cell, how["nx"]) if "nx" in how else yfd.HostMesh.create(cell, how["r"])
     mesh = yfd.Mesh(ctx, hm)
     sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0)
+    sysm.set_operator_mode(yfd.OPERATOR_STREAMED)
     assert len(hm.cells) >= 260_000
     rowptr, colidx, vals = sysm.csr()
     A = sp.csr_matrix((vals, colidx.astype(np.int32), rowptr), shape=(sysm.n, sysm.n))
@@ -187,6 +190,7 @@ def test_config0_full_size_against_live_reference(yfd, ref, ctx):
     out = ref.run_dg(1, eta=1.0)
     mesh = yfd.Mesh(ctx, host_mesh_from_ref(yfd, m))
     sysm = ctx.dg_assemble_sip(mesh, 1, eta=1.0)
+    sysm.set_operator_mode(yfd.OPERATOR_STREAMED)
     assert sysm.n == 49152 and sysm.nnz == 587520 == out["nnz"]
     rowptr, colidx, vals = sysm.csr()
     assert np.array_equal(rowptr, out["rowptr"]) and np.array_equal(colidx, out["colidx"])

@@ -95,6 +95,14 @@ class MaxwellStepInfo(C.Structure):
                 ("operator_applications", C.c_int64)]
 
 
+class OperatorInfo(C.Structure):
+    _fields_ = [("uses_classes", C.c_int), ("classes_available", C.c_int), ("reject_reason", C.c_int), ("nclasses", C.c_int64),
+                ("max_deviation", C.c_double), ("tolerance", C.c_double), ("table_bytes", C.c_int64), ("list_entries", C.c_int64)]
+
+
+OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES = 0, 1, 2
+
+
 class CgInfo(C.Structure):
     _fields_ = [("iterations", C.c_int64), ("nr0", C.c_double), ("nr", C.c_double), ("converged", C.c_int),
                 ("ms_solve", C.c_double), ("ms_spmv", C.c_double), ("history_len", C.c_int64), ("transport", C.c_int)]
@@ -124,6 +132,7 @@ def lib():
         "yfd_ctx_launch_count": (i64, [vp]),
         "yfd_ctx_trim": (cint, [vp, P(C.c_size_t)]),
         "yfd_ctx_device_info": (cint, [vp, C.c_char_p, C.c_size_t, P(cint), P(cint), P(cint)]),
+        "yfd_ctx_measure_fp64": (cint, [vp, P(dbl)]),
         "yfd_comm_unique_id": (cint, [C.c_char_p]),
         "yfd_ctx_attach_comm": (cint, [vp, cint, cint, C.c_char_p]),
         "yfd_ctx_rank": (cint, [vp]),
@@ -176,6 +185,8 @@ def lib():
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_bicgstab_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_solve_bicgstab": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
+        "yfd_system_set_operator_mode": (cint, [vp, cint]),
+        "yfd_system_operator_info": (cint, [vp, P(OperatorInfo)]),
         "yfd_system_apply": (cint, [vp, vp, cint, _f64p, _f64p]),
         "yfd_system_true_residual": (cint, [vp, vp, vp, vp, P(dbl)]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
@@ -254,6 +265,12 @@ class Context:
         sm, ma, mi = C.c_int(), C.c_int(), C.c_int()
         self.check(lib().yfd_ctx_device_info(self._h, name, 256, C.byref(sm), C.byref(ma), C.byref(mi)))
         return dict(name=name.value.decode(), sm_count=sm.value, cc=(ma.value, mi.value))
+
+    def measure_fp64(self):
+        """FP64 FMA peak of this device in TFLOP/s (DFMA microbenchmark, yfd_ctx_measure_fp64)."""
+        t = C.c_double()
+        self.check(lib().yfd_ctx_measure_fp64(self._h, C.byref(t)))
+        return t.value
 
     # ---- multi-GPU ------------------------------------------------------------------
     @staticmethod
@@ -594,6 +611,15 @@ class System:
                                                         C.c_void_p(d_x) if d_x else None, C.byref(info)))
         return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
                     transport=("one GPU", "NCCL", "peer memory")[info.transport])
+
+    def set_operator_mode(self, mode):
+        """OPERATOR_AUTO / OPERATOR_STREAMED / OPERATOR_CLASSES (include/yfd.h)."""
+        self.ctx.check(lib().yfd_system_set_operator_mode(self._h, mode))
+
+    def operator_info(self):
+        oi = OperatorInfo()
+        self.ctx.check(lib().yfd_system_operator_info(self._h, C.byref(oi)))
+        return {k: getattr(oi, k) for k, _ in OperatorInfo._fields_}
 
     def apply(self, x, plain=False):
         """y = A x (reference numbering); plain=True: the independent one-thread-per-row kernel."""

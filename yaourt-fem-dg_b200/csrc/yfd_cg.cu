@@ -335,6 +335,7 @@ struct spmv_op {
     const int64_t *cellptr = nullptr; const int32_t *blk_cell = nullptr; int bs = 0, nf = 0;
     int64_t ncells = 0;
     const double *values_halo = nullptr;     /* block-Jacobi on several ranks: the halo cells' blocks (own allocation) */
+    const dg_classes *cls = nullptr;         /* congruence-class cache (yfd_spmv_class.cu) instead of the streamed values */
     /* several ranks: x carries nhalo*bs halo entries after the nrows owned ones */
     const dist_plan *plan = nullptr;
 };
@@ -380,7 +381,9 @@ static yfd_status launch_csr_spmv(yfd_ctx *ctx, const spmv_op &op, const double 
 template <bool WITH_DOT>
 static yfd_status launch_spmv(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y, cg_scalars *sc, double *partials)
 {
-    if (op.cellptr)         /* DG block rows: the TMA-streamed kernel (yfd_spmv_tma.cu); there is no other path for them */
+    if (op.cls)             /* DG on congruent cells: one block row per class in shared memory (yfd_spmv_class.cu) */
+        return launch_dg_spmv_class<WITH_DOT>(ctx, *op.cls, op.bs, op.nf, x, y, sc, partials);
+    if (op.cellptr)         /* DG block rows: the TMA-streamed kernel (yfd_spmv_tma.cu) */
         return launch_dg_spmv_tma<WITH_DOT>(ctx, op.bs, op.nf, op.cellptr, op.blk_cell, op.values, op.ncells, x, y, sc, partials);
     return launch_csr_spmv<WITH_DOT>(ctx, op, x, y, sc, partials);
 }
@@ -622,10 +625,10 @@ static spmv_op op_of_csr(const yfd_csr *A)
 static spmv_op op_of_system(const yfd_system *sys, bool allow_block_kernel)
 {
     spmv_op op = op_of_csr(&sys->A);
-    (void) allow_block_kernel;
     if (sys->kind == YFD_SYS_DG) {
         op.cellptr = sys->cellptr.p; op.blk_cell = sys->blk_cell.p; op.bs = sys->bs; op.nf = sys->nf; op.ncells = sys->ncells;
         op.plan = sys->plan.get();
+        if (allow_block_kernel && system_uses_classes(sys)) op.cls = &sys->classes;
     }
     return op;
 }
@@ -757,7 +760,7 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
             YFD_LAUNCH(ctx, dg_transpose_blocks, stream_grid(ctx, sys->nnz), 256, 0, sys->cellptr.p, sys->blk_cell.p, sys->A.values.p,
                        sys->values_t.p, sys->ncells, sys->bs);
         }
-        opT = op_of_system(sys, true);
+        opT = op_of_system(sys, false);
         opT.values = sys->values_t.p;
     }
     spmv_op opD;
@@ -808,6 +811,33 @@ yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc,
     return system_solve(ctx, sys, use_pc, p, nullptr, d_x, info, nullptr, 0);
 }
 
+yfd_status yfd_system_set_operator_mode(yfd_system *sys, int mode)
+{
+    if (!sys) return YFD_ERR_INVALID_ARGUMENT;
+    if (mode != YFD_OPERATOR_AUTO && mode != YFD_OPERATOR_STREAMED && mode != YFD_OPERATOR_CLASSES)
+        return fail(sys->ctx, YFD_ERR_INVALID_ARGUMENT, "mode must be YFD_OPERATOR_AUTO, _STREAMED or _CLASSES");
+    if (mode == YFD_OPERATOR_CLASSES && !sys->classes.ready)
+        return fail(sys->ctx, YFD_ERR_INVALID_STATE, "this system has no usable congruence-class cache (reason %d, %d classes, deviation %.3g, tolerance %.3g)",
+                    sys->classes.reject, sys->classes.ncls, sys->classes.max_dev, sys->classes.tol);
+    sys->operator_mode = mode;
+    return YFD_OK;
+}
+
+yfd_status yfd_system_operator_info(const yfd_system *sys, yfd_operator_info *info)
+{
+    if (!sys || !info) return YFD_ERR_INVALID_ARGUMENT;
+    const dg_classes &cl = sys->classes;
+    info->uses_classes = system_uses_classes(sys) ? 1 : 0;
+    info->classes_available = cl.ready ? 1 : 0;
+    info->reject_reason = cl.reject;
+    info->nclasses = cl.ncls;
+    info->max_deviation = cl.max_dev;
+    info->tolerance = cl.tol;
+    info->table_bytes = (int64_t) cl.table_doubles * 8;
+    info->list_entries = cl.npos;
+    return YFD_OK;
+}
+
 yfd_status yfd_system_apply(yfd_ctx *ctx, yfd_system *sys, int kernel, const double *x, double *y)
 {
     if (!ctx || !sys || !x || !y) return YFD_ERR_INVALID_ARGUMENT;
@@ -823,7 +853,8 @@ yfd_status yfd_system_apply(yfd_ctx *ctx, yfd_system *sys, int kernel, const dou
     YFD_TRY(xr.upload(ctx, x, (size_t) n));
     YFD_TRY(operand_from_ref(ctx, sys, xr.p, xi));
     const spmv_op op = op_of_system(sys, true);
-    if (kernel == YFD_APPLY_PLAIN) YFD_TRY(launch_apply_plain(ctx, op, xi.p, yi.p));
+    dbuf<double> applied;
+    if (kernel == YFD_APPLY_PLAIN) YFD_TRY(launch_apply_plain(ctx, sys, op, applied, xi.p, yi.p));
     else YFD_TRY(launch_spmv<false>(ctx, op, xi.p, yi.p, nullptr, nullptr));
     if (!dg) return yi.download(ctx, y, (size_t) n);
     YFD_TRY(yr.alloc(ctx, (size_t) n));
@@ -847,7 +878,8 @@ yfd_status yfd_system_true_residual(yfd_ctx *ctx, yfd_system *sys, const double 
     YFD_TRY(operand_from_ref(ctx, sys, d_x, xi));
     YFD_TRY(yi.alloc(ctx, (size_t) nloc, 2));
     const spmv_op op = op_of_system(sys, true);
-    YFD_TRY(launch_apply_plain(ctx, op, xi.p, yi.p));
+    dbuf<double> applied;
+    YFD_TRY(launch_apply_plain(ctx, sys, op, applied, xi.p, yi.p));
     const int nb = (int) std::max<int64_t>(1, std::min<int64_t>(ceil_div(nloc, 256), 1024));
     YFD_TRY(part.alloc(ctx, (size_t) 2 * nb)); YFD_TRY(tot.alloc(ctx, 2));
     YFD_LAUNCH(ctx, residual_partials, (unsigned) nb, 256, 0, (const double *) sys->rhs.p, (const double *) yi.p, nloc, part.p);
@@ -885,7 +917,9 @@ yfd_status yfd_system_time_spmv(yfd_ctx *ctx, yfd_system *sys, int reps, double 
     /* 12 nnz + row offsets + x read once + y written once */
     if (csr_bytes) *csr_bytes = 12.0 * (double) sys->nnz + 8.0 * (double) (n + 1) + 16.0 * (double) n;
     if (kernel_bytes) {
-        if (op.cellptr)
+        if (op.cls)         /* class ids + cell + neighbour indices per list entry, the class table once per CTA (L2), x and y */
+            *kernel_bytes = 4.0 * (double) op.cls->npos * (1 + sys->nf) + 4.0 * (double) op.cls->ntiles + 16.0 * (double) n;
+        else if (op.cellptr)
             *kernel_bytes = 8.0 * (double) sys->nnz + 8.0 * (double) (sys->ncells + 1) + 4.0 * (double) sys->blk_cell.n + 16.0 * (double) n;
         else
             *kernel_bytes = 12.0 * (double) sys->nnz + 8.0 * (double) (n + 1) + 16.0 * (double) n;

@@ -152,4 +152,8 @@ template <bool WITH_DOT>
 yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellptr, const int32_t *blk_cell, const double *values,
                               int64_t ncells, const double *x, double *y, cg_scalars *sc, double *partials);
 
+/* yfd_spmv_class.cu: the same product from one block row per congruence class held in shared memory */
+template <bool WITH_DOT>
+yfd_status launch_dg_spmv_class(yfd_ctx *ctx, const dg_classes &cl, int bs, int nf, const double *x, double *y, cg_scalars *sc, double *partials);
+
 } // namespace yfd

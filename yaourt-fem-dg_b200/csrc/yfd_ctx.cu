@@ -55,6 +55,26 @@ void pool_trim(yfd_ctx *ctx)
 
 } // namespace yfd
 
+namespace yfd {
+/* FP64 FMA peak of this device ("measure a DFMA microbenchmark before quoting a compute fraction"):
+ * 16 independent multiply-add chains per thread, 8 CTAs of 256 threads per SM, nothing but DFMA in the loop */
+__global__ void __launch_bounds__(256) dfma_peak(int iters, double m, double *__restrict__ sink)
+{
+    double a[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) a[k] = 1.0 + 1e-9 * (threadIdx.x + k);
+    const double c = 1e-12;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) a[k] = fma(a[k], m, c);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += a[k];
+    if (s == 12345.678) sink[0] = s;          /* never true: keeps the chains alive */
+}
+}
+
 extern "C" {
 
 const char *yfd_status_string(yfd_status s)
@@ -155,6 +175,29 @@ yfd_status yfd_ctx_device_info(const yfd_ctx *ctx, char *name, size_t cap, int *
     if (sm_count) *sm_count = ctx->sm_count;
     if (cc_major) *cc_major = ctx->cc_major;
     if (cc_minor) *cc_minor = ctx->cc_minor;
+    return YFD_OK;
+}
+
+yfd_status yfd_ctx_measure_fp64(yfd_ctx *ctx, double *tflops)
+{
+    using namespace yfd;
+    if (!ctx || !tflops) return YFD_ERR_INVALID_ARGUMENT;
+    scoped_device dev(ctx->device);
+    dbuf<double> sink;
+    YFD_TRY(sink.alloc(ctx, 1));
+    const int iters = 4096, grid = ctx->sm_count * 8;
+    YFD_LAUNCH(ctx, yfd::dfma_peak, grid, 256, 0, iters, 1.000000001, sink.p);        /* warm-up */
+    gpu_timer t;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        t.start(ctx->stream);
+        YFD_LAUNCH(ctx, yfd::dfma_peak, grid, 256, 0, iters, 1.000000001, sink.p);
+        t.stop(ctx->stream);
+        const double flops = 2.0 * 16.0 * (double) iters * 256.0 * (double) grid;
+        const double tf = flops / (t.ms() * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    *tflops = best;
     return YFD_OK;
 }
 

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdarg>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 #include <vector>
 #include <memory>
@@ -279,6 +280,24 @@ struct yfd_csr {
 
 enum yfd_system_kind { YFD_SYS_DG = 1, YFD_SYS_CFEM = 2 };
 
+namespace yfd {
+/* congruence-class operator cache of a DG system (yfd_spmv_class.cu): one block row per class instead of one per cell */
+struct dg_classes {
+    bool     ready = false;           /* the solvers use the cache                                                    */
+    int      reject = 0;              /* why not: 1 = table does not fit shared memory / too many classes, 2 = too much
+                                         padding (many small classes), 3 = a block row deviates from its class by > tol */
+    int      ncls = 0;
+    int      table_doubles = 0;
+    int64_t  npos = 0, ntiles = 0;    /* work list length (classes padded to 32), tiles of 32                           */
+    double   max_dev = 0.0, tol = 0.0;/* largest |W_cell - W_class| / max|W_class| found by the verification pass        */
+    dbuf<double>  table;              /* [ncls][nf+1][slot stride]: block rows in canonical slot order (self, faces)     */
+    dbuf<int32_t> work_cell;          /* [npos] local cell index, -1 = padding                                           */
+    dbuf<int32_t> work_nbr;           /* [nf][npos] local x cell index of the neighbour across each local face           */
+    dbuf<int32_t> tile_cls;           /* [ntiles]                                                                        */
+    dbuf<int32_t> cell_cls;           /* [ncells]                                                                        */
+};
+}
+
 struct yfd_system {
     yfd_ctx *ctx = nullptr;
     int      kind = 0;
@@ -304,6 +323,10 @@ struct yfd_system {
     std::shared_ptr<yfd::dist_plan> plan;   /* null on one GPU                      */
     yfd::dbuf<int64_t> cellptr;       /* [ncells+1]                                 */
     yfd::dbuf<int32_t> blk_cell;      /* [nblocks]                                  */
+    yfd::dbuf<int8_t>  slots;         /* [ncells][nf+1]: position of the diagonal block and of the block across each local
+                                         face inside the cell's (id-sorted) block list, -1 on boundary faces */
+    yfd::dg_classes    classes;       /* SIP diffusion on meshes of congruent cells (yfd_spmv_class.cu)      */
+    int      operator_mode = 0;       /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES (yfd_system_set_operator_mode) */
     yfd::dbuf<int32_t> perm, iperm;   /* copies of the mesh's cell permutation      */
     /* CFEM */
     int64_t  npoints = 0;
@@ -315,6 +338,10 @@ namespace yfd {
 /* DG: this rank's rows (internal order) -> the FULL vector in reference numbering, on the device (d_out_ref [n]);
  * with several ranks the parts are combined by an all-reduce, so every rank ends up with the whole vector */
 yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *d_out_ref);
+/* ---- yfd_spmv_class.cu ---- */
+yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int key_bits, double tol);
+yfd_status expand_class_values(yfd_ctx *ctx, const yfd_system *sys, double *d_values_out);
+inline bool system_uses_classes(const yfd_system *sys) { return sys->classes.ready && sys->operator_mode != 1 /* YFD_OPERATOR_STREAMED */; }
 /* ---- yfd_triplets.cu ---- */
 int key_bits_for(int64_t n);
 /* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order.  Entries of

@@ -1,0 +1,336 @@
+/*
+ * yfd_spmv_class.cu -- the CG hot kernel on meshes of congruent cells: y = A d (+ partial sums of d.y) with ONE block row
+ * per congruence class kept in shared memory, instead of one block row per cell streamed from HBM.
+ *
+ * Same product as `y = A*d` in conjugated_gradient (core/solvers.hpp:115; blaze SMatDVecMultExpr.h:204-207).  The
+ * reference assembles every cell's blocks from the cell's PHYSICAL frame (barycentre, diameter: core/bases.hpp:96-155,
+ * 438-442), so on its refinement meshes and on structured meshes thousands to millions of cells hold the same (1+nf)
+ * blocks up to the rounding of their coordinates (hard part 4, names the per-class cache as the
+ * optimisation).  The streamed kernel (yfd_spmv_tma.cu) moves 8 B per non-zero per CG iteration -- 8.4 GB per launch on
+ * the 21 M-dof headline mesh to multiply by nine distinct block rows; this kernel moves the vectors, 4 B of class/cell
+ * index and nf neighbour indices per cell, and nothing else.
+ *
+ * Classes (build_dg_classes): a 40-bit hash of the cell's quantised shape signature -- vertex offsets from the
+ * barycentre, the neighbours' barycentre offsets and diameters, all in units of the cell diameter, boundary flags
+ * (dg_class_keys, yfd_dg.cu) -- is radix-sorted; equal keys are one class, its first cell (lowest internal id) the
+ * representative.  The hash only PROPOSES classes: every cell's assembled block row is then compared entry by entry
+ * with its representative's (dg_class_verify), and the cache is used only if the largest deviation, relative to the
+ * block row's max-norm, stays below a tolerance tied to the rounding noise of the mesh coordinates (eps |x| / h);
+ * otherwise, or with more classes than fit in shared memory (shattered meshes: every cell its own class), the system
+ * keeps the streamed kernel.  yfd_system_get_csr exports the APPLIED values, so the parity tests compare what the
+ * solver multiplies by with the reference (1e-12 bar).
+ *
+ * Kernel shape: cells are listed class by class (ascending internal id inside a class, classes padded to 32), a warp
+ * takes 32 consecutive list entries = 32 cells of ONE class, lane <-> cell.  Per canonical slot (self, then the local
+ * faces in the reference's order) the lane loads its neighbour's bs unknowns (128-bit loads) and runs the bs x bs block
+ * against them with the block entries read as warp-wide BROADCASTS from shared memory (one LDS.128 = one wavefront
+ * feeds two DFMA of every lane): 0.5 shared-memory wavefronts per warp-wide DFMA against 3 in the row-per-lane
+ * layout of the streamed kernel, which is what makes the FP64 pipe, not shared memory, the limit.
+ * Sums run slot by slot, column by column, in one accumulator per row: a fixed order, bit-reproducible run to run and
+ * identical on any number of ranks (the block order is canonical, not id-sorted).
+ */
+#include "yfd_internal.hpp"
+#include "yfd_cg_shared.cuh"
+#include <vector>
+#include <cmath>
+#include <algorithm>
+
+namespace yfd {
+
+constexpr int CLS_THREADS = 256;
+constexpr int CLS_MAX_CLASSES = 4096;        /* beyond this the mesh is not "a few congruence classes" */
+
+__host__ __device__ constexpr int cls_slot_stride(int bs) { return (bs * bs + 1) & ~1; }
+
+/* ---- build: class ids from sorted keys ------------------------------------------------------- */
+__global__ void cls_flag_starts(const uint64_t *__restrict__ keys, int64_t n, int32_t *__restrict__ flag)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
+}
+
+__global__ void cls_collect_starts(const int32_t *__restrict__ flag, const int64_t *__restrict__ excl, int64_t n,
+                                   int64_t *__restrict__ start /* [ncls+1] */)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && flag[i]) start[excl[i]] = i;
+    if (i == n) start[excl[n]] = n;
+}
+
+/* work list: position poff[k] + (i - start[k]) holds the i-th cell of the sorted order */
+__global__ void cls_fill_work(const int32_t *__restrict__ flag, const int64_t *__restrict__ excl, const int64_t *__restrict__ start,
+                              const int64_t *__restrict__ poff, const uint32_t *__restrict__ sorted_cell, int64_t n,
+                              const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const int8_t *__restrict__ slots,
+                              int nf, int64_t npos, int32_t *__restrict__ work_cell, int32_t *__restrict__ work_nbr,
+                              int32_t *__restrict__ cell_cls)
+{
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t k = excl[i] + flag[i] - 1;
+    const int64_t pos = poff[k] + (i - start[k]);
+    const int32_t c = (int32_t) sorted_cell[i];
+    work_cell[pos] = c;
+    cell_cls[c] = (int32_t) k;
+    const int64_t cp = cellptr[c];
+    const int32_t self = blk_cell[cp + slots[(int64_t) c * (nf + 1)]];
+    for (int e = 0; e < nf; e++) {
+        const int s = slots[(int64_t) c * (nf + 1) + 1 + e];
+        work_nbr[(int64_t) e * npos + pos] = s >= 0 ? blk_cell[cp + s] : self;     /* boundary: any valid cell, the block is zero */
+    }
+}
+
+/* one CTA per class: the representative's block row in canonical slot order; scale[k] = its max-norm */
+__global__ void cls_build_table(const int64_t *__restrict__ start, const uint32_t *__restrict__ sorted_cell,
+                                const int64_t *__restrict__ cellptr, const int8_t *__restrict__ slots, const double *__restrict__ values,
+                                int bs, int nf, double *__restrict__ table, double *__restrict__ scale)
+{
+    __shared__ double sm[32];
+    const int k = blockIdx.x, bs2 = bs * bs, ss = cls_slot_stride(bs), nb = nf + 1;
+    const int64_t c = sorted_cell[start[k]];
+    const int64_t cp = cellptr[c];
+    double mx = 0.0;
+    for (int t = threadIdx.x; t < nb * ss; t += blockDim.x) {
+        const int s = t / ss, m = t - s * ss;
+        const int slot = slots[c * nb + s];
+        const double v = (slot >= 0 && m < bs2) ? values[(cp + slot) * bs2 + m] : 0.0;
+        table[(int64_t) k * nb * ss + t] = v;
+        mx = fmax(mx, fabs(v));
+    }
+    /* block max */
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int) (blockDim.x >> 5); w++) mx = fmax(mx, sm[w]);
+        scale[k] = mx;
+    }
+}
+
+/* one warp per cell: largest |W_c - T_class| / max|T_class| over the block row; a slot present on one side only = +inf */
+__global__ void cls_verify(const int32_t *__restrict__ cell_cls, const int64_t *__restrict__ cellptr, const int8_t *__restrict__ slots,
+                           const double *__restrict__ values, const double *__restrict__ table, const double *__restrict__ scale,
+                           int64_t ncells, int bs, int nf, unsigned long long *__restrict__ worst_bits)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const int bs2 = bs * bs, ss = cls_slot_stride(bs), nb = nf + 1;
+    double worst = 0.0;
+    for (int64_t c = warp; c < ncells; c += nwarps) {
+        const int k = cell_cls[c];
+        const int64_t cp = cellptr[c];
+        const double *T = table + (int64_t) k * nb * ss;
+        double d = 0.0;
+        for (int s = 0; s < nb; s++) {
+            const int slot = slots[c * nb + s];
+            for (int m = lane; m < bs2; m += 32) {
+                const double t = T[s * ss + m];
+                d = fmax(d, slot >= 0 ? fabs(values[(cp + slot) * bs2 + m] - t) : (t != 0.0 ? INFINITY : 0.0));
+            }
+        }
+        worst = fmax(worst, d / scale[k]);
+    }
+    for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    if (lane == 0 && worst > 0.0) atomicMax(worst_bits, (unsigned long long) __double_as_longlong(worst));   /* >= 0: bits order as values */
+}
+
+/* the applied values in the streamed layout (yfd_system_get_csr, block-Jacobi): W_c <- T_class(c) */
+__global__ void cls_expand_values(const int32_t *__restrict__ cell_cls, const int64_t *__restrict__ cellptr, const int8_t *__restrict__ slots,
+                                  const double *__restrict__ table, int64_t ncells, int bs, int nf, double *__restrict__ values_out)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const int bs2 = bs * bs, ss = cls_slot_stride(bs), nb = nf + 1;
+    for (int64_t c = warp; c < ncells; c += nwarps) {
+        const double *T = table + (int64_t) cell_cls[c] * nb * ss;
+        const int64_t cp = cellptr[c];
+        for (int s = 0; s < nb; s++) {
+            const int slot = slots[c * nb + s];
+            if (slot < 0) continue;
+            for (int m = lane; m < bs2; m += 32) values_out[(cp + slot) * bs2 + m] = T[s * ss + m];
+        }
+    }
+}
+
+yfd_status expand_class_values(yfd_ctx *ctx, const yfd_system *sys, double *d_values_out)
+{
+    const dg_classes &cl = sys->classes;
+    const int64_t want = ceil_div(sys->ncells, 8), cap = (int64_t) ctx->sm_count * 16;
+    YFD_LAUNCH(ctx, cls_expand_values, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) cl.cell_cls.p,
+               (const int64_t *) sys->cellptr.p, (const int8_t *) sys->slots.p, (const double *) cl.table.p, sys->ncells, sys->bs, sys->nf, d_values_out);
+    return YFD_OK;
+}
+
+/* d_keys [ncells]: class keys in internal cell order (clobbered).  On return sys->classes.ready says whether the cache is
+ * usable; every "no" is a normal outcome (the streamed kernel stays), only CUDA failures are errors. */
+yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int key_bits, double tol)
+{
+    dg_classes &cl = sys->classes;
+    cl = dg_classes();
+    const int64_t nc = sys->ncells;
+    const int bs = sys->bs, nf = sys->nf, nb = nf + 1, ss = cls_slot_stride(bs);
+    if (nc < 1 || (bs != 1 && bs != 3 && bs != 6 && bs != 10 && bs != 15)) return YFD_OK;
+    dbuf<uint32_t> ids, ids_tmp;
+    dbuf<uint64_t> keys_tmp;
+    dbuf<int32_t> flag;
+    dbuf<int64_t> excl;
+    YFD_TRY(ids.alloc(ctx, (size_t) nc)); YFD_TRY(ids_tmp.alloc(ctx, (size_t) nc)); YFD_TRY(keys_tmp.alloc(ctx, (size_t) nc));
+    YFD_TRY(flag.alloc(ctx, (size_t) nc)); YFD_TRY(excl.alloc(ctx, (size_t) nc + 1));
+    YFD_TRY(fill_iota_u32(ctx, ids.p, nc));
+    YFD_TRY(radix_sort_pairs(ctx, d_keys, ids.p, keys_tmp.p, ids_tmp.p, nc, key_bits));     /* stable: ascending cell id inside a class */
+    const unsigned g = (unsigned) ceil_div(nc + 1, 256);
+    YFD_LAUNCH(ctx, cls_flag_starts, g, 256, 0, (const uint64_t *) d_keys, nc, flag.p);
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, flag.p, excl.p, nc));
+    int64_t ncls = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&ncls, excl.p + nc, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cl.ncls = (int) std::min<int64_t>(ncls, 0x7fffffff);
+    const size_t table_bytes = (size_t) ncls * nb * ss * sizeof(double);
+    if (ncls > CLS_MAX_CLASSES || table_bytes + 1024 > ctx->smem_optin) { cl.reject = 1; return YFD_OK; }   /* does not fit shared memory */
+
+    dbuf<int64_t> start, poff;
+    YFD_TRY(start.alloc(ctx, (size_t) ncls + 1)); YFD_TRY(poff.alloc(ctx, (size_t) ncls + 1));
+    YFD_LAUNCH(ctx, cls_collect_starts, g, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, nc, start.p);
+    std::vector<int64_t> hstart((size_t) ncls + 1), hpoff((size_t) ncls + 1);
+    YFD_TRY(start.download(ctx, hstart.data(), (size_t) ncls + 1));
+    int64_t npos = 0;
+    for (int64_t k = 0; k < ncls; k++) { hpoff[k] = npos; npos += (hstart[k + 1] - hstart[k] + 31) / 32 * 32; }
+    hpoff[ncls] = npos;
+    /* padding beyond 25 % of the list = too many small classes for lane-per-cell tiles to pay */
+    if (npos > nc + nc / 4 + 32 * 64) { cl.reject = 2; return YFD_OK; }
+    const int64_t ntiles = npos / 32;
+    std::vector<int32_t> htile((size_t) ntiles);
+    for (int64_t k = 0; k < ncls; k++)
+        for (int64_t t = hpoff[k] / 32; t < hpoff[k + 1] / 32; t++) htile[t] = (int32_t) k;
+    YFD_TRY(poff.upload(ctx, hpoff.data(), (size_t) ncls + 1));
+    YFD_TRY(cl.tile_cls.alloc(ctx, (size_t) ntiles));
+    YFD_TRY(cl.tile_cls.upload(ctx, htile.data(), (size_t) ntiles));
+    YFD_TRY(cl.work_cell.alloc(ctx, (size_t) npos)); YFD_TRY(cl.work_nbr.alloc(ctx, (size_t) (npos * nf)));
+    YFD_TRY(cl.cell_cls.alloc(ctx, (size_t) nc));
+    YFD_CUDA(ctx, cudaMemsetAsync(cl.work_cell.p, 0xff, (size_t) npos * sizeof(int32_t), ctx->stream));      /* -1 = padding */
+    YFD_CUDA(ctx, cudaMemsetAsync(cl.work_nbr.p, 0, (size_t) (npos * nf) * sizeof(int32_t), ctx->stream));
+    YFD_LAUNCH(ctx, cls_fill_work, g, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, (const int64_t *) start.p, (const int64_t *) poff.p,
+               (const uint32_t *) ids.p, nc, (const int64_t *) sys->cellptr.p, (const int32_t *) sys->blk_cell.p, (const int8_t *) sys->slots.p,
+               nf, npos, cl.work_cell.p, cl.work_nbr.p, cl.cell_cls.p);
+    dbuf<double> scale;
+    dbuf<unsigned long long> worst;
+    YFD_TRY(cl.table.alloc(ctx, (size_t) ncls * nb * ss, 2)); YFD_TRY(scale.alloc(ctx, (size_t) ncls));
+    YFD_TRY(worst.alloc(ctx, 1)); YFD_TRY(worst.zero(ctx));
+    YFD_LAUNCH(ctx, cls_build_table, (unsigned) ncls, 128, 0, (const int64_t *) start.p, (const uint32_t *) ids.p, (const int64_t *) sys->cellptr.p,
+               (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, bs, nf, cl.table.p, scale.p);
+    const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
+    YFD_LAUNCH(ctx, cls_verify, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) cl.cell_cls.p, (const int64_t *) sys->cellptr.p,
+               (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, (const double *) cl.table.p, (const double *) scale.p, nc, bs, nf, worst.p);
+    unsigned long long wb = 0;
+    YFD_TRY(worst.download(ctx, &wb, 1));
+    double dev;
+    memcpy(&dev, &wb, sizeof(dev));
+    cl.max_dev = dev; cl.tol = tol; cl.npos = npos; cl.ntiles = ntiles; cl.table_doubles = (int) (ncls * nb * ss);
+    if (!(dev <= tol)) { cl.reject = 3; return YFD_OK; }      /* also catches inf / NaN */
+    cl.ready = true;
+    return YFD_OK;
+}
+
+/* ---- the kernel ------------------------------------------------------------------------------ */
+template <int BS>
+__device__ __forceinline__ void load_cell(const double *__restrict__ x, int32_t cell, double (&v)[BS])
+{
+    if (BS % 2 == 0) {
+        const double2 *p = reinterpret_cast<const double2 *>(x + (int64_t) cell * BS);
+#pragma unroll
+        for (int q = 0; q < BS / 2; q++) { const double2 t = __ldg(p + q); v[2 * q] = t.x; v[2 * q + 1] = t.y; }
+    } else {
+        const double *p = x + (int64_t) cell * BS;
+#pragma unroll
+        for (int q = 0; q < BS; q++) v[q] = __ldg(p + q);
+    }
+}
+
+template <int BS, int NB, bool WITH_DOT>
+__global__ void __launch_bounds__(CLS_THREADS, 2)
+dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t *__restrict__ work_cell,
+              const int32_t *__restrict__ work_nbr, const int32_t *__restrict__ tile_cls, int64_t ntiles, int64_t npos,
+              const double *__restrict__ x, double *__restrict__ y, cg_scalars *__restrict__ sc, double *__restrict__ partials)
+{
+    if (WITH_DOT && sc->done) return;
+    extern __shared__ __align__(16) double T[];
+    constexpr int BS2 = BS * BS, SS = cls_slot_stride(BS);
+    for (int i = threadIdx.x; i < table_doubles; i += blockDim.x) T[i] = table[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    double dot = 0.0;
+    for (int64_t tile = gw; tile < ntiles; tile += nw) {
+        const int k = __ldg(&tile_cls[tile]);
+        const int64_t pos = tile * 32 + lane;
+        const int32_t c = __ldg(&work_cell[pos]);
+        if (c < 0) continue;                                   /* padding at the end of a class */
+        const double *Wk = T + (size_t) k * (NB * SS);
+        double acc[BS];
+#pragma unroll
+        for (int i = 0; i < BS; i++) acc[i] = 0.0;
+#pragma unroll
+        for (int s = 0; s < NB; s++) {
+            const int32_t nb = s == 0 ? c : __ldg(&work_nbr[(int64_t) (s - 1) * npos + pos]);
+            double xv[BS];
+            load_cell<BS>(x, nb, xv);
+            const double *W = Wk + s * SS;
+#pragma unroll
+            for (int m = 0; m + 1 < BS2; m += 2) {
+                const double2 w = *reinterpret_cast<const double2 *>(W + m);       /* same address in every lane: a broadcast */
+                acc[m % BS] = fma(w.x, xv[m / BS], acc[m % BS]);
+                acc[(m + 1) % BS] = fma(w.y, xv[(m + 1) / BS], acc[(m + 1) % BS]);
+            }
+            if (BS2 & 1) acc[BS - 1] = fma(W[BS2 - 1], xv[BS - 1], acc[BS - 1]);
+        }
+        if (BS % 2 == 0) {
+            double2 *p = reinterpret_cast<double2 *>(y + (int64_t) c * BS);
+#pragma unroll
+            for (int q = 0; q < BS / 2; q++) p[q] = make_double2(acc[2 * q], acc[2 * q + 1]);
+        } else {
+#pragma unroll
+            for (int q = 0; q < BS; q++) y[(int64_t) c * BS + q] = acc[q];
+        }
+        if (WITH_DOT) {
+            double xs[BS];
+            load_cell<BS>(x, c, xs);
+#pragma unroll
+            for (int i = 0; i < BS; i++) dot = fma(acc[i], xs[i], dot);
+        }
+    }
+    if (WITH_DOT) {
+        __shared__ double tot[1];
+        const double v[1] = { dot };
+        if (grid_sum<1>(v, partials, &sc->ticket[0], tot)) { xrank_sum<1>(sc, 0, tot); if (threadIdx.x == 0) sc->dy = tot[0]; }
+    }
+}
+
+template <int BS, int NB, bool WITH_DOT>
+static yfd_status launch_cls(yfd_ctx *ctx, const dg_classes &cl, const double *x, double *y, cg_scalars *sc, double *partials)
+{
+    auto kern = dg_spmv_class<BS, NB, WITH_DOT>;
+    const size_t smem = (size_t) cl.table_doubles * sizeof(double);
+    if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    int per_sm = smem * 2 + 4096 <= ctx->smem_per_sm ? 2 : 1;
+    int64_t grid = (int64_t) ctx->sm_count * per_sm;
+    const int64_t want = ceil_div(cl.ntiles, CLS_THREADS / 32);
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    YFD_LAUNCH(ctx, kern, (unsigned) grid, CLS_THREADS, smem, (const double *) cl.table.p, cl.table_doubles, (const int32_t *) cl.work_cell.p,
+               (const int32_t *) cl.work_nbr.p, (const int32_t *) cl.tile_cls.p, cl.ntiles, cl.npos, x, y, sc, partials);
+    return YFD_OK;
+}
+
+template <bool WITH_DOT>
+yfd_status launch_dg_spmv_class(yfd_ctx *ctx, const dg_classes &cl, int bs, int nf, const double *x, double *y, cg_scalars *sc, double *partials)
+{
+#define YFD_CLS_CASE(B, F) if (bs == B && nf == F) return launch_cls<B, F + 1, WITH_DOT>(ctx, cl, x, y, sc, partials)
+    YFD_CLS_CASE(1, 3); YFD_CLS_CASE(3, 3); YFD_CLS_CASE(6, 3); YFD_CLS_CASE(10, 3); YFD_CLS_CASE(15, 3);
+    YFD_CLS_CASE(1, 4); YFD_CLS_CASE(3, 4); YFD_CLS_CASE(6, 4); YFD_CLS_CASE(10, 4); YFD_CLS_CASE(15, 4);
+#undef YFD_CLS_CASE
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "no class-cache SpMV instantiation for block size %d with %d faces", bs, nf);
+}
+
+template yfd_status launch_dg_spmv_class<true>(yfd_ctx *, const dg_classes &, int, int, const double *, double *, cg_scalars *, double *);
+template yfd_status launch_dg_spmv_class<false>(yfd_ctx *, const dg_classes &, int, int, const double *, double *, cg_scalars *, double *);
+
+} // namespace yfd

@@ -534,7 +534,15 @@ yfd_status yfd_system_get_csr(yfd_system *sys, int64_t *rowptr, int64_t *colidx,
     if (colidx) YFD_TRY(d_col.alloc(ctx, (size_t) nnz));
     if (values) YFD_TRY(d_val.alloc(ctx, (size_t) nnz));
     const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
-    YFD_LAUNCH(ctx, export_ref_csr, (unsigned) (want < cap ? want : cap), 256, 0, sys->cellptr.p, sys->blk_cell.p, sys->A.values.p,
+    /* the values the solvers APPLY: with the congruence-class cache active those are the class representatives */
+    const double *src_values = sys->A.values.p;
+    dbuf<double> applied;
+    if (values && system_uses_classes(sys)) {
+        YFD_TRY(applied.alloc(ctx, (size_t) nnz, 4));
+        YFD_TRY(expand_class_values(ctx, sys, applied.p));
+        src_values = applied.p;
+    }
+    YFD_LAUNCH(ctx, export_ref_csr, (unsigned) (want < cap ? want : cap), 256, 0, sys->cellptr.p, sys->blk_cell.p, src_values,
                sys->perm.p, sys->iperm.p, cp_ref.p, nc, sys->bs, d_rowptr.p, d_col.p, d_val.p);
     if (rowptr) YFD_TRY(d_rowptr.download(ctx, rowptr, (size_t) n + 1));
     if (colidx) YFD_TRY(d_col.download(ctx, colidx, (size_t) nnz));

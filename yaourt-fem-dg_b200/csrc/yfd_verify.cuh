@@ -80,11 +80,20 @@ __global__ void gather_local(const double *__restrict__ full, const int32_t *__r
     }
 }
 
-static yfd_status launch_apply_plain(yfd_ctx *ctx, const spmv_op &op, const double *x, double *y)
+/* With the congruence-class cache active the solver multiplies by the class representatives, not by the assembled
+ * per-cell values: the check must use the same numbers, through a different route -- the class table expanded back into
+ * the streamed layout (`applied`, kept alive by the caller) and the one-thread-per-row kernel on that. */
+static yfd_status launch_apply_plain(yfd_ctx *ctx, const yfd_system *sys, const spmv_op &op, dbuf<double> &applied, const double *x, double *y)
 {
     const int64_t n = op.nrows;
     const unsigned g = (unsigned) std::max<int64_t>(1, std::min<int64_t>(ceil_div(n, 256), (int64_t) ctx->sm_count * 16));
-    if (op.cellptr) YFD_LAUNCH(ctx, dg_apply_plain, g, 256, 0, op.cellptr, op.blk_cell, op.values, x, y, op.ncells, op.bs);
+    const double *values = op.values;
+    if (op.cls) {
+        YFD_TRY(applied.alloc(ctx, (size_t) sys->nnz, 4));
+        YFD_TRY(expand_class_values(ctx, sys, applied.p));
+        values = applied.p;
+    }
+    if (op.cellptr) YFD_LAUNCH(ctx, dg_apply_plain, g, 256, 0, op.cellptr, op.blk_cell, values, x, y, op.ncells, op.bs);
     else YFD_LAUNCH(ctx, csr_apply_plain, g, 256, 0, op.rowptr, op.colidx, op.values, x, y, n);
     return YFD_OK;
 }
