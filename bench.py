@@ -58,6 +58,11 @@ WORKLOADS = {
     # the same two configurations with the block-Jacobi preconditioner (extension: SURVEY.md 8f rank 3)
     "dg_sip_quad_k3_20m_bj": dict(cell=1, nx=1448, k=3, pc=2, rr_tol=1e-10, ref_r=5, base_r=6,
                                   desc="DG-SIP diffusion, quadrangles k=3, 1448 x 1448 structured, 20,967,040 dofs, block-Jacobi CG (extension)"),
+    # ... and with the p-multigrid preconditioner (extension: YFD_PC_PMG, yfd_pmg.cu); reference arm: its best, Jacobi (-p)
+    "dg_sip_quad_k3_20m_pmg": dict(cell=1, nx=1448, k=3, pc=3, rr_tol=1e-10, ref_r=5, base_r=6,
+                                   desc="DG-SIP diffusion, quadrangles k=3, 1448 x 1448 structured, 20,967,040 dofs, p-multigrid CG (extension)"),
+    "dg_sip_tri_k2_r11_pmg": dict(cell=0, r=11, k=2, pc=3, rr_tol=1e-10, ref_r=5, base_r=6,
+                                  desc="DG-SIP diffusion, triangles k=2, -r 11: 16,777,216 cells, 100,663,296 dofs (BASELINE configs[4]), p-multigrid CG (extension)"),
     "dg_sip_tri_k2_r9_bj": dict(cell=0, r=9, k=2, pc=2, rr_tol=1e-10, ref_r=5, base_r=6,
                                 desc="DG-SIP diffusion, triangles k=2, -r 9: 6,291,456 dofs, block-Jacobi CG (extension)"),
     "dg_sip_tri_k2_r11": dict(cell=0, r=11, k=2, pc=True, rr_tol=1e-10, ref_r=5, base_r=6,
@@ -167,7 +172,7 @@ def reference_step(ref, wl, r):
         out = ref.run_cfem(r)               # continuous_fem.cpp: builds its own mesh (counted in t_blocks)
     else:
         ref.mesh(wl["cell"], r)
-        out = ref.run_dg(wl["k"], eta=1.0, use_pc=bool(wl["pc"]))     # pc = 2 (block-Jacobi) has no reference: its best, Jacobi (-p)
+        out = ref.run_dg(wl["k"], eta=1.0, use_pc=bool(wl["pc"]))     # pc = 2, 3 (block-Jacobi, p-multigrid) have no reference: its best, Jacobi (-p)
     t = out["t_blocks"] + out["t_csr"] + out["t_cg"]
     return dict(n=out["n"], nnz=out["nnz"], iters=out["iters"], t=t, t_blocks=out["t_blocks"], t_csr=out["t_csr"], t_cg=out["t_cg"])
 
@@ -537,9 +542,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=os.environ.get("YFD_BENCH_WORKLOAD", DEFAULT_WORKLOAD), choices=sorted(WORKLOADS))
-    ap.add_argument("--pc", type=int, default=None, choices=[0, 1, 2], help="override the workload's preconditioner: 0 none, 1 Jacobi (-p), 2 block-Jacobi")
+    ap.add_argument("--pc", type=int, default=None, choices=[0, 1, 2, 3], help="override the workload's preconditioner: 0 none, 1 Jacobi (-p), 2 block-Jacobi")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="weak: the structured mesh grows with the number of GPUs (nx = 1122 sqrt(N): 12.6 M dofs per GPU at k=3, 1.0e8 dofs at N=8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--single-shot", action="store_true",
+                    help="one untimed-warm-up-free pass (W=0, K=1, no e2e, no CPU baseline) for solves that take minutes "
+                         "(the 1e8-dof target): a recorded run, not the driver's bench contract")
     ap.add_argument("--profile-iters", type=int, default=0,
                     help="ncu helper: cap CG at this many iterations, one step, no warm-up; the printed line is NOT a bench value")
     args = ap.parse_args()
@@ -548,10 +558,20 @@ def main():
         wl["pc"] = args.pc
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.scaling == "weak":
+        # fixed load per GPU: the reference mesher only refines x4, the structured one (same conventions, parity-pinned by
+        # tests/test_gpu_structured.py) makes any size.  Iteration counts grow with the mesh, so the line also reports the
+        # time per CG iteration and DOF-iterations/s, the size-independent figures
+        if "nx" not in wl or wl.get("kind"):
+            raise SystemExit("--scaling weak is defined for the structured DG workloads (dg_sip_quad_k3_20m*)")
+        wl["nx"] = int(round(1122 * world ** 0.5))
+        ncell = wl["nx"] ** 2 * (2 if wl["cell"] == 0 else 1)
+        wl["desc"] = "DG-SIP diffusion, %s k=%d, %d x %d structured: %d cells, %d dofs (weak scaling: 1122^2 cells per GPU)" % (
+            "quadrangles" if wl["cell"] == 1 else "triangles", wl["k"], wl["nx"], wl["nx"], ncell, ncell * bs_of(wl["k"]))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         return run_maxwell_reference_arm(args, wl, rank) if wl.get("kind") == "maxwell" else run_reference_arm(args, wl, rank)
-    if args.profile_iters > 0:
+    if args.profile_iters > 0 or args.single_shot:
         args.warmup, args.steps, args.no_e2e, args.no_cpu_baseline = 0, 1, True, True
     elif args.warmup < 3:
         args.warmup = 3
@@ -771,12 +791,12 @@ def main():
                 same_size.append(same_size_leg(torch, yfd, ctx, stream, wl, rr, cpu, assemble, cfem))
 
     if rank == 0:
-        line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else {}
+        line = {"profiling_run_not_a_bench_value": True} if args.profile_iters else ({"single_shot": True} if args.single_shot else {})
         line.update({"metric": "assembled+solved DOFs/sec", "value": value, "unit": "DOFs/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload, "description": wl["desc"], "dofs": int(info["n"]), "nnz": int(nnz_global),
-                           "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], ("no preconditioner (reference default)", "Jacobi (-p)", "block-Jacobi (extension, YFD_PC_BLOCK_JACOBI; reference arm: Jacobi)")[int(wl["pc"])]),
+                           "cg": "rr_tol %.0e, rr_max per the reference driver, max_iter 2N, x0 = 0, %s" % (wl["rr_tol"], ("no preconditioner (reference default)", "Jacobi (-p)", "block-Jacobi (extension, YFD_PC_BLOCK_JACOBI; reference arm: Jacobi)", "p-multigrid V-cycle (extension, YFD_PC_PMG; reference arm: Jacobi)")[int(wl["pc"])]),
                            "cg_iterations": int(info["iterations"]), "converged": bool(info["converged"]),
                            "true_residual": anchors.get("true_residual"), "l2_error": anchors.get("l2_error"),
                            "l2_error_projection": anchors.get("l2_error_projection"),
@@ -786,6 +806,7 @@ def main():
                            "l2_policy": "inputs larger than L2: CSR values alone are %.1f GB vs 126 MB L2" % (8e-9 * info["nnz"]),
                            "phases_ms": {"structure": info["ms_structure"], "elements": info["ms_elements"], "cg": info["ms_solve"],
                                          "host_wall_assemble_call": info["host_ms_assemble"], "host_wall_solve_call": info["host_ms_solve"]},
+                           "ms_per_cg_iteration": info["ms_solve"] / it, "dof_iterations_per_s": info["n"] * it / (info["ms_solve"] * 1e-3),
                            "cg_iteration_gbs": cg_gbs, "parallelism": "1 GPU" if world == 1 else "contiguous blocks of the Z-curve cell order over %d GPUs: rank 0 holds %d rows + %d halo dofs; "
                                           "transport: %s (%s)" % (world, info["n_local"], info["n_halo"], info.get("transport"),
                                                                   "per CG iteration 2 cross-rank scalar sums through NVLink peer memory; no exchange of d: every rank advances its halo "

@@ -336,6 +336,23 @@ typedef struct yfd_cg_info {
                                 /* SpMV; about half the iterations of the point-Jacobi CG.  Same recurrences (:196-227),   */
                                 /* same stopping rule, same solution to the solver tolerance; works on several GPUs.       */
 
+#define YFD_PC_PMG          3   /* EXTENSION, DG-SIP systems on meshes of congruent cells, one GPU: iM = one  */
+                                /* symmetric p-multigrid V-cycle over the degrees k, k-1, ..., 1 (yfd_pmg.cu).  The reference's   */
+                                /* basis is hierarchical by total degree (core/bases.hpp:96-122), so the coarse spaces are index */
+                                /* subsets and the coarse operators sub-blocks of A; smoother: Chebyshev-block-Jacobi; the P1     */
+                                /* level is "solved" by a fixed Chebyshev polynomial.  Same recurrences (core/solvers.hpp:196-227) */
+                                /* and stopping rule as the reference's preconditioned CG.                                         */
+/* p-multigrid parameters (0 = default): nu sweeps before and after each coarse correction (2), Chebyshev degree of the P1
+ * solve (3 ncells^(1/4) clamped to [8, 400]), smoothing interval [lambda_max / smooth_ratio, lambda_max] (4) */
+yfd_status yfd_system_set_pmg_params(yfd_system *sys, int nu, int coarse_degree, double smooth_ratio);
+typedef struct yfd_pmg_info {
+    int    nlevels, nu, coarse_degree;
+    double smooth_ratio;
+    int    degree[4];                 /* finest first                                               */
+    double lambda_max[4];             /* the bound used for D^-1 A_l (1.1 x power-iteration estimate) */
+} yfd_pmg_info;
+yfd_status yfd_system_pmg_info(yfd_ctx *ctx, yfd_system *sys, yfd_pmg_info *info);   /* builds the hierarchy if needed */
+
 /* Solve sys.lhs x = sys.rhs on the device, no host round trip of the matrix.
  * use_pc = YFD_PC_JACOBI -> the 5-argument overload with assm.pc.  x [n] in REFERENCE numbering, in/out
  * (input read only if use_initial_guess).  history may be NULL, else cap >= max_iter+1 is not

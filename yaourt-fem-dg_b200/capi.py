@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 
 TRI, QUAD = 0, 1
-PC_NONE, PC_JACOBI, PC_BLOCK_JACOBI = 0, 1, 2     # use_pc of System.solve_cg (include/yfd.h YFD_PC_*)
+PC_NONE, PC_JACOBI, PC_BLOCK_JACOBI, PC_PMG = 0, 1, 2, 3     # use_pc of System.solve_cg (include/yfd.h YFD_PC_*)
 TI_RK4, TI_EULER = 0, 1
 FIELDS_CAVITY_11, FIELDS_ZERO = 0, 1
 FN_ZERO, FN_SINSIN, FN_ONE, FN_SINSIN_SOL, FN_ADVECTION_RHS, FN_SIN_X_SOL = 0, 1, 2, 3, 4, 5
@@ -101,6 +101,11 @@ class OperatorInfo(C.Structure):
 
 
 OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES = 0, 1, 2
+
+
+class PmgInfo(C.Structure):
+    _fields_ = [("nlevels", C.c_int), ("nu", C.c_int), ("coarse_degree", C.c_int), ("smooth_ratio", C.c_double),
+                ("degree", C.c_int * 4), ("lambda_max", C.c_double * 4)]
 
 
 class CgInfo(C.Structure):
@@ -185,6 +190,8 @@ def lib():
         "yfd_cg_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_bicgstab_solve": (cint, [vp, vp, _f64p, _f64p, vp, P(CgParams), P(CgInfo), vp, i64]),
         "yfd_system_solve_bicgstab": (cint, [vp, vp, cint, P(CgParams), _f64p, P(CgInfo), vp, i64]),
+        "yfd_system_set_pmg_params": (cint, [vp, cint, cint, dbl]),
+        "yfd_system_pmg_info": (cint, [vp, vp, P(PmgInfo)]),
         "yfd_system_set_operator_mode": (cint, [vp, cint]),
         "yfd_system_operator_info": (cint, [vp, P(OperatorInfo)]),
         "yfd_system_apply": (cint, [vp, vp, cint, _f64p, _f64p]),
@@ -611,6 +618,16 @@ class System:
                                                         C.c_void_p(d_x) if d_x else None, C.byref(info)))
         return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
                     transport=("one GPU", "NCCL", "peer memory")[info.transport])
+
+    def set_pmg_params(self, nu=0, coarse_degree=0, smooth_ratio=0.0):
+        """Parameters of the p-multigrid preconditioner (use_pc=PC_PMG); 0 = default."""
+        self.ctx.check(lib().yfd_system_set_pmg_params(self._h, nu, coarse_degree, smooth_ratio))
+
+    def pmg_info(self):
+        pi = PmgInfo()
+        self.ctx.check(lib().yfd_system_pmg_info(self.ctx._h, self._h, C.byref(pi)))
+        return dict(nlevels=pi.nlevels, nu=pi.nu, coarse_degree=pi.coarse_degree, smooth_ratio=pi.smooth_ratio,
+                    degree=list(pi.degree)[:pi.nlevels], lambda_max=list(pi.lambda_max)[:pi.nlevels])
 
     def set_operator_mode(self, mode):
         """OPERATOR_AUTO / OPERATOR_STREAMED / OPERATOR_CLASSES (include/yfd.h)."""

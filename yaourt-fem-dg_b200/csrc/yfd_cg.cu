@@ -398,11 +398,13 @@ static unsigned vec_grid(yfd_ctx *ctx, int64_t n)
 /* The solver proper: all vectors on the device, in the operator's numbering. */
 static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, double *d_x, const double *d_pc,
                             const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap,
-                            const spmv_op *opT = nullptr, const spmv_op *opD = nullptr)
+                            const spmv_op *opT = nullptr, const spmv_op *opD = nullptr, yfd_system *pmg_sys = nullptr)
 {
     const int64_t n = op.nrows;
     const bool normal = p->use_normal_eqns != 0;
-    const bool block = opD != nullptr;          /* block-Jacobi: iM is a block SpMV (yfd_block_jacobi.cuh), d_pc is null */
+    /* block-Jacobi: iM is a block SpMV (yfd_block_jacobi.cuh); p-multigrid: iM is a V-cycle (yfd_pmg.cu); d_pc is null for both
+     * and z = iM r is formed by launches of its own between cg_update_xr and cg_update_d, r.z in sc2->dy */
+    const bool block = opD != nullptr || pmg_sys != nullptr;
     if (block && (d_pc || normal || !op.cellptr)) return fail(ctx, YFD_ERR_INVALID_STATE, "internal: block preconditioner misuse");
     if (normal) {
         /* CG on A^T A x = A^T b as the advection driver runs it (dg2d_advection.cpp:225): r0 = A^T b, y = A^T (A d).
@@ -451,6 +453,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     const double *const zr = (d_pc || block) ? z.p : r.p;
     /* z = iM r on the owned cells (fused dot r.z -> sc2->dy, summed over the ranks) and, on the peer transport, on the halo copies */
     auto apply_block = [&]() -> yfd_status {
+        if (pmg_sys) return pmg_apply(ctx, pmg_sys, r.p, z.p, sc2, partials.p);
         YFD_TRY(launch_dg_spmv_tma<true>(ctx, op.bs, 0, opD->cellptr, opD->blk_cell, opD->values, op.ncells, r.p, z.p, sc2, partials.p));
         if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc2->dy, 1));
         if (nh > 0)
@@ -531,7 +534,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     }
 
     /* one CUDA graph = `batch` iterations */
-    int batch = p->check_every > 0 ? p->check_every : 64;
+    int batch = p->check_every > 0 ? p->check_every : (pmg_sys ? 4 : 64);       /* a V-cycle is ~100 launches: shorter graphs */
     if ((int64_t) batch > p->max_iter) batch = (int) std::max<int64_t>(p->max_iter, 1);
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
@@ -722,10 +725,19 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
                                int method = SOLVER_CG)
 {
     if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
-    if (use_pc != YFD_PC_NONE && use_pc != YFD_PC_JACOBI && use_pc != YFD_PC_BLOCK_JACOBI) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_pc must be YFD_PC_NONE, YFD_PC_JACOBI or YFD_PC_BLOCK_JACOBI");
+    if (use_pc != YFD_PC_NONE && use_pc != YFD_PC_JACOBI && use_pc != YFD_PC_BLOCK_JACOBI && use_pc != YFD_PC_PMG)
+        return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_pc must be YFD_PC_NONE, YFD_PC_JACOBI, YFD_PC_BLOCK_JACOBI or YFD_PC_PMG");
     if (use_pc == YFD_PC_JACOBI && sys->pc.n == 0) return fail(ctx, YFD_ERR_INVALID_STATE, "system was assembled without a preconditioner");
     scoped_device dev(ctx->device);
     const bool block_pc = use_pc == YFD_PC_BLOCK_JACOBI;
+    const bool pmg_pc = use_pc == YFD_PC_PMG;
+    if (pmg_pc) {
+        if (method == SOLVER_BICGSTAB) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab takes the diagonal preconditioner only");
+        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner");
+        if (!system_uses_classes(sys)) return fail(ctx, YFD_ERR_UNSUPPORTED, "the p-multigrid preconditioner needs the congruence-class operator cache in use");
+        YFD_TRY(ensure_pmg(ctx, sys));
+        use_pc = 0;
+    }
     if (block_pc) {
         if (method == SOLVER_BICGSTAB) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab takes the diagonal preconditioner only");
         if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner");
@@ -769,7 +781,7 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         YFD_TRY(bicgstab_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap));
     else
         YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
-                          p->use_normal_eqns ? &opT : nullptr, block_pc ? &opD : nullptr));
+                          p->use_normal_eqns ? &opT : nullptr, block_pc ? &opD : nullptr, pmg_pc ? sys : nullptr));
     const double *result = dx.p;
     if (dg) {
         /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */
@@ -809,6 +821,29 @@ yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc,
     if (!ctx || !sys || !p) return YFD_ERR_INVALID_ARGUMENT;
     if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "device-resident solve starts from x = 0");
     return system_solve(ctx, sys, use_pc, p, nullptr, d_x, info, nullptr, 0);
+}
+
+yfd_status yfd_system_set_pmg_params(yfd_system *sys, int nu, int coarse_degree, double smooth_ratio)
+{
+    if (!sys) return YFD_ERR_INVALID_ARGUMENT;
+    if (nu < 0 || nu > 16 || coarse_degree < 0 || coarse_degree > 100000 || (smooth_ratio != 0.0 && !(smooth_ratio > 1.0)))
+        return fail(sys->ctx, YFD_ERR_INVALID_ARGUMENT, "p-multigrid parameters out of range");
+    scoped_device dev(sys->ctx->device);
+    cudaStreamSynchronize(sys->ctx->stream);
+    sys->pmg.reset();
+    sys->pmg_nu = nu; sys->pmg_coarse_degree = coarse_degree; sys->pmg_smooth_ratio = smooth_ratio;
+    return YFD_OK;
+}
+
+yfd_status yfd_system_pmg_info(yfd_ctx *ctx, yfd_system *sys, yfd_pmg_info *info)
+{
+    if (!ctx || !sys || !info) return YFD_ERR_INVALID_ARGUMENT;
+    scoped_device dev(ctx->device);
+    YFD_TRY(ensure_pmg(ctx, sys));
+    const pmg_hierarchy &H = *sys->pmg;
+    info->nlevels = H.nlevels; info->nu = H.nu; info->coarse_degree = H.coarse_degree; info->smooth_ratio = H.smooth_ratio;
+    for (int l = 0; l < 4; l++) { info->degree[l] = l < H.nlevels ? H.lv[l].k : 0; info->lambda_max[l] = l < H.nlevels ? H.lv[l].lmax : 0.0; }
+    return YFD_OK;
 }
 
 yfd_status yfd_system_set_operator_mode(yfd_system *sys, int mode)

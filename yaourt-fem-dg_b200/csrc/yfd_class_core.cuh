@@ -1,0 +1,74 @@
+/*
+ * yfd_class_core.cuh -- device pieces shared by the kernels that multiply by class block rows held in shared memory
+ * (yfd_spmv_class.cu, yfd_pmg.cu): lane <-> cell, block entries read as warp-wide broadcasts.
+ */
+#pragma once
+#include "yfd_internal.hpp"
+
+namespace yfd {
+
+constexpr int CLS_THREADS = 256;
+
+/* doubles per block in a class table: bs^2 rounded up to even, so every block starts 16-byte aligned */
+__host__ __device__ constexpr int cls_slot_stride(int bs) { return (bs * bs + 1) & ~1; }
+
+template <int BS>
+__device__ __forceinline__ void load_cell(const double *__restrict__ x, int32_t cell, double (&v)[BS])
+{
+    if (BS % 2 == 0) {
+        const double2 *p = reinterpret_cast<const double2 *>(x + (int64_t) cell * BS);
+#pragma unroll
+        for (int q = 0; q < BS / 2; q++) { const double2 t = __ldg(p + q); v[2 * q] = t.x; v[2 * q + 1] = t.y; }
+    } else {
+        const double *p = x + (int64_t) cell * BS;
+#pragma unroll
+        for (int q = 0; q < BS; q++) v[q] = __ldg(p + q);
+    }
+}
+
+template <int BS>
+__device__ __forceinline__ void store_cell(double *__restrict__ y, int32_t cell, const double (&v)[BS])
+{
+    if (BS % 2 == 0) {
+        double2 *p = reinterpret_cast<double2 *>(y + (int64_t) cell * BS);
+#pragma unroll
+        for (int q = 0; q < BS / 2; q++) p[q] = make_double2(v[2 * q], v[2 * q + 1]);
+    } else {
+#pragma unroll
+        for (int q = 0; q < BS; q++) y[(int64_t) cell * BS + q] = v[q];
+    }
+}
+
+/* acc += W v for one bs x bs block W[j][i] (column j contiguous in i) in shared memory; every lane reads the same
+ * addresses, so each LDS.128 is one broadcast wavefront feeding two DFMA per lane */
+template <int BS>
+__device__ __forceinline__ void block_times(const double *__restrict__ W, const double (&v)[BS], double (&acc)[BS])
+{
+    constexpr int BS2 = BS * BS;
+#pragma unroll
+    for (int m = 0; m + 1 < BS2; m += 2) {
+        const double2 w = *reinterpret_cast<const double2 *>(W + m);
+        acc[m % BS] = fma(w.x, v[m / BS], acc[m % BS]);
+        acc[(m + 1) % BS] = fma(w.y, v[(m + 1) / BS], acc[(m + 1) % BS]);
+    }
+    if (BS2 & 1) acc[BS - 1] = fma(W[BS2 - 1], v[BS - 1], acc[BS - 1]);
+}
+
+/* acc = (A x)_c for the cell at list position `pos`: slot 0 = the cell itself, slot 1+e = the neighbour across local face e */
+template <int BS, int NB>
+__device__ __forceinline__ void class_row_product(const double *__restrict__ Wk, const double *__restrict__ x, int32_t c, int64_t pos,
+                                                  const int32_t *__restrict__ work_nbr, int64_t npos, double (&acc)[BS])
+{
+    constexpr int SS = cls_slot_stride(BS);
+#pragma unroll
+    for (int i = 0; i < BS; i++) acc[i] = 0.0;
+#pragma unroll
+    for (int s = 0; s < NB; s++) {
+        const int32_t nb = s == 0 ? c : __ldg(&work_nbr[(int64_t) (s - 1) * npos + pos]);
+        double xv[BS];
+        load_cell<BS>(x, nb, xv);
+        block_times<BS>(Wk + s * SS, xv, acc);
+    }
+}
+
+} // namespace yfd

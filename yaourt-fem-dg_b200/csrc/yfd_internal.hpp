@@ -296,6 +296,19 @@ struct dg_classes {
     dbuf<int32_t> tile_cls;           /* [ntiles]                                                                        */
     dbuf<int32_t> cell_cls;           /* [ncells]                                                                        */
 };
+
+/* p-multigrid preconditioner (yfd_pmg.cu): levels k, k-1, ..., 1 over the class cache */
+struct pmg_level {
+    int    k = 0, bs = 0, nA = 0, nD = 0;
+    double lmax = 0.0;                /* 1.1 x the power-iteration estimate of lambda_max(D^-1 A_l)                     */
+    dbuf<double> tabA, tabD;          /* per class: the level's block row (leading sub-blocks), its inverse diagonal block */
+    dbuf<double> x[2], d, b;          /* work vectors of the level (the finest level's b and second x are the CG's r, z) */
+};
+struct pmg_hierarchy {
+    int    nlevels = 0, nu = 2, coarse_degree = 0;
+    double smooth_ratio = 4.0;
+    pmg_level lv[4];
+};
 }
 
 struct yfd_system {
@@ -327,6 +340,9 @@ struct yfd_system {
                                          face inside the cell's (id-sorted) block list, -1 on boundary faces */
     yfd::dg_classes    classes;       /* SIP diffusion on meshes of congruent cells (yfd_spmv_class.cu)      */
     int      operator_mode = 0;       /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES (yfd_system_set_operator_mode) */
+    std::unique_ptr<yfd::pmg_hierarchy> pmg;   /* built on first YFD_PC_PMG solve (yfd_pmg.cu)                   */
+    int      pmg_nu = 0, pmg_coarse_degree = 0; /* 0 = defaults (yfd_system_set_pmg_params)                      */
+    double   pmg_smooth_ratio = 0.0;
     yfd::dbuf<int32_t> perm, iperm;   /* copies of the mesh's cell permutation      */
     /* CFEM */
     int64_t  npoints = 0;
@@ -342,6 +358,8 @@ yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *
 yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int key_bits, double tol);
 yfd_status expand_class_values(yfd_ctx *ctx, const yfd_system *sys, double *d_values_out);
 inline bool system_uses_classes(const yfd_system *sys) { return sys->classes.ready && sys->operator_mode != 1 /* YFD_OPERATOR_STREAMED */; }
+/* ---- yfd_pmg.cu ---- */
+yfd_status ensure_pmg(yfd_ctx *ctx, yfd_system *sys);
 /* ---- yfd_triplets.cu ---- */
 int key_bits_for(int64_t n);
 /* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order.  Entries of

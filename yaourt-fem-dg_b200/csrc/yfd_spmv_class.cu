@@ -31,16 +31,14 @@
  */
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
+#include "yfd_class_core.cuh"
 #include <vector>
 #include <cmath>
 #include <algorithm>
 
 namespace yfd {
 
-constexpr int CLS_THREADS = 256;
 constexpr int CLS_MAX_CLASSES = 4096;        /* beyond this the mesh is not "a few congruence classes" */
-
-__host__ __device__ constexpr int cls_slot_stride(int bs) { return (bs * bs + 1) & ~1; }
 
 /* ---- build: class ids from sorted keys ------------------------------------------------------- */
 __global__ void cls_flag_starts(const uint64_t *__restrict__ keys, int64_t n, int32_t *__restrict__ flag)
@@ -231,20 +229,6 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
 }
 
 /* ---- the kernel ------------------------------------------------------------------------------ */
-template <int BS>
-__device__ __forceinline__ void load_cell(const double *__restrict__ x, int32_t cell, double (&v)[BS])
-{
-    if (BS % 2 == 0) {
-        const double2 *p = reinterpret_cast<const double2 *>(x + (int64_t) cell * BS);
-#pragma unroll
-        for (int q = 0; q < BS / 2; q++) { const double2 t = __ldg(p + q); v[2 * q] = t.x; v[2 * q + 1] = t.y; }
-    } else {
-        const double *p = x + (int64_t) cell * BS;
-#pragma unroll
-        for (int q = 0; q < BS; q++) v[q] = __ldg(p + q);
-    }
-}
-
 template <int BS, int NB, bool WITH_DOT>
 __global__ void __launch_bounds__(CLS_THREADS, 2)
 dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t *__restrict__ work_cell,
@@ -253,7 +237,7 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
 {
     if (WITH_DOT && sc->done) return;
     extern __shared__ __align__(16) double T[];
-    constexpr int BS2 = BS * BS, SS = cls_slot_stride(BS);
+    constexpr int SS = cls_slot_stride(BS);
     for (int i = threadIdx.x; i < table_doubles; i += blockDim.x) T[i] = table[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -266,30 +250,8 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
         if (c < 0) continue;                                   /* padding at the end of a class */
         const double *Wk = T + (size_t) k * (NB * SS);
         double acc[BS];
-#pragma unroll
-        for (int i = 0; i < BS; i++) acc[i] = 0.0;
-#pragma unroll
-        for (int s = 0; s < NB; s++) {
-            const int32_t nb = s == 0 ? c : __ldg(&work_nbr[(int64_t) (s - 1) * npos + pos]);
-            double xv[BS];
-            load_cell<BS>(x, nb, xv);
-            const double *W = Wk + s * SS;
-#pragma unroll
-            for (int m = 0; m + 1 < BS2; m += 2) {
-                const double2 w = *reinterpret_cast<const double2 *>(W + m);       /* same address in every lane: a broadcast */
-                acc[m % BS] = fma(w.x, xv[m / BS], acc[m % BS]);
-                acc[(m + 1) % BS] = fma(w.y, xv[(m + 1) / BS], acc[(m + 1) % BS]);
-            }
-            if (BS2 & 1) acc[BS - 1] = fma(W[BS2 - 1], xv[BS - 1], acc[BS - 1]);
-        }
-        if (BS % 2 == 0) {
-            double2 *p = reinterpret_cast<double2 *>(y + (int64_t) c * BS);
-#pragma unroll
-            for (int q = 0; q < BS / 2; q++) p[q] = make_double2(acc[2 * q], acc[2 * q + 1]);
-        } else {
-#pragma unroll
-            for (int q = 0; q < BS; q++) y[(int64_t) c * BS + q] = acc[q];
-        }
+        class_row_product<BS, NB>(Wk, x, c, pos, work_nbr, npos, acc);
+        store_cell<BS>(y, c, acc);
         if (WITH_DOT) {
             double xs[BS];
             load_cell<BS>(x, c, xs);
