@@ -465,7 +465,16 @@ typedef struct yfd_maxwell_info {
     int64_t operator_bytes;           /* bytes of the factored operator held in HBM     */
     int64_t reference_operator_bytes; /* (1 + nf) (3bs)^2 8 ncells: gOp_ondiag + gOp_offdiag */
     double  ms_assemble;              /* device time of the element/face kernel incl. the M^-1 solves */
+    /* congruence-class cache of the factored operator (see YFD_OPERATOR_*): the 2 + 2 nf blocks of a cell depend on its
+     * shape, size and neighbours' frames only, so on refinement meshes one block set per class serves every cell and the
+     * operator application streams vectors only (BASELINE configs[3] "matrix-free element+face operator") */
+    int     uses_classes;
+    int     class_reject_reason;      /* as yfd_operator_info.reject_reason                 */
+    int64_t nclasses;
+    double  class_max_deviation, class_tolerance;
+    int64_t class_table_bytes;
 } yfd_maxwell_info;
+yfd_status yfd_maxwell_set_operator_mode(yfd_maxwell *m, int mode);   /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES */
 
 /* maxwell_context ctor (storage) + assemble(ctx).  mu_r / eps_r: [ncells] in REFERENCE cell order, or NULL
  * for 1.0 everywhere (the context's default, :149-150).  The mesh may be destroyed afterwards. */

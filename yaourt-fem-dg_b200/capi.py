@@ -87,7 +87,9 @@ class MaxwellConfig(C.Structure):
 
 class MaxwellInfo(C.Structure):
     _fields_ = [("ncells", C.c_int64), ("basis_size", C.c_int64), ("faces_per_elem", C.c_int64), ("ndofs", C.c_int64),
-                ("operator_bytes", C.c_int64), ("reference_operator_bytes", C.c_int64), ("ms_assemble", C.c_double)]
+                ("operator_bytes", C.c_int64), ("reference_operator_bytes", C.c_int64), ("ms_assemble", C.c_double),
+                ("uses_classes", C.c_int), ("class_reject_reason", C.c_int), ("nclasses", C.c_int64),
+                ("class_max_deviation", C.c_double), ("class_tolerance", C.c_double), ("class_table_bytes", C.c_int64)]
 
 
 class MaxwellStepInfo(C.Structure):
@@ -204,6 +206,7 @@ def lib():
         "yfd_maxwell_destroy": (None, [vp]),
         "yfd_maxwell_get_info": (None, [vp, P(MaxwellInfo)]),
         "yfd_maxwell_set_time_integration": (cint, [vp, dbl, cint]),
+        "yfd_maxwell_set_operator_mode": (cint, [vp, cint]),
         "yfd_maxwell_get_operator": (cint, [vp, vp, vp, vp, vp, vp]),
         "yfd_maxwell_apply_initial_condition": (cint, [vp, cint, dbl]),
         "yfd_maxwell_get_dofs": (cint, [vp, _f64p]),
@@ -713,6 +716,11 @@ class Maxwell:
             self.close()
         except Exception:
             pass
+
+    def set_operator_mode(self, mode):
+        """OPERATOR_AUTO / OPERATOR_STREAMED / OPERATOR_CLASSES: which operator storage the time loop uses."""
+        self.ctx.check(lib().yfd_maxwell_set_operator_mode(self._h, mode))
+        lib().yfd_maxwell_get_info(self._h, C.byref(self.info))
 
     def set_time_integration(self, delta_t, euler=False):
         self.ctx.check(lib().yfd_maxwell_set_time_integration(self._h, delta_t, TI_EULER if euler else TI_RK4))

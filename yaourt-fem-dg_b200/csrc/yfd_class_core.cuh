@@ -26,6 +26,34 @@ __device__ __forceinline__ void load_cell(const double *__restrict__ x, int32_t 
     }
 }
 
+/* the same on a pointer (16-byte aligned when BS is even) */
+template <int BS>
+__device__ __forceinline__ void load_vec(const double *__restrict__ p, double (&v)[BS])
+{
+    if (BS % 2 == 0) {
+        const double2 *q2 = reinterpret_cast<const double2 *>(p);
+#pragma unroll
+        for (int q = 0; q < BS / 2; q++) { const double2 t = __ldg(q2 + q); v[2 * q] = t.x; v[2 * q + 1] = t.y; }
+    } else {
+#pragma unroll
+        for (int q = 0; q < BS; q++) v[q] = __ldg(p + q);
+    }
+}
+
+/* acc += W v with W read through the read-only path from GLOBAL memory (same address in every lane: one request) */
+template <int BS>
+__device__ __forceinline__ void block_times_ldg(const double *__restrict__ W, const double (&v)[BS], double (&acc)[BS])
+{
+    constexpr int BS2 = BS * BS;
+#pragma unroll
+    for (int m = 0; m + 1 < BS2; m += 2) {
+        const double2 w = __ldg(reinterpret_cast<const double2 *>(W + m));
+        acc[m % BS] = fma(w.x, v[m / BS], acc[m % BS]);
+        acc[(m + 1) % BS] = fma(w.y, v[(m + 1) / BS], acc[(m + 1) % BS]);
+    }
+    if (BS2 & 1) acc[BS - 1] = fma(__ldg(W + BS2 - 1), v[BS - 1], acc[BS - 1]);
+}
+
 template <int BS>
 __device__ __forceinline__ void store_cell(double *__restrict__ y, int32_t cell, const double (&v)[BS])
 {

@@ -25,6 +25,7 @@
  */
 #include "yfd_internal.hpp"
 #include "yfd_elem.cuh"
+#include "yfd_class_keys.cuh"
 #include <cmath>
 
 namespace yfd {
@@ -352,71 +353,6 @@ __global__ void dg_fill_blocks(const dg_args a, int32_t *__restrict__ blk_cell, 
     for (int s = 0; s < NV + 1; s++) slots_out[cell * (NV + 1) + s] = slots[s];
 }
 
-/* ------------------------------------------------------------------------------------ */
-/* congruence classes (yfd_spmv_class.cu): a hash of the cell's quantised shape signature  */
-/* ------------------------------------------------------------------------------------ */
-__device__ __forceinline__ uint64_t cls_mix(uint64_t h, int64_t v)
-{
-    h ^= (uint64_t) v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
-    h ^= h >> 30; h *= 0xbf58476d1ce4e5b9ull;
-    h ^= h >> 27; h *= 0x94d049bb133111ebull;
-    return h ^ (h >> 31);
-}
-
-/* What a SIP block row depends on (dg2d_diffusion.cpp:133-193 with constant coefficients): the cell's vertices relative to
- * its barycentre, and per face whether there is a neighbour and that neighbour's frame (barycentre, diameter) -- the
- * neighbour basis is evaluated from its frame alone (core/bases.hpp:96-155).  Everything in units of the cell diameter
- * (the blocks are scale-invariant in 2D), rounded to 2^-16: the hash only PROPOSES classes, cls_verify decides.
- * Also reduces the smallest diameter and the largest coordinate (the rounding-noise scale eps |x| / h of the blocks). */
-template <int NV>
-__global__ void dg_class_keys(const dg_args a, int key_bits, uint64_t *__restrict__ keys, unsigned long long *__restrict__ hmin_bits,
-                              unsigned long long *__restrict__ xmax_bits)
-{
-    const int64_t cell = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    double hloc = INFINITY, xloc = 0.0;
-    if (cell < a.ncells) {
-        const int32_t rc = a.perm[cell + a.cell_begin];
-        double2 P[NV];
-#pragma unroll
-        for (int v = 0; v < NV; v++) P[v] = __ldg(&a.pts[a.cells[(int64_t) NV * rc + v]]);
-        double xb, yb, h;
-        cell_frame<NV>(P, xb, yb, h);
-        const double q = 65536.0 / h;
-        uint64_t key = (uint64_t) NV;
-#pragma unroll
-        for (int v = 0; v < NV; v++) {
-            key = cls_mix(key, llrint((P[v].x - xb) * q));
-            key = cls_mix(key, llrint((P[v].y - yb) * q));
-            xloc = fmax(xloc, fmax(fabs(P[v].x), fabs(P[v].y)));
-        }
-#pragma unroll
-        for (int e = 0; e < NV; e++) {
-            const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
-            const int2 own = __ldg(&a.face_owners[f]);
-            const int32_t nrc = own.x == rc ? own.y : own.x;
-            if (nrc < 0) { key = cls_mix(key, 0x7fffffffffffll); continue; }
-            double2 Q[NV];
-#pragma unroll
-            for (int v = 0; v < NV; v++) Q[v] = __ldg(&a.pts[a.cells[(int64_t) NV * nrc + v]]);
-            double nxb, nyb, nh;
-            cell_frame<NV>(Q, nxb, nyb, nh);
-            key = cls_mix(key, llrint((nxb - xb) * q));
-            key = cls_mix(key, llrint((nyb - yb) * q));
-            key = cls_mix(key, llrint(nh * q));
-        }
-        keys[cell] = key_bits >= 64 ? key : (key & ((1ull << key_bits) - 1));
-        hloc = h;
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        hloc = fmin(hloc, __shfl_xor_sync(0xffffffffu, hloc, o));
-        xloc = fmax(xloc, __shfl_xor_sync(0xffffffffu, xloc, o));
-    }
-    if ((threadIdx.x & 31) == 0 && isfinite(hloc)) {      /* positive doubles: the bit patterns order as the values */
-        atomicMin(hmin_bits, (unsigned long long) __double_as_longlong(hloc));
-        atomicMax(xmax_bits, (unsigned long long) __double_as_longlong(xloc));
-    }
-}
-
 template <int NV, int K, bool ADV>
 static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
 {
@@ -558,7 +494,7 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
         YFD_TRY(keys.alloc(ctx, (size_t) nc)); YFD_TRY(red.alloc(ctx, 2));
         const unsigned long long init[2] = { 0x7ff0000000000000ull, 0ull };
         YFD_CUDA(ctx, cudaMemcpyAsync(red.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
-        YFD_LAUNCH(ctx, dg_class_keys<NV>, g, 256, 0, a, KEY_BITS, keys.p, red.p, red.p + 1);
+        YFD_LAUNCH(ctx, (cell_class_keys<NV, dg_args>), g, 256, 0, a, KEY_BITS, 0, keys.p, red.p, red.p + 1);
         unsigned long long hred[2];
         YFD_TRY(red.download(ctx, hred, 2));
         double hmin, xmax;

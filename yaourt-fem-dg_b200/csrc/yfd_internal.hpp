@@ -297,6 +297,15 @@ struct dg_classes {
     dbuf<int32_t> cell_cls;           /* [ncells]                                                                        */
 };
 
+/* cells grouped into classes by a key (yfd_spmv_class.cu: group_cells_by_key) */
+struct class_groups {
+    int64_t  ncls = 0, npos = 0, ntiles = 0;
+    int      reject = 0;
+    dbuf<uint32_t> sorted_cell;       /* [ncells] cells class by class, ascending id inside a class                    */
+    dbuf<int64_t>  start;             /* [ncls+1] into sorted_cell: start[k] is class k's representative                */
+    dbuf<int32_t>  tile_cls, work_cell, cell_cls;
+};
+
 /* p-multigrid preconditioner (yfd_pmg.cu): levels k, k-1, ..., 1 over the class cache */
 struct pmg_level {
     int    k = 0, bs = 0, nA = 0, nD = 0;
@@ -355,6 +364,8 @@ namespace yfd {
  * with several ranks the parts are combined by an all-reduce, so every rank ends up with the whole vector */
 yfd_status system_vector_to_ref(yfd_system *sys, const double *d_local, double *d_out_ref);
 /* ---- yfd_spmv_class.cu ---- */
+yfd_status group_cells_by_key(yfd_ctx *ctx, int64_t nc, uint64_t *d_keys, int key_bits, size_t table_bytes_per_class, size_t table_budget,
+                              class_groups &g);
 yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int key_bits, double tol);
 yfd_status expand_class_values(yfd_ctx *ctx, const yfd_system *sys, double *d_values_out);
 inline bool system_uses_classes(const yfd_system *sys) { return sys->classes.ready && sys->operator_mode != 1 /* YFD_OPERATOR_STREAMED */; }

@@ -23,6 +23,7 @@
 #include "yfd_lu.cuh"
 #include <cmath>
 #include <vector>
+#include "yfd_class_keys.cuh"
 
 namespace yfd {
 
@@ -490,6 +491,11 @@ mx_step_args step_args(yfd_maxwell *m)
     s.op = m->op.p; s.fc = m->fc.p; s.cs = m->cs.p; s.nbr = m->nbr.p;
     s.ncells = m->ncells; s.nchunks = m->nchunks;
     s.vin = m->u.p; s.u = m->u.p; s.out = m->s1.p; s.acc = m->acc.p; s.kb = m->kb.p; s.dt = m->delta_t;
+    const bool cls = maxwell_uses_classes(m);
+    s.table = cls ? m->classes.table.p : nullptr;
+    s.work_cell = cls ? m->classes.work_cell.p : nullptr;
+    s.tile_cls = cls ? m->classes.tile_cls.p : nullptr;
+    s.ntiles = cls ? m->classes.ntiles : 0;
     return s;
 }
 
@@ -614,6 +620,29 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     YFD_TRY(derr.download(ctx, &herr, 1));
     if (herr) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "singular elemental mass matrix (degenerate cell)");
     m->ms_assemble = tm.ms();
+    /* congruence classes of the factored operator (maxwell_stage_class): proposed by the shape + size hash, accepted only if
+     * every cell's blocks agree with the representative's to the coordinate-rounding noise (as for DG-SIP, yfd_dg.cu) */
+    if (nc && env_int("YFD_MX_CLASSES", 1) != 0) {
+        constexpr int KEY_BITS = 40;
+        dbuf<uint64_t> keys;
+        dbuf<unsigned long long> red;
+        YFD_TRY(keys.alloc(ctx, (size_t) nc)); YFD_TRY(red.alloc(ctx, 2));
+        const unsigned long long init[2] = { 0x7ff0000000000000ull, 0ull };
+        YFD_CUDA(ctx, cudaMemcpyAsync(red.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+        const unsigned g = (unsigned) ceil_div(nc, 256);
+        if (nv == 3) YFD_LAUNCH(ctx, (cell_class_keys<3, mx_asm_args>), g, 256, 0, a, KEY_BITS, 1, keys.p, red.p, red.p + 1);
+        else         YFD_LAUNCH(ctx, (cell_class_keys<4, mx_asm_args>), g, 256, 0, a, KEY_BITS, 1, keys.p, red.p, red.p + 1);
+        unsigned long long hred[2];
+        YFD_TRY(red.download(ctx, hred, 2));
+        double hmin, xmax;
+        memcpy(&hmin, &hred[0], 8); memcpy(&xmax, &hred[1], 8);
+        /* M^-1 amplifies the rounding of the frame by cond(M) (1.4e5 at k = 4 in the scaled monomials):
+         * the noise floor of the blocks is cond(M) eps, on top of the eps |x| / h of the coordinates */
+        double tol = 64.0 * 2.220446049250313e-16 * (xmax > 0.0 ? xmax : 1.0) / hmin;
+        if (!(tol > 1e-11)) tol = 1e-11;
+        if (const char *e = getenv("YFD_CLASS_TOL")) { const double v = atof(e); if (v > 0.0) tol = v; }
+        YFD_TRY(maxwell_build_classes(ctx, m.get(), keys.p, KEY_BITS, tol));
+    }
     if (info) yfd_maxwell_get_info(m.get(), info);
     *out = m.release();
     return YFD_OK;
@@ -636,6 +665,24 @@ void yfd_maxwell_get_info(const yfd_maxwell *m, yfd_maxwell_info *info)
                                       + m->nbr.n * sizeof(int32_t));
     info->reference_operator_bytes = (int64_t) (1 + m->nf) * L * L * 8 * m->ncells_global;
     info->ms_assemble = m->ms_assemble;
+    info->uses_classes = maxwell_uses_classes(m) ? 1 : 0;
+    info->nclasses = m->classes.ncls;
+    info->class_reject_reason = m->classes.reject;
+    info->class_max_deviation = m->classes.max_dev;
+    info->class_tolerance = m->classes.tol;
+    info->class_table_bytes = (int64_t) m->classes.table.n * 8;
+}
+
+yfd_status yfd_maxwell_set_operator_mode(yfd_maxwell *m, int mode)
+{
+    if (!m) return YFD_ERR_INVALID_ARGUMENT;
+    if (mode != YFD_OPERATOR_AUTO && mode != YFD_OPERATOR_STREAMED && mode != YFD_OPERATOR_CLASSES)
+        return fail(m->ctx, YFD_ERR_INVALID_ARGUMENT, "mode must be YFD_OPERATOR_AUTO, _STREAMED or _CLASSES");
+    if (mode == YFD_OPERATOR_CLASSES && !m->classes.ready)
+        return fail(m->ctx, YFD_ERR_INVALID_STATE, "this operator has no usable congruence-class cache (reason %d, %d classes, deviation %.3g, tolerance %.3g)",
+                    m->classes.reject, m->classes.ncls, m->classes.max_dev, m->classes.tol);
+    m->operator_mode = mode;
+    return YFD_OK;
 }
 
 yfd_status yfd_maxwell_set_time_integration(yfd_maxwell *m, double delta_t, int time_integrator)
@@ -820,7 +867,10 @@ yfd_status yfd_maxwell_time_apply(yfd_maxwell *m, int reps, double *ms_per_apply
     if (ms_per_apply) *ms_per_apply = tm.ms() / reps;
     const double L = 3.0 * m->bs, nc = (double) m->ncells;
     if (reference_bytes) *reference_bytes = nc * ((1 + m->nf) * L * L * 8.0 + 2 * L * 8.0);
-    if (kernel_bytes)
+    if (kernel_bytes && maxwell_uses_classes(m))          /* cell list + class ids, fc, cs, nbr, operand read once, result written */
+        *kernel_bytes = 4.0 * (double) m->classes.npos + 4.0 * (double) m->classes.ntiles + (double) m->fc.n * sizeof(mx_face_coef)
+                        + (double) m->cs.n * 8.0 + (double) m->nbr.n * 4.0 + 2 * nc * L * 8.0;
+    else if (kernel_bytes)
         *kernel_bytes = (double) m->op.n * 8.0 + (double) m->fc.n * sizeof(mx_face_coef) + (double) m->cs.n * 8.0
                         + (double) m->nbr.n * 4.0 + 2 * nc * L * 8.0;
     return YFD_OK;

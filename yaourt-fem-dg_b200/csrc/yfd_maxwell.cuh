@@ -24,6 +24,18 @@ __host__ __device__ constexpr int mx_nb(int nf) { return 2 + 2 * nf; }
 /* per (cell, face): everything the flux terms need besides the two blocks */
 struct mx_face_coef { double nx, ny, cE, cH, vH, vE; };
 
+/* congruence-class cache of the factored operator (yfd_maxwell_step.cu: maxwell_stage_class): the 2 + 2 nf blocks depend on
+ * the cell's shape AND size and on its neighbours' frames only (materials live in fc / cs, which stay per cell), so on the
+ * reference's refinement meshes a handful of block sets serves every cell */
+struct mx_classes {
+    bool     ready = false;
+    int      reject = 0, ncls = 0;          /* reject as in dg_classes */
+    int64_t  npos = 0, ntiles = 0;
+    double   max_dev = 0.0, tol = 0.0;
+    dbuf<double>  table;                    /* [ncls][2 + 2 nf][slot stride], blocks as [j][i]                         */
+    dbuf<int32_t> work_cell, tile_cls, cell_cls;
+};
+
 } // namespace yfd
 
 struct yfd_maxwell {
@@ -46,6 +58,8 @@ struct yfd_maxwell {
     yfd::dbuf<yfd::mx_face_coef> fc;  /* [ncells][nf]                                                     */
     yfd::dbuf<double>  cs;            /* [ncells][2] = inv_mu, inv_eps                                    */
     yfd::dbuf<double>  gM;            /* [ncells][bs][bs] row-major, internal order                       */
+    yfd::mx_classes    classes;
+    int      operator_mode = 0;       /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES                         */
     /* state: gDofs and the RK stage operands [nlocal][3][bs] (owned | halo), k1 / k2 [ncells][3][bs]; internal order */
     yfd::dbuf<double>  u, s1, s2, acc, kb;
 };
@@ -61,6 +75,10 @@ struct mx_step_args {
     double *out;            /* MX_APPLY: L(vin); stages 1-3: next stage operand          */
     double *acc, *kb;       /* k1 (+ 2(k2+k3)) and k2                                    */
     double dt;
+    /* class cache in use: one block set per class (global memory, read as warp-uniform loads) + the class-sorted cell list */
+    const double *table; const int32_t *work_cell, *tile_cls; int64_t ntiles;
 };
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
+yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol);
+inline bool maxwell_uses_classes(const yfd_maxwell *m) { return m->classes.ready && m->operator_mode != 1; }
 } // namespace yfd

@@ -29,7 +29,9 @@
  * u + ((1/6) dt) (k1 + 2 (k2 + k3) + k4)  in its own order.  Per step: 4 launches.
  */
 #include "yfd_maxwell.cuh"
+#include "yfd_class_core.cuh"
 #include <cstdlib>
+#include <algorithm>
 
 namespace yfd {
 
@@ -152,6 +154,198 @@ maxwell_stage(const mx_step_args a, const int mode, const int prefetch)
     }
 }
 
+/* ---- the same operator application from ONE block set per congruence class (BASELINE configs[3]: "matrix-free
+ * element+face operator") ------------------------------------------------------------------------------------------
+ * lane <-> cell over the class-sorted cell list, 32 cells of one class per warp; the class's blocks are read as
+ * warp-uniform loads (one request feeds every lane), the per-cell state is the vectors, nbr, fc and cs.  The linear
+ * maps are applied AFTER combining the fields, one output field at a time (15 accumulators + 15 operands in registers):
+ *     Hx' = 1/mu  [ Gy (-Ez) + sum_f T_f w_c - N_f w_n ],  w = ny cE Ez - vH ny ny Hx + vH nx ny Hy
+ *     Hy' = 1/mu  [ Gx ( Ez) + sum_f T_f w_c - N_f w_n ],  w = -nx cE Ez + vH nx ny Hx - vH nx nx Hy
+ *     Ez' = 1/eps [ Gx Hy + Gy (-Hx) + sum_f T_f w_c - N_f w_n ],  w = cH ny Hx - cH nx Hy - vE Ez
+ * which is the streamed kernel's formula with the scalar factors moved inside the block products (22 products of bs x bs
+ * per triangle either way).  Same sinks (plain application / RK stages) as maxwell_stage. */
+template <int BS>
+__device__ __forceinline__ void mx_combo(const double *__restrict__ v /* [3][BS] of one cell */, double ahx, double ahy, double aez,
+                                         double sign, double (&w)[BS])
+{
+#pragma unroll
+    for (int i = 0; i < BS; i++) w[i] = 0.0;
+    double t[BS];
+    if (ahx != 0.0) { load_vec<BS>(v, t);
+#pragma unroll
+        for (int i = 0; i < BS; i++) w[i] = fma(sign * ahx, t[i], w[i]); }
+    if (ahy != 0.0) { load_vec<BS>(v + BS, t);
+#pragma unroll
+        for (int i = 0; i < BS; i++) w[i] = fma(sign * ahy, t[i], w[i]); }
+    if (aez != 0.0) { load_vec<BS>(v + 2 * BS, t);
+#pragma unroll
+        for (int i = 0; i < BS; i++) w[i] = fma(sign * aez, t[i], w[i]); }
+}
+
+template <int NV, int K>
+__global__ void __launch_bounds__(CLS_THREADS, 2)
+maxwell_stage_class(const mx_step_args a, const int mode)
+{
+    constexpr int BS = mx_bs(K), NB = mx_nb(NV), SS = cls_slot_stride(BS), L = 3 * BS;
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    for (int64_t tile = gw; tile < a.ntiles; tile += nw) {
+        const int k = __ldg(&a.tile_cls[tile]);
+        const int32_t c = __ldg(&a.work_cell[tile * 32 + lane]);
+        if (c < 0) continue;
+        const double *Tk = a.table + (size_t) k * (NB * SS);
+        const double *vc = a.vin + (int64_t) c * L;
+        const double inv_mu = __ldg(&a.cs[2 * c]), inv_eps = __ldg(&a.cs[2 * c + 1]);
+#pragma unroll 1
+        for (int fld = 0; fld < 3; fld++) {
+            double acc[BS], w[BS];
+#pragma unroll
+            for (int i = 0; i < BS; i++) acc[i] = 0.0;
+            /* cell blocks: Gx = block 0, Gy = block 1 */
+            /* Hx: Gy (-Ez) ; Hy: Gx Ez ; Ez: Gx Hy + Gy (-Hx) */
+            mx_combo<BS>(vc, 0.0, fld == 2 ? 1.0 : 0.0, fld == 2 ? 0.0 : 1.0, fld == 0 ? -1.0 : 1.0, w);
+            block_times_ldg<BS>(Tk + (fld == 0 ? SS : 0), w, acc);
+            if (fld == 2) { mx_combo<BS>(vc, 1.0, 0.0, 0.0, -1.0, w); block_times_ldg<BS>(Tk + SS, w, acc); }
+#pragma unroll 1
+            for (int f = 0; f < NV; f++) {
+                const mx_face_coef q = a.fc[(int64_t) c * NV + f];
+                double ahx, ahy, aez;
+                if (fld == 0)      { aez = q.ny * q.cE;  ahx = -q.vH * q.ny * q.ny; ahy = q.vH * q.nx * q.ny; }
+                else if (fld == 1) { aez = -q.nx * q.cE; ahx = q.vH * q.nx * q.ny;  ahy = -q.vH * q.nx * q.nx; }
+                else               { ahx = q.cH * q.ny;  ahy = -q.cH * q.nx;        aez = -q.vE; }
+                mx_combo<BS>(vc, ahx, ahy, aez, 1.0, w);
+                block_times_ldg<BS>(Tk + (size_t) (2 + f) * SS, w, acc);
+                const int32_t nb = __ldg(&a.nbr[(int64_t) c * NV + f]);
+                if (nb >= 0) {
+                    mx_combo<BS>(a.vin + (int64_t) nb * L, ahx, ahy, aez, -1.0, w);
+                    block_times_ldg<BS>(Tk + (size_t) (2 + NV + f) * SS, w, acc);
+                }
+            }
+            const double sc = fld == 2 ? inv_eps : inv_mu;
+            const int64_t base = (int64_t) c * L + fld * BS;
+#pragma unroll
+            for (int i = 0; i < BS; i++) {
+                const int64_t idx = base + i;
+                const double kk = sc * acc[i];
+                switch (mode) {
+                case MX_APPLY: a.out[idx] = kk; break;
+                case MX_RK1:   a.acc[idx] = kk; a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt / 2., kk)); break;
+                case MX_RK2:   a.kb[idx] = kk;  a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt / 2., kk)); break;
+                case MX_RK3:   a.acc[idx] = __dadd_rn(a.acc[idx], __dmul_rn(__dadd_rn(a.kb[idx], kk), 2.0));
+                               a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt, kk)); break;
+                case MX_RK4:   a.u[idx] = __dadd_rn(a.u[idx], __dmul_rn(__dadd_rn(a.acc[idx], kk), (1. / 6.) * a.dt)); break;
+                case MX_EULER: a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt, kk)); break;
+                }
+            }
+        }
+    }
+}
+
+/* ---- class build: table from the representatives' blocks, verification of every cell against it ---- */
+__global__ void mx_cls_build_table(const int64_t *__restrict__ start, const uint32_t *__restrict__ sorted_cell, const double *__restrict__ op,
+                                   int bs, int nb, int cpw, int rwp, double *__restrict__ table, double *__restrict__ scale)
+{
+    __shared__ double sm[32];
+    const int k = blockIdx.x, bs2 = bs * bs, ss = cls_slot_stride(bs);
+    const int64_t c = sorted_cell[start[k]];
+    const int64_t chunk = c / cpw;
+    const int slot = (int) (c - chunk * cpw);
+    const double *src = op + (size_t) chunk * ((size_t) nb * bs * rwp) + slot * bs;
+    double mx = 0.0;
+    for (int t = threadIdx.x; t < nb * ss; t += blockDim.x) {
+        const int b = t / ss, m = t - b * ss, j = m / bs, i = m - j * bs;
+        const double v = m < bs2 ? src[(size_t) (b * bs + j) * rwp + i] : 0.0;
+        table[(size_t) k * nb * ss + t] = v;
+        mx = fmax(mx, fabs(v));
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int) (blockDim.x >> 5); w++) mx = fmax(mx, sm[w]);
+        scale[k] = mx;
+    }
+}
+
+__global__ void mx_cls_verify(const int32_t *__restrict__ cell_cls, const double *__restrict__ op, const double *__restrict__ table,
+                              const double *__restrict__ scale, int64_t ncells, int bs, int nb, int cpw, int rwp,
+                              unsigned long long *__restrict__ worst_bits)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    const int bs2 = bs * bs, ss = cls_slot_stride(bs);
+    double worst = 0.0;
+    for (int64_t c = warp; c < ncells; c += nwarps) {
+        const int k = cell_cls[c];
+        const int64_t chunk = c / cpw;
+        const int slot = (int) (c - chunk * cpw);
+        const double *src = op + (size_t) chunk * ((size_t) nb * bs * rwp) + slot * bs;
+        const double *T = table + (size_t) k * nb * ss;
+        double d = 0.0;
+        for (int t = lane; t < nb * bs2; t += 32) {
+            const int b = t / bs2, m = t - b * bs2, j = m / bs, i = m - j * bs;
+            d = fmax(d, fabs(src[(size_t) (b * bs + j) * rwp + i] - T[b * ss + m]));
+        }
+        worst = fmax(worst, d / scale[k]);
+    }
+    for (int o = 16; o > 0; o >>= 1) worst = fmax(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    if (lane == 0 && worst > 0.0) atomicMax(worst_bits, (unsigned long long) __double_as_longlong(worst));
+}
+
+yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol)
+{
+    mx_classes &cl = m->classes;
+    cl = mx_classes();
+    const int bs = m->bs, nb = mx_nb(m->nv), ss = cls_slot_stride(bs), cpw = mx_cpw(bs), rwp = mx_rwp(bs);
+    const int64_t nc = m->ncells;
+    if (nc < 1 || m->degree < 1 || m->degree > 4) return YFD_OK;
+    class_groups g;
+    /* the table is read from global memory (L1 / L2 hits): 2 MB keeps it L2-resident beside the vectors' working set */
+    YFD_TRY(group_cells_by_key(ctx, nc, d_keys, key_bits, (size_t) nb * ss * sizeof(double), (size_t) 2 << 20, g));
+    cl.ncls = (int) std::min<int64_t>(g.ncls, 0x7fffffff);
+    if (g.reject) { cl.reject = g.reject; return YFD_OK; }
+    dbuf<double> scale;
+    dbuf<unsigned long long> worst;
+    YFD_TRY(cl.table.alloc(ctx, (size_t) g.ncls * nb * ss, 2)); YFD_TRY(scale.alloc(ctx, (size_t) g.ncls));
+    YFD_TRY(worst.alloc(ctx, 1)); YFD_TRY(worst.zero(ctx));
+    YFD_LAUNCH(ctx, mx_cls_build_table, (unsigned) g.ncls, 128, 0, (const int64_t *) g.start.p, (const uint32_t *) g.sorted_cell.p,
+               (const double *) m->op.p, bs, nb, cpw, rwp, cl.table.p, scale.p);
+    const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
+    YFD_LAUNCH(ctx, mx_cls_verify, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) g.cell_cls.p, (const double *) m->op.p,
+               (const double *) cl.table.p, (const double *) scale.p, nc, bs, nb, cpw, rwp, worst.p);
+    unsigned long long wb = 0;
+    YFD_TRY(worst.download(ctx, &wb, 1));
+    double dev;
+    memcpy(&dev, &wb, sizeof(dev));
+    cl.max_dev = dev; cl.tol = tol; cl.npos = g.npos; cl.ntiles = g.ntiles;
+    cl.work_cell = std::move(g.work_cell); cl.tile_cls = std::move(g.tile_cls); cl.cell_cls = std::move(g.cell_cls);
+    if (!(dev <= tol)) { cl.reject = 3; return YFD_OK; }
+    cl.ready = true;
+    return YFD_OK;
+}
+
+template <int NV, int K>
+static yfd_status launch_stage_class(yfd_ctx *ctx, int mode, const mx_step_args &a)
+{
+    int64_t grid = (int64_t) ctx->sm_count * 2;
+    const int64_t want = ceil_div(a.ntiles, CLS_THREADS / 32);
+    if (grid > want) grid = want;
+    YFD_LAUNCH(ctx, (maxwell_stage_class<NV, K>), (unsigned) (grid < 1 ? 1 : grid), CLS_THREADS, 0, a, mode);
+    return YFD_OK;
+}
+
+template <int NV>
+static yfd_status dispatch_stage_class(yfd_ctx *ctx, int degree, int mode, const mx_step_args &a)
+{
+    switch (degree) {
+    case 1: return launch_stage_class<NV, 1>(ctx, mode, a);
+    case 2: return launch_stage_class<NV, 2>(ctx, mode, a);
+    case 3: return launch_stage_class<NV, 3>(ctx, mode, a);
+    case 4: return launch_stage_class<NV, 4>(ctx, mode, a);
+    }
+    return fail(ctx, YFD_ERR_UNSUPPORTED, "Maxwell class operator: degrees 1..4");
+}
+
 /* Measured on B200 (profiles/README.md, r01 Maxwell sweep): the L2 bulk prefetch is worth +8-10 % at every degree;
  * 2 CTAs per SM (128 registers: all loads of a face in flight at once) is best for bs >= 6, 4 CTAs for bs <= 3. */
 template <int K>
@@ -191,6 +385,7 @@ static yfd_status dispatch_stage(yfd_ctx *ctx, int degree, int mode, const mx_st
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a)
 {
     if (a.nchunks <= 0) return YFD_OK;
+    if (a.table) return nv == 3 ? dispatch_stage_class<3>(ctx, degree, mode, a) : dispatch_stage_class<4>(ctx, degree, mode, a);
     return nv == 3 ? dispatch_stage<3>(ctx, degree, mode, a) : dispatch_stage<4>(ctx, degree, mode, a);
 }
 

@@ -58,17 +58,24 @@ __global__ void cls_collect_starts(const int32_t *__restrict__ flag, const int64
 /* work list: position poff[k] + (i - start[k]) holds the i-th cell of the sorted order */
 __global__ void cls_fill_work(const int32_t *__restrict__ flag, const int64_t *__restrict__ excl, const int64_t *__restrict__ start,
                               const int64_t *__restrict__ poff, const uint32_t *__restrict__ sorted_cell, int64_t n,
-                              const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk_cell, const int8_t *__restrict__ slots,
-                              int nf, int64_t npos, int32_t *__restrict__ work_cell, int32_t *__restrict__ work_nbr,
-                              int32_t *__restrict__ cell_cls)
+                              int32_t *__restrict__ work_cell, int32_t *__restrict__ cell_cls)
 {
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int64_t k = excl[i] + flag[i] - 1;
-    const int64_t pos = poff[k] + (i - start[k]);
     const int32_t c = (int32_t) sorted_cell[i];
-    work_cell[pos] = c;
+    work_cell[poff[k] + (i - start[k])] = c;
     cell_cls[c] = (int32_t) k;
+}
+
+/* DG: where the x entries of the cell across each local face live (canonical slot order) */
+__global__ void cls_fill_nbr(const int32_t *__restrict__ work_cell, int64_t npos, const int64_t *__restrict__ cellptr,
+                             const int32_t *__restrict__ blk_cell, const int8_t *__restrict__ slots, int nf, int32_t *__restrict__ work_nbr)
+{
+    const int64_t pos = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= npos) return;
+    const int32_t c = work_cell[pos];
+    if (c < 0) return;
     const int64_t cp = cellptr[c];
     const int32_t self = blk_cell[cp + slots[(int64_t) c * (nf + 1)]];
     for (int e = 0; e < nf; e++) {
@@ -158,6 +165,53 @@ yfd_status expand_class_values(yfd_ctx *ctx, const yfd_system *sys, double *d_va
     return YFD_OK;
 }
 
+/* Group cells by key: equal keys = one class; classes are laid out one after the other, each padded to a multiple of
+ * 32, cells in ascending id inside a class (the sort is stable).  d_keys [nc] is clobbered.  g.reject != 0 = a normal "no"
+ * (1: the class tables would exceed table_budget bytes or too many classes, 2: too many small classes). */
+yfd_status group_cells_by_key(yfd_ctx *ctx, int64_t nc, uint64_t *d_keys, int key_bits, size_t table_bytes_per_class, size_t table_budget,
+                              class_groups &g)
+{
+    g = class_groups();
+    dbuf<uint32_t> ids_tmp;
+    dbuf<uint64_t> keys_tmp;
+    dbuf<int32_t> flag;
+    dbuf<int64_t> excl, poff;
+    YFD_TRY(g.sorted_cell.alloc(ctx, (size_t) nc)); YFD_TRY(ids_tmp.alloc(ctx, (size_t) nc)); YFD_TRY(keys_tmp.alloc(ctx, (size_t) nc));
+    YFD_TRY(flag.alloc(ctx, (size_t) nc)); YFD_TRY(excl.alloc(ctx, (size_t) nc + 1));
+    YFD_TRY(fill_iota_u32(ctx, g.sorted_cell.p, nc));
+    YFD_TRY(radix_sort_pairs(ctx, d_keys, g.sorted_cell.p, keys_tmp.p, ids_tmp.p, nc, key_bits));
+    const unsigned grid = (unsigned) ceil_div(nc + 1, 256);
+    YFD_LAUNCH(ctx, cls_flag_starts, grid, 256, 0, (const uint64_t *) d_keys, nc, flag.p);
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, flag.p, excl.p, nc));
+    int64_t ncls = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&ncls, excl.p + nc, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    g.ncls = ncls;
+    if (ncls > CLS_MAX_CLASSES || (table_budget && (size_t) ncls * table_bytes_per_class > table_budget)) { g.reject = 1; return YFD_OK; }
+    YFD_TRY(g.start.alloc(ctx, (size_t) ncls + 1)); YFD_TRY(poff.alloc(ctx, (size_t) ncls + 1));
+    YFD_LAUNCH(ctx, cls_collect_starts, grid, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, nc, g.start.p);
+    std::vector<int64_t> hstart((size_t) ncls + 1), hpoff((size_t) ncls + 1);
+    YFD_TRY(g.start.download(ctx, hstart.data(), (size_t) ncls + 1));
+    int64_t npos = 0;
+    for (int64_t k = 0; k < ncls; k++) { hpoff[k] = npos; npos += (hstart[k + 1] - hstart[k] + 31) / 32 * 32; }
+    hpoff[ncls] = npos;
+    /* padding beyond 25 % of the list = too many small classes for lane-per-cell tiles to pay */
+    if (npos > nc + nc / 4 + 32 * 64) { g.reject = 2; return YFD_OK; }
+    g.npos = npos; g.ntiles = npos / 32;
+    std::vector<int32_t> htile((size_t) g.ntiles);
+    for (int64_t k = 0; k < ncls; k++)
+        for (int64_t t = hpoff[k] / 32; t < hpoff[k + 1] / 32; t++) htile[t] = (int32_t) k;
+    YFD_TRY(poff.upload(ctx, hpoff.data(), (size_t) ncls + 1));
+    YFD_TRY(g.tile_cls.alloc(ctx, (size_t) g.ntiles));
+    YFD_TRY(g.tile_cls.upload(ctx, htile.data(), (size_t) g.ntiles));
+    YFD_TRY(g.work_cell.alloc(ctx, (size_t) npos)); YFD_TRY(g.cell_cls.alloc(ctx, (size_t) nc));
+    YFD_CUDA(ctx, cudaMemsetAsync(g.work_cell.p, 0xff, (size_t) npos * sizeof(int32_t), ctx->stream));      /* -1 = padding */
+    YFD_LAUNCH(ctx, cls_fill_work, grid, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, (const int64_t *) g.start.p, (const int64_t *) poff.p,
+               (const uint32_t *) g.sorted_cell.p, nc, g.work_cell.p, g.cell_cls.p);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));          /* the temporaries go out of scope */
+    return YFD_OK;
+}
+
 /* d_keys [ncells]: class keys in internal cell order (clobbered).  On return sys->classes.ready says whether the cache is
  * usable; every "no" is a normal outcome (the streamed kernel stays), only CUDA failures are errors. */
 yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int key_bits, double tol)
@@ -167,62 +221,30 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
     const int64_t nc = sys->ncells;
     const int bs = sys->bs, nf = sys->nf, nb = nf + 1, ss = cls_slot_stride(bs);
     if (nc < 1 || (bs != 1 && bs != 3 && bs != 6 && bs != 10 && bs != 15)) return YFD_OK;
-    dbuf<uint32_t> ids, ids_tmp;
-    dbuf<uint64_t> keys_tmp;
-    dbuf<int32_t> flag;
-    dbuf<int64_t> excl;
-    YFD_TRY(ids.alloc(ctx, (size_t) nc)); YFD_TRY(ids_tmp.alloc(ctx, (size_t) nc)); YFD_TRY(keys_tmp.alloc(ctx, (size_t) nc));
-    YFD_TRY(flag.alloc(ctx, (size_t) nc)); YFD_TRY(excl.alloc(ctx, (size_t) nc + 1));
-    YFD_TRY(fill_iota_u32(ctx, ids.p, nc));
-    YFD_TRY(radix_sort_pairs(ctx, d_keys, ids.p, keys_tmp.p, ids_tmp.p, nc, key_bits));     /* stable: ascending cell id inside a class */
-    const unsigned g = (unsigned) ceil_div(nc + 1, 256);
-    YFD_LAUNCH(ctx, cls_flag_starts, g, 256, 0, (const uint64_t *) d_keys, nc, flag.p);
-    YFD_TRY(exclusive_scan_i32_to_i64(ctx, flag.p, excl.p, nc));
-    int64_t ncls = 0;
-    YFD_CUDA(ctx, cudaMemcpyAsync(&ncls, excl.p + nc, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cl.ncls = (int) std::min<int64_t>(ncls, 0x7fffffff);
-    const size_t table_bytes = (size_t) ncls * nb * ss * sizeof(double);
-    if (ncls > CLS_MAX_CLASSES || table_bytes + 1024 > ctx->smem_optin) { cl.reject = 1; return YFD_OK; }   /* does not fit shared memory */
-
-    dbuf<int64_t> start, poff;
-    YFD_TRY(start.alloc(ctx, (size_t) ncls + 1)); YFD_TRY(poff.alloc(ctx, (size_t) ncls + 1));
-    YFD_LAUNCH(ctx, cls_collect_starts, g, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, nc, start.p);
-    std::vector<int64_t> hstart((size_t) ncls + 1), hpoff((size_t) ncls + 1);
-    YFD_TRY(start.download(ctx, hstart.data(), (size_t) ncls + 1));
-    int64_t npos = 0;
-    for (int64_t k = 0; k < ncls; k++) { hpoff[k] = npos; npos += (hstart[k + 1] - hstart[k] + 31) / 32 * 32; }
-    hpoff[ncls] = npos;
-    /* padding beyond 25 % of the list = too many small classes for lane-per-cell tiles to pay */
-    if (npos > nc + nc / 4 + 32 * 64) { cl.reject = 2; return YFD_OK; }
-    const int64_t ntiles = npos / 32;
-    std::vector<int32_t> htile((size_t) ntiles);
-    for (int64_t k = 0; k < ncls; k++)
-        for (int64_t t = hpoff[k] / 32; t < hpoff[k + 1] / 32; t++) htile[t] = (int32_t) k;
-    YFD_TRY(poff.upload(ctx, hpoff.data(), (size_t) ncls + 1));
-    YFD_TRY(cl.tile_cls.alloc(ctx, (size_t) ntiles));
-    YFD_TRY(cl.tile_cls.upload(ctx, htile.data(), (size_t) ntiles));
-    YFD_TRY(cl.work_cell.alloc(ctx, (size_t) npos)); YFD_TRY(cl.work_nbr.alloc(ctx, (size_t) (npos * nf)));
-    YFD_TRY(cl.cell_cls.alloc(ctx, (size_t) nc));
-    YFD_CUDA(ctx, cudaMemsetAsync(cl.work_cell.p, 0xff, (size_t) npos * sizeof(int32_t), ctx->stream));      /* -1 = padding */
+    class_groups g;
+    YFD_TRY(group_cells_by_key(ctx, nc, d_keys, key_bits, (size_t) nb * ss * sizeof(double), ctx->smem_optin - 1024, g));
+    cl.ncls = (int) std::min<int64_t>(g.ncls, 0x7fffffff);
+    if (g.reject) { cl.reject = g.reject; return YFD_OK; }
+    const int64_t ncls = g.ncls, npos = g.npos;
+    YFD_TRY(cl.work_nbr.alloc(ctx, (size_t) (npos * nf)));
     YFD_CUDA(ctx, cudaMemsetAsync(cl.work_nbr.p, 0, (size_t) (npos * nf) * sizeof(int32_t), ctx->stream));
-    YFD_LAUNCH(ctx, cls_fill_work, g, 256, 0, (const int32_t *) flag.p, (const int64_t *) excl.p, (const int64_t *) start.p, (const int64_t *) poff.p,
-               (const uint32_t *) ids.p, nc, (const int64_t *) sys->cellptr.p, (const int32_t *) sys->blk_cell.p, (const int8_t *) sys->slots.p,
-               nf, npos, cl.work_cell.p, cl.work_nbr.p, cl.cell_cls.p);
+    YFD_LAUNCH(ctx, cls_fill_nbr, (unsigned) ceil_div(npos, 256), 256, 0, (const int32_t *) g.work_cell.p, npos, (const int64_t *) sys->cellptr.p,
+               (const int32_t *) sys->blk_cell.p, (const int8_t *) sys->slots.p, nf, cl.work_nbr.p);
     dbuf<double> scale;
     dbuf<unsigned long long> worst;
     YFD_TRY(cl.table.alloc(ctx, (size_t) ncls * nb * ss, 2)); YFD_TRY(scale.alloc(ctx, (size_t) ncls));
     YFD_TRY(worst.alloc(ctx, 1)); YFD_TRY(worst.zero(ctx));
-    YFD_LAUNCH(ctx, cls_build_table, (unsigned) ncls, 128, 0, (const int64_t *) start.p, (const uint32_t *) ids.p, (const int64_t *) sys->cellptr.p,
+    YFD_LAUNCH(ctx, cls_build_table, (unsigned) ncls, 128, 0, (const int64_t *) g.start.p, (const uint32_t *) g.sorted_cell.p, (const int64_t *) sys->cellptr.p,
                (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, bs, nf, cl.table.p, scale.p);
     const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
-    YFD_LAUNCH(ctx, cls_verify, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) cl.cell_cls.p, (const int64_t *) sys->cellptr.p,
+    YFD_LAUNCH(ctx, cls_verify, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) g.cell_cls.p, (const int64_t *) sys->cellptr.p,
                (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, (const double *) cl.table.p, (const double *) scale.p, nc, bs, nf, worst.p);
     unsigned long long wb = 0;
     YFD_TRY(worst.download(ctx, &wb, 1));
     double dev;
     memcpy(&dev, &wb, sizeof(dev));
-    cl.max_dev = dev; cl.tol = tol; cl.npos = npos; cl.ntiles = ntiles; cl.table_doubles = (int) (ncls * nb * ss);
+    cl.max_dev = dev; cl.tol = tol; cl.npos = npos; cl.ntiles = g.ntiles; cl.table_doubles = (int) (ncls * nb * ss);
+    cl.work_cell = std::move(g.work_cell); cl.tile_cls = std::move(g.tile_cls); cl.cell_cls = std::move(g.cell_cls);
     if (!(dev <= tol)) { cl.reject = 3; return YFD_OK; }      /* also catches inf / NaN */
     cl.ready = true;
     return YFD_OK;
