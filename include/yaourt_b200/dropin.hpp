@@ -16,8 +16,11 @@
  * continuous_fem.cpp:80) sit inside templates whose calls are resolved at instantiation, so the reference's
  * drivers pick these up without a source change.  Plus the batched entry the reference lacks:
  *
- *   yaourt::b200::assemble_dg_sip(msh, degree, eta, use_pc)   the whole cell loop of run_diffusion_solver
+ *   yaourt::b200::assemble_dg_sip(msh, degree, eta, rhs_fn_id, dirichlet_fn_id[, use_pc, solve_with])
+ *                                                        the whole cell loop of run_diffusion_solver
  *                                                        (dg2d_diffusion.cpp:133-201) + assembler::finalize on the GPU
+ *   yaourt::b200::assemble_dg_advection(msh, degree, eta, use_upwinding[, solve_with])   dg2d_advection.cpp:137-215
+ *   yaourt::b200::assemble_cfem_p1(msh[, rhs_fn_id, solve_with])                          continuous_fem.cpp:64-80
  *
  * Error behaviour follows the reference: std::invalid_argument / std::logic_error with its messages for the
  * mesh / assembler errors, `false` from conjugated_gradient on a shape mismatch, `true` otherwise -- also when
@@ -99,17 +102,26 @@ struct dg_sip_system {
     blaze::DynamicVector<double>    sol;          /* filled by solve()   */
 };
 
+/* physics of the batched DG entries */
+enum dg_physics { DG_SIP_DIFFUSION = 0, DG_ADVECTION_REACTION = 1 };
+
+/* assemble_dg_sip(msh, degree, eta, rhs_fn_id, dirichlet_fn_id) -- the whole cell loop of
+ * run_diffusion_solver (dg2d_diffusion.cpp:133-201) + assembler::finalize on the GPU, the data functions chosen by id
+ * (YFD_FN_*: per-cell host callbacks cannot feed a GPU).  use_pc builds assm.pc (methods/dg.hpp:133-142); solve_with, if
+ * given, also runs conjugated_gradient with the matrix resident on the device. */
 template <typename Mesh>
-dg_sip_system<Mesh> assemble_dg_sip(const Mesh &msh, size_t degree, double eta, bool use_pc,
-                                    const conjugated_gradient_params<double> *solve_with = nullptr)
+dg_sip_system<Mesh> assemble_dg_sip(const Mesh &msh, size_t degree, double eta, int rhs_fn_id, int dirichlet_fn_id, bool use_pc = false,
+                                    const conjugated_gradient_params<double> *solve_with = nullptr, int physics = DG_SIP_DIFFUSION,
+                                    bool use_upwinding = false)
 {
     auto &ctx = context::global();
     yfd_mesh *dm = upload_mesh(ctx, msh);
     yfd_dg_config cfg;
-    cfg.degree = (int) degree; cfg.eta = eta; cfg.rhs_fn = YFD_FN_SINSIN; cfg.dirichlet_fn = YFD_FN_ZERO; cfg.build_preconditioner = use_pc ? 1 : 0;
+    cfg.degree = (int) degree; cfg.eta = eta; cfg.rhs_fn = rhs_fn_id; cfg.dirichlet_fn = dirichlet_fn_id; cfg.build_preconditioner = use_pc ? 1 : 0;
     yfd_system *sys = nullptr;
     yfd_assembly_info ai;
-    yfd_status st = yfd_dg_assemble_sip(ctx.get(), dm, &cfg, &sys, &ai);
+    yfd_status st = physics == DG_ADVECTION_REACTION ? yfd_dg_assemble_advection(ctx.get(), dm, &cfg, use_upwinding ? 1 : 0, &sys, &ai)
+                                                     : yfd_dg_assemble_sip(ctx.get(), dm, &cfg, &sys, &ai);
     if (st != YFD_OK) { yfd_mesh_destroy(dm); check(ctx.get(), st); }
     dg_sip_system<Mesh> out;
     const size_t n = (size_t) ai.system_size, nnz = (size_t) ai.nnz;
@@ -123,10 +135,74 @@ dg_sip_system<Mesh> assemble_dg_sip(const Mesh &msh, size_t degree, double eta, 
         yfd_cg_params p;
         yfd_cg_params_default(&p);
         p.rr_tol = solve_with->rr_tol; p.rr_max = solve_with->rr_max; p.max_iter = (int64_t) solve_with->max_iter;
+        p.use_normal_eqns = solve_with->use_normal_eqns ? 1 : 0;          /* the advection driver's solve (dg2d_advection.cpp:225) */
         yfd_cg_info info;
         st = yfd_system_solve_cg(ctx.get(), sys, use_pc ? 1 : 0, &p, v.data(), &info, nullptr, 0);   /* matrix never leaves the GPU */
         out.sol.resize(n);
         for (size_t i = 0; i < n; i++) out.sol[i] = v[i];
+        auto &rep = last_cg_report();
+        rep.iterations = (size_t) info.iterations; rep.nr0 = info.nr0; rep.nr = info.nr; rep.converged = info.converged != 0; rep.ms_solve = info.ms_solve;
+    }
+    yfd_system_destroy(sys);
+    yfd_mesh_destroy(dm);
+    check(ctx.get(), st);
+    return out;
+}
+
+/* the reference driver's own data functions (dg2d_diffusion.cpp:53-66) */
+template <typename Mesh>
+dg_sip_system<Mesh> assemble_dg_sip(const Mesh &msh, size_t degree, double eta, bool use_pc,
+                                    const conjugated_gradient_params<double> *solve_with = nullptr)
+{
+    return assemble_dg_sip(msh, degree, eta, YFD_FN_SINSIN, YFD_FN_ZERO, use_pc, solve_with);
+}
+
+/* the cell loop of run_advection_reaction_solver (dg2d_advection.cpp:137-213) + finalize; solve_with->use_normal_eqns = true
+ * reproduces the driver's solve (:225) */
+template <typename Mesh>
+dg_sip_system<Mesh> assemble_dg_advection(const Mesh &msh, size_t degree, double eta, bool use_upwinding,
+                                          const conjugated_gradient_params<double> *solve_with = nullptr)
+{
+    return assemble_dg_sip(msh, degree, eta, YFD_FN_ADVECTION_RHS, YFD_FN_ZERO, false, solve_with, DG_ADVECTION_REACTION, use_upwinding);
+}
+
+/* continuous P1: the cell loop of continuous_fem.cpp:64-71 + cfem::assembler (methods/cfem.hpp:119-186) + finalize;
+ * `expanded` = assm.expand(sol) (:189-197) when solve_with is given */
+template <typename Mesh>
+struct cfem_system {
+    blaze::CompressedMatrix<double> lhs;
+    blaze::DynamicVector<double>    rhs, sol, expanded;
+    std::vector<int64_t>            compress_map;     /* [points], -1 on Dirichlet nodes (methods/cfem.hpp:140-148) */
+};
+
+template <typename Mesh>
+cfem_system<Mesh> assemble_cfem_p1(const Mesh &msh, int rhs_fn_id = YFD_FN_SINSIN,
+                                   const conjugated_gradient_params<double> *solve_with = nullptr)
+{
+    auto &ctx = context::global();
+    yfd_mesh *dm = upload_mesh(ctx, msh);
+    yfd_system *sys = nullptr;
+    yfd_assembly_info ai;
+    yfd_status st = yfd_cfem_assemble_p1(ctx.get(), dm, rhs_fn_id, &sys, &ai);
+    if (st != YFD_OK) { yfd_mesh_destroy(dm); check(ctx.get(), st); }
+    cfem_system<Mesh> out;
+    const size_t n = (size_t) ai.system_size, nnz = (size_t) ai.nnz, np = msh.points.size();
+    std::vector<int64_t> rowptr(n + 1), colidx(nnz);
+    std::vector<double> values(nnz), v(n), ex(np);
+    out.compress_map.resize(np);
+    st = yfd_system_get_csr(sys, rowptr.data(), colidx.data(), values.data());
+    if (st == YFD_OK) { fill_compressed(out.lhs, n, n, rowptr, colidx, values); st = yfd_system_get_rhs(sys, v.data()); }
+    if (st == YFD_OK) { out.rhs.resize(n); for (size_t i = 0; i < n; i++) out.rhs[i] = v[i]; st = yfd_cfem_get_compress_map(sys, out.compress_map.data()); }
+    if (st == YFD_OK && solve_with) {
+        yfd_cg_params p;
+        yfd_cg_params_default(&p);
+        p.rr_tol = solve_with->rr_tol; p.rr_max = solve_with->rr_max; p.max_iter = (int64_t) solve_with->max_iter;
+        yfd_cg_info info;
+        st = yfd_system_solve_cg(ctx.get(), sys, 0, &p, v.data(), &info, nullptr, 0);
+        if (st == YFD_OK) st = yfd_cfem_expand(sys, v.data(), ex.data());
+        out.sol.resize(n); out.expanded.resize(np);
+        for (size_t i = 0; i < n; i++) out.sol[i] = v[i];
+        for (size_t i = 0; i < np; i++) out.expanded[i] = ex[i];
         auto &rep = last_cg_report();
         rep.iterations = (size_t) info.iterations; rep.nr0 = info.nr0; rep.nr = info.nr; rep.converged = info.converged != 0; rep.ms_solve = info.ms_solve;
     }

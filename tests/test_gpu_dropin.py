@@ -108,3 +108,65 @@ def test_unmodified_advection_driver_on_gpu(name):
     # CG on A^T A is ill-conditioned: iteration counts of two correct implementations differ by a few percent
     assert abs(qp - float(g["l2_qp"])) <= 0.02 * float(g["l2_qp"])
     assert abs(it - int(g["iters"])) <= max(5, 0.15 * int(g["iters"]))
+
+
+# ---- the batched C++ entries SURVEY.md 8b asks for beyond the reference's per-block interface ----
+@pytest.mark.parametrize("spec,t,r,k,pc", [("tri 3 2 1 fn", 0, 3, 2, True), ("quad 2 3 0 fn", 1, 2, 3, False)])
+def test_batched_entry_with_function_ids(ref, spec, t, r, k, pc):
+    """assemble_dg_sip(msh, degree, eta, rhs_fn_id, dirichlet_fn_id, ...) with the driver's own data functions"""
+    out = run([], env={"YFD_DROPIN_BATCHED": spec})
+    m = re.search(r"batched: n (\d+) nnz (\d+) iterations (\d+) sol_norm (\S+) rhs_norm (\S+)", out)
+    n, nnz, it, sn, rn = int(m.group(1)), int(m.group(2)), int(m.group(3)), float(m.group(4)), float(m.group(5))
+    ref.mesh(t, r)
+    ref.set_cg(rr_tol=1e-12, rr_max=1e4, max_iter=-1)
+    o = ref.run_dg(k, use_pc=pc)
+    assert (n, nnz) == (o["n"], o["nnz"])
+    assert abs(sn - np.linalg.norm(o["sol"])) <= 1e-10 * np.linalg.norm(o["sol"])
+    assert abs(rn - np.linalg.norm(o["rhs"])) <= 1e-12 * np.linalg.norm(o["rhs"])
+    assert abs(it - o["iters"]) <= max(3, 0.05 * o["iters"])
+
+
+@pytest.mark.parametrize("levels", [2, 4])
+def test_batched_cfem_entry(ref, levels):
+    """assemble_cfem_p1(msh, rhs_fn_id, &cgp) against the unmodified continuous_fem.cpp"""
+    out = run([], env={"YFD_DROPIN_BATCHED": "tri %d 1 0 cfem" % levels})
+    m = re.search(r"batched cfem: n (\d+) nnz (\d+) iterations (\d+) sol_norm (\S+) rhs_norm (\S+) expanded_norm (\S+) dirichlet (\d+)", out)
+    n, nnz, it = int(m.group(1)), int(m.group(2)), int(m.group(3))
+    sn, rn, en, nd = float(m.group(4)), float(m.group(5)), float(m.group(6)), int(m.group(7))
+    ref.set_cg(rr_tol=1e-12, rr_max=1e3)
+    o = ref.run_cfem(levels)
+    assert (n, nnz) == (o["n"], o["nnz"])
+    assert abs(sn - np.linalg.norm(o["sol"])) <= 1e-10 * np.linalg.norm(o["sol"])
+    assert abs(rn - np.linalg.norm(o["rhs"])) <= 1e-12 * np.linalg.norm(o["rhs"])
+    assert abs(en - sn) <= 1e-12 * sn                      # expand() pads the Dirichlet nodes with zeros
+    assert nd == 4 * 2 ** levels                           # boundary points of the reference's triangle mesh
+    assert abs(it - o["iters"]) <= max(3, 0.05 * o["iters"])
+
+
+@pytest.mark.parametrize("name", ["tri_r2_k1", "quad_r1_k3_up"])
+def test_batched_advection_entry(name):
+    """assemble_dg_advection(msh, degree, eta, use_upwinding, &cgp) with cgp.use_normal_eqns as the driver solves
+    (dg2d_advection.cpp:225): sizes and rhs of the reference's fixture, solution in the same distance class"""
+    if not os.path.exists(ADV_EXE):
+        pytest.skip("oracle/_ref/dropin_dg2d_advection not built (needs /root/reference at build time)")
+    try:
+        g = golden("adv_%s.npz" % name)
+    except FileNotFoundError:
+        pytest.skip("no fixture adv_%s.npz" % name)
+    spec = "%s %d %d %d" % ("tri" if int(g["mtype"]) == 0 else "quad", int(g["levels"]), int(g["degree"]), int(g["upwinding"]))
+    e = dict(os.environ)
+    e["YFD_DROPIN_BATCHED"] = spec
+    res = subprocess.run([ADV_EXE], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=e, timeout=600, cwd="/tmp")
+    assert res.returncode == 0, res.stdout[-2000:]
+    m = re.search(r"batched: n (\d+) nnz (\d+) iterations (\d+) sol_norm (\S+) rhs_norm (\S+)", res.stdout)
+    n, nnz, it, sn, rn = int(m.group(1)), int(m.group(2)), int(m.group(3)), float(m.group(4)), float(m.group(5))
+    assert n == len(g["rhs"]) and nnz == len(g["values"])
+    assert abs(rn - np.linalg.norm(g["rhs"])) <= 1e-12 * np.linalg.norm(g["rhs"])
+    # CG on A^T A: iterates of two correct implementations drift (DESIGN.md section 2, deviation 3); the solution is pinned by
+    # a direct solve of the reference's own matrix
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    A = sp.csr_matrix((g["values"], g["colidx"], g["rowptr"]), shape=(n, n))
+    want = spla.spsolve(A.tocsc(), g["rhs"])
+    assert abs(sn - np.linalg.norm(want)) <= 1e-4 * np.linalg.norm(want)
+    assert abs(it - int(g["iters"])) <= max(5, 0.15 * int(g["iters"]))
