@@ -77,5 +77,41 @@ def test_transposed_blocks(yfd, ctx):
     csr = yfd.Csr.from_arrays(ctx, sysm.n, sysm.n, rowptr, colidx, vals)
     h2 = csr.solve_cg(sysm.rhs(), p, history=True)["history"]
     assert np.allclose(h1, h2, rtol=1e-9)
+    # from an initial guess (core/solvers.hpp:79-91: r0 = A^T (b - A x0)): x0 = 0 reproduces the cold start bit for bit, and
+    # x0 = the cold solution starts from a residual already reduced by the cold solve's factor
+    q = dict(rr_tol=1e-8, rr_max=1e4, max_iter=2 * sysm.n, use_normal_eqns=1)
+    cold = sysm.solve_cg(yfd.CgParams(**q))
+    warm0 = sysm.solve_cg(yfd.CgParams(**q), x0=np.zeros(sysm.n))
+    assert warm0["iterations"] == cold["iterations"] and np.array_equal(warm0["x"], cold["x"])
+    again = sysm.solve_cg(yfd.CgParams(rr_tol=1e-3, rr_max=1e4, max_iter=5, use_normal_eqns=1), x0=cold["x"])
+    assert again["nr0"] <= 1e-6 * cold["nr0"]
+
+
+def test_normal_equations_with_diagonal_iM(yfd, ctx):
+    """conjugated_gradient(cgp, A, b, x, iM) with cgp.use_normal_eqns (core/solvers.hpp:185-227: r0 = A^T (b - A x),
+    y = A^T A d, z = iM r) against a numpy restatement of exactly those lines; bicgstab with iM ignores the flag (:356-467)."""
+    import scipy.sparse as sp
+    mesh = yfd.Mesh(ctx, yfd.HostMesh.create(0, 2))
+    sysm = ctx.dg_assemble_advection(mesh, 2, eta=1.0, upwinding=True)
+    rowptr, colidx, vals = sysm.csr()
+    n = sysm.n
+    A = sp.csr_matrix((vals, colidx, rowptr), shape=(n, n))
+    b = sysm.rhs()
+    iM = 1.0 / (A.T @ A).diagonal()
+    csr = yfd.Csr.from_arrays(ctx, n, n, rowptr, colidx, vals)
+    res = csr.solve_cg(b, yfd.CgParams(rr_tol=1e-30, rr_max=1e30, max_iter=12, use_normal_eqns=1), pc_diag=iM, history=True)
+    x = np.zeros(n); r = A.T @ (b - A @ x); d = iM * r; nr0 = np.linalg.norm(r); hist = [1.0]
+    for _ in range(12):
+        y = A.T @ (A @ d)
+        rho = r @ (iM * r)
+        alpha = rho / (d @ y)
+        x = x + alpha * d; r = r - alpha * y
+        d = iM * r + (r @ (iM * r)) / rho * d
+        hist.append(np.linalg.norm(r) / nr0)
+    assert np.allclose(res["history"], hist, rtol=1e-7)
+    assert np.linalg.norm(res["x"] - x) <= 1e-7 * np.linalg.norm(x)
+    a = csr.solve_bicgstab(b, yfd.CgParams(rr_tol=1e-8, rr_max=1e6, max_iter=200, use_normal_eqns=1), pc_diag=1.0 / A.diagonal())
+    c = csr.solve_bicgstab(b, yfd.CgParams(rr_tol=1e-8, rr_max=1e6, max_iter=200), pc_diag=1.0 / A.diagonal())
+    assert a["iterations"] == c["iterations"] and np.array_equal(a["x"], c["x"])
     with pytest.raises(yfd.YfdError):
-        sysm.solve_cg(yfd.CgParams(use_normal_eqns=1, use_initial_guess=1), x0=np.zeros(sysm.n))
+        csr.solve_bicgstab(b, yfd.CgParams(max_iter=5, use_normal_eqns=1))

@@ -83,7 +83,7 @@ def test_block_jacobi_errors(yfd, ctx):
         cf.solve_cg(use_pc=yfd.PC_BLOCK_JACOBI)
     dg = ctx.dg_assemble_sip(tri, 1, eta=1.0, build_pc=False)
     with pytest.raises(yfd.YfdError):
-        dg.solve_cg(use_pc=3)
+        dg.solve_cg(use_pc=7)
     with pytest.raises(yfd.YfdError):
         dg.solve_bicgstab(use_pc=yfd.PC_BLOCK_JACOBI)
     with pytest.raises(yfd.YfdError):

@@ -17,7 +17,8 @@
  * iterations are one CUDA graph, the host polls one flag per replay.
  *
  * iM is applied as a diagonal (the only preconditioner the reference's drivers build, dg2d_diffusion.cpp:200-212).
- * Not supported: use_normal_eqns (:297,:330,:337), distributed systems.
+ * Not supported: use_normal_eqns in the overload without iM (:289,:318-337; the overload with iM ignores the flag, as here),
+ * distributed systems.
  */
 #pragma once
 
@@ -184,7 +185,9 @@ static yfd_status bicgstab_device(yfd_ctx *ctx, const spmv_op &op, const double 
                                   const yfd_cg_params *p, yfd_cg_info *info, double *host_history, int64_t history_cap)
 {
     const int64_t n = op.nrows;
-    if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab with use_normal_eqns");
+    /* the reference's overload WITH iM never looks at use_normal_eqns (core/solvers.hpp:356-467 has no such branch): with a
+     * preconditioner the flag is ignored, as there; the overload without iM does honour it (:289,:318-337) -- not built */
+    if (p->use_normal_eqns && !d_pc) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab without iM on the normal equations (core/solvers.hpp:289,318-337)");
     if (op.plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab on a distributed system");
     dbuf<double> r, r0, pv, v, s, t, y, yv, z, partials, hist;
     dbuf<bicg_scalars> bs;

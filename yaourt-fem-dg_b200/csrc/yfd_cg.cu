@@ -147,6 +147,12 @@ __global__ void cg_halo_r(double *__restrict__ r, const double *__restrict__ y_h
         r[i] = fma(-alpha, __ldcg(&y_halo[i]), r[i]);
 }
 
+/* t = b - y (normal equations with an initial guess: the operand of A^T) */
+__global__ void cg_b_minus_y(const double *__restrict__ b, const double *__restrict__ y, double *__restrict__ t, int64_t n)
+{
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) t[i] = b[i] - y[i];
+}
+
 /* ---- K2 ------------------------------------------------------------------------------------ */
 /* Peer-memory transport (several ranks, yfd_peer.cu): what the neighbours need each iteration is not d but y = A d on
  * the cells they hold as halo -- with it they advance their own halo copies of r, z and d by the same recurrences
@@ -411,8 +417,8 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
          * d.y is formed as |A d|^2 (equal in exact arithmetic, one reduction pass over A d instead of a fused one) */
         if (!opT) return fail(ctx, YFD_ERR_INVALID_STATE, "internal: normal equations without the transposed operator");
         if (op.plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a distributed system");
-        if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with use_initial_guess");
-        if (d_pc) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner (the reference's 5-argument overload ignores the flag, core/solvers.hpp:141-243)");
+        /* with iM (core/solvers.hpp:185-194,217-218): r0 = A^T (b - A x), y = A^T A d, z = iM r -- the diagonal scale of
+         * cg_init / cg_update_xr applies unchanged; block preconditioners are defined for A, not A^T A */
     }
     dbuf<double> r, d, y, z, partials, hist, t_ad, atb;
     dbuf<cg_scalars> sc;
@@ -421,7 +427,6 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     dbuf<double> sendbuf;
     bool peer = false;                  /* peer-memory transport (yfd_peer.cu) or NCCL calls */
     if (pl) {
-        if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
         YFD_TRY(ensure_peer_region(ctx, (size_t) (pl->max_local_cells * op.bs) + 8));
         peer = ctx->peer_enabled;
         YFD_TRY(sendbuf.alloc(ctx, (size_t) (pl->nsend * op.bs), 2));     /* NCCL: every iteration; peer: start-up only */
@@ -475,32 +480,36 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     gpu_timer timer;
     timer.start(ctx->stream);
     const unsigned vg = vec_grid(ctx, n);
+    /* start-up: r0 = b - A x0 (x0 = 0 unless use_initial_guess, core/solvers.hpp:79-91); normal equations:
+     * r0 = A^T (b - A x0) (:88-89).  Distributed with an initial guess: d_x arrives as [owned | halo] (system_solve). */
+    const double *ax0 = nullptr;
     if (p->use_initial_guess) {
-        YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));          /* r0 = b - A x (core/solvers.hpp:91) */
-        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, y.p, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
-        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap, sc2);
-        if (block) {
-            YFD_TRY(apply_block());
-            YFD_LAUNCH(ctx, cg_block_init, vg, CG_THREADS, 0, dv, (const double *) z.p, n, sc.p, (const cg_scalars *) sc2);
-        }
+        YFD_TRY(launch_spmv<false>(ctx, op, d_x, y.p, sc.p, partials.p));
+        ax0 = y.p;
     } else {
-        YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));   /* x = 0 (core/solvers.hpp:79-80) */
-        if (normal) {                                                                        /* r0 = A^T (b - A 0) (:88-89) */
-            YFD_TRY(t_ad.alloc(ctx, (size_t) n, 2)); YFD_TRY(atb.alloc(ctx, (size_t) n, 2));
-            YFD_TRY(launch_spmv<false>(ctx, *opT, d_b, atb.p, sc.p, partials.p));
-            d_b = atb.p;
+        YFD_CUDA(ctx, cudaMemsetAsync(d_x, 0, (size_t) n * sizeof(double), ctx->stream));
+    }
+    if (normal) {
+        YFD_TRY(t_ad.alloc(ctx, (size_t) n, 2)); YFD_TRY(atb.alloc(ctx, (size_t) n, 2));
+        const double *bb = d_b;
+        if (ax0) {
+            YFD_LAUNCH(ctx, cg_b_minus_y, vg, CG_THREADS, 0, d_b, ax0, t_ad.p, n);
+            bb = t_ad.p;
         }
-        YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, (const double *) nullptr, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
-        if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
-        YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap, sc2);
-        if (peer) YFD_TRY(halo_exchange(ctx, *pl, op.bs, r.p, sendbuf.p));      /* halo copies of r0, fetched once */
-        if (block) {                                      /* z0 = iM r0 (owned + halo copies), d0 = z0, rho = r0.z0 */
-            YFD_TRY(apply_block());
-            YFD_LAUNCH(ctx, cg_block_init, vec_grid(ctx, n + nh), CG_THREADS, 0, dv, (const double *) z.p, n + nh, sc.p, (const cg_scalars *) sc2);
-        } else if (peer && nh > 0) {                      /* z0 and d0 of the halo copies */
-            YFD_LAUNCH(ctx, cg_init_halo, (unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0,
-                       (const double *) r.p, z.p, dv, d_pc, n, nh);
-        }
+        YFD_TRY(launch_spmv<false>(ctx, *opT, bb, atb.p, sc.p, partials.p));
+        d_b = atb.p;
+        ax0 = nullptr;
+    }
+    YFD_LAUNCH(ctx, cg_init, vg, CG_THREADS, 0, d_b, ax0, d_pc, r.p, z.p, dv, n, sc.p, partials.p, hist.p, hcap);
+    if (pl && !peer) YFD_TRY(comm_allreduce_sum_f64(ctx, &sc.p->rr_new, 2));
+    YFD_LAUNCH(ctx, cg_init_finish, 1, 1, 0, sc.p, hist.p, hcap, sc2);
+    if (peer) YFD_TRY(halo_exchange(ctx, *pl, op.bs, r.p, sendbuf.p));      /* halo copies of r0, fetched once */
+    if (block) {                                      /* z0 = iM r0 (owned + halo copies), d0 = z0, rho = r0.z0 */
+        YFD_TRY(apply_block());
+        YFD_LAUNCH(ctx, cg_block_init, vec_grid(ctx, n + nh), CG_THREADS, 0, dv, (const double *) z.p, n + nh, sc.p, (const cg_scalars *) sc2);
+    } else if (peer && nh > 0) {                      /* z0 and d0 of the halo copies */
+        YFD_LAUNCH(ctx, cg_init_halo, (unsigned) std::min<int64_t>(ceil_div(nh, 256), ctx->sm_count), 256, 0,
+                   (const double *) r.p, z.p, dv, d_pc, n, nh);
     }
 
     /* YFD_CG_TRACE=1: time 200 iterations kernel by kernel with CUDA events (no graph) and print the averages; the
@@ -733,14 +742,14 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     const bool pmg_pc = use_pc == YFD_PC_PMG;
     if (pmg_pc) {
         if (method == SOLVER_BICGSTAB) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab takes the diagonal preconditioner only");
-        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner");
+        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a block preconditioner (defined for A, not A^T A)");
         if (!system_uses_classes(sys)) return fail(ctx, YFD_ERR_UNSUPPORTED, "the p-multigrid preconditioner needs the congruence-class operator cache in use");
         YFD_TRY(ensure_pmg(ctx, sys));
         use_pc = 0;
     }
     if (block_pc) {
         if (method == SOLVER_BICGSTAB) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab takes the diagonal preconditioner only");
-        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a preconditioner");
+        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns with a block preconditioner (defined for A, not A^T A)");
         YFD_TRY(ensure_block_jacobi(ctx, sys));
         use_pc = 0;
     }
@@ -749,11 +758,16 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     if (!dg) YFD_TRY(csr_prepare(ctx, &sys->A));
     const int64_t nloc = dg ? sys->n_local : n;
     dbuf<double> dx, tmp;
-    YFD_TRY(dx.alloc(ctx, (size_t) nloc, 2));
+    if (!(p->use_initial_guess && sys->plan)) YFD_TRY(dx.alloc(ctx, (size_t) nloc, 2));
     if (p->use_initial_guess) {
         if (!x_host) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "use_initial_guess needs a host x");
-        if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_initial_guess on a distributed system");
-        if (dg) {
+        if (sys->plan) {
+            /* several ranks: every rank passes the full vector (as it receives the full solution); this rank keeps its rows
+             * and the halo cells' values, which the start-up product A x0 reads (core/solvers.hpp:91) */
+            YFD_TRY(tmp.alloc(ctx, (size_t) n));
+            YFD_TRY(tmp.upload(ctx, x_host, (size_t) n));
+            YFD_TRY(operand_from_ref(ctx, sys, tmp.p, dx));
+        } else if (dg) {
             YFD_TRY(tmp.alloc(ctx, (size_t) n));
             YFD_TRY(tmp.upload(ctx, x_host, (size_t) n));
             YFD_LAUNCH(ctx, permute_blocks, stream_grid(ctx, n), 256, 0, tmp.p, dx.p, sys->perm.p, sys->ncells, sys->bs);
@@ -763,7 +777,7 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
     }
     spmv_op opT;
     if (method == SOLVER_BICGSTAB) {
-        if (p->use_normal_eqns) return fail(ctx, YFD_ERR_UNSUPPORTED, "bicgstab with use_normal_eqns");
+        /* bicgstab_device: honoured nowhere -- ignored with iM as in the reference, refused without */
     } else if (p->use_normal_eqns) {
         if (!dg) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a CFEM system (symmetric): use yfd_cg_solve for a general CSR");
         if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "use_normal_eqns on a distributed system");
