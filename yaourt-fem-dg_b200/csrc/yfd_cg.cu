@@ -477,6 +477,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     YFD_CUDA(ctx, cudaMemcpyAsync(sc.p, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
     YFD_CUDA(ctx, cudaMemcpyAsync(sc.p + 1, &h0, sizeof(h0), cudaMemcpyHostToDevice, ctx->stream));
 
+    std::unique_ptr<nvtx_range> nr_phase(new nvtx_range("yfd: CG start-up"));
     gpu_timer timer;
     timer.start(ctx->stream);
     const unsigned vg = vec_grid(ctx, n);
@@ -543,6 +544,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     }
 
     /* one CUDA graph = `batch` iterations */
+    nr_phase.reset(new nvtx_range("yfd: CG iterations (graph replays)"));
     int batch = p->check_every > 0 ? p->check_every : (pmg_sys ? 4 : 64);       /* a V-cycle is ~100 launches: shorter graphs */
     if ((int64_t) batch > p->max_iter) batch = (int) std::max<int64_t>(p->max_iter, 1);
     cudaGraph_t graph = nullptr;

@@ -448,6 +448,7 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     int herr = 0;
 
     /* ---- sparsity pattern: block counts -> cellptr -> block lists -> rowptr / colidx ---- */
+    std::unique_ptr<nvtx_range> nr_struct(new nvtx_range("yfd: DG block structure"));     /* popped on any exit */
     t_struct.start(ctx->stream);
     YFD_TRY(derr.alloc(ctx, 1));
     YFD_TRY(derr.zero(ctx));
@@ -473,6 +474,7 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     t_struct.stop(ctx->stream);
     YFD_TRY(derr.download(ctx, &herr, 1));
     if (herr) return fail(ctx, YFD_ERR_UNSUPPORTED, "two faces of one cell lead to the same neighbour; use the triplet path");
+    nr_struct.reset();
 
     /* ---- values: the element kernel writes finished rows into the CSR ---- */
     a.slots = slots.p;
@@ -480,12 +482,13 @@ static yfd_status build_dg_system(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_dg_con
     a.rhs = sys->rhs.p;
     a.pc = cfg->build_preconditioner ? sys->pc.p : nullptr;
     t_elem.start(ctx->stream);
-    YFD_TRY(dispatch_cells<NV>(ctx, cfg->degree, a));
+    { nvtx_range nr("yfd: DG element kernel"); YFD_TRY(dispatch_cells<NV>(ctx, cfg->degree, a)); }
     t_elem.stop(ctx->stream);
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
     /* ---- congruence classes: SIP diffusion only (constant coefficients: the blocks depend on the cell's shape alone) ---- */
     if (a.physics == 0 && env_int("YFD_DG_CLASSES", 1) != 0) {
+        nvtx_range nr("yfd: congruence classes");
         gpu_timer t_cls;
         t_cls.start(ctx->stream);
         constexpr int KEY_BITS = 40;

@@ -6,6 +6,7 @@
  */
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <cstdint>
 #include <cstdio>
 #include <cstdarg>
@@ -158,6 +159,15 @@ struct dbuf {
         if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "sync after D2H: %s", cudaGetErrorString(e));
         return YFD_OK;
     }
+};
+
+/* NVTX range per phase (header-only NVTX 3: a no-op unless a profiler injects itself): nsys / ncu timelines show
+ * mesh -> structure -> elements -> classes -> CSR -> CG set-up -> CG iterations, per rank */
+struct nvtx_range {
+    explicit nvtx_range(const char *name) { nvtxRangePushA(name); }
+    ~nvtx_range() { nvtxRangePop(); }
+    nvtx_range(const nvtx_range &) = delete;
+    nvtx_range &operator=(const nvtx_range &) = delete;
 };
 
 struct scoped_device {

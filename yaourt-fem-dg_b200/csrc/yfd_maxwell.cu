@@ -614,6 +614,7 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     a.op = m->op.p; a.fc = m->fc.p; a.cs = m->cs.p; a.gM = m->gM.p; a.cell_pts = m->cell_pts.p; a.err = derr.p;
     gpu_timer tm;
     tm.start(ctx->stream);
+    nvtx_range nr_asm("yfd: Maxwell assemble");
     if (nc) YFD_TRY(dispatch_assemble(ctx, nv, cfg->degree, a));
     tm.stop(ctx->stream);
     int herr = 0;
@@ -800,6 +801,7 @@ yfd_status yfd_maxwell_timesteps(yfd_maxwell *m, int64_t nsteps, yfd_maxwell_ste
     if (!m || nsteps < 0) return YFD_ERR_INVALID_ARGUMENT;
     yfd_ctx *ctx = m->ctx;
     scoped_device dev(ctx->device);
+    nvtx_range nr_steps("yfd: Maxwell timesteps");
     gpu_timer tm;
     tm.start(ctx->stream);
     for (int64_t st = 0; st < nsteps; st++) {

@@ -242,6 +242,7 @@ yfd_status yfd_mesh_create(yfd_ctx *ctx, int cell_type, int64_t npoints, const d
 {
     if (!ctx || !out) return YFD_ERR_INVALID_ARGUMENT;
     *out = nullptr;
+    yfd::nvtx_range nr_mesh("yfd: mesh upload + connectivity + Z-curve order");
     if (cell_type != YFD_CELL_TRIANGLE && cell_type != YFD_CELL_QUADRANGLE)
         return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "unknown cell type %d", cell_type);
     if (npoints < 0 || ncells < 0 || nfaces < 0 || (npoints && !points) || (ncells && !cells) || (nfaces && (!faces || !face_boundary)))

@@ -384,6 +384,7 @@ static yfd_status estimate_lmax(yfd_ctx *ctx, const yfd_system *sys, pmg_level &
 yfd_status ensure_pmg(yfd_ctx *ctx, yfd_system *sys)
 {
     if (sys->pmg) return YFD_OK;
+    nvtx_range nr_setup("yfd: p-multigrid set-up");
     if (sys->kind != YFD_SYS_DG || !sys->symmetric) return fail(ctx, YFD_ERR_UNSUPPORTED, "the p-multigrid preconditioner is defined for the symmetric DG-SIP systems");
     if (sys->plan) return fail(ctx, YFD_ERR_UNSUPPORTED, "the p-multigrid preconditioner runs on one GPU (DESIGN.md section 6)");
     if (!sys->classes.ready) return fail(ctx, YFD_ERR_UNSUPPORTED, "the p-multigrid preconditioner needs the congruence-class operator cache (this system: reason %d)", sys->classes.reject);

@@ -108,6 +108,7 @@ static inline unsigned stream_grid(yfd_ctx *ctx, int64_t n)
 static yfd_status build_from_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t count,
                                       const int64_t *rows, const int64_t *cols, const double *vals, yfd_csr *A)
 {
+    nvtx_range nr_csr("yfd: triplets -> CSR (radix sort + segmented fold)");
     A->ctx = ctx; A->nrows = nrows; A->ncols = ncols; A->nnz = 0;
     YFD_TRY(A->rowptr.alloc(ctx, (size_t) nrows + 1, 2));
     if (count == 0) {
