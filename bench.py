@@ -653,11 +653,17 @@ def main():
     d_x = torch.empty(n if world == 1 else 1, dtype=torch.float64, device="cuda")
     info = {}
 
+    x_shot = np.empty(n, np.float64) if (args.single_shot and world > 1) else None
+    kept = []
+
     def step_resident():
         t0 = time.perf_counter()
         sysm = assemble(mesh)
         t1 = time.perf_counter()
-        res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr() if world == 1 else None)
+        if x_shot is not None:          # --single-shot on several ranks: the gathered host solution feeds the anchors below
+            res = sysm.solve_cg_into(params, x_shot, use_pc=wl["pc"])
+        else:
+            res = sysm.solve_cg_device(params, use_pc=wl["pc"], d_x=d_x.data_ptr() if world == 1 else None)
         info.update(host_ms_assemble=1e3 * (t1 - t0), host_ms_solve=1e3 * (time.perf_counter() - t1))
         info.update(res, nnz=sysm.nnz, n=sysm.n, ms_elements=sysm.info.ms_elements, ms_structure=sysm.info.ms_structure)
         info.update(sysm.local_sizes())
@@ -674,7 +680,11 @@ def main():
     l0 = ctx.launches
     e0.record(stream)
     for _ in range(args.steps):
-        step_resident().close()
+        sy = step_resident()
+        if args.single_shot:
+            kept.append(sy)             # a solve that takes minutes is not repeated for the roofline leg
+        else:
+            sy.close()
     e1.record(stream)
     barrier()
     clocks = sampler.stop()
@@ -684,12 +694,17 @@ def main():
     value = n / (ms_step * 1e-3)
 
     # ---------------- roofline leg: the CG SpMV, CUDA events on the launching stream ----------------
-    sysm = step_resident()
+    sysm = kept.pop() if kept else step_resident()
     # correctness anchors of the solution just produced (after the timed region, never inside it): the TRUE residual
     # ||b - A x|| / ||b|| through an independent one-thread-per-row kernel (yfd_system_true_residual; the solver itself
     # stops on the recurrence residual, core/solvers.hpp:99,124) and the driver's L2 error against the analytic
     # solution (dg2d_diffusion.cpp:225-268, yfd_dg_postprocess)
     anchors = {}
+    if x_shot is not None:
+        anchors["true_residual"] = sysm.true_residual(x=x_shot)
+        if not cfem:
+            qp, mm = ctx.dg_postprocess(mesh, k, x_shot)
+            anchors["l2_error"], anchors["l2_error_projection"] = float(np.sqrt(qp)), float(np.sqrt(mm))
     if world == 1:
         anchors["true_residual"] = sysm.true_residual(d_x=d_x.data_ptr())
         if not cfem:
