@@ -742,6 +742,7 @@ def main():
                         "time: what a CSR kernel would have to sustain to be as fast (can exceed the peak)"}
     flops_spmv = 2.0 * info["nnz"]
     roofline["fp64"] = {"achieved_tflops": flops_spmv / (sp["ms"] * 1e-3) / 1e12, "peak_tflops": fp64_peak,
+                        "tensor_peak_tflops": ctx.measure_fp64_tensor(),
                         "frac": flops_spmv / (sp["ms"] * 1e-3) / 1e12 / fp64_peak,
                         "peak_source": "DFMA microbenchmark run just now on this device (yfd_ctx_measure_fp64)"}
     if oi is not None:

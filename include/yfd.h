@@ -74,6 +74,9 @@ yfd_status  yfd_ctx_device_info(const yfd_ctx *ctx, char *name, size_t cap, int 
 /* FP64 FMA throughput of the device, measured now (16 independent DFMA chains per thread, 8 x 256 threads per SM, best of
  * 5 launches, CUDA events): the denominator for the compute fraction of the element kernels and of the class SpMV */
 yfd_status  yfd_ctx_measure_fp64(yfd_ctx *ctx, double *tflops);
+/* the same for the FP64 TENSOR cores (mma.sync m8n8k4 f64 = DMMA.8x8x4, 8 independent accumulator chains per warp): the
+ * evidence north_star asks for before any DMMA path ("only if ncu shows a win over FP64 FMA") */
+yfd_status  yfd_ctx_measure_fp64_tensor(yfd_ctx *ctx, double *tflops);
 
 /* Multi-GPU: attach an NCCL communicator (one rank per context).  `unique_id` is the
  * 128-byte ncclUniqueId made by rank 0 (yfd_comm_unique_id) and shipped by the host

@@ -140,6 +140,7 @@ def lib():
         "yfd_ctx_trim": (cint, [vp, P(C.c_size_t)]),
         "yfd_ctx_device_info": (cint, [vp, C.c_char_p, C.c_size_t, P(cint), P(cint), P(cint)]),
         "yfd_ctx_measure_fp64": (cint, [vp, P(dbl)]),
+        "yfd_ctx_measure_fp64_tensor": (cint, [vp, P(dbl)]),
         "yfd_comm_unique_id": (cint, [C.c_char_p]),
         "yfd_ctx_attach_comm": (cint, [vp, cint, cint, C.c_char_p]),
         "yfd_ctx_rank": (cint, [vp]),
@@ -280,6 +281,12 @@ class Context:
         """FP64 FMA peak of this device in TFLOP/s (DFMA microbenchmark, yfd_ctx_measure_fp64)."""
         t = C.c_double()
         self.check(lib().yfd_ctx_measure_fp64(self._h, C.byref(t)))
+        return t.value
+
+    def measure_fp64_tensor(self):
+        """FP64 tensor-core (DMMA m8n8k4) peak of this device in TFLOP/s (yfd_ctx_measure_fp64_tensor)."""
+        t = C.c_double()
+        self.check(lib().yfd_ctx_measure_fp64_tensor(self._h, C.byref(t)))
         return t.value
 
     # ---- multi-GPU ------------------------------------------------------------------

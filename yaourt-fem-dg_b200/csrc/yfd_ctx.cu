@@ -73,6 +73,26 @@ __global__ void __launch_bounds__(256) dfma_peak(int iters, double m, double *__
     for (int k = 0; k < 16; k++) s += a[k];
     if (s == 12345.678) sink[0] = s;          /* never true: keeps the chains alive */
 }
+
+/* FP64 TENSOR-core peak (north_star: "FP64 tensor cores are used only if ncu shows a win over FP64 FMA"): 8 independent
+ * mma.sync m8n8k4 f64 accumulator chains per warp (SASS: DMMA.8x8x4), 256 multiply-adds per instruction per warp */
+__global__ void __launch_bounds__(256) dmma_peak(int iters, double m, double *__restrict__ sink)
+{
+    double c[8][2];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { c[k][0] = 1e-9 * (threadIdx.x + k); c[k][1] = 2e-9 * (threadIdx.x + k); }
+    const double a = m, b = 1.0 / 4.0;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[k][0]), "+d"(c[k][1]) : "d"(a), "d"(b));
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += c[k][0] + c[k][1];
+    if (s == 12345.678) sink[0] = s;
+}
 }
 
 extern "C" {
@@ -194,6 +214,30 @@ yfd_status yfd_ctx_measure_fp64(yfd_ctx *ctx, double *tflops)
         YFD_LAUNCH(ctx, yfd::dfma_peak, grid, 256, 0, iters, 1.000000001, sink.p);
         t.stop(ctx->stream);
         const double flops = 2.0 * 16.0 * (double) iters * 256.0 * (double) grid;
+        const double tf = flops / (t.ms() * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    *tflops = best;
+    return YFD_OK;
+}
+
+yfd_status yfd_ctx_measure_fp64_tensor(yfd_ctx *ctx, double *tflops)
+{
+    using namespace yfd;
+    if (!ctx || !tflops) return YFD_ERR_INVALID_ARGUMENT;
+    scoped_device dev(ctx->device);
+    dbuf<double> sink;
+    YFD_TRY(sink.alloc(ctx, 1));
+    const int iters = 4096, grid = ctx->sm_count * 8;
+    YFD_LAUNCH(ctx, yfd::dmma_peak, grid, 256, 0, iters, 1.000000001, sink.p);
+    gpu_timer t;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        t.start(ctx->stream);
+        YFD_LAUNCH(ctx, yfd::dmma_peak, grid, 256, 0, iters, 1.000000001, sink.p);
+        t.stop(ctx->stream);
+        /* per warp and iteration: 8 instructions x (8 x 8 x 4) multiply-adds */
+        const double flops = 2.0 * 8.0 * 256.0 * (double) iters * 8.0 /* warps per CTA */ * (double) grid;
         const double tf = flops / (t.ms() * 1e-3) / 1e12;
         if (tf > best) best = tf;
     }
