@@ -396,7 +396,7 @@ yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double 
 typedef struct yfd_operator_info {
     int     uses_classes;         /* what the next solve / apply will do                              */
     int     classes_available;
-    int     reject_reason;        /* 0 none; 1 too many classes for shared memory; 2 too many small classes; 3 deviation > tolerance */
+    int     reject_reason;        /* 0 none; 1 too many classes (> 4096, or tables beyond 8 MB); 2 too many small classes; 3 deviation > tolerance */
     int64_t nclasses;
     double  max_deviation;        /* max over cells of |W_cell - W_class|_max / |W_class|_max          */
     double  tolerance;

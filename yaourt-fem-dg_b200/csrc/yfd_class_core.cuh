@@ -40,20 +40,6 @@ __device__ __forceinline__ void load_vec(const double *__restrict__ p, double (&
     }
 }
 
-/* acc += W v with W read through the read-only path from GLOBAL memory (same address in every lane: one request) */
-template <int BS>
-__device__ __forceinline__ void block_times_ldg(const double *__restrict__ W, const double (&v)[BS], double (&acc)[BS])
-{
-    constexpr int BS2 = BS * BS;
-#pragma unroll
-    for (int m = 0; m + 1 < BS2; m += 2) {
-        const double2 w = __ldg(reinterpret_cast<const double2 *>(W + m));
-        acc[m % BS] = fma(w.x, v[m / BS], acc[m % BS]);
-        acc[(m + 1) % BS] = fma(w.y, v[(m + 1) / BS], acc[(m + 1) % BS]);
-    }
-    if (BS2 & 1) acc[BS - 1] = fma(__ldg(W + BS2 - 1), v[BS - 1], acc[BS - 1]);
-}
-
 template <int BS>
 __device__ __forceinline__ void store_cell(double *__restrict__ y, int32_t cell, const double (&v)[BS])
 {
@@ -67,23 +53,31 @@ __device__ __forceinline__ void store_cell(double *__restrict__ y, int32_t cell,
     }
 }
 
-/* acc += W v for one bs x bs block W[j][i] (column j contiguous in i) in shared memory; every lane reads the same
- * addresses, so each LDS.128 is one broadcast wavefront feeding two DFMA per lane */
-template <int BS>
+/* acc += W v for one bs x bs block W[j][i] (column j contiguous in i); every lane reads the same addresses.  GLOBAL = false:
+ * the table sits in shared memory, each LDS.128 is one broadcast wavefront feeding two DFMA per lane.  GLOBAL = true: the
+ * table is too large for shared memory (many small classes, e.g. the 28-40 classes of the reference's triangle meshes at
+ * k = 4) and is read through the read-only path instead -- one request per instruction, the bulk classes stay in L1 */
+template <int BS, bool GLOBAL = false>
 __device__ __forceinline__ void block_times(const double *__restrict__ W, const double (&v)[BS], double (&acc)[BS])
 {
     constexpr int BS2 = BS * BS;
 #pragma unroll
     for (int m = 0; m + 1 < BS2; m += 2) {
-        const double2 w = *reinterpret_cast<const double2 *>(W + m);
+        const double2 w = GLOBAL ? __ldg(reinterpret_cast<const double2 *>(W + m)) : *reinterpret_cast<const double2 *>(W + m);
         acc[m % BS] = fma(w.x, v[m / BS], acc[m % BS]);
         acc[(m + 1) % BS] = fma(w.y, v[(m + 1) / BS], acc[(m + 1) % BS]);
     }
-    if (BS2 & 1) acc[BS - 1] = fma(W[BS2 - 1], v[BS - 1], acc[BS - 1]);
+    if (BS2 & 1) acc[BS - 1] = fma(GLOBAL ? __ldg(W + BS2 - 1) : W[BS2 - 1], v[BS - 1], acc[BS - 1]);
+}
+
+template <int BS>
+__device__ __forceinline__ void block_times_ldg(const double *__restrict__ W, const double (&v)[BS], double (&acc)[BS])
+{
+    block_times<BS, true>(W, v, acc);
 }
 
 /* acc = (A x)_c for the cell at list position `pos`: slot 0 = the cell itself, slot 1+e = the neighbour across local face e */
-template <int BS, int NB>
+template <int BS, int NB, bool GLOBAL = false>
 __device__ __forceinline__ void class_row_product(const double *__restrict__ Wk, const double *__restrict__ x, int32_t c, int64_t pos,
                                                   const int32_t *__restrict__ work_nbr, int64_t npos, double (&acc)[BS])
 {
@@ -95,7 +89,7 @@ __device__ __forceinline__ void class_row_product(const double *__restrict__ Wk,
         const int32_t nb = s == 0 ? c : __ldg(&work_nbr[(int64_t) (s - 1) * npos + pos]);
         double xv[BS];
         load_cell<BS>(x, nb, xv);
-        block_times<BS>(Wk + s * SS, xv, acc);
+        block_times<BS, GLOBAL>(Wk + s * SS, xv, acc);
     }
 }
 

@@ -294,7 +294,7 @@ namespace yfd {
 /* congruence-class operator cache of a DG system (yfd_spmv_class.cu): one block row per class instead of one per cell */
 struct dg_classes {
     bool     ready = false;           /* the solvers use the cache                                                    */
-    int      reject = 0;              /* why not: 1 = table does not fit shared memory / too many classes, 2 = too much
+    int      reject = 0;              /* why not: 1 = too many classes (> 4096 or tables beyond 8 MB), 2 = too much
                                          padding (many small classes), 3 = a block row deviates from its class by > tol */
     int      ncls = 0;
     int      table_doubles = 0;

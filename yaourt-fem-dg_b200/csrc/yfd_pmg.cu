@@ -77,7 +77,7 @@ __global__ void pmg_build_tables(const double *__restrict__ full, int bs, int bl
 }
 
 /* ---- one Chebyshev-block-Jacobi sweep --------------------------------------------------------- */
-template <int BS, int NB>
+template <int BS, int NB, bool GLOBAL>
 __global__ void __launch_bounds__(CLS_THREADS, 2)
 pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ tabD, int nD,
           const int32_t *__restrict__ work_cell, const int32_t *__restrict__ work_nbr, const int32_t *__restrict__ tile_cls,
@@ -86,12 +86,15 @@ pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ ta
           const cg_scalars *__restrict__ gate)
 {
     if (gate && gate->done) return;
-    extern __shared__ __align__(16) double T[];
+    extern __shared__ __align__(16) double Tsm[];
     constexpr int SS = cls_slot_stride(BS);
-    double *TD = T + nA;
-    for (int i = threadIdx.x; i < nA; i += blockDim.x) T[i] = tabA[i];
-    for (int i = threadIdx.x; i < nD; i += blockDim.x) TD[i] = tabD[i];
-    __syncthreads();
+    const double *T = tabA, *TD = tabD;         /* GLOBAL: tables too large for shared memory, read through L1 / L2 */
+    if (!GLOBAL) {
+        for (int i = threadIdx.x; i < nA; i += blockDim.x) Tsm[i] = tabA[i];
+        for (int i = threadIdx.x; i < nD; i += blockDim.x) Tsm[nA + i] = tabD[i];
+        __syncthreads();
+        T = Tsm; TD = Tsm + nA;
+    }
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
     for (int64_t tile = gw; tile < ntiles; tile += nw) {
@@ -101,7 +104,7 @@ pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ ta
         if (c < 0) continue;
         double r[BS], xs[BS];
         if (x_in) {
-            class_row_product<BS, NB>(T + (size_t) k * (NB * SS), x_in, c, pos, work_nbr, npos, r);
+            class_row_product<BS, NB, GLOBAL>(T + (size_t) k * (NB * SS), x_in, c, pos, work_nbr, npos, r);
             load_cell<BS>(x_in, c, xs);
         } else {
 #pragma unroll
@@ -119,7 +122,7 @@ pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ ta
         double t[BS];
 #pragma unroll
         for (int i = 0; i < BS; i++) t[i] = 0.0;
-        block_times<BS>(TD + (size_t) k * SS, r, t);
+        block_times<BS, GLOBAL>(TD + (size_t) k * SS, r, t);
         if (c1 != 0.0) {
             double dv[BS];
             load_cell<BS>(d, c, dv);
@@ -137,17 +140,21 @@ pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ ta
 }
 
 /* residual of level BS restricted to level BC: out_c = (b - A x)_c[0 .. BC) */
-template <int BS, int BC, int NB>
+template <int BS, int BC, int NB, bool GLOBAL>
 __global__ void __launch_bounds__(CLS_THREADS, 2)
 pmg_residual_restrict(const double *__restrict__ tabA, int nA, const int32_t *__restrict__ work_cell, const int32_t *__restrict__ work_nbr,
                       const int32_t *__restrict__ tile_cls, int64_t ntiles, int64_t npos, const double *__restrict__ x,
                       const double *__restrict__ b, double *__restrict__ out, const cg_scalars *__restrict__ gate)
 {
     if (gate && gate->done) return;
-    extern __shared__ __align__(16) double T[];
+    extern __shared__ __align__(16) double Tsm[];
     constexpr int SS = cls_slot_stride(BS);
-    for (int i = threadIdx.x; i < nA; i += blockDim.x) T[i] = tabA[i];
-    __syncthreads();
+    const double *T = tabA;
+    if (!GLOBAL) {
+        for (int i = threadIdx.x; i < nA; i += blockDim.x) Tsm[i] = tabA[i];
+        __syncthreads();
+        T = Tsm;
+    }
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
     for (int64_t tile = gw; tile < ntiles; tile += nw) {
@@ -156,7 +163,7 @@ pmg_residual_restrict(const double *__restrict__ tabA, int nA, const int32_t *__
         const int32_t c = __ldg(&work_cell[pos]);
         if (c < 0) continue;
         double r[BS], bv[BS];
-        class_row_product<BS, NB>(T + (size_t) k * (NB * SS), x, c, pos, work_nbr, npos, r);
+        class_row_product<BS, NB, GLOBAL>(T + (size_t) k * (NB * SS), x, c, pos, work_nbr, npos, r);
         load_cell<BS>(b, c, bv);
         double o[BC];
 #pragma unroll
@@ -235,8 +242,9 @@ template <int BS, int NB>
 static yfd_status sweep_t(yfd_ctx *ctx, const pmg_level &L, const pmg_lists &w, const double *x_in, double *d, const double *b, double *x_out,
                           double c1, double c2, const cg_scalars *gate)
 {
-    auto kern = pmg_sweep<BS, NB>;
-    const size_t smem = (size_t) (L.nA + L.nD) * sizeof(double);
+    const bool global = (size_t) (L.nA + L.nD) * sizeof(double) + 1024 > ctx->smem_optin;
+    auto kern = global ? pmg_sweep<BS, NB, true> : pmg_sweep<BS, NB, false>;
+    const size_t smem = global ? 0 : (size_t) (L.nA + L.nD) * sizeof(double);
     if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     YFD_LAUNCH(ctx, kern, pmg_grid(ctx, w.ntiles, smem), CLS_THREADS, smem, (const double *) L.tabA.p, L.nA, (const double *) L.tabD.p, L.nD,
                w.work_cell, w.work_nbr, w.tile_cls, w.ntiles, w.npos, x_in, d, b, x_out, c1, c2, gate);
@@ -256,8 +264,9 @@ static yfd_status launch_sweep(yfd_ctx *ctx, int nf, const pmg_level &L, const p
 template <int BS, int BC, int NB>
 static yfd_status restrict_t(yfd_ctx *ctx, const pmg_level &L, const pmg_lists &w, const double *x, const double *b, double *out, const cg_scalars *gate)
 {
-    auto kern = pmg_residual_restrict<BS, BC, NB>;
-    const size_t smem = (size_t) L.nA * sizeof(double);
+    const bool global = (size_t) L.nA * sizeof(double) + 1024 > ctx->smem_optin;
+    auto kern = global ? pmg_residual_restrict<BS, BC, NB, true> : pmg_residual_restrict<BS, BC, NB, false>;
+    const size_t smem = global ? 0 : (size_t) L.nA * sizeof(double);
     if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     YFD_LAUNCH(ctx, kern, pmg_grid(ctx, w.ntiles, smem), CLS_THREADS, smem, (const double *) L.tabA.p, L.nA, w.work_cell, w.work_nbr, w.tile_cls,
                w.ntiles, w.npos, x, b, out, gate);
@@ -412,7 +421,6 @@ yfd_status ensure_pmg(yfd_ctx *ctx, yfd_system *sys)
         L.k = k - l; L.bs = basis_size_2d(L.k);
         const int ssl = cls_slot_stride(L.bs);
         L.nA = ncls * nb * ssl; L.nD = ncls * ssl;
-        if ((size_t) (L.nA + L.nD) * 8 + 1024 > ctx->smem_optin) return fail(ctx, YFD_ERR_UNSUPPORTED, "p-multigrid: class tables of level %d do not fit shared memory", L.k);
         YFD_TRY(L.tabA.alloc(ctx, (size_t) L.nA, 2)); YFD_TRY(L.tabD.alloc(ctx, (size_t) L.nD, 2));
         YFD_LAUNCH(ctx, pmg_build_tables, (unsigned) ncls, 64, 0, (const double *) cl.table.p, sys->bs, L.bs, nb, L.tabA.p, L.tabD.p, derr.p);
         const size_t n = (size_t) sys->ncells * L.bs;

@@ -222,7 +222,8 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
     const int bs = sys->bs, nf = sys->nf, nb = nf + 1, ss = cls_slot_stride(bs);
     if (nc < 1 || (bs != 1 && bs != 3 && bs != 6 && bs != 10 && bs != 15)) return YFD_OK;
     class_groups g;
-    YFD_TRY(group_cells_by_key(ctx, nc, d_keys, key_bits, (size_t) nb * ss * sizeof(double), ctx->smem_optin - 1024, g));
+    /* tables beyond shared memory are read from global memory (L1 / L2 hits): 8 MB keeps them far inside the 126 MB L2 */
+    YFD_TRY(group_cells_by_key(ctx, nc, d_keys, key_bits, (size_t) nb * ss * sizeof(double), (size_t) 8 << 20, g));
     cl.ncls = (int) std::min<int64_t>(g.ncls, 0x7fffffff);
     if (g.reject) { cl.reject = g.reject; return YFD_OK; }
     const int64_t ncls = g.ncls, npos = g.npos;
@@ -251,17 +252,21 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
 }
 
 /* ---- the kernel ------------------------------------------------------------------------------ */
-template <int BS, int NB, bool WITH_DOT>
+template <int BS, int NB, bool WITH_DOT, bool GLOBAL>
 __global__ void __launch_bounds__(CLS_THREADS, 2)
 dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t *__restrict__ work_cell,
               const int32_t *__restrict__ work_nbr, const int32_t *__restrict__ tile_cls, int64_t ntiles, int64_t npos,
               const double *__restrict__ x, double *__restrict__ y, cg_scalars *__restrict__ sc, double *__restrict__ partials)
 {
     if (WITH_DOT && sc->done) return;
-    extern __shared__ __align__(16) double T[];
+    extern __shared__ __align__(16) double Tsm[];
     constexpr int SS = cls_slot_stride(BS);
-    for (int i = threadIdx.x; i < table_doubles; i += blockDim.x) T[i] = table[i];
-    __syncthreads();
+    const double *T = table;                    /* GLOBAL: too many classes for shared memory, read through L1 / L2 */
+    if (!GLOBAL) {
+        for (int i = threadIdx.x; i < table_doubles; i += blockDim.x) Tsm[i] = table[i];
+        __syncthreads();
+        T = Tsm;
+    }
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
     double dot = 0.0;
@@ -272,7 +277,7 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
         if (c < 0) continue;                                   /* padding at the end of a class */
         const double *Wk = T + (size_t) k * (NB * SS);
         double acc[BS];
-        class_row_product<BS, NB>(Wk, x, c, pos, work_nbr, npos, acc);
+        class_row_product<BS, NB, GLOBAL>(Wk, x, c, pos, work_nbr, npos, acc);
         store_cell<BS>(y, c, acc);
         if (WITH_DOT) {
             double xs[BS];
@@ -291,8 +296,9 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
 template <int BS, int NB, bool WITH_DOT>
 static yfd_status launch_cls(yfd_ctx *ctx, const dg_classes &cl, const double *x, double *y, cg_scalars *sc, double *partials)
 {
-    auto kern = dg_spmv_class<BS, NB, WITH_DOT>;
-    const size_t smem = (size_t) cl.table_doubles * sizeof(double);
+    const bool global = (size_t) cl.table_doubles * sizeof(double) + 1024 > ctx->smem_optin;
+    auto kern = global ? dg_spmv_class<BS, NB, WITH_DOT, true> : dg_spmv_class<BS, NB, WITH_DOT, false>;
+    const size_t smem = global ? 0 : (size_t) cl.table_doubles * sizeof(double);
     if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = smem * 2 + 4096 <= ctx->smem_per_sm ? 2 : 1;
     int64_t grid = (int64_t) ctx->sm_count * per_sm;
