@@ -40,12 +40,17 @@ def test_hot_kernels_do_not_spill(usage):
     # the instantiations bench.py measures: DG block SpMV bs = 10 (quad k=3) and 6 / 15 (tri k=2 / k=4), the CSR SpMV of the
     # continuous-FEM systems, the Maxwell stage kernel tri k=4 / quad k=3, and the CG vector kernels
     for parts in (("dg_spmv_tma", "ILi10E"), ("dg_spmv_tma", "ILi6E"), ("dg_spmv_tma", "ILi15E"), ("csr_spmv_tma",),
-                  ("maxwell_stage", "ILi3ELi4E"), ("maxwell_stage", "ILi4ELi3E"), ("cg_update_xr",), ("cg_update_d",)):
+                  ("13maxwell_stageI", "ILi3ELi4E"), ("13maxwell_stageI", "ILi4ELi3E"), ("cg_update_xr",), ("cg_update_d",),
+                  ("dg_spmv_class", "ILi10E"), ("dg_spmv_class", "ILi6E"), ("pmg_sweep", "ILi10E"), ("pmg_sweep", "ILi6E"), ("pmg_sweep", "ILi3E")):
         for name, u in find(usage, *parts).items():
             assert u["stack"] == 0 and u["local"] == 0, (name, u)
     # two CTAs per SM for the Maxwell stage kernel at the benchmarked degrees need <= 128 registers (256 threads)
-    for name, u in find(usage, "maxwell_stage", "ILi3ELi4E").items():
+    for name, u in find(usage, "13maxwell_stageI", "ILi3ELi4E").items():
         assert u["reg"] <= 128, (name, u)
+    # the class kernels run 2 CTAs of 256 threads per SM: <= 128 registers, at most a few spilled words at bs = 15
+    for parts in (("dg_spmv_class",), ("pmg_sweep",), ("maxwell_stage_class",)):
+        for name, u in find(usage, *parts).items():
+            assert u["reg"] <= 128 and u["stack"] <= 64, (name, u)
 
 
 def test_spmv_kernels_use_the_tma_engine():
@@ -57,5 +62,10 @@ def test_spmv_kernels_use_the_tma_engine():
         for b in blocks:
             assert "UBLKCP" in b and "SYNCS" in b, b.split("\n", 1)[0]
     # the Maxwell stage kernel prefetches its operator slab into L2 with one bulk request per chunk
-    blocks = [b for b in out.split("Function : ")[1:] if "maxwell_stage" in b.split("\n", 1)[0]]
+    blocks = [b for b in out.split("Function : ")[1:] if "13maxwell_stageI" in b.split("\n", 1)[0]]
     assert blocks and all("UBLKPF.L2" in b for b in blocks)          # cp.async.bulk.prefetch.L2
+    # the class kernels read their block entries as 128-bit shared-memory broadcasts: one LDS.128 per two DFMA
+    blocks = [b for b in out.split("Function : ")[1:] if "dg_spmv_classILi10ELi5ELb1ELb0" in b.split("\n", 1)[0]]
+    assert blocks
+    for b in blocks:
+        assert b.count("LDS.128") >= 250 and b.count("DFMA") >= 500 and "DMMA" not in b
