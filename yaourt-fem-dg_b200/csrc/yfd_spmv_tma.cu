@@ -160,18 +160,39 @@ dg_spmv_tma(const int64_t *__restrict__ cellptr, const int32_t *__restrict__ blk
         if (lane < nrows) {
             const int i = lane / BS, irow = lane - i * BS;
             const int cr = (int) (cur.CP[i] - cur.lo);
-            const int L = (int) (cur.CP[i + 1] - cur.CP[i]) * BS;
+            const int nblk = (int) (cur.CP[i + 1] - cur.CP[i]);
             const double *w = cur.V + (size_t) cr * BS2 + irow;
             const double *xr = xs + cr * BS;
+            /* one block per trip, the trip fully unrolled on the compile-time block size: no loop control, no index
+             * arithmetic inside, and (even block sizes) two x entries per 128-bit shared-memory load -- the instruction
+             * count per DFMA falls from ~4.8 to ~2.7 (every wasted instruction costs clock under the board's power cap) */
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            int l = 0;
-            for (; l + 3 < L; l += 4) {
-                a0 += w[(l) * BS] * xr[l];
-                a1 += w[(l + 1) * BS] * xr[l + 1];
-                a2 += w[(l + 2) * BS] * xr[l + 2];
-                a3 += w[(l + 3) * BS] * xr[l + 3];
+#pragma unroll 1
+            for (int b = 0; b < nblk; b++, w += BS2, xr += BS) {
+                if (BS % 2 == 0) {
+#pragma unroll
+                    for (int j = 0; j + 3 < BS; j += 4) {
+                        const double2 x01 = *reinterpret_cast<const double2 *>(xr + j), x23 = *reinterpret_cast<const double2 *>(xr + j + 2);
+                        a0 = fma(w[j * BS], x01.x, a0);
+                        a1 = fma(w[(j + 1) * BS], x01.y, a1);
+                        a2 = fma(w[(j + 2) * BS], x23.x, a2);
+                        a3 = fma(w[(j + 3) * BS], x23.y, a3);
+                    }
+                    if (BS % 4 != 0) {
+                        const double2 x01 = *reinterpret_cast<const double2 *>(xr + BS - 2);
+                        a0 = fma(w[(BS - 2) * BS], x01.x, a0);
+                        a1 = fma(w[(BS - 1) * BS], x01.y, a1);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BS; j++) {
+                        if ((j & 3) == 0) a0 = fma(w[j * BS], xr[j], a0);
+                        else if ((j & 3) == 1) a1 = fma(w[j * BS], xr[j], a1);
+                        else if ((j & 3) == 2) a2 = fma(w[j * BS], xr[j], a2);
+                        else a3 = fma(w[j * BS], xr[j], a3);
+                    }
+                }
             }
-            for (; l < L; l++) a0 += w[l * BS] * xr[l];
             const double acc = (a0 + a1) + (a2 + a3);
             const int64_t row = cur.c0 * BS + lane;
             y[row] = acc;
