@@ -182,59 +182,82 @@ __device__ __forceinline__ void mx_combo(const double *__restrict__ v /* [3][BS]
         for (int i = 0; i < BS; i++) w[i] = fma(sign * aez, t[i], w[i]); }
 }
 
-template <int NV, int K>
-__global__ void __launch_bounds__(CLS_THREADS, 2)
+template <int NV, int K, int C>
+__global__ void __launch_bounds__(CLS_THREADS, C == 1 ? 2 : 1)
 maxwell_stage_class(const mx_step_args a, const int mode)
 {
     constexpr int BS = mx_bs(K), NB = mx_nb(NV), SS = cls_slot_stride(BS), L = 3 * BS;
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    for (int64_t tile = gw; tile < a.ntiles; tile += nw) {
-        const int k = __ldg(&a.tile_cls[tile]);
-        const int32_t c = __ldg(&a.work_cell[tile * 32 + lane]);
-        if (c < 0) continue;
+    /* C cells per lane: every class-block entry fetched is used C times (yfd_class_core.cuh) */
+    const int64_t nunits = a.ntiles * (CLS_TILE / (32 * C));
+    for (int64_t u = gw; u < nunits; u += nw) {
+        const int k = __ldg(&a.tile_cls[(u * (32 * C)) / CLS_TILE]);
+        int32_t c[C];
+#pragma unroll
+        for (int q = 0; q < C; q++) c[q] = __ldg(&a.work_cell[u * (32 * C) + lane + 32 * q]);
+        if (c[0] < 0) continue;
+        bool live[C];
+#pragma unroll
+        for (int q = 0; q < C; q++) { live[q] = c[q] >= 0; if (!live[q]) c[q] = c[0]; }      /* padding: cell 0's operands, no sink */
         const double *Tk = a.table + (size_t) k * (NB * SS);
-        const double *vc = a.vin + (int64_t) c * L;
-        const double inv_mu = __ldg(&a.cs[2 * c]), inv_eps = __ldg(&a.cs[2 * c + 1]);
 #pragma unroll 1
         for (int fld = 0; fld < 3; fld++) {
-            double acc[BS], w[BS];
+            double acc[C][BS], w[C][BS];
 #pragma unroll
-            for (int i = 0; i < BS; i++) acc[i] = 0.0;
-            /* cell blocks: Gx = block 0, Gy = block 1 */
-            /* Hx: Gy (-Ez) ; Hy: Gx Ez ; Ez: Gx Hy + Gy (-Hx) */
-            mx_combo<BS>(vc, 0.0, fld == 2 ? 1.0 : 0.0, fld == 2 ? 0.0 : 1.0, fld == 0 ? -1.0 : 1.0, w);
-            block_times_ldg<BS>(Tk + (fld == 0 ? SS : 0), w, acc);
-            if (fld == 2) { mx_combo<BS>(vc, 1.0, 0.0, 0.0, -1.0, w); block_times_ldg<BS>(Tk + SS, w, acc); }
+            for (int q = 0; q < C; q++)
+#pragma unroll
+                for (int i = 0; i < BS; i++) acc[q][i] = 0.0;
+            /* cell blocks (Gx = block 0, Gy = block 1): Hx: Gy (-Ez) ; Hy: Gx Ez ; Ez: Gx Hy + Gy (-Hx) */
+#pragma unroll
+            for (int q = 0; q < C; q++)
+                mx_combo<BS>(a.vin + (int64_t) c[q] * L, 0.0, fld == 2 ? 1.0 : 0.0, fld == 2 ? 0.0 : 1.0, fld == 0 ? -1.0 : 1.0, w[q]);
+            block_times_n<BS, C, true>(Tk + (fld == 0 ? SS : 0), w, acc);
+            if (fld == 2) {
+#pragma unroll
+                for (int q = 0; q < C; q++) mx_combo<BS>(a.vin + (int64_t) c[q] * L, 1.0, 0.0, 0.0, -1.0, w[q]);
+                block_times_n<BS, C, true>(Tk + SS, w, acc);
+            }
 #pragma unroll 1
             for (int f = 0; f < NV; f++) {
-                const mx_face_coef q = a.fc[(int64_t) c * NV + f];
-                double ahx, ahy, aez;
-                if (fld == 0)      { aez = q.ny * q.cE;  ahx = -q.vH * q.ny * q.ny; ahy = q.vH * q.nx * q.ny; }
-                else if (fld == 1) { aez = -q.nx * q.cE; ahx = q.vH * q.nx * q.ny;  ahy = -q.vH * q.nx * q.nx; }
-                else               { ahx = q.cH * q.ny;  ahy = -q.cH * q.nx;        aez = -q.vE; }
-                mx_combo<BS>(vc, ahx, ahy, aez, 1.0, w);
-                block_times_ldg<BS>(Tk + (size_t) (2 + f) * SS, w, acc);
-                const int32_t nb = __ldg(&a.nbr[(int64_t) c * NV + f]);
-                if (nb >= 0) {
-                    mx_combo<BS>(a.vin + (int64_t) nb * L, ahx, ahy, aez, -1.0, w);
-                    block_times_ldg<BS>(Tk + (size_t) (2 + NV + f) * SS, w, acc);
+                double ahx[C], ahy[C], aez[C];
+#pragma unroll
+                for (int q = 0; q < C; q++) {
+                    const mx_face_coef fq = a.fc[(int64_t) c[q] * NV + f];
+                    if (fld == 0)      { aez[q] = fq.ny * fq.cE;  ahx[q] = -fq.vH * fq.ny * fq.ny; ahy[q] = fq.vH * fq.nx * fq.ny; }
+                    else if (fld == 1) { aez[q] = -fq.nx * fq.cE; ahx[q] = fq.vH * fq.nx * fq.ny;  ahy[q] = -fq.vH * fq.nx * fq.nx; }
+                    else               { ahx[q] = fq.cH * fq.ny;  ahy[q] = -fq.cH * fq.nx;         aez[q] = -fq.vE; }
+                    mx_combo<BS>(a.vin + (int64_t) c[q] * L, ahx[q], ahy[q], aez[q], 1.0, w[q]);
+                }
+                block_times_n<BS, C, true>(Tk + (size_t) (2 + f) * SS, w, acc);
+                /* whether face f has a neighbour is part of the class key: the same answer for every cell of the tile */
+                if (__ldg(&a.nbr[(int64_t) c[0] * NV + f]) >= 0) {
+#pragma unroll
+                    for (int q = 0; q < C; q++) {
+                        const int32_t nb = __ldg(&a.nbr[(int64_t) c[q] * NV + f]);
+                        mx_combo<BS>(a.vin + (int64_t) nb * L, ahx[q], ahy[q], aez[q], -1.0, w[q]);
+                    }
+                    block_times_n<BS, C, true>(Tk + (size_t) (2 + NV + f) * SS, w, acc);
                 }
             }
-            const double sc = fld == 2 ? inv_eps : inv_mu;
-            const int64_t base = (int64_t) c * L + fld * BS;
 #pragma unroll
-            for (int i = 0; i < BS; i++) {
-                const int64_t idx = base + i;
-                const double kk = sc * acc[i];
-                switch (mode) {
-                case MX_APPLY: a.out[idx] = kk; break;
-                case MX_RK1:   a.acc[idx] = kk; a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt / 2., kk)); break;
-                case MX_RK2:   a.kb[idx] = kk;  a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt / 2., kk)); break;
-                case MX_RK3:   a.acc[idx] = __dadd_rn(a.acc[idx], __dmul_rn(__dadd_rn(a.kb[idx], kk), 2.0));
-                               a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt, kk)); break;
-                case MX_RK4:   a.u[idx] = __dadd_rn(a.u[idx], __dmul_rn(__dadd_rn(a.acc[idx], kk), (1. / 6.) * a.dt)); break;
-                case MX_EULER: a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt, kk)); break;
+            for (int q = 0; q < C; q++) {
+                if (!live[q]) continue;
+                const double sc = fld == 2 ? __ldg(&a.cs[2 * c[q] + 1]) : __ldg(&a.cs[2 * c[q]]);
+                const int64_t base = (int64_t) c[q] * L + fld * BS;
+#pragma unroll
+                for (int i = 0; i < BS; i++) {
+                    const int64_t idx = base + i;
+                    const double kk = sc * acc[q][i];
+                    switch (mode) {
+                    case MX_APPLY: a.out[idx] = kk; break;
+                    case MX_RK1:   a.acc[idx] = kk; a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt / 2., kk)); break;
+                    case MX_RK2:   a.kb[idx] = kk;  a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt / 2., kk)); break;
+                    case MX_RK3:   a.acc[idx] = __dadd_rn(a.acc[idx], __dmul_rn(__dadd_rn(a.kb[idx], kk), 2.0));
+                                   a.out[idx] = __dadd_rn(a.u[idx], __dmul_rn(a.dt, kk)); break;
+                    case MX_RK4:   a.u[idx] = __dadd_rn(a.u[idx], __dmul_rn(__dadd_rn(a.acc[idx], kk), (1. / 6.) * a.dt)); break;
+                    case MX_EULER: a.out[idx] = __dadd_rn(__ldg(&a.vin[idx]), __dmul_rn(a.dt, kk)); break;
+                    }
                 }
             }
         }
@@ -327,10 +350,14 @@ yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys,
 template <int NV, int K>
 static yfd_status launch_stage_class(yfd_ctx *ctx, int mode, const mx_step_args &a)
 {
-    int64_t grid = (int64_t) ctx->sm_count * 2;
-    const int64_t want = ceil_div(a.ntiles, CLS_THREADS / 32);
+    /* two cells per lane (255 registers, one CTA per SM) unless YFD_MX_CLASS_CELLS=1 asks for the one-cell variant */
+    const int cells = env_int("YFD_MX_CLASS_CELLS", 2) == 1 ? 1 : 2;
+    int64_t grid = (int64_t) ctx->sm_count * (cells == 1 ? 2 : 1);
+    const int64_t want = ceil_div(a.ntiles * (CLS_TILE / (32 * cells)), CLS_THREADS / 32);
     if (grid > want) grid = want;
-    YFD_LAUNCH(ctx, (maxwell_stage_class<NV, K>), (unsigned) (grid < 1 ? 1 : grid), CLS_THREADS, 0, a, mode);
+    if (grid < 1) grid = 1;
+    if (cells == 1) YFD_LAUNCH(ctx, (maxwell_stage_class<NV, K, 1>), (unsigned) grid, CLS_THREADS, 0, a, mode);
+    else            YFD_LAUNCH(ctx, (maxwell_stage_class<NV, K, 2>), (unsigned) grid, CLS_THREADS, 0, a, mode);
     return YFD_OK;
 }
 

@@ -97,45 +97,65 @@ pmg_sweep(const double *__restrict__ tabA, int nA, const double *__restrict__ ta
     }
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    for (int64_t tile = gw; tile < ntiles; tile += nw) {
-        const int k = __ldg(&tile_cls[tile]);
-        const int64_t pos = tile * 32 + lane;
-        const int32_t c = __ldg(&work_cell[pos]);
-        if (c < 0) continue;
-        double r[BS], xs[BS];
+    /* C cells per lane (yfd_class_core.cuh: every block entry delivered by shared memory is used C times); one at bs = 15,
+     * where two cells' residual + correction would not fit 128 registers */
+    constexpr int C = BS <= 10 ? 2 : 1;
+    const int64_t nunits = ntiles * (CLS_TILE / (32 * C));
+    for (int64_t u = gw; u < nunits; u += nw) {
+        const int k = __ldg(&tile_cls[(u * (32 * C)) / CLS_TILE]);
+        const int64_t pos = u * (32 * C) + lane;
+        int32_t c[C];
+#pragma unroll
+        for (int q = 0; q < C; q++) c[q] = __ldg(&work_cell[pos + 32 * q]);
+        if (c[0] < 0) continue;
+        double r[C][BS];
         if (x_in) {
-            class_row_product<BS, NB, GLOBAL>(T + (size_t) k * (NB * SS), x_in, c, pos, work_nbr, npos, r);
-            load_cell<BS>(x_in, c, xs);
+            class_row_product_n<BS, NB, C, GLOBAL>(T + (size_t) k * (NB * SS), x_in, c, pos, work_nbr, npos, r);
         } else {
 #pragma unroll
-            for (int i = 0; i < BS; i++) { r[i] = 0.0; xs[i] = 0.0; }
+            for (int q = 0; q < C; q++)
+#pragma unroll
+                for (int i = 0; i < BS; i++) r[q][i] = 0.0;
         }
-        if (b) {
-            double bv[BS];
-            load_cell<BS>(b, c, bv);
 #pragma unroll
-            for (int i = 0; i < BS; i++) r[i] = bv[i] - r[i];
-        } else {
+        for (int q = 0; q < C; q++) {
+            if (b) {
+                double bv[BS];
+                load_cell<BS>(b, c[q] < 0 ? c[0] : c[q], bv);
 #pragma unroll
-            for (int i = 0; i < BS; i++) r[i] = -r[i];
+                for (int i = 0; i < BS; i++) r[q][i] = bv[i] - r[q][i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < BS; i++) r[q][i] = -r[q][i];
+            }
         }
-        double t[BS];
+        double t[C][BS];
 #pragma unroll
-        for (int i = 0; i < BS; i++) t[i] = 0.0;
-        block_times<BS, GLOBAL>(TD + (size_t) k * SS, r, t);
-        if (c1 != 0.0) {
-            double dv[BS];
-            load_cell<BS>(d, c, dv);
+        for (int q = 0; q < C; q++)
 #pragma unroll
-            for (int i = 0; i < BS; i++) t[i] = fma(c2, t[i], c1 * dv[i]);
-        } else {
+            for (int i = 0; i < BS; i++) t[q][i] = 0.0;
+        block_times_n<BS, C, GLOBAL>(TD + (size_t) k * SS, r, t);
 #pragma unroll
-            for (int i = 0; i < BS; i++) t[i] = c2 * t[i];
+        for (int q = 0; q < C; q++) {
+            if (c[q] < 0) continue;
+            if (c1 != 0.0) {
+                double dv[BS];
+                load_cell<BS>(d, c[q], dv);
+#pragma unroll
+                for (int i = 0; i < BS; i++) t[q][i] = fma(c2, t[q][i], c1 * dv[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < BS; i++) t[q][i] = c2 * t[q][i];
+            }
+            store_cell<BS>(d, c[q], t[q]);
+            if (x_in) {
+                double xs[BS];
+                load_cell<BS>(x_in, c[q], xs);
+#pragma unroll
+                for (int i = 0; i < BS; i++) t[q][i] += xs[i];
+            }
+            store_cell<BS>(x_out, c[q], t[q]);
         }
-        store_cell<BS>(d, c, t);
-#pragma unroll
-        for (int i = 0; i < BS; i++) xs[i] += t[i];
-        store_cell<BS>(x_out, c, xs);
     }
 }
 
@@ -157,9 +177,9 @@ pmg_residual_restrict(const double *__restrict__ tabA, int nA, const int32_t *__
     }
     const int lane = threadIdx.x & 31;
     const int64_t gw = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((int64_t) gridDim.x * blockDim.x) >> 5;
-    for (int64_t tile = gw; tile < ntiles; tile += nw) {
-        const int k = __ldg(&tile_cls[tile]);
-        const int64_t pos = tile * 32 + lane;
+    for (int64_t ht = gw; ht < 2 * ntiles; ht += nw) {          /* half tiles: 32 list entries of one class */
+        const int k = __ldg(&tile_cls[ht >> 1]);
+        const int64_t pos = ht * 32 + lane;
         const int32_t c = __ldg(&work_cell[pos]);
         if (c < 0) continue;
         double r[BS], bv[BS];
@@ -233,7 +253,7 @@ static unsigned pmg_grid(yfd_ctx *ctx, int64_t ntiles, size_t smem)
 {
     const int per_sm = smem * 2 + 4096 <= ctx->smem_per_sm ? 2 : 1;
     int64_t grid = (int64_t) ctx->sm_count * per_sm;
-    const int64_t want = ceil_div(ntiles, CLS_THREADS / 32);
+    const int64_t want = ceil_div(2 * ntiles, CLS_THREADS / 32);
     if (grid > want) grid = want;
     return (unsigned) (grid < 1 ? 1 : grid);
 }

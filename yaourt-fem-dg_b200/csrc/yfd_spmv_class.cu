@@ -193,14 +193,14 @@ yfd_status group_cells_by_key(yfd_ctx *ctx, int64_t nc, uint64_t *d_keys, int ke
     std::vector<int64_t> hstart((size_t) ncls + 1), hpoff((size_t) ncls + 1);
     YFD_TRY(g.start.download(ctx, hstart.data(), (size_t) ncls + 1));
     int64_t npos = 0;
-    for (int64_t k = 0; k < ncls; k++) { hpoff[k] = npos; npos += (hstart[k + 1] - hstart[k] + 31) / 32 * 32; }
+    for (int64_t k = 0; k < ncls; k++) { hpoff[k] = npos; npos += (hstart[k + 1] - hstart[k] + CLS_TILE - 1) / CLS_TILE * CLS_TILE; }
     hpoff[ncls] = npos;
     /* padding beyond 25 % of the list = too many small classes for lane-per-cell tiles to pay */
-    if (npos > nc + nc / 4 + 32 * 64) { g.reject = 2; return YFD_OK; }
-    g.npos = npos; g.ntiles = npos / 32;
+    if (npos > nc + nc / 4 + CLS_TILE * 64) { g.reject = 2; return YFD_OK; }
+    g.npos = npos; g.ntiles = npos / CLS_TILE;
     std::vector<int32_t> htile((size_t) g.ntiles);
     for (int64_t k = 0; k < ncls; k++)
-        for (int64_t t = hpoff[k] / 32; t < hpoff[k + 1] / 32; t++) htile[t] = (int32_t) k;
+        for (int64_t t = hpoff[k] / CLS_TILE; t < hpoff[k + 1] / CLS_TILE; t++) htile[t] = (int32_t) k;
     YFD_TRY(poff.upload(ctx, hpoff.data(), (size_t) ncls + 1));
     YFD_TRY(g.tile_cls.alloc(ctx, (size_t) g.ntiles));
     YFD_TRY(g.tile_cls.upload(ctx, htile.data(), (size_t) g.ntiles));
@@ -272,18 +272,22 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
     double dot = 0.0;
     for (int64_t tile = gw; tile < ntiles; tile += nw) {
         const int k = __ldg(&tile_cls[tile]);
-        const int64_t pos = tile * 32 + lane;
-        const int32_t c = __ldg(&work_cell[pos]);
-        if (c < 0) continue;                                   /* padding at the end of a class */
+        const int64_t pos = tile * CLS_TILE + lane;
+        const int32_t c[2] = { __ldg(&work_cell[pos]), __ldg(&work_cell[pos + 32]) };
+        if (c[0] < 0) continue;                                /* padding at the end of a class (then c[1] < 0 too) */
         const double *Wk = T + (size_t) k * (NB * SS);
-        double acc[BS];
-        class_row_product<BS, NB, GLOBAL>(Wk, x, c, pos, work_nbr, npos, acc);
-        store_cell<BS>(y, c, acc);
-        if (WITH_DOT) {
-            double xs[BS];
-            load_cell<BS>(x, c, xs);
+        double acc[2][BS];
+        class_row_product_n<BS, NB, 2, GLOBAL>(Wk, x, c, pos, work_nbr, npos, acc);
 #pragma unroll
-            for (int i = 0; i < BS; i++) dot = fma(acc[i], xs[i], dot);
+        for (int q = 0; q < 2; q++) {
+            if (c[q] < 0) continue;
+            store_cell<BS>(y, c[q], acc[q]);
+            if (WITH_DOT) {
+                double xs[BS];
+                load_cell<BS>(x, c[q], xs);
+#pragma unroll
+                for (int i = 0; i < BS; i++) dot = fma(acc[q][i], xs[i], dot);
+            }
         }
     }
     if (WITH_DOT) {
