@@ -41,7 +41,7 @@ def test_hot_kernels_do_not_spill(usage):
     # continuous-FEM systems, the Maxwell stage kernel tri k=4 / quad k=3, and the CG vector kernels
     for parts in (("dg_spmv_tma", "ILi10E"), ("dg_spmv_tma", "ILi6E"), ("dg_spmv_tma", "ILi15E"), ("csr_spmv_tma",),
                   ("13maxwell_stageI", "ILi3ELi4E"), ("13maxwell_stageI", "ILi4ELi3E"), ("cg_update_xr",), ("cg_update_d",),
-                  ("dg_spmv_class", "ILi10E", "ELb0EEE"), ("dg_spmv_class", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi10E"), ("pmg_sweep", "ILi6E"), ("pmg_sweep", "ILi3E")):
+                  ("dg_spmv_class", "ILi10E", "ELb0EEE"), ("dg_spmv_class", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi10E", "ELb0EEE"), ("pmg_sweep", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi3E", "ELb0EEE")):
         for name, u in find(usage, *parts).items():
             assert u["stack"] == 0 and u["local"] == 0, (name, u)
     # two CTAs per SM for the Maxwell stage kernel at the benchmarked degrees need <= 128 registers (256 threads)
