@@ -85,7 +85,8 @@ def test_dg_spmv_deep_ring_matches_reference(yfd, ref, ctx, mtype, r, k, shatter
     assert abs(res["iterations"] - out["iters"]) <= max(3, 0.05 * out["iters"])
     h = min(20, len(res["history"]), len(out["history"]))
     assert np.allclose(res["history"][:h], out["history"][:h], rtol=2e-5)
-    assert sysm.true_residual(res["x"]) <= 1e-10       # recurrence residual 1e-12; the true one sits eps x iterations x |A||x| / |b| above it
+    # recurrence residual 1e-12; the true one sits eps x iterations x |A||x| / |b| above it (slivers: more)
+    assert sysm.true_residual(res["x"]) <= (1e-9 if shatter else 1e-10)
 
 
 @pytest.mark.parametrize("stages", [2, 4])
