@@ -129,6 +129,46 @@ __global__ void cls_build_table(const int64_t *__restrict__ start, const uint32_
     }
 }
 
+/* several ranks: pack (key, block row) of every local class for the all-gather; unused slots carry the key ~0 */
+__global__ void cls_pack_classes(const uint64_t *__restrict__ sorted_keys, const int64_t *__restrict__ start, int64_t ncls, int64_t maxc,
+                                 const double *__restrict__ table, int row_doubles, uint64_t *__restrict__ out_keys, double *__restrict__ out_rows)
+{
+    const int64_t k = blockIdx.x;
+    if (threadIdx.x == 0) out_keys[k] = k < ncls ? sorted_keys[start[k]] : ~0ull;
+    for (int t = threadIdx.x; t < row_doubles; t += blockDim.x) out_rows[k * row_doubles + t] = k < ncls ? table[k * row_doubles + t] : 0.0;
+}
+
+/* ... and adopt, for every local class, the block row of the LOWEST rank that has a class with the same key: every rank then
+ * multiplies by identical numbers, and they are the numbers a single GPU uses (its representative is the globally first
+ * cell of the class, which lives on the lowest such rank).  One CTA per local class. */
+__global__ void cls_adopt_global(const uint64_t *__restrict__ sorted_keys, const int64_t *__restrict__ start, int nranks, int64_t maxc,
+                                 const uint64_t *__restrict__ all_keys, const double *__restrict__ all_rows, int row_doubles,
+                                 double *__restrict__ table, double *__restrict__ scale)
+{
+    __shared__ double sm[32];
+    __shared__ int64_t src;
+    const int64_t k = blockIdx.x;
+    if (threadIdx.x == 0) {
+        const uint64_t key = sorted_keys[start[k]];
+        src = -1;
+        for (int64_t q = 0; q < (int64_t) nranks * maxc && src < 0; q++) if (all_keys[q] == key) src = q;
+    }
+    __syncthreads();
+    double mx = 0.0;
+    for (int t = threadIdx.x; t < row_doubles; t += blockDim.x) {
+        const double v = src >= 0 ? all_rows[src * row_doubles + t] : table[k * row_doubles + t];
+        table[k * row_doubles + t] = v;
+        mx = fmax(mx, fabs(v));
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int) (blockDim.x >> 5); w++) mx = fmax(mx, sm[w]);
+        scale[k] = mx;
+    }
+}
+
 /* one warp per cell: largest |W_c - T_class| / max|T_class| over the block row; a slot present on one side only = +inf */
 __global__ void cls_verify(const int32_t *__restrict__ cell_cls, const int64_t *__restrict__ cellptr, const int8_t *__restrict__ slots,
                            const double *__restrict__ values, const double *__restrict__ table, const double *__restrict__ scale,
@@ -255,6 +295,20 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
     /* tables beyond shared memory are read from global memory (L1 / L2 hits): 8 MB keeps them far inside the 126 MB L2 */
     YFD_TRY(group_cells_by_key(ctx, nc, d_keys, key_bits, (size_t) nb * ss * sizeof(double), (size_t) 8 << 20, g));
     cl.ncls = (int) std::min<int64_t>(g.ncls, 0x7fffffff);
+    const bool multi = sys->plan && ctx->nranks > 1;
+    /* several ranks: the decision is collective (a rank that declines makes every rank decline), so that the all-gathers
+     * below are entered by all of them */
+    int64_t maxc = g.ncls;
+    if (multi) {
+        dbuf<int64_t> mine, all;
+        YFD_TRY(mine.alloc(ctx, 1)); YFD_TRY(all.alloc(ctx, (size_t) ctx->nranks));
+        const int64_t word = g.reject ? -1 : g.ncls;
+        YFD_CUDA(ctx, cudaMemcpyAsync(mine.p, &word, sizeof(word), cudaMemcpyHostToDevice, ctx->stream));
+        YFD_TRY(comm_allgather_bytes(ctx, mine.p, all.p, sizeof(int64_t)));
+        std::vector<int64_t> h((size_t) ctx->nranks);
+        YFD_TRY(all.download(ctx, h.data(), h.size()));
+        for (int64_t v : h) { if (v < 0 && !g.reject) g.reject = 4; maxc = std::max(maxc, v); }
+    }
     if (g.reject) { cl.reject = g.reject; return YFD_OK; }
     const int64_t ncls = g.ncls, npos = g.npos;
     YFD_TRY(cl.work_nbr.alloc(ctx, (size_t) (npos * nf)));
@@ -267,6 +321,22 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
     YFD_TRY(worst.alloc(ctx, 1)); YFD_TRY(worst.zero(ctx));
     YFD_LAUNCH(ctx, cls_build_table, (unsigned) ncls, 128, 0, (const int64_t *) g.start.p, (const uint32_t *) g.sorted_cell.p, (const int64_t *) sys->cellptr.p,
                (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, bs, nf, cl.table.p, scale.p);
+    if (multi) {
+        /* identical tables on every rank (see cls_adopt_global): CG is sensitive to a COHERENT asymmetry of the operator at the
+         * 1e-13 level -- with rank-local representatives the 2-GPU solve of the 21 M-dof system took 3.5x the iterations */
+        const int row = nb * ss;
+        dbuf<uint64_t> pk, ak;
+        dbuf<double> pr, ar;
+        YFD_TRY(pk.alloc(ctx, (size_t) maxc)); YFD_TRY(pr.alloc(ctx, (size_t) (maxc * row)));
+        YFD_TRY(ak.alloc(ctx, (size_t) (maxc * ctx->nranks))); YFD_TRY(ar.alloc(ctx, (size_t) (maxc * row * ctx->nranks)));
+        YFD_LAUNCH(ctx, cls_pack_classes, (unsigned) maxc, 128, 0, (const uint64_t *) d_keys, (const int64_t *) g.start.p, ncls, maxc,
+                   (const double *) cl.table.p, row, pk.p, pr.p);
+        YFD_TRY(comm_allgather_bytes(ctx, pk.p, ak.p, (size_t) maxc * sizeof(uint64_t)));
+        YFD_TRY(comm_allgather_bytes(ctx, pr.p, ar.p, (size_t) (maxc * row) * sizeof(double)));
+        YFD_LAUNCH(ctx, cls_adopt_global, (unsigned) ncls, 128, 0, (const uint64_t *) d_keys, (const int64_t *) g.start.p, ctx->nranks, maxc,
+                   (const uint64_t *) ak.p, (const double *) ar.p, row, cl.table.p, scale.p);
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     const int64_t want = ceil_div(nc, 8), cap = (int64_t) ctx->sm_count * 16;
     YFD_LAUNCH(ctx, cls_verify, (unsigned) std::max<int64_t>(1, std::min(want, cap)), 256, 0, (const int32_t *) g.cell_cls.p, (const int64_t *) sys->cellptr.p,
                (const int8_t *) sys->slots.p, (const double *) sys->A.values.p, (const double *) cl.table.p, (const double *) scale.p, nc, bs, nf, worst.p);
@@ -276,7 +346,18 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
     memcpy(&dev, &wb, sizeof(dev));
     cl.max_dev = dev; cl.tol = tol; cl.npos = npos; cl.ntiles = g.ntiles; cl.table_doubles = (int) (ncls * nb * ss);
     cl.work_cell = std::move(g.work_cell); cl.tile_cls = std::move(g.tile_cls); cl.cell_cls = std::move(g.cell_cls);
-    if (!(dev <= tol)) { cl.reject = 3; return YFD_OK; }      /* also catches inf / NaN */
+    int ok = (dev <= tol) ? 1 : 0;                             /* also catches inf / NaN */
+    if (multi) {
+        dbuf<int64_t> mine, all;
+        YFD_TRY(mine.alloc(ctx, 1)); YFD_TRY(all.alloc(ctx, (size_t) ctx->nranks));
+        const int64_t word = ok;
+        YFD_CUDA(ctx, cudaMemcpyAsync(mine.p, &word, sizeof(word), cudaMemcpyHostToDevice, ctx->stream));
+        YFD_TRY(comm_allgather_bytes(ctx, mine.p, all.p, sizeof(int64_t)));
+        std::vector<int64_t> h((size_t) ctx->nranks);
+        YFD_TRY(all.download(ctx, h.data(), h.size()));
+        for (int64_t v : h) if (!v && ok) { ok = 0; cl.reject = 4; }
+    }
+    if (!ok) { if (!cl.reject) cl.reject = 3; return YFD_OK; }
     cl.ready = true;
     return YFD_OK;
 }
