@@ -756,6 +756,18 @@ def main():
                              "shared memory (dg_spmv_class): the matrix stream is gone, the kernel is bound by FP64 issue / shared-memory broadcasts "
                              "(see fp64) and by the x / y vectors, and its HBM fraction is low BY DESIGN; streamed_kernel is the HBM-bound general path "
                              "on the same system" % oi["nclasses"])
+    # element kernel (dg_sip_cells): SURVEY.md 8d's flop count and minimum bytes over its CUDA-event time
+    roofline_elements = None
+    if not cfem:
+        nvv = 3 if wl["cell"] == 0 else 4
+        nq = {1: 3, 2: 6, 3: 12, 4: 16, 5: 25, 6: 33}.get(k, 1) if nvv == 3 else (k + 1) ** 2
+        ncl = info["n_local"] / bs
+        fl = ncl * (nq * (5 * bs * bs + 2 * bs) + nvv * (k + 1) * (12 * bs * bs + 6 * bs))
+        by = 8.0 * info["nnz_local"] + 8.0 * info["n_local"]
+        tms = info["ms_elements"] * 1e-3
+        roofline_elements = {"kernel": "dg_sip_cells (K, Att, Atn, rhs per cell on quadrature)", "ms": info["ms_elements"], "flops": fl, "bytes_written": by,
+                             "achieved_tflops": fl / tms / 1e12, "fp64_frac": fl / tms / 1e12 / fp64_peak, "written_gbs": by / tms / 1e9, "hbm_frac": by / tms / 1e9 / peak,
+                             "note": "one lane per block entry, 2-5 scalar LDS per FMA: shared-memory latency bound, far from both roofs; 2-3 % of a step"}
     # whole CG iteration (SpMV + 2 fused vector kernels) over the timed solve: B_cg = B_spmv + 72 n,
     # summed over ranks
     it = max(1, info["iterations"])
@@ -853,7 +865,7 @@ def main():
                                                                   "per CG iteration 2 cross-rank scalar sums through NVLink peer memory; no exchange of d: every rank advances its halo "
                                                                   "copies of r and d from the neighbours' y = A d, stored into its landing zone ahead of the r.r sum"
                                                                   if info.get("transport") == "peer memory" else "per CG iteration one halo exchange and 2 scalar all-reduces")},
-                "roofline": roofline, "cpu_baseline": base, "same_size": same_size, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
+                "roofline": roofline, "roofline_elements": roofline_elements, "cpu_baseline": base, "same_size": same_size, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks})
         print(json.dumps(line))
     ctx.close()
     if dist is not None:
