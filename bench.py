@@ -398,12 +398,19 @@ def run_maxwell(args, wl, rank, world, local_rank):
     uses_classes = bool(mx.info.uses_classes)
     cls_info = dict(uses_classes=uses_classes, nclasses=int(mx.info.nclasses), reject_reason=int(mx.info.class_reject_reason),
                     max_deviation=mx.info.class_max_deviation, tolerance=mx.info.class_tolerance, table_bytes=int(mx.info.class_table_bytes))
-    streamed = None
-    if uses_classes:                         # the general (streamed) kernel on the same operator, timed beside the class kernel
+    streamed, other = None, None
+    if cls_info["nclasses"] > 0 and cls_info["reject_reason"] == 0:
+        # both kernels on the same operator (AUTO took the faster one when the operator was created)
         mx.set_operator_mode(yfd.OPERATOR_STREAMED)
         ms_s, _, kb_s = mx.time_apply(10)
-        streamed = dict(ms_per_launch=ms_s, kernel_requested_bytes_per_launch=kb_s)
+        mx.set_operator_mode(yfd.OPERATOR_CLASSES)
+        ms_c, _, kb_c = mx.time_apply(10)
         mx.set_operator_mode(yfd.OPERATOR_AUTO)
+        if uses_classes:
+            streamed = dict(ms_per_launch=ms_s, kernel_requested_bytes_per_launch=kb_s)
+        else:
+            other = dict(kernel="maxwell_stage_class (not chosen: slower than the streamed kernel on this operator)", ms_per_launch=ms_c,
+                         kernel_requested_bytes_per_launch=kb_c)
     fp64_peak = ctx.measure_fp64()
     flops_apply = 2.0 * mx.bs * mx.bs * (4 + 6 * mx.nf) * (info["cells"] / world)
     mx.close()
@@ -437,6 +444,8 @@ def run_maxwell(args, wl, rank, world, local_rank):
         sg = streamed["kernel_requested_bytes_per_launch"] / (streamed["ms_per_launch"] * 1e-3) / 1e9
         streamed.update(kernel="maxwell_stage (factored blocks streamed per cell)", achieved=sg, frac=sg / peak, speedup_of_class_kernel=streamed["ms_per_launch"] / ms_apply)
         roofline["streamed_kernel"] = streamed
+    if other is not None:
+        roofline["class_kernel"] = other
 
     e2e = None
     if not args.no_e2e:

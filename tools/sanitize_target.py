@@ -69,6 +69,7 @@ res = adv.solve_cg(yfd.CgParams(rr_tol=1e-8, rr_max=1e4, max_iter=200, use_norma
 check("advection-reaction + CG on the normal equations", np.isfinite(res["x"]).all())
 for cell, r, k, up in ((yfd.TRI, 2, 4, False), (yfd.QUAD, 2, 2, True)):
     mx = yfd.Maxwell(ctx, yfd.Mesh(ctx, yfd.HostMesh.create(cell, r)), k, delta_t=1e-3, upwind=up)
+    mx.set_operator_mode(yfd.OPERATOR_CLASSES)
     mx.apply_initial_condition(); mx.timesteps(3); a = mx.dofs()
     mx.set_operator_mode(yfd.OPERATOR_STREAMED)
     mx.apply_initial_condition(); mx.timesteps(3); b = mx.dofs()

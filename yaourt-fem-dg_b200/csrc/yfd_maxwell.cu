@@ -643,6 +643,29 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
         if (!(tol > 1e-11)) tol = 1e-11;
         if (const char *e = getenv("YFD_CLASS_TOL")) { const double v = atof(e); if (v > 0.0) tol = v; }
         YFD_TRY(maxwell_build_classes(ctx, m.get(), keys.p, KEY_BITS, tol));
+        if (m->classes.ready) {
+            /* which kernel for AUTO: time both on this operator (one warm-up + 3 launches each, plain application of the zero
+             * state into a stage buffer); YFD_MX_CLASSES=2 skips the timing and takes the class kernel */
+            if (env_int("YFD_MX_CLASSES", 1) == 2) m->classes_faster = true;
+            else {
+                double ms[2] = { 0.0, 0.0 };
+                for (int mode = 1; mode <= 2; mode++) {
+                    m->operator_mode = mode;
+                    mx_step_args s = step_args(m.get());
+                    s.vin = m->u.p; s.out = m->s2.p;
+                    YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+                    gpu_timer tt;
+                    tt.start(ctx->stream);
+                    for (int r = 0; r < 3; r++) YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+                    tt.stop(ctx->stream);
+                    ms[mode - 1] = tt.ms() / 3.0;
+                }
+                m->operator_mode = 0;
+                m->ms_apply_streamed = ms[0]; m->ms_apply_classes = ms[1];
+                m->classes_faster = ms[1] < ms[0];
+                YFD_TRY(m->s2.zero(ctx));
+            }
+        }
     }
     if (info) yfd_maxwell_get_info(m.get(), info);
     *out = m.release();

@@ -60,6 +60,8 @@ struct yfd_maxwell {
     yfd::dbuf<double>  gM;            /* [ncells][bs][bs] row-major, internal order                       */
     yfd::mx_classes    classes;
     int      operator_mode = 0;       /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES                         */
+    bool     classes_faster = false;  /* outcome of the timing at creation (AUTO follows it)              */
+    double   ms_apply_streamed = 0.0, ms_apply_classes = 0.0;
     /* state: gDofs and the RK stage operands [nlocal][3][bs] (owned | halo), k1 / k2 [ncells][3][bs]; internal order */
     yfd::dbuf<double>  u, s1, s2, acc, kb;
 };
@@ -80,5 +82,10 @@ struct mx_step_args {
 };
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
 yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol);
-inline bool maxwell_uses_classes(const yfd_maxwell *m) { return m->classes.ready && m->operator_mode != 1; }
+/* AUTO = whichever of the two kernels was faster on this operator when it was created (timed there: the class kernel wins
+ * on the reference's triangle meshes at k = 4, the streamed one -- already at the HBM roof -- on quadrangles k = 3) */
+inline bool maxwell_uses_classes(const yfd_maxwell *m)
+{
+    return m->classes.ready && (m->operator_mode == 2 || (m->operator_mode == 0 && m->classes_faster));
+}
 } // namespace yfd
