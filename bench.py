@@ -790,6 +790,9 @@ def main():
     if oi is not None and oi["uses_classes"]:
         mat_bytes = (sp["kernel_bytes"] - 16.0 * info["n_local"]) * world       # index lists only
     cg_gbs = (mat_bytes + 16.0 * info["n"] + 72.0 * info["n"]) * it / (info["ms_solve"] * 1e-3) / 1e9
+    # the whole CG iteration = this SpMV + cg_update_xr + cg_update_d (72 n bytes, both at the HBM roof): requested bytes / time
+    roofline["cg_iteration"] = {"requested_gbs": cg_gbs, "frac": cg_gbs / peak / max(1, world), "ms": info["ms_solve"] / it,
+                                "note": "bytes the three kernels of an iteration request (index lists or matrix + x, y + 72 n) over the solve's time per iteration, per GPU"}
     sysm.close()
 
     # ---------------- end-to-end leg: host buffers in, host solution out ----------------
