@@ -595,7 +595,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
         cudaError_t e = cudaMemcpyAsync(&hs, sc.p, sizeof(hs), cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "CG poll: %s", cudaGetErrorString(e)); break; }
-        if (hs.comm_error) { st = fail(ctx, YFD_ERR_COMM, "peer-memory transport: a rank did not arrive within the spin bound"); break; }
+        if (hs.comm_error) { ctx->peer_failed = true; st = fail(ctx, YFD_ERR_COMM, "peer-memory transport: a rank did not arrive within the spin bound"); break; }
         if (hs.done) break;
         e = cudaGraphLaunch(exec, ctx->stream);
         if (e != cudaSuccess) { st = fail(ctx, YFD_ERR_CUDA, "graph launch: %s", cudaGetErrorString(e)); break; }

@@ -61,6 +61,8 @@ struct yfd_ctx {
     void         *peer_opened[YFD_MAX_RANKS] = {};   /* cudaIpcOpenMemHandle results, to close later  */
     peer_view    *d_peer_view = nullptr;       /* device copy handed to the kernels                   */
     bool          peer_enabled = false;
+    bool          peer_failed = false;          /* a spin bound was hit on this rank ...                  */
+    bool          peer_off = false;             /* ... and the ranks have agreed to stay on NCCL          */
 };
 
 namespace yfd {
@@ -232,7 +234,7 @@ yfd_status comm_allgather_bytes(yfd_ctx *ctx, const void *d_send, void *d_recv, 
 /* collective: make sure every rank's landing zone holds at least `land_doubles` (same value on all ranks);
  * on failure the context silently stays on the NCCL transport (peer_enabled = false) */
 yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles);
-void       peer_release(yfd_ctx *ctx);
+void       peer_release(yfd_ctx *ctx, bool collective = false);
 
 /* ---- yfd_dist.cu: this rank's share of a replicated mesh ---- */
 struct dist_plan {

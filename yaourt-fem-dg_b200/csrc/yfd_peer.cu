@@ -32,11 +32,35 @@ static size_t region_bytes(size_t land_doubles)
     return ((sizeof(peer_ctl) + 4095) & ~(size_t) 4095) + land_doubles * sizeof(double) + 256;
 }
 
-void peer_release(yfd_ctx *ctx)
+/* one word per rank through ncclAllGather; returns the OR of the words (doubles as a barrier: every rank has passed this
+ * point of its stream when the call returns) */
+static yfd_status agree_any(yfd_ctx *ctx, int mine, int *any)
+{
+    dbuf<int> d_send, d_recv;
+    YFD_TRY(d_send.alloc(ctx, 1)); YFD_TRY(d_recv.alloc(ctx, (size_t) ctx->nranks));
+    YFD_TRY(d_send.upload(ctx, &mine, 1));
+    YFD_TRY(comm_allgather_bytes(ctx, d_send.p, d_recv.p, sizeof(int)));
+    std::vector<int> all((size_t) ctx->nranks);
+    YFD_TRY(d_recv.download(ctx, all.data(), all.size()));
+    *any = 0;
+    for (int v : all) *any |= v;
+    return YFD_OK;
+}
+
+/* collective = every rank of the communicator is inside this call (rebuild, agreed tear-down): the ranks then meet between
+ * closing their imported mappings and freeing the exported region, so that no region is freed while a peer still maps it.
+ * The non-collective form (context destruction, possibly after a peer died) cannot wait for anybody. */
+void peer_release(yfd_ctx *ctx, bool collective)
 {
     if (!ctx) return;
+    const bool had_region = ctx->peer_region != nullptr;
+    if (had_region) cudaStreamSynchronize(ctx->stream);
     for (int q = 0; q < YFD_MAX_RANKS; q++)
         if (ctx->peer_opened[q]) { cudaIpcCloseMemHandle(ctx->peer_opened[q]); ctx->peer_opened[q] = nullptr; }
+    if (collective && ctx->comm && ctx->nranks > 1) {
+        int any = 0;
+        if (agree_any(ctx, 0, &any) != YFD_OK) cudaGetLastError();      /* the free below is all that is left to do anyway */
+    }
     if (ctx->peer_region) { cudaFree(ctx->peer_region); ctx->peer_region = nullptr; }
     if (ctx->d_peer_view) { cudaFree(ctx->d_peer_view); ctx->d_peer_view = nullptr; }
     ctx->peer_land_cap = 0;
@@ -49,10 +73,20 @@ yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles)
     if (ctx->nranks <= 1 || ctx->nranks > YFD_MAX_RANKS) return YFD_OK;
     const char *mode = getenv("YFD_COMM");
     if (mode && mode[0] == 'n') { ctx->peer_enabled = false; return YFD_OK; }       /* YFD_COMM=nccl */
+    /* a rank whose kernels ran into the spin bound (cg_device: comm_error) has epochs and flags nobody can trust any more:
+     * the ranks agree on that here, drop the mappings together and stay on NCCL for the rest of the context's life */
+    if (ctx->peer_off) return YFD_OK;
+    int any_failed = 0;
+    YFD_TRY(agree_any(ctx, ctx->peer_failed ? 1 : 0, &any_failed));
+    if (any_failed) {
+        ctx->peer_failed = ctx->peer_off = true;
+        peer_release(ctx, /*collective=*/true);
+        return YFD_OK;
+    }
     if (ctx->peer_region && ctx->peer_land_cap >= land_doubles) return YFD_OK;
     /* (re)build, collectively: `land_doubles` is the same on every rank */
     YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    peer_release(ctx);
+    peer_release(ctx, /*collective=*/true);
     const size_t cap = land_doubles + land_doubles / 2 + 1024;
     const size_t bytes = region_bytes(cap);
     bool ok = true;
@@ -98,7 +132,7 @@ yfd_status ensure_peer_region(yfd_ctx *ctx, size_t land_doubles)
     bool all_ok = true;
     for (auto &a : all) all_ok = all_ok && a.ok;
     ctx->peer_region = region;
-    if (!all_ok) { peer_release(ctx); return YFD_OK; }       /* stay on NCCL */
+    if (!all_ok) { peer_release(ctx, /*collective=*/true); return YFD_OK; }       /* stay on NCCL */
     YFD_CUDA(ctx, cudaMalloc((void **) &ctx->d_peer_view, sizeof(peer_view)));
     YFD_CUDA(ctx, cudaMemcpy(ctx->d_peer_view, &pv, sizeof(pv), cudaMemcpyHostToDevice));
     ctx->peer_land_cap = cap;
