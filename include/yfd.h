@@ -162,6 +162,11 @@ yfd_status yfd_mesh_get_neighbours(yfd_mesh *m, int64_t *neighbours);
 /* ---------------------------------------------------------------------------------- */
 typedef struct yfd_partition yfd_partition;
 yfd_status yfd_partition_create(int64_t ncells, int nf, const int64_t *neighbours, int nranks, int rank, yfd_partition **out);
+/* The same plan from the cut faces alone: pairs (cut_cell[i], cut_nbr[i]) of face-adjacent cells owned by different ranks
+ * (both directions listed; pairs of other ranks are ignored, so one list of all cuts serves every rank).  This is what the
+ * library uses itself: the device finds the O(sqrt(cells)) cut faces and only those reach the host. */
+yfd_status yfd_partition_create_from_cuts(int64_t ncells, int nranks, int rank, int64_t ncut, const int64_t *cut_cell,
+                                          const int64_t *cut_nbr, yfd_partition **out);
 void       yfd_partition_destroy(yfd_partition *p);
 void       yfd_partition_sizes(const yfd_partition *p, int64_t *cell_begin, int64_t *cell_end, int64_t *nhalo,
                                int64_t *nsend, int *npeers);

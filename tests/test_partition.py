@@ -59,6 +59,31 @@ def test_plan_invariants(yfd, oracle, t, r, nranks):
         assert len(plans[0]["halo_cells"]) == 0 and len(plans[0]["peers"]) == 0
 
 
+@pytest.mark.parametrize("t,r", [(0, 3), (1, 3)])
+@pytest.mark.parametrize("nranks", [2, 3, 8])
+def test_plan_from_cut_faces_is_the_same_plan(yfd, oracle, t, r, nranks):
+    """yfd_partition_create_from_cuts (what the library feeds from the device's cut-face list) == yfd_partition_create,
+    from ONE list of all cuts of the mesh, in any order, duplicates allowed."""
+    m, nbr = neighbours_from_oracle(oracle, t, r)
+    nc, nf = nbr.shape
+    begins = [(nc * q) // nranks for q in range(nranks + 1)]
+    owner = np.searchsorted(begins, np.arange(nc), side="right") - 1
+    c = np.repeat(np.arange(nc), nf); n = nbr.reshape(-1)
+    cut = (n >= 0) & (owner[c] != owner[np.maximum(n, 0)])
+    cc, cn = c[cut], n[cut]
+    rng = np.random.default_rng(5)
+    order = rng.permutation(len(cc))
+    cc, cn = np.concatenate([cc[order], cc[:3]]), np.concatenate([cn[order], cn[:3]])
+    for q in range(nranks):
+        a = yfd.partition_plan(nbr, nranks, q)
+        b = yfd.partition_plan_from_cuts(nc, nranks, q, cc, cn)
+        assert a["cell_begin"] == b["cell_begin"] and a["cell_end"] == b["cell_end"]
+        for key in ("halo_cells", "send_cells", "peers", "recv_counts", "send_counts"):
+            assert np.array_equal(a[key], b[key]), key
+    with pytest.raises(yfd.YfdError):
+        yfd.partition_plan_from_cuts(nc, nranks, 0, np.array([0]), np.array([nc]))
+
+
 def test_plan_rejects_bad_arguments(yfd):
     nbr = np.full((4, 3), -1, np.int64)
     with pytest.raises(yfd.YfdError):

@@ -163,6 +163,7 @@ def lib():
         "yfd_mesh_set_points": (cint, [vp, _f64p]),
         "yfd_mesh_get_neighbours": (cint, [vp, _i64p]),
         "yfd_partition_create": (cint, [i64, cint, _i64p, cint, cint, P(vp)]),
+        "yfd_partition_create_from_cuts": (cint, [i64, cint, cint, i64, _i64p, _i64p, P(vp)]),
         "yfd_partition_destroy": (None, [vp]),
         "yfd_partition_sizes": (None, [vp, P(i64), P(i64), P(i64), P(i64), P(cint)]),
         "yfd_partition_get": (cint, [vp, vp, vp, vp, vp, vp]),
@@ -455,13 +456,7 @@ class Mesh:
         self.ctx.check(lib().yfd_mesh_set_points(self._h, points))
 
 
-def partition_plan(neighbours, nranks, rank):
-    """yfd_partition_create (host, no CUDA): contiguous blocks of the internal cell order + halo / send lists."""
-    nbr = np.ascontiguousarray(neighbours, np.int64)
-    h = C.c_void_p()
-    st = lib().yfd_partition_create(nbr.shape[0], nbr.shape[1], nbr, nranks, rank, C.byref(h))
-    if st != 0:
-        raise YfdError(st, lib().yfd_status_string(st).decode())
+def _read_partition(h):
     try:
         b, e, nh, ns, npr = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
         lib().yfd_partition_sizes(h, C.byref(b), C.byref(e), C.byref(nh), C.byref(ns), C.byref(npr))
@@ -471,6 +466,27 @@ def partition_plan(neighbours, nranks, rank):
     finally:
         lib().yfd_partition_destroy(h)
     return dict(cell_begin=b.value, cell_end=e.value, halo_cells=halo, send_cells=send, peers=peers, recv_counts=rc, send_counts=sc)
+
+
+def partition_plan(neighbours, nranks, rank):
+    """yfd_partition_create (host, no CUDA): contiguous blocks of the internal cell order + halo / send lists."""
+    nbr = np.ascontiguousarray(neighbours, np.int64)
+    h = C.c_void_p()
+    st = lib().yfd_partition_create(nbr.shape[0], nbr.shape[1], nbr, nranks, rank, C.byref(h))
+    if st != 0:
+        raise YfdError(st, lib().yfd_status_string(st).decode())
+    return _read_partition(h)
+
+
+def partition_plan_from_cuts(ncells, nranks, rank, cut_cell, cut_nbr):
+    """yfd_partition_create_from_cuts: the same plan from the (cell, neighbour) pairs that straddle two ranks' blocks."""
+    cc = np.ascontiguousarray(cut_cell, np.int64); cn = np.ascontiguousarray(cut_nbr, np.int64)
+    assert cc.shape == cn.shape and cc.ndim == 1
+    h = C.c_void_p()
+    st = lib().yfd_partition_create_from_cuts(ncells, nranks, rank, cc.size, cc, cn, C.byref(h))
+    if st != 0:
+        raise YfdError(st, lib().yfd_status_string(st).decode())
+    return _read_partition(h)
 
 
 def _solve_common(ctx, call, n, params, x0, history):

@@ -46,6 +46,31 @@ __global__ void pack_cells(const double *__restrict__ x, const int32_t *__restri
     }
 }
 
+/* the faces between two ranks' blocks: (cell, neighbour) for every cell whose neighbour has another owner; O(sqrt(cells)) of
+ * them on a Z-curve order, so only these -- not the neighbour table -- travel to the host planner */
+/* yfd_partition.cpp: partition_begin / partition_owner in 64-bit arithmetic (cell ids are int32 here, nranks small) */
+__device__ __forceinline__ int64_t begin_of(int64_t ncells, int nranks, int r) { return ncells * r / nranks; }
+__device__ __forceinline__ int owner_of(int64_t ncells, int nranks, int64_t c)
+{
+    int r = (int) (((c + 1) * nranks - 1) / ncells);
+    if (r >= nranks) r = nranks - 1;
+    while (r > 0 && begin_of(ncells, nranks, r) > c) r--;
+    while (r + 1 < nranks && begin_of(ncells, nranks, r + 1) <= c) r++;
+    return r;
+}
+__global__ void cut_faces(const int32_t *__restrict__ nbr, int64_t ncells, int nf, int nranks,
+                          int2 *__restrict__ out, unsigned long long cap, unsigned long long *__restrict__ count)
+{
+    const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ncells * nf) return;
+    const int32_t n = nbr[t];
+    if (n < 0) return;
+    const int64_t c = t / nf;
+    if (owner_of(ncells, nranks, c) == owner_of(ncells, nranks, n)) return;
+    const unsigned long long k = atomicAdd(count, 1ull);
+    if (k < cap) out[k] = make_int2((int) c, n);
+}
+
 yfd_status mesh_neighbours_device(yfd_ctx *ctx, yfd_mesh *m, dbuf<int32_t> &nbr)
 {
     const int64_t n = m->ncells * m->nf;
@@ -63,11 +88,30 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
     const int nf = mesh->nf;
     dbuf<int32_t> d_nbr;
     YFD_TRY(mesh_neighbours_device(ctx, mesh, d_nbr));
-    std::vector<int32_t> nbr32((size_t) (nc * nf));
-    YFD_TRY(d_nbr.download(ctx, nbr32.data(), nbr32.size()));
-    std::vector<int64_t> nbr(nbr32.begin(), nbr32.end());
+    /* cut faces on the device, planner on the host from those alone (the order of the list does not matter: the planner sorts) */
+    std::vector<int64_t> cut_cell, cut_nbr;
+    {
+        dbuf<unsigned long long> d_count;
+        YFD_TRY(d_count.alloc(ctx, 1)); YFD_TRY(d_count.zero(ctx));
+        unsigned long long cap = (unsigned long long) (64 * 1024), found = 0;
+        dbuf<int2> d_cut;
+        for (int pass = 0; pass < 2; pass++) {
+            YFD_TRY(d_cut.alloc(ctx, (size_t) cap));
+            if (nc * nf > 0)
+                YFD_LAUNCH(ctx, cut_faces, (unsigned) ceil_div(nc * nf, 256), 256, 0, d_nbr.p, nc, nf, ctx->nranks, d_cut.p, cap, d_count.p);
+            YFD_TRY(d_count.download(ctx, &found, 1));
+            if (found <= cap) break;
+            cap = found;                                    /* a mesh that is mostly cuts (tiny, or not a Z-curve order) */
+            YFD_TRY(d_count.zero(ctx));
+        }
+        std::vector<int2> cut((size_t) found);
+        if (found) YFD_TRY(d_cut.download(ctx, cut.data(), cut.size()));
+        cut_cell.resize(cut.size()); cut_nbr.resize(cut.size());
+        for (size_t i = 0; i < cut.size(); i++) { cut_cell[i] = cut[i].x; cut_nbr[i] = cut[i].y; }
+    }
     yfd_partition *hp = nullptr;
-    const yfd_status st = yfd_partition_create(nc, nf, nbr.data(), ctx->nranks, ctx->rank, &hp);
+    const yfd_status st = yfd_partition_create_from_cuts(nc, ctx->nranks, ctx->rank, (int64_t) cut_cell.size(), cut_cell.data(),
+                                                         cut_nbr.data(), &hp);
     if (st != YFD_OK) return fail(ctx, st, "partition planner failed");
     auto pl = std::make_shared<dist_plan>();
     int npeers = 0;
@@ -92,7 +136,7 @@ yfd_status ensure_dist_plan(yfd_ctx *ctx, yfd_mesh *mesh)
         for (int q = 0; q < ctx->nranks; q++) {
             if (q == ctx->rank) continue;
             yfd_partition *qp = nullptr;
-            if (yfd_partition_create(nc, nf, nbr.data(), ctx->nranks, q, &qp) != YFD_OK) return fail(ctx, YFD_ERR_INVALID_STATE, "partition planner failed for rank %d", q);
+            if (yfd_partition_create_from_cuts(nc, ctx->nranks, q, (int64_t) cut_cell.size(), cut_cell.data(), cut_nbr.data(), &qp) != YFD_OK) return fail(ctx, YFD_ERR_INVALID_STATE, "partition planner failed for rank %d", q);
             int64_t qh = 0; int qn = 0;
             yfd_partition_sizes(qp, nullptr, nullptr, &qh, nullptr, &qn);
             if (qh > pl->max_halo_cells) pl->max_halo_cells = qh;

@@ -45,30 +45,23 @@ int partition_owner(int64_t ncells, int nranks, int64_t cell)
 
 } // namespace yfd
 
-extern "C" {
-
-yfd_status yfd_partition_create(int64_t ncells, int nf, const int64_t *nbr, int nranks, int rank, yfd_partition **out)
+/* the plan of `rank` from the CUT FACES alone: pairs (cell, neighbour) whose two cells have different owners.  Pairs whose
+ * cell belongs to another rank are skipped, so one list of all cuts of the mesh serves every rank. */
+static yfd_status plan_from_pairs(yfd_partition *p, int64_t ncut, const int64_t *cut_cell, const int64_t *cut_nbr)
 {
-    if (!out) return YFD_ERR_INVALID_ARGUMENT;
-    *out = nullptr;
-    if (ncells < 0 || nf < 1 || nf > 4 || (ncells && !nbr) || nranks < 1 || rank < 0 || rank >= nranks) return YFD_ERR_INVALID_ARGUMENT;
-    yfd_partition *p = new (std::nothrow) yfd_partition();
-    if (!p) return YFD_ERR_OUT_OF_MEMORY;
-    p->nranks = nranks; p->rank = rank; p->ncells = ncells;
-    p->cell_begin = yfd::partition_begin(ncells, nranks, rank);
-    p->cell_end = yfd::partition_begin(ncells, nranks, rank + 1);
+    const int64_t ncells = p->ncells;
+    const int nranks = p->nranks;
     /* (peer, cell) pairs, then sort + unique */
     std::vector<std::pair<int32_t, int64_t>> halo, send;
-    for (int64_t c = p->cell_begin; c < p->cell_end; c++)
-        for (int e = 0; e < nf; e++) {
-            const int64_t n = nbr[c * nf + e];
-            if (n < 0) continue;
-            if (n >= ncells) { delete p; return YFD_ERR_INVALID_ARGUMENT; }
-            if (n >= p->cell_begin && n < p->cell_end) continue;
-            const int32_t q = (int32_t) yfd::partition_owner(ncells, nranks, n);
-            halo.emplace_back(q, n);
-            send.emplace_back(q, c);
-        }
+    for (int64_t i = 0; i < ncut; i++) {
+        const int64_t c = cut_cell[i], n = cut_nbr[i];
+        if (c < 0 || c >= ncells || n < 0 || n >= ncells) return YFD_ERR_INVALID_ARGUMENT;
+        if (c < p->cell_begin || c >= p->cell_end) continue;
+        if (n >= p->cell_begin && n < p->cell_end) continue;
+        const int32_t q = (int32_t) yfd::partition_owner(ncells, nranks, n);
+        halo.emplace_back(q, n);
+        send.emplace_back(q, c);
+    }
     std::sort(halo.begin(), halo.end()); halo.erase(std::unique(halo.begin(), halo.end()), halo.end());
     std::sort(send.begin(), send.end()); send.erase(std::unique(send.begin(), send.end()), send.end());
     for (auto &h : halo) if (p->peers.empty() || p->peers.back() != h.first) p->peers.push_back(h.first);
@@ -81,9 +74,56 @@ yfd_status yfd_partition_create(int64_t ncells, int nf, const int64_t *nbr, int 
     for (auto &s : send) {
         /* every peer I send to also sends to me (the relation is symmetric), so it is in `peers` */
         const size_t k = std::lower_bound(p->peers.begin(), p->peers.end(), s.first) - p->peers.begin();
-        if (k >= p->peers.size() || p->peers[k] != s.first) { delete p; return YFD_ERR_INVALID_ARGUMENT; }
+        if (k >= p->peers.size() || p->peers[k] != s.first) return YFD_ERR_INVALID_ARGUMENT;
         p->send_counts[k]++; p->send_cells.push_back(s.second);
     }
+    return YFD_OK;
+}
+
+static yfd_partition *new_partition(int64_t ncells, int nranks, int rank)
+{
+    yfd_partition *p = new (std::nothrow) yfd_partition();
+    if (!p) return nullptr;
+    p->nranks = nranks; p->rank = rank; p->ncells = ncells;
+    p->cell_begin = yfd::partition_begin(ncells, nranks, rank);
+    p->cell_end = yfd::partition_begin(ncells, nranks, rank + 1);
+    return p;
+}
+
+extern "C" {
+
+yfd_status yfd_partition_create(int64_t ncells, int nf, const int64_t *nbr, int nranks, int rank, yfd_partition **out)
+{
+    if (!out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if (ncells < 0 || nf < 1 || nf > 4 || (ncells && !nbr) || nranks < 1 || rank < 0 || rank >= nranks) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_partition *p = new_partition(ncells, nranks, rank);
+    if (!p) return YFD_ERR_OUT_OF_MEMORY;
+    std::vector<int64_t> cc, cn;
+    for (int64_t c = p->cell_begin; c < p->cell_end; c++)
+        for (int e = 0; e < nf; e++) {
+            const int64_t n = nbr[c * nf + e];
+            if (n < 0) continue;
+            if (n >= ncells) { delete p; return YFD_ERR_INVALID_ARGUMENT; }
+            if (n >= p->cell_begin && n < p->cell_end) continue;
+            cc.push_back(c); cn.push_back(n);
+        }
+    const yfd_status st = plan_from_pairs(p, (int64_t) cc.size(), cc.data(), cn.data());
+    if (st != YFD_OK) { delete p; return st; }
+    *out = p;
+    return YFD_OK;
+}
+
+yfd_status yfd_partition_create_from_cuts(int64_t ncells, int nranks, int rank, int64_t ncut, const int64_t *cut_cell,
+                                          const int64_t *cut_nbr, yfd_partition **out)
+{
+    if (!out) return YFD_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    if (ncells < 0 || ncut < 0 || (ncut && (!cut_cell || !cut_nbr)) || nranks < 1 || rank < 0 || rank >= nranks) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_partition *p = new_partition(ncells, nranks, rank);
+    if (!p) return YFD_ERR_OUT_OF_MEMORY;
+    const yfd_status st = plan_from_pairs(p, ncut, cut_cell, cut_nbr);
+    if (st != YFD_OK) { delete p; return st; }
     *out = p;
     return YFD_OK;
 }
