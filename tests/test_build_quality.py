@@ -41,16 +41,19 @@ def test_hot_kernels_do_not_spill(usage):
     # continuous-FEM systems, the Maxwell stage kernel tri k=4 / quad k=3, and the CG vector kernels
     for parts in (("dg_spmv_tma", "ILi10E"), ("dg_spmv_tma", "ILi6E"), ("dg_spmv_tma", "ILi15E"), ("csr_spmv_tma",),
                   ("13maxwell_stageI", "ILi3ELi4E"), ("13maxwell_stageI", "ILi4ELi3E"), ("cg_update_xr",), ("cg_update_d",),
-                  ("dg_spmv_class", "ILi10E", "ELb0EEE"), ("dg_spmv_class", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi10E", "ELb0EEE"), ("pmg_sweep", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi3E", "ELb0EEE")):
+                  ("13dg_spmv_classI", "ILi10E", "ELb0EEE"), ("13dg_spmv_classI", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi10E", "ELb0EEE"), ("pmg_sweep", "ILi6E", "ELb0EEE"), ("pmg_sweep", "ILi3E", "ELb0EEE")):
         for name, u in find(usage, *parts).items():
             assert u["stack"] == 0 and u["local"] == 0, (name, u)
     # two CTAs per SM for the Maxwell stage kernel at the benchmarked degrees need <= 128 registers (256 threads)
     for name, u in find(usage, "13maxwell_stageI", "ILi3ELi4E").items():
         assert u["reg"] <= 128, (name, u)
     # the class kernels run 2 CTAs of 256 threads per SM: <= 128 registers, at most a few spilled words at bs = 15
-    for parts in (("dg_spmv_class",), ("pmg_sweep",)):
+    for parts in (("13dg_spmv_classI",), ("pmg_sweep",)):
         for name, u in find(usage, *parts).items():
             assert u["reg"] <= 128 and u["stack"] <= 64, (name, u)
+    # the tensor-pipe class kernel: 2 CTAs of 256 threads (16 warps per SM hide the operand latency), a few spilled words
+    for name, u in find(usage, "17dg_spmv_class_mmaI").items():
+        assert u["reg"] <= 128 and u["stack"] <= 96, (name, u)
     # the Maxwell class kernel holds two cells per lane (one CTA of 256 threads per SM: up to 255 registers)
     for name, u in find(usage, "maxwell_stage_class").items():
         assert u["stack"] <= 64, (name, u)
@@ -68,7 +71,17 @@ def test_spmv_kernels_use_the_tma_engine():
     blocks = [b for b in out.split("Function : ")[1:] if "13maxwell_stageI" in b.split("\n", 1)[0]]
     assert blocks and all("UBLKPF.L2" in b for b in blocks)          # cp.async.bulk.prefetch.L2
     # the class kernels read their block entries as 128-bit shared-memory broadcasts: one LDS.128 per two DFMA
-    blocks = [b for b in out.split("Function : ")[1:] if "dg_spmv_classILi10ELi5ELb1ELb0" in b.split("\n", 1)[0]]
+    blocks = [b for b in out.split("Function : ")[1:] if "13dg_spmv_classILi10ELi5ELb1ELb0" in b.split("\n", 1)[0]]
     assert blocks
     for b in blocks:
         assert b.count("LDS.128") >= 250 and b.count("DFMA") >= 1000 and "DMMA" not in b        # two cells per lane: 4 DFMA per LDS.128
+    # the tensor-pipe class kernel: mma.sync m8n8k4 f64 = DMMA.8x8x4; bs = 15 is two n-tiles x four k-steps x five slots x four m-tiles
+    blocks = [b for b in out.split("Function : ")[1:] if "17dg_spmv_class_mmaILi15ELi5ELb1E" in b.split("\n", 1)[0]]
+    assert blocks
+    for b in blocks:
+        assert b.count("DMMA") >= 160, b.count("DMMA")
+    # bs = 10: one n-tile on the tensor pipe, rows 8 and 9 on DFMA
+    blocks = [b for b in out.split("Function : ")[1:] if "17dg_spmv_class_mmaILi10ELi5ELb1E" in b.split("\n", 1)[0]]
+    assert blocks
+    for b in blocks:
+        assert b.count("DMMA") >= 60 and b.count("DFMA") >= 120, (b.count("DMMA"), b.count("DFMA"))

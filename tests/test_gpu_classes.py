@@ -180,3 +180,32 @@ def test_class_operator_large_mesh(yfd, ctx):
     sysm.set_operator_mode(yfd.OPERATOR_AUTO)
     ta = sysm.true_residual(a["x"])
     assert ta <= 2e-8 and tb <= 2e-8 and abs(ta - tb) <= 0.2 * tb
+
+
+@pytest.mark.parametrize("mtype,r,k", [(0, 4, 2), (0, 4, 3), (0, 3, 4), (1, 4, 2), (1, 4, 3), (1, 3, 4), (0, 6, 3)])
+def test_tensor_pipe_class_kernel_equals_the_cuda_core_one(yfd, ctx, mtype, r, k):
+    """dg_spmv_class_mma (mma.sync m8n8k4 f64, yfd_class_mma.cuh) against dg_spmv_class on the same class cache: the same
+    products summed slot by slot, column chunks in a different order -- y agrees to rounding (1e-14 of |A||x| per row), the
+    fused d.y too, and a CG solve takes the same number of iterations (+-1) to the same solution.  Both the shared-memory
+    (few classes) and the read-through-L1 variant (> 108 KB of fragments: tri k = 3, 4) are covered; ragged tiles come from the
+    boundary classes."""
+    hm = yfd.HostMesh.create(yfd.TRI if mtype == 0 else yfd.QUAD, r)
+    mesh = yfd.Mesh(ctx, hm)
+    sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0)
+    oi = sysm.operator_info()
+    assert oi["uses_classes"], oi
+    x = np.random.default_rng(7).standard_normal(sysm.n)
+    res = {}
+    p = yfd.CgParams(rr_tol=1e-11, rr_max=1e4, max_iter=2 * sysm.n)
+    for mode in (0, 2):
+        with env(YFD_CLS_MMA=mode):
+            res[mode] = (sysm.apply(x), sysm.solve_cg(p))
+    y_plain = sysm.apply(x, plain=True)
+    scale = np.abs(y_plain).max()
+    assert np.abs(res[2][0] - res[0][0]).max() <= 1e-14 * scale
+    assert np.abs(res[2][0] - y_plain).max() <= 1e-14 * scale
+    a, b = res[0][1], res[2][1]
+    assert a["converged"] and b["converged"]
+    assert abs(a["iterations"] - b["iterations"]) <= max(1, a["iterations"] // 200), (a["iterations"], b["iterations"])
+    assert np.linalg.norm(a["x"] - b["x"]) <= 1e-9 * np.linalg.norm(a["x"])
+    sysm.close(); mesh.close()

@@ -303,6 +303,7 @@ struct dg_classes {
     int64_t  npos = 0, ntiles = 0;    /* work list length (classes padded to 32), tiles of 32                           */
     double   max_dev = 0.0, tol = 0.0;/* largest |W_cell - W_class| / max|W_class| found by the verification pass        */
     dbuf<double>  table;              /* [ncls][nf+1][slot stride]: block rows in canonical slot order (self, faces)     */
+    dbuf<double>  table_mma;          /* the same blocks as mma.sync fragments (yfd_class_mma.cuh); bs = 6, 10, 15 only        */
     dbuf<int32_t> work_cell;          /* [npos] local cell index, -1 = padding                                           */
     dbuf<int32_t> work_nbr;           /* [nf][npos] local x cell index of the neighbour across each local face           */
     dbuf<int32_t> tile_cls;           /* [ntiles]                                                                        */

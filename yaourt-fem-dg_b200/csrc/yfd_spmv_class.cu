@@ -38,6 +38,8 @@
 
 namespace yfd {
 
+#include "yfd_class_mma.cuh"
+
 constexpr int CLS_MAX_CLASSES = 4096;        /* beyond this the mesh is not "a few congruence classes" */
 
 /* ---- build: class ids from sorted keys ------------------------------------------------------- */
@@ -358,6 +360,7 @@ yfd_status build_dg_classes(yfd_ctx *ctx, yfd_system *sys, uint64_t *d_keys, int
         for (int64_t v : h) if (!v && ok) { ok = 0; cl.reject = 4; }
     }
     if (!ok) { if (!cl.reject) cl.reject = 3; return YFD_OK; }
+    YFD_TRY(mma_prepare(ctx, cl, bs, nb));
     cl.ready = true;
     return YFD_OK;
 }
@@ -408,9 +411,26 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
     }
 }
 
+/* which systems go to the tensor-pipe kernel (yfd_class_mma.cuh): YFD_CLS_MMA = 0 none, 2 all it is instantiated for, 1 (default)
+ * the ones it was measured faster on (profiles/r02_class_mma.md): bs = 15 always (2.2-2.4x), and any bs >= 6 once there are more
+ * than 16 classes (the reference's triangle meshes: 1.3-1.9x) -- on a handful of classes with bs = 6 or 10 the two kernels tie */
+template <int BS>
+static bool mma_wanted(const dg_classes &cl)
+{
+    const int mode = env_int("YFD_CLS_MMA", 1);
+    if (mode <= 0 || BS < 6) return false;
+    return mode >= 2 || BS == 15 || cl.ncls > 16;
+}
+
 template <int BS, int NB, bool WITH_DOT>
 static yfd_status launch_cls(yfd_ctx *ctx, const dg_classes &cl, const double *x, double *y, cg_scalars *sc, double *partials)
 {
+    if constexpr (BS >= 6) {
+        if (mma_wanted<BS>(cl)) {
+            yfd_status st = YFD_OK;
+            if (launch_cls_mma<BS, NB, WITH_DOT>(ctx, cl, x, y, sc, partials, &st)) return st;
+        }
+    }
     const bool global = (size_t) cl.table_doubles * sizeof(double) + 1024 > ctx->smem_optin;
     auto kern = global ? dg_spmv_class<BS, NB, WITH_DOT, true> : dg_spmv_class<BS, NB, WITH_DOT, false>;
     const size_t smem = global ? 0 : (size_t) cl.table_doubles * sizeof(double);
