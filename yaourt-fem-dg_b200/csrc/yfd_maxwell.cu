@@ -493,6 +493,7 @@ mx_step_args step_args(yfd_maxwell *m)
     s.vin = m->u.p; s.u = m->u.p; s.out = m->s1.p; s.acc = m->acc.p; s.kb = m->kb.p; s.dt = m->delta_t;
     const bool cls = maxwell_uses_classes(m);
     s.table = cls ? m->classes.table.p : nullptr;
+    s.table_mma = cls ? m->classes.table_mma.p : nullptr;
     s.work_cell = cls ? m->classes.work_cell.p : nullptr;
     s.tile_cls = cls ? m->classes.tile_cls.p : nullptr;
     s.ntiles = cls ? m->classes.ntiles : 0;

@@ -33,6 +33,7 @@ struct mx_classes {
     int64_t  npos = 0, ntiles = 0;
     double   max_dev = 0.0, tol = 0.0;
     dbuf<double>  table;                    /* [ncls][2 + 2 nf][slot stride], blocks as [j][i]                         */
+    dbuf<double>  table_mma;                /* the same blocks as mma.sync fragments (yfd_mma_core.cuh); bs = 6, 10, 15 */
     dbuf<int32_t> work_cell, tile_cls, cell_cls;
 };
 
@@ -79,6 +80,7 @@ struct mx_step_args {
     double dt;
     /* class cache in use: one block set per class (global memory, read as warp-uniform loads) + the class-sorted cell list */
     const double *table; const int32_t *work_cell, *tile_cls; int64_t ntiles;
+    const double *table_mma;    /* fragment form of `table` for the tensor-pipe kernel, or null */
 };
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
 yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol);

@@ -30,6 +30,7 @@
  */
 #include "yfd_maxwell.cuh"
 #include "yfd_class_core.cuh"
+#include "yfd_mma_core.cuh"
 #include <cstdlib>
 #include <algorithm>
 
@@ -343,13 +344,27 @@ yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys,
     cl.max_dev = dev; cl.tol = tol; cl.npos = g.npos; cl.ntiles = g.ntiles;
     cl.work_cell = std::move(g.work_cell); cl.tile_cls = std::move(g.tile_cls); cl.cell_cls = std::move(g.cell_cls);
     if (!(dev <= tol)) { cl.reject = 3; return YFD_OK; }
+    YFD_TRY(mma_fragment_table(ctx, cl.table.p, cl.ncls, bs, nb, cl.table_mma));
     cl.ready = true;
     return YFD_OK;
 }
 
+#include "yfd_maxwell_mma.cuh"
+
 template <int NV, int K>
 static yfd_status launch_stage_class(yfd_ctx *ctx, int mode, const mx_step_args &a)
 {
+    /* block sizes the tensor-pipe kernel exists for (YFD_MX_CLASS_MMA=0: the CUDA-core class kernel) */
+    if constexpr (mx_bs(K) == 6 || mx_bs(K) == 10 || mx_bs(K) == 15) {
+        if (a.table_mma && env_int("YFD_MX_CLASS_MMA", 1) != 0) {
+            int64_t grid = (int64_t) ctx->sm_count * 2;
+            const int64_t want = ceil_div(a.ntiles, MMA_THREADS / 32);
+            if (grid > want) grid = want;
+            if (grid < 1) grid = 1;
+            YFD_LAUNCH(ctx, (maxwell_stage_class_mma<NV, K>), (unsigned) grid, MMA_THREADS, 0, a, mode);
+            return YFD_OK;
+        }
+    }
     /* two cells per lane (255 registers, one CTA per SM) unless YFD_MX_CLASS_CELLS=1 asks for the one-cell variant */
     const int cells = env_int("YFD_MX_CLASS_CELLS", 2) == 1 ? 1 : 2;
     int64_t grid = (int64_t) ctx->sm_count * (cells == 1 ? 2 : 1);

@@ -32,6 +32,7 @@
 #include "yfd_internal.hpp"
 #include "yfd_cg_shared.cuh"
 #include "yfd_class_core.cuh"
+#include "yfd_mma_core.cuh"
 #include <vector>
 #include <cmath>
 #include <algorithm>
