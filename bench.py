@@ -412,6 +412,8 @@ def run_maxwell(args, wl, rank, world, local_rank):
             other = dict(kernel="maxwell_stage_class (not chosen: slower than the streamed kernel on this operator)", ms_per_launch=ms_c,
                          kernel_requested_bytes_per_launch=kb_c)
     fp64_peak = ctx.measure_fp64()
+    tensor_pipe = bool(getattr(mx.info, "class_tensor_pipe", 0))
+    tensor_peak = ctx.measure_fp64_tensor() if tensor_pipe else None
     flops_apply = 2.0 * mx.bs * mx.bs * (4 + 6 * mx.nf) * (info["cells"] / world)
     mx.close()
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -438,8 +440,20 @@ def run_maxwell(args, wl, rank, world, local_rank):
                 "note": "achieved / frac = the bytes the kernel requests per launch / CUDA-event time against the measured HBM peak; reference_layout = "
                         "the reference's dense layout, (1+nf)(3bs)^2 8 B per cell + 2 vectors (SURVEY.md 8, cfg 4), over the same time"
                         + ("; this mesh has %d congruence classes of cells, the kernel multiplies by one block set per class and streams vectors and "
-                           "per-cell coefficients only: it is bound by FP64 issue (see fp64), its HBM fraction is low BY DESIGN; streamed_kernel is the "
+                           "per-cell coefficients only: it is bound by FP64 issue (see fp64 / bound), its HBM fraction is low BY DESIGN; streamed_kernel is the "
                            "HBM-bound general path on the same operator" % cls_info["nclasses"] if uses_classes else "")}
+    if uses_classes and tensor_pipe:
+        # the class kernel on the FP64 tensor pipe is bound by that pipe, not by HBM: report it against the DMMA peak measured
+        # now on this device (mma.sync m8n8k4 f64 microbenchmark, yfd_ctx_measure_fp64_tensor), with the HBM figures beside it
+        tf = flops_apply / (ms_apply * 1e-3) / 1e12
+        roofline.update({"bound": "tensor", "kernel": "maxwell_stage_class_mma (operator application, one block set per congruence class, mma.sync m8n8k4 f64)"
+                                                       + ("" if world == 1 else ", rank 0's share of the cells"),
+                         "achieved": tf, "peak": tensor_peak, "unit": "TFLOP/s", "frac": tf / tensor_peak,
+                         "peak_source": "FP64 mma.sync microbenchmark run just now on this device (yfd_ctx_measure_fp64_tensor); useful flops only: "
+                                        "2 bs^2 per block product, the padding of bs to the 8x8x4 tiles is not counted",
+                         "hbm": {"requested_gbs": req, "peak": peak, "frac": req / peak, "peak_source": peak_src}})
+        roofline.pop("hw_frac", None)
+        roofline["fp64"]["tensor_peak_tflops"] = tensor_peak
     if streamed is not None:
         sg = streamed["kernel_requested_bytes_per_launch"] / (streamed["ms_per_launch"] * 1e-3) / 1e9
         streamed.update(kernel="maxwell_stage (factored blocks streamed per cell)", achieved=sg, frac=sg / peak, speedup_of_class_kernel=streamed["ms_per_launch"] / ms_apply)
@@ -738,7 +752,7 @@ def main():
     tpath = os.path.join(ROOT, "profiles", "spmv_traffic.json")
     if os.path.exists(tpath) and world == 1:
         traffic = json.load(open(tpath)).get(args.workload)
-    kname = "csr_spmv_tma" if cfem else ("dg_spmv_class" if oi["uses_classes"] else "dg_spmv_tma")
+    kname = "csr_spmv_tma" if cfem else (("dg_spmv_class_mma" if oi.get("tensor_pipe") else "dg_spmv_class") if oi["uses_classes"] else "dg_spmv_tma")
     roofline = {"bound": "hbm", "kernel": kname + " (y = A d fused with d.y)%s" % ("" if world == 1 else ", rank 0's share of the rows"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "hw_frac": achieved / peak, "traffic": traffic,
                 "traffic_source": None if traffic is None else "static: profiles/spmv_traffic.json (one ncu --set full capture of this kernel on this workload, dram__bytes_read.sum + dram__bytes_write.sum; not a live counter)",

@@ -407,6 +407,7 @@ typedef struct yfd_operator_info {
     double  tolerance;
     int64_t table_bytes;          /* all class block rows                                              */
     int64_t list_entries;         /* class-sorted cell list incl. padding to 32 per class              */
+    int     tensor_pipe;          /* 1: the class kernel is the mma.sync (FP64 tensor pipe) one, dg_spmv_class_mma */
 } yfd_operator_info;
 yfd_status yfd_system_set_operator_mode(yfd_system *sys, int mode);
 yfd_status yfd_system_operator_info(const yfd_system *sys, yfd_operator_info *info);
@@ -481,6 +482,7 @@ typedef struct yfd_maxwell_info {
     int64_t nclasses;
     double  class_max_deviation, class_tolerance;
     int64_t class_table_bytes;
+    int     class_tensor_pipe;        /* 1: the class kernel is maxwell_stage_class_mma (mma.sync m8n8k4 f64)   */
 } yfd_maxwell_info;
 yfd_status yfd_maxwell_set_operator_mode(yfd_maxwell *m, int mode);   /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES */
 

@@ -89,7 +89,7 @@ class MaxwellInfo(C.Structure):
     _fields_ = [("ncells", C.c_int64), ("basis_size", C.c_int64), ("faces_per_elem", C.c_int64), ("ndofs", C.c_int64),
                 ("operator_bytes", C.c_int64), ("reference_operator_bytes", C.c_int64), ("ms_assemble", C.c_double),
                 ("uses_classes", C.c_int), ("class_reject_reason", C.c_int), ("nclasses", C.c_int64),
-                ("class_max_deviation", C.c_double), ("class_tolerance", C.c_double), ("class_table_bytes", C.c_int64)]
+                ("class_max_deviation", C.c_double), ("class_tolerance", C.c_double), ("class_table_bytes", C.c_int64), ("class_tensor_pipe", C.c_int)]
 
 
 class MaxwellStepInfo(C.Structure):
@@ -99,7 +99,7 @@ class MaxwellStepInfo(C.Structure):
 
 class OperatorInfo(C.Structure):
     _fields_ = [("uses_classes", C.c_int), ("classes_available", C.c_int), ("reject_reason", C.c_int), ("nclasses", C.c_int64),
-                ("max_deviation", C.c_double), ("tolerance", C.c_double), ("table_bytes", C.c_int64), ("list_entries", C.c_int64)]
+                ("max_deviation", C.c_double), ("tolerance", C.c_double), ("table_bytes", C.c_int64), ("list_entries", C.c_int64), ("tensor_pipe", C.c_int)]
 
 
 OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES = 0, 1, 2

@@ -886,6 +886,7 @@ yfd_status yfd_system_operator_info(const yfd_system *sys, yfd_operator_info *in
     info->tolerance = cl.tol;
     info->table_bytes = (int64_t) cl.table_doubles * 8;
     info->list_entries = cl.npos;
+    info->tensor_pipe = (info->uses_classes && dg_class_kernel_is_mma(cl, sys->bs)) ? 1 : 0;
     return YFD_OK;
 }
 

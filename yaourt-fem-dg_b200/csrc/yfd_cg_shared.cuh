@@ -156,6 +156,9 @@ yfd_status launch_dg_spmv_tma(yfd_ctx *ctx, int bs, int nf, const int64_t *cellp
 template <bool WITH_DOT>
 yfd_status launch_dg_spmv_class(yfd_ctx *ctx, const dg_classes &cl, int bs, int nf, const double *x, double *y, cg_scalars *sc, double *partials);
 
+/* whether launch_dg_spmv_class takes the tensor-pipe kernel (yfd_class_mma.cuh) for this cache */
+bool dg_class_kernel_is_mma(const dg_classes &cl, int bs);
+
 /* yfd_pmg.cu: z = M^-1 r by one p-multigrid V-cycle, then r.z -> sc2->dy; every launch is gated by sc2->done */
 yfd_status pmg_apply(yfd_ctx *ctx, yfd_system *sys, const double *r, double *z, cg_scalars *sc2, double *partials);
 

@@ -696,6 +696,7 @@ void yfd_maxwell_get_info(const yfd_maxwell *m, yfd_maxwell_info *info)
     info->class_max_deviation = m->classes.max_dev;
     info->class_tolerance = m->classes.tol;
     info->class_table_bytes = (int64_t) m->classes.table.n * 8;
+    info->class_tensor_pipe = (info->uses_classes && m->classes.table_mma.p && env_int("YFD_MX_CLASS_MMA", 1) != 0) ? 1 : 0;
 }
 
 yfd_status yfd_maxwell_set_operator_mode(yfd_maxwell *m, int mode)

@@ -415,19 +415,18 @@ dg_spmv_class(const double *__restrict__ table, int table_doubles, const int32_t
 /* which systems go to the tensor-pipe kernel (yfd_class_mma.cuh): YFD_CLS_MMA = 0 none, 2 all it is instantiated for, 1 (default)
  * the ones it was measured faster on (profiles/r02_class_mma.md): bs = 15 always (2.2-2.4x), and any bs >= 6 once there are more
  * than 16 classes (the reference's triangle meshes: 1.3-1.9x) -- on a handful of classes with bs = 6 or 10 the two kernels tie */
-template <int BS>
-static bool mma_wanted(const dg_classes &cl)
+bool dg_class_kernel_is_mma(const dg_classes &cl, int bs)
 {
     const int mode = env_int("YFD_CLS_MMA", 1);
-    if (mode <= 0 || BS < 6) return false;
-    return mode >= 2 || BS == 15 || cl.ncls > 16;
+    if (mode <= 0 || !cl.table_mma.p || (bs != 6 && bs != 10 && bs != 15)) return false;
+    return mode >= 2 || bs == 15 || cl.ncls > 16;
 }
 
 template <int BS, int NB, bool WITH_DOT>
 static yfd_status launch_cls(yfd_ctx *ctx, const dg_classes &cl, const double *x, double *y, cg_scalars *sc, double *partials)
 {
-    if constexpr (BS >= 6) {
-        if (mma_wanted<BS>(cl)) {
+    if constexpr (BS == 6 || BS == 10 || BS == 15) {
+        if (dg_class_kernel_is_mma(cl, BS)) {
             yfd_status st = YFD_OK;
             if (launch_cls_mma<BS, NB, WITH_DOT>(ctx, cl, x, y, sc, partials, &st)) return st;
         }
