@@ -14,6 +14,10 @@
  *     self:  Hx += Gy (-Ez);  Hy += Gx Ez;  Ez += Gx Hy + Gy (-Hx);  field += T_f w_field,f(self)   for every face f
  *     nbr f: field -= N_f w_field,f(nbr)
  * The sink (plain application, RK4 stages, Euler) is maxwell_stage's.
+ *
+ * Measured and not kept (profiles/r02_class_mma.md): two m-tiles per warp sharing every block fragment (236-255 registers, one
+ * CTA per SM) is 30-45 % slower than one m-tile with two CTAs per SM; sending the results through a per-warp shared-memory
+ * buffer so that they leave as flat runs instead of 8-byte pieces of 8 cells is 5-10 % slower as well.
  */
 #pragma once
 
