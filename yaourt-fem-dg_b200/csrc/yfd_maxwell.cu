@@ -647,7 +647,10 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
         if (m->classes.ready) {
             /* which kernel for AUTO: time both on this operator (one warm-up + 3 launches each, plain application of the zero
              * state into a stage buffer); YFD_MX_CLASSES=2 skips the timing and takes the class kernel */
-            if (env_int("YFD_MX_CLASSES", 1) == 2) m->classes_faster = true;
+            /* the tensor-pipe class kernel beat the streamed one on every operator it was measured on (2.7-4.2x at 7.9-47 M
+             * unknowns, profiles/r02_class_mma.md): no timing needed, which would cost 8 launches of every creation */
+            const bool tensor = m->classes.table_mma.p && env_int("YFD_MX_CLASS_MMA", 1) != 0;
+            if (env_int("YFD_MX_CLASSES", 1) == 2 || (tensor && env_int("YFD_MX_CLASSES", 1) != 3)) m->classes_faster = true;
             else {
                 double ms[2] = { 0.0, 0.0 };
                 for (int mode = 1; mode <= 2; mode++) {
