@@ -92,3 +92,27 @@ def test_cfem_p1_matches_reference(yfd, ref, ctx, levels):
     assert np.array_equal(cmap[~bnd], np.arange(sysm.n))
     ex = sysm.expand(res["x"])
     assert np.array_equal(ex[~bnd], res["x"]) and not ex[bnd].any()
+
+
+@pytest.mark.parametrize("order,kind,size", [(1, "r", 5), (2, "r", 4), (2, "s", 37), (1, "s", 200)])
+def test_cfem_rows_gathered_from_cells_equal_the_triplet_sort(yfd, ctx, order, kind, size):
+    """The continuous-FEM builder gathers each row from the cells around its node (csr_from_cell_rows) instead of sorting all
+    triplets; duplicates are added in cell order either way, so pattern, values and right-hand side are the SAME BITS as the
+    generic path (YFD_CFEM_SORT=1 = blaze::init_from_triplets restated, core/blaze_sparse_init.hpp:101-155)."""
+    import os
+    hm = yfd.HostMesh.create(yfd.TRI, size) if kind == "r" else yfd.HostMesh.structured(yfd.TRI, size)
+    mesh = yfd.Mesh(ctx, hm)
+    res = {}
+    for mode in ("0", "1"):
+        os.environ["YFD_CFEM_SORT"] = mode
+        try:
+            sysm = ctx.cfem_assemble_p2(mesh) if order == 2 else ctx.cfem_assemble_p1(mesh)
+        finally:
+            os.environ.pop("YFD_CFEM_SORT", None)
+        res[mode] = (sysm.n, sysm.nnz) + sysm.csr() + (sysm.rhs(),)
+        sysm.close()
+    a, b = res["0"], res["1"]
+    assert a[0] == b[0] and a[1] == b[1] and a[1] > 0
+    for u, v in zip(a[2:], b[2:]):
+        assert np.array_equal(u, v)
+    mesh.close()

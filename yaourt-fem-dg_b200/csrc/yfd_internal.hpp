@@ -388,6 +388,8 @@ yfd_status ensure_pmg(yfd_ctx *ctx, yfd_system *sys);
 int key_bits_for(int64_t n);
 /* keys = row << col_bits | col, already on the device (clobbered); folds duplicates in input order.  Entries of
  * `discard_row` (-1: none) keep their slot but are not summed (the CFEM assemblers' sentinel row) */
+yfd_status csr_from_cell_rows(yfd_ctx *ctx, int64_t n, int64_t ncells, int ld, const uint64_t *d_mkeys, int col_bits, int row_bits,
+                              const double *d_mvals, const uint64_t *d_rkeys, const double *d_rvals, yfd_csr *A, double *d_rhs, bool *built);
 yfd_status csr_from_device_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, int64_t count,
                                     uint64_t *d_keys, int col_bits, int row_bits, const double *d_vals, yfd_csr *A,
                                     int64_t discard_row = -1);

@@ -377,27 +377,36 @@ static yfd_status build_cfem(yfd_ctx *ctx, yfd_mesh *mesh, int order, int rhs_fn
     t_elem.stop(ctx->stream);
     unsigned long long hc[2] = { 0, 0 };
     YFD_TRY(counts.download(ctx, hc, 2));
-    /* the fold ignores the sentinel tail: sort everything, then build from the first hc[] records.
-     * A sentinel has row n, so give the builder n+1 rows and drop the last one afterwards. */
-    yfd_csr full;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, ntrip, mkeys.p, col_bits, row_bits, mvals.p, &full, n));
-    /* rows 0..n-1 of `full` are the matrix; row n holds the folded sentinel (one entry) */
-    sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n;
-    int64_t nnz = 0;
-    YFD_CUDA(ctx, cudaMemcpyAsync(&nnz, full.rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    sys->A.nnz = nnz; sys->nnz = nnz;
-    sys->A.rowptr = std::move(full.rowptr);      /* first n+1 entries are exactly the matrix's offsets */
-    sys->A.rowptr.n = (size_t) n + 1;
-    sys->A.colidx = std::move(full.colidx);
-    sys->A.values = std::move(full.values);
-    sys->A.colidx.n = (size_t) nnz; sys->A.values.n = (size_t) nnz;
-
-    yfd_csr rf;
-    YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nrtrip, rkeys.p, 1, row_bits, rvals.p, &rf, n));
+    /* rows gathered from the cells around each node (yfd_triplets.cu: csr_from_cell_rows); YFD_CFEM_SORT=1, or a row with more
+     * columns than that path holds, takes the generic triplet sort instead -- same fold order, same bits */
+    bool built = false;
     YFD_TRY(sys->rhs.alloc(ctx, (size_t) n, 2));
-    YFD_LAUNCH(ctx, rhs_from_fold, (unsigned) ceil_div(std::max<int64_t>(n, 1), 256), 256, 0, rf.rowptr.p, rf.values.p, n, sys->rhs.p);
-    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (env_int("YFD_CFEM_SORT", 0) == 0)
+        YFD_TRY(csr_from_cell_rows(ctx, n, nc, ldofs, mkeys.p, col_bits, row_bits, mvals.p, rkeys.p, rvals.p, &sys->A, sys->rhs.p, &built));
+    int64_t nnz = 0;
+    if (built) {
+        nnz = sys->A.nnz; sys->nnz = nnz;
+    } else {
+        /* the fold ignores the sentinel tail: sort everything, then build from the first hc[] records.
+         * A sentinel has row n, so give the builder n+1 rows and drop the last one afterwards. */
+        yfd_csr full;
+        YFD_TRY(csr_from_device_triplets(ctx, n + 1, n > 0 ? n : 1, ntrip, mkeys.p, col_bits, row_bits, mvals.p, &full, n));
+        /* rows 0..n-1 of `full` are the matrix; row n holds the folded sentinel (one entry) */
+        sys->A.ctx = ctx; sys->A.nrows = n; sys->A.ncols = n;
+        YFD_CUDA(ctx, cudaMemcpyAsync(&nnz, full.rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        sys->A.nnz = nnz; sys->nnz = nnz;
+        sys->A.rowptr = std::move(full.rowptr);      /* first n+1 entries are exactly the matrix's offsets */
+        sys->A.rowptr.n = (size_t) n + 1;
+        sys->A.colidx = std::move(full.colidx);
+        sys->A.values = std::move(full.values);
+        sys->A.colidx.n = (size_t) nnz; sys->A.values.n = (size_t) nnz;
+
+        yfd_csr rf;
+        YFD_TRY(csr_from_device_triplets(ctx, n + 1, 2, nrtrip, rkeys.p, 1, row_bits, rvals.p, &rf, n));
+        YFD_LAUNCH(ctx, rhs_from_fold, (unsigned) ceil_div(std::max<int64_t>(n, 1), 256), 256, 0, rf.rowptr.p, rf.values.p, n, sys->rhs.p);
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     (void) hc;
     if (info) {
         info->system_size = n; info->nnz = nnz; info->basis_size = ldofs;

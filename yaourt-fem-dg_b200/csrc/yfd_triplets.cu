@@ -196,6 +196,108 @@ yfd_status csr_from_device_triplets(yfd_ctx *ctx, int64_t nrows, int64_t ncols, 
     return YFD_OK;
 }
 
+/* ---- continuous FEM: rows gathered from the cells around each node ---------------------------------------------------------
+ * The generic path above sorts every triplet by (row, col): 72 M records and six radix passes for 2 M P2 cells.  A continuous-FEM
+ * row, though, is the sum of the local rows of the few cells around its node: sorting the nc * ld (row, cell-local row) pairs
+ * by row (6x fewer records, row bits only) gives each row its cells in ascending cell order, and one thread per row then merges
+ * their ld-entry local rows into a sorted list of unique columns -- adding duplicates in cell order, i.e. in the order the
+ * stable triplet sort would have produced (same bits).  The right-hand side falls out of the same traversal. */
+constexpr int CFEM_MAX_ROW = 64;             /* unique columns a row may have on this path (P2, valence 8: 25); beyond: generic path */
+
+__global__ void lower_bound_rows(const uint64_t *__restrict__ sorted_keys, int64_t count, int64_t nrows, int shift, int64_t *__restrict__ start)
+{
+    const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (r > nrows) return;
+    int64_t lo = 0, hi = count;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if ((int64_t) (sorted_keys[mid] >> shift) < r) lo = mid + 1; else hi = mid;
+    }
+    start[r] = lo;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(128)
+cfem_gather_rows(const int64_t *__restrict__ adj_start, const uint32_t *__restrict__ adj, int ld, const uint64_t *__restrict__ mkeys,
+                 const double *__restrict__ mvals, const double *__restrict__ rvals, int64_t nrows, int col_bits,
+                 int32_t *__restrict__ cnt, const int64_t *__restrict__ rowptr, int32_t *__restrict__ colidx, double *__restrict__ values,
+                 double *__restrict__ rhs, int *__restrict__ overflow)
+{
+    const int64_t r = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nrows) return;
+    const uint64_t cmask = (col_bits >= 64 ? ~0ull : ((1ull << col_bits) - 1));
+    int32_t cols[CFEM_MAX_ROW];
+    double vals[FILL ? CFEM_MAX_ROW : 1];
+    int nu = 0;
+    double b = 0.0;
+    bool over = false;
+    for (int64_t p = adj_start[r]; p < adj_start[r + 1]; p++) {
+        const uint32_t e = adj[p];                         /* cell * ld + local row: ascending, the sort is stable */
+        if (FILL) b += rvals[e];
+        const int64_t base = (int64_t) e * ld;
+        for (int j = 0; j < ld; j++) {
+            const uint64_t key = mkeys[base + j];
+            if ((int64_t) (key >> col_bits) != r) continue;          /* a Dirichlet column: parked under the sentinel row */
+            const int32_t c = (int32_t) (key & cmask);
+            int k = nu;
+            while (k > 0 && cols[k - 1] > c) k--;
+            if (k > 0 && cols[k - 1] == c) { if (FILL) vals[k - 1] += mvals[base + j]; continue; }
+            if (nu == CFEM_MAX_ROW) { over = true; continue; }
+            for (int q = nu; q > k; q--) { cols[q] = cols[q - 1]; if (FILL) vals[q] = vals[q - 1]; }
+            cols[k] = c;
+            if (FILL) vals[k] = mvals[base + j];
+            nu++;
+        }
+    }
+    if (over) atomicExch(overflow, 1);
+    if (!FILL) { cnt[r] = nu; return; }
+    const int64_t o = rowptr[r];
+    for (int k = 0; k < nu; k++) { colidx[o + k] = cols[k]; values[o + k] = vals[k]; }
+    rhs[r] = b;
+}
+
+/* *built = false (nothing allocated in A) when a row has more than CFEM_MAX_ROW columns: the caller takes the generic path */
+yfd_status csr_from_cell_rows(yfd_ctx *ctx, int64_t n, int64_t ncells, int ld, const uint64_t *d_mkeys, int col_bits, int row_bits,
+                              const double *d_mvals, const uint64_t *d_rkeys, const double *d_rvals, yfd_csr *A, double *d_rhs, bool *built)
+{
+    *built = false;
+    const int64_t npairs = ncells * ld;
+    if (n <= 0 || npairs <= 0 || npairs >= 0xffffffffll) return YFD_OK;
+    dbuf<uint64_t> keys, keys2;
+    dbuf<uint32_t> adj, adj2;
+    YFD_TRY(keys.alloc(ctx, (size_t) npairs)); YFD_TRY(keys2.alloc(ctx, (size_t) npairs));
+    YFD_TRY(adj.alloc(ctx, (size_t) npairs)); YFD_TRY(adj2.alloc(ctx, (size_t) npairs));
+    YFD_CUDA(ctx, cudaMemcpyAsync(keys.p, d_rkeys, (size_t) npairs * sizeof(uint64_t), cudaMemcpyDeviceToDevice, ctx->stream));
+    YFD_TRY(fill_iota_u32(ctx, adj.p, npairs));
+    YFD_TRY(radix_sort_pairs(ctx, keys.p, adj.p, keys2.p, adj2.p, npairs, row_bits + 1));      /* rkeys = row << 1, sentinel row n */
+    keys2.release(); adj2.release();
+    dbuf<int64_t> start;
+    dbuf<int32_t> cnt;
+    dbuf<int> over;
+    YFD_TRY(start.alloc(ctx, (size_t) n + 1)); YFD_TRY(cnt.alloc(ctx, (size_t) n)); YFD_TRY(over.alloc(ctx, 1)); YFD_TRY(over.zero(ctx));
+    YFD_LAUNCH(ctx, lower_bound_rows, (unsigned) ceil_div(n + 1, 256), 256, 0, (const uint64_t *) keys.p, npairs, n, 1, start.p);
+    const unsigned g = (unsigned) ceil_div(n, 128);
+    YFD_LAUNCH(ctx, cfem_gather_rows<false>, g, 128, 0, (const int64_t *) start.p, (const uint32_t *) adj.p, ld, d_mkeys, d_mvals, d_rvals, n, col_bits,
+               cnt.p, (const int64_t *) nullptr, (int32_t *) nullptr, (double *) nullptr, (double *) nullptr, over.p);
+    int hover = 0;
+    YFD_TRY(over.download(ctx, &hover, 1));
+    if (hover) return YFD_OK;
+    A->ctx = ctx; A->nrows = n; A->ncols = n;
+    YFD_TRY(A->rowptr.alloc(ctx, (size_t) n + 1, 2));
+    YFD_TRY(exclusive_scan_i32_to_i64(ctx, cnt.p, A->rowptr.p, n));
+    int64_t nnz = 0;
+    YFD_CUDA(ctx, cudaMemcpyAsync(&nnz, A->rowptr.p + n, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    A->nnz = nnz;
+    YFD_TRY(A->colidx.alloc(ctx, (size_t) nnz, 4));
+    YFD_TRY(A->values.alloc(ctx, (size_t) nnz, 4));
+    YFD_LAUNCH(ctx, cfem_gather_rows<true>, g, 128, 0, (const int64_t *) start.p, (const uint32_t *) adj.p, ld, d_mkeys, d_mvals, d_rvals, n, col_bits,
+               cnt.p, (const int64_t *) A->rowptr.p, A->colidx.p, A->values.p, d_rhs, over.p);
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *built = true;
+    return YFD_OK;
+}
+
 int key_bits_for(int64_t n) { return bits_for(n); }
 
 } // namespace yfd
