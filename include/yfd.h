@@ -427,6 +427,18 @@ yfd_status yfd_system_apply(yfd_ctx *ctx, yfd_system *sys, int kernel, const dou
  * yfd_system_solve_cg returns it; the sums are combined over the ranks). */
 yfd_status yfd_system_true_residual(yfd_ctx *ctx, yfd_system *sys, const double *x_host, const double *d_x, double *rel_residual);
 
+/* The same true residual for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The call allocates nothing -- no cudaMalloc / cudaFree, no pool, no allocating library routine: its scratch (y = A x, the
+ * partial sums) lives in one static device array of YFD_NOALLOC_MAX_ROWS doubles + 16 KiB (4 MiB in all) that every GPU
+ * loading this library holds until the process exits.  d_x [n]: DEVICE vector in REFERENCE numbering; *rel_residual: host.
+ * One GPU only (YFD_ERR_UNSUPPORTED on a partitioned system); YFD_ERR_UNSUPPORTED with a message naming the limit when the
+ * system has more than YFD_NOALLOC_MAX_ROWS rows.  Same arithmetic in the same order as yfd_system_true_residual: the two
+ * agree bit for bit.  The array is shared by all calls on a device and keeps the last call's contents (every word read
+ * is written first by the same call); calls that OVERLAP on one GPU race on it -- serialise them. */
+#define YFD_NOALLOC_MAX_ROWS 524288
+yfd_status yfd_system_true_residual_noalloc(yfd_ctx *ctx, yfd_system *sys, const double *d_x, double *rel_residual);
+
 /* Time `reps` launches of y = A d for this system with CUDA events on the context's stream
  * (bench.py's roofline leg).  Returns average ms per launch and the algorithmic CSR bytes of one
  * launch (12 nnz + 8 (n+1) + 16 n) plus the bytes the kernel actually

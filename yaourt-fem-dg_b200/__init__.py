@@ -9,5 +9,5 @@ from .capi import (  # noqa: F401
     YfdError, lib, lib_path, Context, HostMesh, Mesh, Csr, System, CgParams, CgInfo, AssemblyInfo,
     declared_symbols, partition_plan, partition_plan_from_cuts, Maxwell, MaxwellConfig, MaxwellInfo, MaxwellStepInfo,
     TI_RK4, TI_EULER, FIELDS_CAVITY_11, FIELDS_ZERO, PC_NONE, PC_JACOBI, PC_BLOCK_JACOBI,
-    OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES, OperatorInfo, PC_PMG, PmgInfo,
+    OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES, OperatorInfo, PC_PMG, PmgInfo, NOALLOC_MAX_ROWS,
 )

@@ -103,6 +103,7 @@ class OperatorInfo(C.Structure):
 
 
 OPERATOR_AUTO, OPERATOR_STREAMED, OPERATOR_CLASSES = 0, 1, 2
+NOALLOC_MAX_ROWS = 524288          # YFD_NOALLOC_MAX_ROWS (include/yfd.h)
 
 
 class PmgInfo(C.Structure):
@@ -200,6 +201,7 @@ def lib():
         "yfd_system_operator_info": (cint, [vp, P(OperatorInfo)]),
         "yfd_system_apply": (cint, [vp, vp, cint, _f64p, _f64p]),
         "yfd_system_true_residual": (cint, [vp, vp, vp, vp, P(dbl)]),
+        "yfd_system_true_residual_noalloc": (cint, [vp, vp, vp, P(dbl)]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
         "yfd_dg_postprocess": (cint, [vp, vp, cint, cint, _f64p, P(dbl), P(dbl)]),
         "yfd_dg_postprocess_device": (cint, [vp, vp, cint, cint, vp, P(dbl), P(dbl)]),
@@ -679,6 +681,13 @@ class System:
             x = np.ascontiguousarray(x, np.float64)
             assert x.shape == (self.n,)
         self.ctx.check(lib().yfd_system_true_residual(self.ctx._h, self._h, _ptr(x), C.c_void_p(d_x) if d_x else None, C.byref(r)))
+        return r.value
+
+    def true_residual_noalloc(self, d_x):
+        """yfd_system_true_residual_noalloc: the same number from a call that allocates nothing (static device scratch,
+        at most NOALLOC_MAX_ROWS rows, one GPU); d_x = raw device pointer, reference numbering.  No reference counterpart."""
+        r = C.c_double()
+        self.ctx.check(lib().yfd_system_true_residual_noalloc(self.ctx._h, self._h, C.c_void_p(d_x), C.byref(r)))
         return r.value
 
     def local_sizes(self):
