@@ -61,4 +61,61 @@ __device__ __forceinline__ void lu_solve_column(const double *A, const int *piv,
     }
 }
 
+/* The same solve with the column held in registers and the factors read from a TRANSPOSED copy FT[k * LDT + i] = A[i][k]
+ * (LDT even, FT 16-byte aligned): for a fixed step k the entries below / above the diagonal are contiguous, so every lane reads the
+ * same 16 bytes (one broadcast wavefront per two updates) and the updates of one step are independent FMAs on registers -- no
+ * load / store of the column and no address arithmetic per update, which is what the shared-memory form above spends most of
+ * its instructions on.  Same operations in the same order: identical bits. */
+template <int BS, int LDT>
+__device__ __forceinline__ void lu_transpose_factors(const double *A, double *FT, int lane)
+{
+    for (int m = lane; m < BS * BS; m += 32) {
+        const int i = m / BS, k = m - i * BS;
+        FT[k * LDT + i] = A[i * BS + k];
+    }
+}
+
+template <int BS, int LDT>
+__device__ __forceinline__ void lu_solve_column_reg(const double *FT, const int *piv, double *R, int ld, int c)
+{
+    static_assert(LDT % 2 == 0 && LDT >= BS, "transposed factors: even leading dimension");
+#pragma unroll 1
+    for (int k = 0; k < BS; k++) {
+        const int p = piv[k];
+        if (p != k) { const double t = R[k * ld + c]; R[k * ld + c] = R[p * ld + c]; R[p * ld + c] = t; }
+    }
+    double r[BS];
+#pragma unroll
+    for (int i = 0; i < BS; i++) r[i] = R[i * ld + c];
+#pragma unroll
+    for (int k = 0; k < BS; k++) {
+        const double bk = r[k];
+        const double *col = FT + k * LDT;
+        const int ie = (k + 2) & ~1;                          /* first even row below the diagonal */
+        if (k + 1 < ie && k + 1 < BS) r[k + 1] = fma(-col[k + 1], bk, r[k + 1]);
+#pragma unroll
+        for (int i = ie; i + 1 < BS; i += 2) {
+            const double2 l = *reinterpret_cast<const double2 *>(col + i);
+            r[i] = fma(-l.x, bk, r[i]);
+            r[i + 1] = fma(-l.y, bk, r[i + 1]);
+        }
+        if (ie < BS && ((BS - ie) & 1)) r[BS - 1] = fma(-col[BS - 1], bk, r[BS - 1]);
+    }
+#pragma unroll
+    for (int k = BS - 1; k >= 0; k--) {
+        const double *col = FT + k * LDT;
+        const double bk = r[k] / col[k];
+        r[k] = bk;
+#pragma unroll
+        for (int i = 0; i + 1 < k; i += 2) {
+            const double2 u = *reinterpret_cast<const double2 *>(col + i);
+            r[i] = fma(-u.x, bk, r[i]);
+            r[i + 1] = fma(-u.y, bk, r[i + 1]);
+        }
+        if (k & 1) r[k - 1] = fma(-col[k - 1], bk, r[k - 1]);
+    }
+#pragma unroll
+    for (int i = 0; i < BS; i++) R[i * ld + c] = r[i];
+}
+
 } // namespace yfd

@@ -63,7 +63,9 @@ struct mx_asm_shape {
     static constexpr int BS = mx_bs(K), NB = mx_nb(NV), NR = NB * BS, LD = NR | 1;
     static constexpr int NQ = dg_nq_cell(NV, K), NFQ = K + 1;
     static constexpr int CELL_TAB = NQ * (1 + 3 * BS), FACE_TAB = NFQ * (1 + 2 * BS);
-    static constexpr int TAB = CELL_TAB > FACE_TAB ? CELL_TAB : FACE_TAB;
+    static constexpr int LDT = (BS + 1) & ~1;                             /* transposed LU factors for the column solves */
+    static constexpr int TAB0 = CELL_TAB > FACE_TAB ? CELL_TAB : FACE_TAB;
+    static constexpr int TAB = TAB0 > BS * LDT + 1 ? TAB0 : BS * LDT + 1;  /* the factors' copy reuses the table area */
     static constexpr int WARP_DBL = BS * BS + BS * LD + TAB + 16;          /* + pivots (32 ints) */
     static constexpr int WARPS = (200 * 1024 / 8) / WARP_DBL >= 4 ? 4 : (200 * 1024 / 8) / WARP_DBL >= 2 ? 2 : 1;
 };
@@ -99,20 +101,22 @@ maxwell_assemble(const mx_asm_args a)
 
         /* ---- 1. cell tables and M, Sx, Sy ---- */
         {
+            /* tables as [q][function] (BS odd or not, lanes j = consecutive functions read consecutive words: no bank conflicts;
+             * [function][q] with NQ = 16 put every j on the same bank) */
             double *W = T, *PHI = T + NQ, *DX = PHI + NQ * BS, *DY = DX + NQ * BS;
             for (int q = lane; q < NQ; q += 32) {
                 double x, y, w;
                 cell_quad_point<NV, K>(P, q, a.cell_rule, a.gx, a.gw, x, y, w);
                 W[q] = w;
-                basis_eval<K>::run(x, y, xb, yb, h, PHI + q, DX + q, DY + q, NQ);
+                basis_eval<K>::run(x, y, xb, yb, h, PHI + q * BS, DX + q * BS, DY + q * BS, 1);
             }
             __syncwarp();
             for (int m = lane; m < BS2; m += 32) {
                 const int i = m / BS, j = m - i * BS;
                 double sm = 0.0, sx = 0.0, sy = 0.0;
                 for (int q = 0; q < NQ; q++) {
-                    const double wp = W[q] * PHI[i * NQ + q];
-                    sm += wp * PHI[j * NQ + q]; sx += wp * DX[j * NQ + q]; sy += wp * DY[j * NQ + q];
+                    const double wp = W[q] * PHI[q * BS + i];
+                    sm += wp * PHI[q * BS + j]; sx += wp * DX[q * BS + j]; sy += wp * DY[q * BS + j];
                 }
                 MM[i * BS + j] = sm;
                 a.gM[cell * BS2 + m] = sm;
@@ -191,7 +195,12 @@ maxwell_assemble(const mx_asm_args a)
 
         /* ---- 3. M^-1: factor once, then independent columns ---- */
         if (!warp_lu_factor<BS>(MM, piv, lane) && lane == 0) atomicExch(a.err, 1);
-        for (int c = lane; c < NR; c += 32) lu_solve_column<BS>(MM, piv, R, LD, c);
+        {
+            double *FT = T + ((reinterpret_cast<uintptr_t>(T) & 8) ? 1 : 0);        /* 16-byte aligned */
+            lu_transpose_factors<BS, S::LDT>(MM, FT, lane);
+            __syncwarp();
+            for (int c = lane; c < NR; c += 32) lu_solve_column_reg<BS, S::LDT>(FT, piv, R, LD, c);
+        }
         __syncwarp();
 
         /* ---- 4. blocks -> HBM, [chunk][b][j][slot * BS + i] ---- */
