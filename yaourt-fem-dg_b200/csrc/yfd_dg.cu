@@ -134,7 +134,7 @@ dg_sip_cells(const dg_args a)
             }
             W[q] = w;
             WF[q] = w * eval_fn(a.rhs_fn, x, y);
-            basis_eval<K>::run(x, y, xb, yb, h, PHI + q, DX + q, DY + q, NQ);     /* [i][q] layout */
+            basis_eval<K>::run(x, y, xb, yb, h, PHI + q * BS, DX + q * BS, DY + q * BS, 1);     /* [q][i] layout: lanes = consecutive i, no bank conflicts */
         }
         __syncwarp();
 
@@ -148,16 +148,16 @@ dg_sip_cells(const dg_args a)
                 const int j = m / BS, i = m - j * BS;
                 for (int q = 0; q < NQ; q++) {
                     if (ADV)        /* K += mu w phi phi^T + w phi (dphi beta)^T, dg2d_advection.cpp:151-154 */
-                        s += W[q] * PHI[i * NQ + q] * (ADV_MU * PHI[j * NQ + q] + ADV_BX * DX[j * NQ + q] + ADV_BY * DY[j * NQ + q]);
+                        s += W[q] * PHI[q * BS + i] * (ADV_MU * PHI[q * BS + j] + ADV_BX * DX[q * BS + j] + ADV_BY * DY[q * BS + j]);
                     else
-                        s += W[q] * (DX[i * NQ + q] * DX[j * NQ + q] + DY[i * NQ + q] * DY[j * NQ + q]);
+                        s += W[q] * (DX[q * BS + i] * DX[q * BS + j] + DY[q * BS + i] * DY[q * BS + j]);
                 }
             }
             accD[t] = s;
         }
         double rhs_i = 0.0;                     /* lanes < BS; BS <= 28 */
         if (lane < BS)
-            for (int q = 0; q < NQ; q++) rhs_i += WF[q] * PHI[lane * NQ + q];
+            for (int q = 0; q < NQ; q++) rhs_i += WF[q] * PHI[q * BS + lane];
 
         if (a.blocks_mode) {
             if (a.oK) {
@@ -214,11 +214,11 @@ dg_sip_cells(const dg_args a)
                 double phi[BS], gx[BS], gy[BS];
                 basis_eval<K>::run(x, y, xb, yb, h, phi, gx, gy, 1);
 #pragma unroll
-                for (int i = 0; i < BS; i++) { TPHI[i * NFQ + q] = phi[i]; TGN[i * NFQ + q] = gx[i] * nx + gy[i] * ny; }
+                for (int i = 0; i < BS; i++) { TPHI[q * BS + i] = phi[i]; TGN[q * BS + i] = gx[i] * nx + gy[i] * ny; }
                 if (has_nb) {
                     basis_eval<K>::run(x, y, nxb, nyb, nh, phi, gx, gy, 1);
 #pragma unroll
-                    for (int i = 0; i < BS; i++) { NPHI[i * NFQ + q] = phi[i]; NGN[i * NFQ + q] = gx[i] * nx + gy[i] * ny; }
+                    for (int i = 0; i < BS; i++) { NPHI[q * BS + i] = phi[i]; NGN[q * BS + i] = gx[i] * nx + gy[i] * ny; }
                 }
             }
             __syncwarp();
@@ -237,15 +237,15 @@ dg_sip_cells(const dg_args a)
                     double att = 0.0, atn = 0.0;
                     for (int q = 0; q < NFQ; q++) {
                         const double w = FW[q];
-                        const double ti = TPHI[i * NFQ + q], tj = TPHI[j * NFQ + q];
+                        const double ti = TPHI[q * BS + i], tj = TPHI[q * BS + j];
                         if (ADV) {
                             att += w * att_c * ti * tj;
-                            if (has_nb) atn += w * fi_coeff * 0.5 * ti * NPHI[j * NFQ + q];      /* dg2d_advection.cpp:206 */
+                            if (has_nb) atn += w * fi_coeff * 0.5 * ti * NPHI[q * BS + j];      /* dg2d_advection.cpp:206 */
                         } else {
-                            const double gi = TGN[i * NFQ + q], gj = TGN[j * NFQ + q];
+                            const double gi = TGN[q * BS + i], gj = TGN[q * BS + j];
                             att += w * (eta_l * ti * tj - c * ti * gj - c * gi * tj);
                             if (has_nb) {
-                                const double pj = NPHI[j * NFQ + q], hj = NGN[j * NFQ + q];
+                                const double pj = NPHI[q * BS + j], hj = NGN[q * BS + j];
                                 atn += w * (-eta_l * ti * pj - 0.5 * ti * hj + 0.5 * gi * pj);    /* :178-180 */
                             }
                         }
@@ -263,7 +263,7 @@ dg_sip_cells(const dg_args a)
             if (!ADV && !has_nb && lane < BS) {
                 /* loc_rhs -= w g (grad phi . n) ; loc_rhs += w eta_l g phi   (:190-191) */
                 for (int q = 0; q < NFQ; q++)
-                    rhs_i += FG[q] * (eta_l * TPHI[lane * NFQ + q] - TGN[lane * NFQ + q]);
+                    rhs_i += FG[q] * (eta_l * TPHI[q * BS + lane] - TGN[q * BS + lane]);
             }
             __syncwarp();
         }
