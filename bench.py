@@ -226,6 +226,16 @@ def cpu_baseline(wl, r):
                                                               s["t_csr"], s["t_cg"], 1e9 * s["t_cg"] / max(1, s["n"] * s["iters"])))
 
 
+def cpu_single_thread(wl, r):
+    """the reference AS SHIPPED -- it has no threading -- on one host core, at the reference arm's size."""
+    import refbind
+    if wl.get("order") == 2 or not refbind.available(omp=False):
+        return None
+    s = reference_step(refbind.Ref(omp=False), wl, r)
+    return dict(value=s["n"] / s["t"], unit="DOFs/s", cores=1, kind="reference", dofs=int(s["n"]), cg_iterations=int(s["iters"]),
+                sample="unmodified reference as shipped (no OpenMP), -r %d: blocks %.2fs + finalize %.2fs + CG %.2fs" % (r, s["t_blocks"], s["t_csr"], s["t_cg"]))
+
+
 def run_reference_arm(args, wl, rank):
     if rank != 0:
         return 0
@@ -859,6 +869,10 @@ def main():
     same_size = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:      # the CPU baseline is an N=1 figure (torchrun pins ranks to one thread)
         base = cpu_baseline(wl, wl["base_r"])
+        if base is not None:
+            st = cpu_single_thread(wl, wl["ref_r"])
+            if st is not None:
+                base["as_shipped_single_thread"] = st
         # like-for-like: the GPU path on EXACTLY the systems the CPU reference runs (the reference arm's -r ref_r sample and
         # this line's cpu_baseline at -r base_r), resident and end to end, with both sides' iteration counts
         if base is not None:
