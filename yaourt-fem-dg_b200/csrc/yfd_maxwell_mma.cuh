@@ -148,8 +148,59 @@ maxwell_stage_class_mma(const mx_step_args a, const int mode)
                     accl[fld][r] += __shfl_xor_sync(0xffffffffu, accl[fld][r], 2);
                 }
             }
-            if (cm >= 0) {
-                const double s_mu = __ldg(&a.cs[2 * (int64_t) cm]), s_eps = __ldg(&a.cs[2 * (int64_t) cm + 1]);
+            /* the same sink on two adjacent rows at once (16-byte accesses: half the requests of the scattered 8-byte ones, which is
+             * what the RK stages spend their time on: up to five accesses per entry) */
+            auto sink2 = [&](int64_t idx, double kx, double ky) {
+                auto ld2 = [](const double *p) { return *reinterpret_cast<const double2 *>(p); };
+                auto st2 = [](double *p, double x, double y) { *reinterpret_cast<double2 *>(p) = make_double2(x, y); };
+                switch (mode) {
+                case MX_APPLY: st2(a.out + idx, kx, ky); break;
+                case MX_RK1: { st2(a.acc + idx, kx, ky); const double2 v = __ldg(reinterpret_cast<const double2 *>(a.vin + idx));
+                               st2(a.out + idx, __dadd_rn(v.x, __dmul_rn(a.dt / 2., kx)), __dadd_rn(v.y, __dmul_rn(a.dt / 2., ky))); break; }
+                case MX_RK2: { st2(a.kb + idx, kx, ky); const double2 v = ld2(a.u + idx);
+                               st2(a.out + idx, __dadd_rn(v.x, __dmul_rn(a.dt / 2., kx)), __dadd_rn(v.y, __dmul_rn(a.dt / 2., ky))); break; }
+                case MX_RK3: { const double2 ac = ld2(a.acc + idx), kb = ld2(a.kb + idx), v = ld2(a.u + idx);
+                               st2(a.acc + idx, __dadd_rn(ac.x, __dmul_rn(__dadd_rn(kb.x, kx), 2.0)), __dadd_rn(ac.y, __dmul_rn(__dadd_rn(kb.y, ky), 2.0)));
+                               st2(a.out + idx, __dadd_rn(v.x, __dmul_rn(a.dt, kx)), __dadd_rn(v.y, __dmul_rn(a.dt, ky))); break; }
+                case MX_RK4: { const double2 v = ld2(a.u + idx), ac = ld2(a.acc + idx);
+                               st2(a.u + idx, __dadd_rn(v.x, __dmul_rn(__dadd_rn(ac.x, kx), (1. / 6.) * a.dt)),
+                                   __dadd_rn(v.y, __dmul_rn(__dadd_rn(ac.y, ky), (1. / 6.) * a.dt))); break; }
+                case MX_EULER: { const double2 v = __ldg(reinterpret_cast<const double2 *>(a.vin + idx));
+                                 st2(a.out + idx, __dadd_rn(v.x, __dmul_rn(a.dt, kx)), __dadd_rn(v.y, __dmul_rn(a.dt, ky))); break; }
+                }
+            };
+            const int64_t cq = cm < 0 ? 0 : cm;
+            const double s_mu = __ldg(&a.cs[2 * cq]), s_eps = __ldg(&a.cs[2 * cq + 1]);
+            if constexpr (BS == 15) {
+                /* a field's 15 rows start at cm * 45 + fld * 15: even or odd with cm + fld.  Even: the lane's own pairs (2t, 2t+1),
+                 * (8+2t, 9+2t) are aligned, row 14 is single.  Odd: pairs start at odd rows -- (2t+1, 2t+2), (9+2t, 10+2t), row 0 single --
+                 * and the second row of each comes from the next lane of the cell (lane 3 takes row 8 from lane 0). */
+                const int src = (lane & ~3) | ((t + 1) & 3);
+#pragma unroll
+                for (int fld = 0; fld < 3; fld++) {
+                    const double sc = fld == 2 ? s_eps : s_mu;
+                    const double d0 = sc * acc[fld][0][0], d1 = sc * acc[fld][0][1], d2 = sc * acc[fld][1][0], d3 = sc * acc[fld][1][1];
+                    const double nA = __shfl_sync(0xffffffffu, t == 0 ? d2 : d0, src);
+                    const double nB = __shfl_sync(0xffffffffu, d2, src);
+                    if (cm < 0) continue;
+                    const bool odd = ((cm + fld) & 1) != 0;
+                    const int64_t base = (int64_t) cm * L + fld * BS;
+                    sink2(base + (odd ? 2 * t + 1 : 2 * t), odd ? d1 : d0, odd ? nA : d1);
+                    if (t < 3) sink2(base + (odd ? 9 + 2 * t : 8 + 2 * t), odd ? d3 : d2, odd ? nB : d3);
+                    if (odd ? t == 0 : t == 3) sink(base + (odd ? 0 : 14), odd ? d0 : d2);
+                }
+            } else if constexpr (BS == 10 || BS == 6) {
+                /* 3 bs even: every pair (2t, 2t+1) is aligned; bs = 10: rows 8, 9 (the DFMA rows, summed over the 4 lanes) leave from lane 0 */
+                if (cm >= 0) {
+#pragma unroll
+                    for (int fld = 0; fld < 3; fld++) {
+                        const double sc = fld == 2 ? s_eps : s_mu;
+                        const int64_t base = (int64_t) cm * L + fld * BS;
+                        if (2 * t + 1 < BS) sink2(base + 2 * t, sc * acc[fld][0][0], sc * acc[fld][0][1]);
+                        if (LEFT == 2 && t == 0) sink2(base + 8, sc * accl[fld][0], sc * accl[fld][LEFT - 1]);
+                    }
+                }
+            } else if (cm >= 0) {
 #pragma unroll
                 for (int fld = 0; fld < 3; fld++) {
                     const double sc = fld == 2 ? s_eps : s_mu;
