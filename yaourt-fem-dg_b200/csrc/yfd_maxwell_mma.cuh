@@ -17,7 +17,9 @@
  *
  * Measured and not kept (profiles/r02_class_mma.md): two m-tiles per warp sharing every block fragment (236-255 registers, one
  * CTA per SM) is 30-45 % slower than one m-tile with two CTAs per SM; sending the results through a per-warp shared-memory
- * buffer so that they leave as flat runs instead of 8-byte pieces of 8 cells is 5-10 % slower as well.
+ * buffer so that they leave as flat runs instead of 8-byte pieces of 8 cells is 5-10 % slower as well; loading the next
+ * neighbour's fragments while the current one's three products run (24 more registers, spills at 128) changes nothing
+ * (0.62 vs 0.61 ms): 16 warps per SM already cover the operand latency that the tensor pipe leaves visible.
  */
 #pragma once
 
