@@ -503,6 +503,7 @@ mx_step_args step_args(yfd_maxwell *m)
     const bool cls = maxwell_uses_classes(m);
     s.table = cls ? m->classes.table.p : nullptr;
     s.table_mma = cls ? m->classes.table_mma.p : nullptr;
+    s.upwind = m->upwind;
     s.work_cell = cls ? m->classes.work_cell.p : nullptr;
     s.tile_cls = cls ? m->classes.tile_cls.p : nullptr;
     s.ntiles = cls ? m->classes.ntiles : 0;

@@ -81,6 +81,7 @@ struct mx_step_args {
     /* class cache in use: one block set per class (global memory, read as warp-uniform loads) + the class-sorted cell list */
     const double *table; const int32_t *work_cell, *tile_cls; int64_t ntiles;
     const double *table_mma;    /* fragment form of `table` for the tensor-pipe kernel, or null */
+    int upwind;                 /* 0: centred fluxes -- vH = vE = 0 in every face coefficient (yfd_maxwell.cu: maxwell_assemble) */
 };
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
 yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol);

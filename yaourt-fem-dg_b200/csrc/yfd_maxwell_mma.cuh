@@ -9,10 +9,10 @@
  *
  * Order of work per m-tile (8 consecutive entries of the class-sorted list): SOURCE-major -- the three fields of a source
  * cell (the cell itself, then the neighbour across each face) are loaded once as operand fragments, combined in registers
- * into the operand of each product (the scalar flux factors are applied BEFORE the block, as in maxwell_stage_class), and all
- * three output fields accumulate side by side:
- *     self:  Hx += Gy (-Ez);  Hy += Gx Ez;  Ez += Gx Hy + Gy (-Hx);  field += T_f w_field,f(self)   for every face f
- *     nbr f: field -= N_f w_field,f(nbr)
+ * into the operands of the products, and all three output fields accumulate side by side:
+ *     self:  Hx += Gy (-Ez);  Hy += Gx Ez;  Ez += Gx Hy + Gy (-Hx)
+ *     face f, self:  Hx += ny (T_f q1),  Hy += -nx (T_f q1),  Ez += T_f q2       (q1, q2: see the kernel)
+ *     face f, nbr:   the same with N_f and the opposite sign
  * The sink (plain application, RK4 stages, Euler) is maxwell_stage's.
  *
  * Measured and not kept (profiles/r02_class_mma.md): two m-tiles per warp sharing every block fragment (236-255 registers, one
@@ -55,7 +55,8 @@ __device__ __forceinline__ void mx_face_factors(const mx_face_coef &fq, int fld,
     else               { ahx = fq.cH * fq.ny;  ahy = -fq.cH * fq.nx;         aez = -fq.vE; }
 }
 
-template <int NV, int K>
+/* UPW = false: centred fluxes, vH = vE = 0 in every face coefficient: the terms they multiply are skipped (exact zeros) */
+template <int NV, int K, bool UPW>
 __global__ void __launch_bounds__(MMA_THREADS, 2)
 maxwell_stage_class_mma(const mx_step_args a, const int mode)
 {
@@ -100,17 +101,43 @@ maxwell_stage_class_mma(const mx_step_args a, const int mode)
 #pragma unroll
             for (int q = 0; q < KS; q++) w[q] = -v[0][q];
             mm::product(Fk, 1, lane, t, w, acc[2], accl[2]);                      /*     + Gy (-Hx) */
+            /* faces.  With z = ny Hx - nx Hy the three flux operands of a source are
+             *     Hx: ny q1,   Hy: -nx q1,   Ez: q2,      q1 = cE Ez - vH z,   q2 = cH z - vE Ez
+             * (maxwell_stage_class's w_field,f, factored): ONE product B q1 serves both H fields -- its result is scaled by the
+             * cell's own ny / -nx afterwards, a lane's accumulators all belong to its cell g -- and B q2 goes straight into Ez:
+             * two block products per face and source instead of three (16 instead of 22 per triangle). */
+            auto face_source = [&](const mx_face_coef &fq, int b, double sign) {
+                double p1[NT1][2], p1l[LF1];
+#pragma unroll
+                for (int h = 0; h < NT1; h++) p1[h][0] = p1[h][1] = 0.0;
+#pragma unroll
+                for (int r = 0; r < LF1; r++) p1l[r] = 0.0;
+#pragma unroll
+                for (int q = 0; q < KS; q++) {
+                    const double z = fma(fq.ny, v[0][q], -fq.nx * v[1][q]);
+                    w[q] = UPW ? fma(fq.cE, v[2][q], -fq.vH * z) : fq.cE * v[2][q];
+                    v[0][q] = sign * (UPW ? fma(fq.cH, z, -fq.vE * v[2][q]) : fq.cH * z);      /* q2 (v[0] is not needed any more) */
+                }
+                mm::product(Fk, b, lane, t, w, p1, p1l);
+                const double sx = sign * fq.ny, sy = -sign * fq.nx;
+#pragma unroll
+                for (int h = 0; h < NTM; h++) {
+                    acc[0][h][0] = fma(sx, p1[h][0], acc[0][h][0]); acc[0][h][1] = fma(sx, p1[h][1], acc[0][h][1]);
+                    acc[1][h][0] = fma(sy, p1[h][0], acc[1][h][0]); acc[1][h][1] = fma(sy, p1[h][1], acc[1][h][1]);
+                }
+#pragma unroll
+                for (int r = 0; r < LEFT; r++) { accl[0][r] = fma(sx, p1l[r], accl[0][r]); accl[1][r] = fma(sy, p1l[r], accl[1][r]); }
+                mm::product(Fk, b, lane, t, v[0], acc[2], accl[2]);
+            };
+            /* the cell's own faces need its fields three times: keep Hx aside (face_source overwrites v[0]) */
+            double hx[KS];
+#pragma unroll
+            for (int q = 0; q < KS; q++) hx[q] = v[0][q];
 #pragma unroll
             for (int f = 0; f < NV; f++) {
-                const mx_face_coef fq = a.fc[(int64_t) cc * NV + f];
 #pragma unroll
-                for (int fld = 0; fld < 3; fld++) {
-                    double ahx, ahy, aez;
-                    mx_face_factors(fq, fld, ahx, ahy, aez);
-#pragma unroll
-                    for (int q = 0; q < KS; q++) w[q] = fma(aez, v[2][q], fma(ahy, v[1][q], ahx * v[0][q]));
-                    mm::product(Fk, 2 + f, lane, t, w, acc[fld], accl[fld]);
-                }
+                for (int q = 0; q < KS; q++) v[0][q] = hx[q];
+                face_source(a.fc[(int64_t) cc * NV + f], 2 + f, 1.0);
             }
             /* ---- the neighbours ---- */
 #pragma unroll
@@ -119,15 +146,7 @@ maxwell_stage_class_mma(const mx_step_args a, const int mode)
                 const int32_t nb = __ldg(&a.nbr[(int64_t) cc * NV + f]);
 #pragma unroll
                 for (int fld = 0; fld < 3; fld++) mma_operand<BS>(a.vin + (int64_t) nb * L + fld * BS, t, v[fld]);
-                const mx_face_coef fq = a.fc[(int64_t) cc * NV + f];
-#pragma unroll
-                for (int fld = 0; fld < 3; fld++) {
-                    double ahx, ahy, aez;
-                    mx_face_factors(fq, fld, ahx, ahy, aez);
-#pragma unroll
-                    for (int q = 0; q < KS; q++) w[q] = fma(-aez, v[2][q], fma(-ahy, v[1][q], -ahx * v[0][q]));
-                    mm::product(Fk, 2 + NV + f, lane, t, w, acc[fld], accl[fld]);
-                }
+                face_source(a.fc[(int64_t) cc * NV + f], 2 + NV + f, -1.0);
             }
             /* ---- sink: rows 8 h + 2 t, + 1 of cell g from the tensor tiles; LEFT rows summed over the cell's 4 lanes,
              * lane t = r keeps row 8 NTM + r ---- */

@@ -361,7 +361,8 @@ static yfd_status launch_stage_class(yfd_ctx *ctx, int mode, const mx_step_args 
             const int64_t want = ceil_div(a.ntiles, MMA_THREADS / 32);
             if (grid > want) grid = want;
             if (grid < 1) grid = 1;
-            YFD_LAUNCH(ctx, (maxwell_stage_class_mma<NV, K>), (unsigned) grid, MMA_THREADS, 0, a, mode);
+            if (a.upwind) YFD_LAUNCH(ctx, (maxwell_stage_class_mma<NV, K, true>), (unsigned) grid, MMA_THREADS, 0, a, mode);
+            else          YFD_LAUNCH(ctx, (maxwell_stage_class_mma<NV, K, false>), (unsigned) grid, MMA_THREADS, 0, a, mode);
             return YFD_OK;
         }
     }
