@@ -424,7 +424,10 @@ def run_maxwell(args, wl, rank, world, local_rank):
     fp64_peak = ctx.measure_fp64()
     tensor_pipe = bool(getattr(mx.info, "class_tensor_pipe", 0))
     tensor_peak = ctx.measure_fp64_tensor() if tensor_pipe else None
-    flops_apply = 2.0 * mx.bs * mx.bs * (4 + 6 * mx.nf) * (info["cells"] / world)
+    # block products the kernel EXECUTES per cell: 4 cell products + per face 3 (self) + 3 (neighbour) in the streamed / CUDA-core
+    # kernels; the tensor-pipe kernel factors the flux operands and needs 2 + 2 per face (yfd_maxwell_mma.cuh)
+    products = (4 + 4 * mx.nf) if tensor_pipe else (4 + 6 * mx.nf)
+    flops_apply = 2.0 * mx.bs * mx.bs * products * (info["cells"] / world)
     mx.close()
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -445,6 +448,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
                 "reference_layout": {"bytes_per_launch": ref_bytes, "gbs": achieved, "frac": achieved / peak},
                 "fp64": {"achieved_tflops": flops_apply / (ms_apply * 1e-3) / 1e12, "peak_tflops": fp64_peak,
                          "frac": flops_apply / (ms_apply * 1e-3) / 1e12 / fp64_peak, "flops_per_launch": flops_apply,
+                         "block_products_per_cell": products,
                          "peak_source": "DFMA microbenchmark run just now on this device (yfd_ctx_measure_fp64)"},
                 "operator": cls_info,
                 "note": "achieved / frac = the bytes the kernel requests per launch / CUDA-event time against the measured HBM peak; reference_layout = "
@@ -460,7 +464,8 @@ def run_maxwell(args, wl, rank, world, local_rank):
                                                        + ("" if world == 1 else ", rank 0's share of the cells"),
                          "achieved": tf, "peak": tensor_peak, "unit": "TFLOP/s", "frac": tf / tensor_peak,
                          "peak_source": "FP64 mma.sync microbenchmark run just now on this device (yfd_ctx_measure_fp64_tensor); useful flops only: "
-                                        "2 bs^2 per block product, the padding of bs to the 8x8x4 tiles is not counted",
+                                        "2 bs^2 per block product EXECUTED (4 + 4 nf per cell after factoring the flux operands; the streamed kernel needs 4 + 6 nf), "
+                                        "the padding of bs to the 8x8x4 tiles is not counted",
                          "hbm": {"requested_gbs": req, "peak": peak, "frac": req / peak, "peak_source": peak_src}})
         roofline.pop("hw_frac", None)
         roofline["fp64"]["tensor_peak_tflops"] = tensor_peak
