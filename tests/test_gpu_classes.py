@@ -209,3 +209,25 @@ def test_tensor_pipe_class_kernel_equals_the_cuda_core_one(yfd, ctx, mtype, r, k
     assert abs(a["iterations"] - b["iterations"]) <= max(1, a["iterations"] // 200), (a["iterations"], b["iterations"])
     assert np.linalg.norm(a["x"] - b["x"]) <= 1e-9 * np.linalg.norm(a["x"])
     sysm.close(); mesh.close()
+
+
+def test_class_kernels_launch_on_every_small_table_size(yfd, ctx):
+    """Tiny meshes give every class count from 1 up, i.e. class tables of every size around the 48 KiB a kernel gets without
+    opting in to more dynamic shared memory -- which its static shared memory shares: 6 classes of tri k=4 fragments are exactly
+    48 KiB and did not launch (found by tools/multi_gpu_check.py at 2 ranks).  Every solve must run and converge."""
+    seen = set()
+    for k in (4, 3):
+        for nx in range(1, 5):
+            for ny in range(nx, 6):
+                for cell in (yfd.TRI, yfd.QUAD):
+                    mesh = yfd.Mesh(ctx, yfd.HostMesh.structured(cell, nx, ny))
+                    sysm = ctx.dg_assemble_sip(mesh, k, eta=1.0, build_pc=True)
+                    oi = sysm.operator_info()
+                    for mode in (0, 2):
+                        with env(YFD_CLS_MMA=mode):
+                            res = sysm.solve_cg(yfd.CgParams(rr_tol=1e-10, rr_max=1e6, max_iter=20 * sysm.n), use_pc=True)
+                            assert res["converged"], (cell, nx, ny, k, mode, oi)
+                    seen.add((cell, k, oi["nclasses"]))
+                    sysm.close(); mesh.close()
+    # (the exact 48 KiB case needs a rank-local half of a 5 x 7 triangle mesh: tools/multi_gpu_check.py at 2 ranks runs it)
+    assert len({n for c, kk, n in seen}) >= 4, sorted(seen)

@@ -65,7 +65,7 @@ static yfd_status bj_launch_build(yfd_ctx *ctx, yfd_system *sys, int *d_err)
 {
     constexpr int PER_WARP = 2 * BS * BS * 8 + ((BS * 4 + 15) & ~15);
     const size_t smem = (size_t) BJ_WARPS * PER_WARP;
-    if (smem > 48 * 1024)
+    if (smem > YFD_SMEM_OPTIN_FROM)
         YFD_CUDA(ctx, cudaFuncSetAttribute(dg_block_jacobi_build<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const int64_t want = ceil_div(std::max<int64_t>(sys->ncells, 1), BJ_WARPS), cap = (int64_t) ctx->sm_count * 8;
     YFD_LAUNCH(ctx, dg_block_jacobi_build<BS>, (unsigned) std::min(want, cap), BJ_WARPS * 32, smem, sys->cellptr.p, sys->blk_cell.p,

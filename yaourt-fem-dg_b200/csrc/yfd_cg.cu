@@ -580,7 +580,7 @@ static yfd_status cg_device(yfd_ctx *ctx, const spmv_op &op, const double *d_b, 
     }
     {
         cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
-        if (cap_st != YFD_OK) { if (graph) cudaGraphDestroy(graph); return cap_st; }
+        if (cap_st != YFD_OK) { if (graph) cudaGraphDestroy(graph); cudaGetLastError(); return cap_st; }      /* the capture is over, its error reported */
         if (e != cudaSuccess) return fail(ctx, YFD_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
     }
     const int64_t launches_per_graph = ctx->launches - launches_before;

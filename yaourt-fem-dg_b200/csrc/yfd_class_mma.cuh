@@ -184,7 +184,7 @@ static bool launch_cls_mma(yfd_ctx *ctx, const dg_classes &cl, const double *x, 
     const size_t smem = global ? 0 : bytes;
     auto kern = global ? dg_spmv_class_mma<BS, NB, WITH_DOT, true> : dg_spmv_class_mma<BS, NB, WITH_DOT, false>;
     *st = YFD_OK;
-    if (smem > 48 * 1024) {
+    if (smem > YFD_SMEM_OPTIN_FROM) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) { *st = fail(ctx, YFD_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return true; }
     }

@@ -363,7 +363,7 @@ static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
     constexpr int FACE_DBL = NFQ * (2 + 4 * BS);
     constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
     const size_t smem = (size_t) DG_WARPS * WARP_DBL * sizeof(double);
-    if (smem > 48 * 1024)
+    if (smem > YFD_SMEM_OPTIN_FROM)
         YFD_CUDA(ctx, cudaFuncSetAttribute(dg_sip_cells<NV, K, ADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const int64_t want = ceil_div(a.ncells, DG_WARPS);
     const int64_t cap = (int64_t) ctx->sm_count * 32;        /* grid-stride beyond 32 CTAs per SM */

@@ -88,15 +88,22 @@ void  pool_trim(yfd_ctx *ctx);
         if (s_ != YFD_OK) return s_;                   \
     } while (0)
 
+/* dynamic shared memory from which a kernel is opted in (cudaFuncAttributeMaxDynamicSharedMemorySize).  The 48 KiB a kernel
+ * gets without opting in cover its STATIC shared memory too (reduction scratch: a few hundred bytes), so a request of exactly
+ * 48 KiB -- 6 classes of bs = 15 triangle fragments -- fails to launch unless it is opted in as well. */
+constexpr size_t YFD_SMEM_OPTIN_FROM = 40 * 1024;
+
 /* kernel launch on the context's stream, counted (bench.py reports gpu_launches) */
 #define YFD_LAUNCH(ctx, kernel, grid, block, smem, ...)                                        \
     do {                                                                                      \
         kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                      \
         (ctx)->launches++;                                                                    \
         cudaError_t e_ = cudaPeekAtLastError();                                               \
-        if (e_ != cudaSuccess)                                                                \
+        if (e_ != cudaSuccess) {                                                              \
+            cudaGetLastError();                       /* reported once, not again by the next launch */ \
             return yfd::fail((ctx), YFD_ERR_CUDA, "%s:%d: launch %s: %s", __FILE__, __LINE__,  \
                              #kernel, cudaGetErrorString(e_));                                \
+        }                                                                                     \
     } while (0)
 
 /* device array with explicit lifetime (freed on the context's device) */

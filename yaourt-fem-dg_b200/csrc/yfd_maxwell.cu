@@ -431,7 +431,7 @@ yfd_status launch_assemble(yfd_ctx *ctx, const mx_asm_args &a)
 {
     using S = mx_asm_shape<NV, K>;
     const size_t smem = (size_t) S::WARPS * S::WARP_DBL * sizeof(double);
-    if (smem > 48 * 1024)
+    if (smem > YFD_SMEM_OPTIN_FROM)
         YFD_CUDA(ctx, cudaFuncSetAttribute(maxwell_assemble<NV, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const int64_t want = ceil_div(a.ncells, S::WARPS);
     const int64_t cap = (int64_t) ctx->sm_count * 16;
@@ -449,7 +449,7 @@ yfd_status launch_cellwise(yfd_ctx *ctx, int which, const mx_cell_args &a)
     const unsigned grid = (unsigned) (want < cap ? (want > 0 ? want : 1) : cap);
     if (which == 0) {
         const size_t smem = (size_t) MXC_WARPS * (BS * BS + BS * 3 + NQ * (3 + BS) + 16) * sizeof(double);
-        if (smem > 48 * 1024)
+        if (smem > YFD_SMEM_OPTIN_FROM)
             YFD_CUDA(ctx, cudaFuncSetAttribute(maxwell_project<NV, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         YFD_LAUNCH(ctx, (maxwell_project<NV, K>), grid, MXC_WARPS * 32, smem, a);
     } else {

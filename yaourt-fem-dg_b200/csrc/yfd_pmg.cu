@@ -265,7 +265,7 @@ static yfd_status sweep_t(yfd_ctx *ctx, const pmg_level &L, const pmg_lists &w, 
     const bool global = (size_t) (L.nA + L.nD) * sizeof(double) + 1024 > ctx->smem_optin;
     auto kern = global ? pmg_sweep<BS, NB, true> : pmg_sweep<BS, NB, false>;
     const size_t smem = global ? 0 : (size_t) (L.nA + L.nD) * sizeof(double);
-    if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (smem > YFD_SMEM_OPTIN_FROM) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     YFD_LAUNCH(ctx, kern, pmg_grid(ctx, w.ntiles, smem), CLS_THREADS, smem, (const double *) L.tabA.p, L.nA, (const double *) L.tabD.p, L.nD,
                w.work_cell, w.work_nbr, w.tile_cls, w.ntiles, w.npos, x_in, d, b, x_out, c1, c2, gate);
     return YFD_OK;
@@ -287,7 +287,7 @@ static yfd_status restrict_t(yfd_ctx *ctx, const pmg_level &L, const pmg_lists &
     const bool global = (size_t) L.nA * sizeof(double) + 1024 > ctx->smem_optin;
     auto kern = global ? pmg_residual_restrict<BS, BC, NB, true> : pmg_residual_restrict<BS, BC, NB, false>;
     const size_t smem = global ? 0 : (size_t) L.nA * sizeof(double);
-    if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (smem > YFD_SMEM_OPTIN_FROM) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     YFD_LAUNCH(ctx, kern, pmg_grid(ctx, w.ntiles, smem), CLS_THREADS, smem, (const double *) L.tabA.p, L.nA, w.work_cell, w.work_nbr, w.tile_cls,
                w.ntiles, w.npos, x, b, out, gate);
     return YFD_OK;

@@ -128,7 +128,7 @@ static yfd_status launch_post(yfd_ctx *ctx, const post_args &a)
 {
     constexpr int BS = (K + 2) * (K + 1) / 2, NQ = dg_nq_cell(NV, K);
     const size_t smem = (size_t) POST_WARPS * (2 * BS * BS + 2 * BS + NQ * (2 + BS) + 16) * sizeof(double);
-    if (smem > 48 * 1024)
+    if (smem > YFD_SMEM_OPTIN_FROM)
         YFD_CUDA(ctx, cudaFuncSetAttribute(dg_postprocess<NV, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const int64_t want = ceil_div(a.ncells, POST_WARPS);
     const int64_t cap = (int64_t) ctx->sm_count * 16;

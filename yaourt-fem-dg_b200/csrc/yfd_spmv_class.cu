@@ -434,7 +434,7 @@ static yfd_status launch_cls(yfd_ctx *ctx, const dg_classes &cl, const double *x
     const bool global = (size_t) cl.table_doubles * sizeof(double) + 1024 > ctx->smem_optin;
     auto kern = global ? dg_spmv_class<BS, NB, WITH_DOT, true> : dg_spmv_class<BS, NB, WITH_DOT, false>;
     const size_t smem = global ? 0 : (size_t) cl.table_doubles * sizeof(double);
-    if (smem > 48 * 1024) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (smem > YFD_SMEM_OPTIN_FROM) YFD_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = smem * 2 + 4096 <= ctx->smem_per_sm ? 2 : 1;
     int64_t grid = (int64_t) ctx->sm_count * per_sm;
     const int64_t want = ceil_div(cl.ntiles, CLS_THREADS / 32);
