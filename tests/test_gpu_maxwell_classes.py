@@ -105,3 +105,26 @@ def test_switch_and_large_mesh(yfd, ctx):
     mx.timesteps(20)
     e2 = mx.report_errors(19 * 2e-4)
     assert np.abs(e1 - e2).max() <= 1e-11
+
+
+@pytest.mark.parametrize("t,r,k,up", [(0, 3, 4, False), (0, 3, 2, True), (1, 3, 3, False), (0, 3, 3, True)])
+def test_split_rk_equals_fused_rk(yfd, ctx, t, r, k, up):
+    """The RK4 step of the tensor-pipe class kernel in its two forms -- vector work fused into the stage kernel's sinks, or plain
+    applications + maxwell_rk_vector streaming kernels (YFD_MX_SPLIT_RK) -- performs the same operations in the same order:
+    identical bits after several steps, odd vector lengths included."""
+    mesh = yfd.Mesh(ctx, yfd.HostMesh.create(t, r))
+    res = {}
+    for mode in ("0", "2"):
+        os.environ["YFD_MX_SPLIT_RK"] = mode
+        try:
+            mx = yfd.Maxwell(ctx, mesh, k, delta_t=0.002, upwind=up)
+            mx.set_operator_mode(yfd.OPERATOR_CLASSES)
+            assert mx.info.class_tensor_pipe
+            mx.set_dofs(np.random.default_rng(3).standard_normal(mx.ndofs))
+            mx.timesteps(5)
+            res[mode] = mx.dofs()
+            mx.close()
+        finally:
+            os.environ.pop("YFD_MX_SPLIT_RK", None)
+    assert np.array_equal(res["0"], res["2"])
+    mesh.close()

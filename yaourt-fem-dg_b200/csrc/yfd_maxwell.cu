@@ -709,7 +709,7 @@ void yfd_maxwell_get_info(const yfd_maxwell *m, yfd_maxwell_info *info)
     info->class_max_deviation = m->classes.max_dev;
     info->class_tolerance = m->classes.tol;
     info->class_table_bytes = (int64_t) m->classes.table.n * 8;
-    info->class_tensor_pipe = (info->uses_classes && m->classes.table_mma.p && env_int("YFD_MX_CLASS_MMA", 1) != 0) ? 1 : 0;
+    info->class_tensor_pipe = maxwell_uses_tensor_pipe(m) ? 1 : 0;
 }
 
 yfd_status yfd_maxwell_set_operator_mode(yfd_maxwell *m, int mode)
@@ -849,6 +849,25 @@ yfd_status yfd_maxwell_timesteps(yfd_maxwell *m, int64_t nsteps, yfd_maxwell_ste
             YFD_TRY(exchange(m, m->u.p));
             YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_EULER, s));
             std::swap(m->u, m->s1);
+            continue;
+        }
+        /* YFD_MX_SPLIT_RK: 0 never, 2 always, 1 (default) on triangles -- measured (profiles/r02_class_mma.md): tri k=4 -r 9 3.16 ->
+         * 2.90 ms per step, tri k=2 1.59 -> 1.46; on the quadrangle meshes consecutive list entries are consecutive cells, the
+         * fused sinks are nearly coalesced already and splitting costs 3 % (2.07 -> 2.13 ms at k=3) */
+        const int split_rk = env_int("YFD_MX_SPLIT_RK", 1);
+        if (maxwell_uses_tensor_pipe(m) && (split_rk >= 2 || (split_rk == 1 && m->nv == 3))) {
+            /* plain applications (one store per entry) + the RK vector work as streaming kernels: maxwell_rk_vector; same
+             * operations in the same order as the fused sinks */
+            const int64_t n = m->ncells * 3 * m->bs;
+            const double dt = m->delta_t;
+            s.vin = m->u.p;  s.out = m->acc.p; YFD_TRY(exchange(m, m->u.p));  YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+            YFD_TRY(maxwell_launch_rk_vector(ctx, 1, n, dt, m->u.p, m->acc.p, m->kb.p, m->acc.p, m->s1.p));
+            s.vin = m->s1.p; s.out = m->kb.p;  YFD_TRY(exchange(m, m->s1.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+            YFD_TRY(maxwell_launch_rk_vector(ctx, 2, n, dt, m->u.p, m->acc.p, m->kb.p, m->kb.p, m->s2.p));
+            s.vin = m->s2.p; s.out = m->s1.p;  YFD_TRY(exchange(m, m->s2.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+            YFD_TRY(maxwell_launch_rk_vector(ctx, 3, n, dt, m->u.p, m->acc.p, m->kb.p, m->s1.p, nullptr));
+            s.vin = m->s1.p; s.out = m->s2.p;  YFD_TRY(exchange(m, m->s1.p)); YFD_TRY(maxwell_launch_stage(ctx, m->nv, m->degree, MX_APPLY, s));
+            YFD_TRY(maxwell_launch_rk_vector(ctx, 4, n, dt, m->u.p, m->acc.p, m->kb.p, m->s2.p, nullptr));
             continue;
         }
         /* distributed: the operand's halo cells are refreshed from their owners before every application */

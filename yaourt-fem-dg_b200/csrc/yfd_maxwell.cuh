@@ -84,11 +84,17 @@ struct mx_step_args {
     int upwind;                 /* 0: centred fluxes -- vH = vE = 0 in every face coefficient (yfd_maxwell.cu: maxwell_assemble) */
 };
 yfd_status maxwell_launch_stage(yfd_ctx *ctx, int nv, int degree, int mode, const mx_step_args &a);
+yfd_status maxwell_launch_rk_vector(yfd_ctx *ctx, int stage, int64_t n, double dt, double *u, double *acc, const double *kb, double *k, double *o);
 yfd_status maxwell_build_classes(yfd_ctx *ctx, yfd_maxwell *m, uint64_t *d_keys, int key_bits, double tol);
 /* AUTO = whichever of the two kernels was faster on this operator when it was created (timed there: the class kernel wins
  * on the reference's triangle meshes at k = 4, the streamed one -- already at the HBM roof -- on quadrangles k = 3) */
 inline bool maxwell_uses_classes(const yfd_maxwell *m)
 {
     return m->classes.ready && (m->operator_mode == 2 || (m->operator_mode == 0 && m->classes_faster));
+}
+/* the tensor-pipe class kernel is what an application launches (yfd_maxwell_step.cu: launch_stage_class) */
+inline bool maxwell_uses_tensor_pipe(const yfd_maxwell *m)
+{
+    return maxwell_uses_classes(m) && m->classes.table_mma.p && env_int("YFD_MX_CLASS_MMA", 1) != 0;
 }
 } // namespace yfd
