@@ -370,6 +370,7 @@ def run_maxwell(args, wl, rank, world, local_rank):
     T = args.profile_iters or wl["timesteps"]
     hm = make_host_mesh(yfd, wl)                             # mesher: input generation, untimed
     info = {}
+    e2e_buf = {}
 
     def one_pass(mesh, x_host=None):
         mx = yfd.Maxwell(ctx, mesh, wl["k"], delta_t=wl["dt"], upwind=wl["upwind"])
@@ -377,7 +378,14 @@ def run_maxwell(args, wl, rank, world, local_rank):
         st = mx.timesteps(T)
         err = mx.report_errors((T - 1) * wl["dt"])
         if x_host is not None:
-            ctx.check(yfd.lib().yfd_maxwell_get_dofs(mx._h, x_host))
+            if world > 1:        # several ranks: every rank reads back the unknowns of ITS cells (no gather, 1/N of the bytes per rank)
+                nown = len(x_host) // world + 3 * mx.bs * 2
+                if "own" not in e2e_buf or e2e_buf["own"].numel() < mx.ncells_owned() * 3 * mx.bs:
+                    e2e_buf["own"] = torch.empty(max(nown, mx.ncells_owned() * 3 * mx.bs), dtype=torch.float64).pin_memory()
+                mx.dofs_owned(e2e_buf["own"].numpy()[:mx.ncells_owned() * 3 * mx.bs])
+                e2e_buf["d2h"] = mx.ncells_owned() * 3 * mx.bs * 8
+            else:
+                ctx.check(yfd.lib().yfd_maxwell_get_dofs(mx._h, x_host))
         info.update(n=mx.ndofs, cells=mx.ncells, ms_assemble=mx.info.ms_assemble, ms_timesteps=st.ms_total, errors=[float(e) for e in err],
                     operator_bytes=mx.info.operator_bytes, reference_operator_bytes=mx.info.reference_operator_bytes)
         return mx
@@ -503,8 +511,11 @@ def run_maxwell(args, wl, rank, world, local_rank):
         wall = (time.perf_counter() - t0) / args.steps
         ms_e2e = max_over_ranks(f0.elapsed_time(f1)) / args.steps
         e2e = {"value": n * T / (ms_e2e * 1e-3), "unit": MAXWELL_UNIT, "h2d_bytes_per_step": int(sum(a.nbytes for a in arrs.values())),
-               "d2h_bytes_per_step": int(x_host.nbytes), "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
-               "path": "yfd_mesh_create -> yfd_maxwell_create -> apply_initial_condition -> timesteps -> report_errors -> get_dofs (host) through include/yfd.h"}
+               "d2h_bytes_per_step": int(e2e_buf.get("d2h", x_host.nbytes)), "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
+               "path": "yfd_mesh_create -> yfd_maxwell_create -> apply_initial_condition -> timesteps -> report_errors -> "
+                       + ("get_dofs (host) through include/yfd.h" if world == 1 else
+                          "get_dofs_owned (every rank reads back the unknowns of its own cells: d2h_bytes_per_step is rank 0's share; "
+                          "h2d: every rank uploads the whole mesh) through include/yfd.h")}
 
     base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:      # the CPU baseline is an N=1 figure (torchrun pins ranks to one thread)
@@ -838,10 +849,19 @@ def main():
         h2d = sum(a.nbytes for a in arrs.values())
         d2h = x_host.nbytes
 
+        own = {}
+
         def step_e2e():
             m2 = yfd.Mesh(ctx, hm_p)
             s2 = assemble(m2)
-            s2.solve_cg_into(params, x_host, use_pc=wl["pc"])
+            if world > 1 and not cfem:      # several ranks: every rank reads back ITS rows (no gather, 1/N of the bytes per rank)
+                nl = s2.local_sizes()["n_local"]
+                if "t" not in own or own["t"].numel() < nl:
+                    own["t"] = torch.empty(nl, dtype=torch.float64).pin_memory()
+                s2.solve_cg_owned_into(params, own["t"].numpy()[:nl], use_pc=wl["pc"])
+                own["d2h"] = nl * 8
+            else:
+                s2.solve_cg_into(params, x_host, use_pc=wl["pc"])
             s2.close(); m2.close()
 
         mesh.close()
@@ -866,9 +886,11 @@ def main():
                 qp, mm = ctx.dg_postprocess(m2, k, x_host)
                 anchors["l2_error"], anchors["l2_error_projection"] = float(np.sqrt(qp)), float(np.sqrt(mm))
             s2.close(); m2.close()
-        e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+        e2e = {"value": n / (ms_e2e * 1e-3), "unit": "DOFs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(own.get("d2h", d2h)),
                "ms_per_step": ms_e2e, "wall_ms_per_step": 1e3 * wall,
-               "path": "yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" % (("yfd_cfem_assemble_p2" if wl.get("order") == 2 else "yfd_cfem_assemble_p1") if cfem else "yfd_dg_assemble_sip")}
+               "path": ("yfd_mesh_create -> %s -> yfd_system_solve_cg (host x) through include/yfd.h" if "d2h" not in own else
+                        "yfd_mesh_create -> %s -> yfd_system_solve_cg_owned (every rank reads back its own rows: d2h_bytes_per_step is rank 0's "
+                        "share; h2d: every rank uploads the whole mesh) through include/yfd.h") % (("yfd_cfem_assemble_p2" if wl.get("order") == 2 else "yfd_cfem_assemble_p1") if cfem else "yfd_dg_assemble_sip")}
 
     base = None
     same_size = None

@@ -374,6 +374,15 @@ yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
 yfd_status yfd_system_solve_cg_device(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
                                       double *d_x, yfd_cg_info *info);
 
+/* Several ranks: yfd_system_solve_cg hands EVERY rank the whole solution (gather + n doubles over PCIe per rank).  A distributed
+ * host program usually wants its own rows only: x_owned [n_local] (yfd_system_local_sizes) receives the rows of the cells this
+ * rank owns, cell after cell in the library's internal order; yfd_system_owned_cells gives the REFERENCE id of each of them
+ * ([n_local / bs] ids; DG systems), so that x_owned[c * bs + i] = x_ref[ref_cell[c] * bs + i].  On one GPU: all rows, in the
+ * internal order.  New, no reference counterpart. */
+yfd_status yfd_system_solve_cg_owned(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                     double *x_owned, yfd_cg_info *info);
+yfd_status yfd_system_owned_cells(yfd_system *sys, int64_t *ref_cell);
+
 /* The drop-in shape: A, b, x and optional DIAGONAL iM given as host data. */
 yfd_status yfd_cg_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double *x, const double *pc_diag,
                         const yfd_cg_params *p, yfd_cg_info *info, double *history, int64_t history_cap);
@@ -521,6 +530,10 @@ yfd_status yfd_maxwell_apply_initial_condition(yfd_maxwell *m, int fields, doubl
 /* gDofs, host, reference numbering */
 yfd_status yfd_maxwell_get_dofs(yfd_maxwell *m, double *dofs);
 yfd_status yfd_maxwell_set_dofs(yfd_maxwell *m, const double *dofs);
+/* the unknowns of the cells this rank owns, [ncells_owned][3][bs] cell after cell in the internal order, and the REFERENCE id of
+ * each of those cells (no gather, ncells_owned * 3 bs doubles over PCIe; one GPU: all cells).  *ncells_owned may be NULL. */
+yfd_status yfd_maxwell_get_dofs_owned(yfd_maxwell *m, double *dofs_owned);
+yfd_status yfd_maxwell_owned_cells(yfd_maxwell *m, int64_t *ncells_owned, int64_t *ref_cell);
 /* v_next = apply_operator(v) (:586-625) on host vectors in reference numbering */
 yfd_status yfd_maxwell_apply_operator(yfd_maxwell *m, const double *v, double *v_next);
 

@@ -173,3 +173,26 @@ def test_full_size_properties_tri_k1_r6(yfd, ctx):
     assert res["converged"]
     b = sysm.rhs()
     assert np.linalg.norm(b - A @ res["x"]) <= 5e-10 * np.linalg.norm(b)
+
+
+def test_owned_rows_entry_points_on_one_gpu(yfd, ctx):
+    """yfd_system_solve_cg_owned / yfd_system_owned_cells and the Maxwell pair (new, SURVEY 8e: a rank reads back its own rows
+    instead of the gathered vector): on one GPU "owned" is every cell, in the library's internal order -- the same numbers as the
+    full entry points return in reference numbering, bit for bit.  The several-rank form is checked by tools/multi_gpu_check.py."""
+    mesh = yfd.Mesh(ctx, yfd.HostMesh.create(yfd.QUAD, 3))
+    sysm = ctx.dg_assemble_sip(mesh, 2, eta=1.0, build_pc=True)
+    p = yfd.CgParams(rr_tol=1e-10, rr_max=1e4, max_iter=2 * sysm.n)
+    full = sysm.solve_cg(p, use_pc=True)
+    x_own = np.empty(sysm.local_sizes()["n_local"])
+    res = sysm.solve_cg_owned_into(p, x_own, use_pc=True)
+    ids = sysm.owned_cells()
+    assert res["iterations"] == full["iterations"] and sorted(ids.tolist()) == list(range(mesh.ncells))
+    bs = sysm.info.basis_size
+    assert np.array_equal(x_own.reshape(-1, bs), full["x"].reshape(-1, bs)[ids])
+    mx = yfd.Maxwell(ctx, mesh, 2, delta_t=0.002)
+    mx.apply_initial_condition()
+    mx.timesteps(3)
+    ids = mx.owned_cells()
+    assert sorted(ids.tolist()) == list(range(mesh.ncells))
+    assert np.array_equal(mx.dofs_owned().reshape(-1, 3 * mx.bs), mx.dofs().reshape(-1, 3 * mx.bs)[ids])
+    mx.close(); sysm.close(); mesh.close()

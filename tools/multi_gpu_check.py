@@ -43,7 +43,13 @@ for (t, r, k, pc) in CASES:
     rhs = sysm.rhs()
     tres = sysm.true_residual(res["x"])          # independent kernel, sums combined over the ranks
     fails += 0 if tres <= 1e-10 else 1
-    line = "case t=%d r=%s k=%d pc=%d: n=%d local rows %d halo dofs %d iters %d true residual %.1e" % (t, r, k, pc, sysm.n, loc["n_local"], loc["n_halo"], res["iterations"], tres)
+    # yfd_system_solve_cg_owned: this rank's rows of the same solution, bit for bit, without the gather
+    x_own = np.empty(loc["n_local"])
+    sysm.solve_cg_owned_into(p, x_own, use_pc=pc)
+    bs_ = sysm.info.basis_size
+    own_ok = np.array_equal(x_own.reshape(-1, bs_), res["x"].reshape(-1, bs_)[sysm.owned_cells()])
+    fails += 0 if own_ok else 1
+    line = "case t=%d r=%s k=%d pc=%d: n=%d local rows %d halo dofs %d iters %d true residual %.1e owned rows %s" % (t, r, k, pc, sysm.n, loc["n_local"], loc["n_halo"], res["iterations"], tres, "OK" if own_ok else "WRONG")
     if ref is not None and rank == 0:
         if isinstance(r, tuple):
             ref.set_mesh(t, hm.points, hm.cells, hm.faces, hm.face_boundary, hm.face_boundary_id)
@@ -95,8 +101,18 @@ for (t, r, k, up) in ((0, 3, 2, False), (1, 3, 3, True), (0, 2, 4, True), (0, 4,
     dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     same = bool(torch.equal(lo, hi))
     fails += 0 if same else 1
+    # the owned slice (yfd_maxwell_get_dofs_owned / _owned_cells) is this rank's part of the gathered vector, bit for bit,
+    # and the ranks' cells cover the mesh exactly once
+    ids, own = mx.owned_cells(), mx.dofs_owned()
+    L3 = 3 * mx.bs
+    owned_ok = np.array_equal(own.reshape(-1, L3), d.reshape(-1, L3)[ids])
+    cover = torch.zeros(mx.ncells, device="cuda", dtype=torch.int32)
+    cover[torch.from_numpy(ids).cuda()] += 1
+    dist.all_reduce(cover)
+    owned_ok = owned_ok and bool((cover == 1).all())
+    fails += 0 if owned_ok else 1
     if rank == 0:
-        print(line + (" | identical on all ranks" if same else " | RANKS DIFFER"), flush=True)
+        print(line + (" | identical on all ranks" if same else " | RANKS DIFFER") + (" | owned slices OK" if owned_ok else " | OWNED SLICES WRONG"), flush=True)
     mx.close(); mesh.close()
 t = torch.tensor([fails], device="cuda")
 dist.all_reduce(t)

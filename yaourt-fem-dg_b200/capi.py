@@ -200,6 +200,10 @@ def lib():
         "yfd_system_set_operator_mode": (cint, [vp, cint]),
         "yfd_system_operator_info": (cint, [vp, P(OperatorInfo)]),
         "yfd_system_apply": (cint, [vp, vp, cint, _f64p, _f64p]),
+        "yfd_system_solve_cg_owned": (cint, [vp, vp, cint, vp, vp, vp]),
+        "yfd_system_owned_cells": (cint, [vp, _i64p]),
+        "yfd_maxwell_get_dofs_owned": (cint, [vp, vp]),
+        "yfd_maxwell_owned_cells": (cint, [vp, P(i64), vp]),
         "yfd_system_true_residual": (cint, [vp, vp, vp, vp, P(dbl)]),
         "yfd_system_true_residual_noalloc": (cint, [vp, vp, vp, P(dbl)]),
         "yfd_system_time_spmv": (cint, [vp, vp, cint, P(dbl), P(dbl), P(dbl)]),
@@ -638,6 +642,20 @@ class System:
         return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
                     transport=("one GPU", "NCCL", "peer memory")[info.transport])
 
+    def solve_cg_owned_into(self, params, x_owned, use_pc=False):
+        """yfd_system_solve_cg_owned: this rank's rows only (internal cell order, see owned_cells), into the caller's host array."""
+        assert x_owned.dtype == np.float64 and x_owned.flags.c_contiguous and x_owned.shape == (self.local_sizes()["n_local"],)
+        info = CgInfo()
+        self.ctx.check(lib().yfd_system_solve_cg_owned(self.ctx._h, self._h, int(use_pc), C.byref(params), x_owned.ctypes.data_as(C.c_void_p), C.byref(info)))
+        return dict(iterations=info.iterations, nr0=info.nr0, nr=info.nr, converged=bool(info.converged), ms_solve=info.ms_solve,
+                    transport=("one GPU", "NCCL", "peer memory")[info.transport])
+
+    def owned_cells(self):
+        """REFERENCE ids of the cells whose rows this rank owns, in the order solve_cg_owned_into returns them (DG systems)."""
+        out = np.empty(self.local_sizes()["n_local"] // self.info.basis_size, np.int64)
+        self.ctx.check(lib().yfd_system_owned_cells(self._h, out))
+        return out
+
     def solve_cg_device(self, params=None, use_pc=False, d_x=None):
         """Resident solve: x0 = 0, solution left in the device buffer `d_x` (raw pointer int or None)."""
         params = params or CgParams()
@@ -776,6 +794,29 @@ class Maxwell:
         d = np.empty(self.ndofs)
         self.ctx.check(lib().yfd_maxwell_get_dofs(self._h, d))
         return d
+
+    def ncells_owned(self):
+        nc = C.c_int64()
+        self.ctx.check(lib().yfd_maxwell_owned_cells(self._h, C.byref(nc), None))
+        return nc.value
+
+    def owned_cells(self):
+        """REFERENCE ids of the cells this rank owns, in the order dofs_owned returns them."""
+        nc = C.c_int64()
+        self.ctx.check(lib().yfd_maxwell_owned_cells(self._h, C.byref(nc), None))
+        out = np.empty(nc.value, np.int64)
+        self.ctx.check(lib().yfd_maxwell_owned_cells(self._h, C.byref(nc), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def dofs_owned(self, out=None):
+        """yfd_maxwell_get_dofs_owned: [ncells_owned][3][bs], no gather (one GPU: all cells, internal order)."""
+        nc = C.c_int64()
+        self.ctx.check(lib().yfd_maxwell_owned_cells(self._h, C.byref(nc), None))
+        if out is None:
+            out = np.empty(nc.value * 3 * self.bs)
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.size == nc.value * 3 * self.bs
+        self.ctx.check(lib().yfd_maxwell_get_dofs_owned(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
 
     def set_dofs(self, d):
         d = np.ascontiguousarray(d, np.float64)

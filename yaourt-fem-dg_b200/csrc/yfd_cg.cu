@@ -733,7 +733,7 @@ yfd_status yfd_bicgstab_solve(yfd_ctx *ctx, yfd_csr *A, const double *b, double 
 /* shared by the host- and device-resident entry points: x_host in/out (may be null), d_x_out device out (may be null) */
 static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
                                double *x_host, double *d_x_out, yfd_cg_info *info, double *history, int64_t history_cap,
-                               int method = SOLVER_CG)
+                               int method = SOLVER_CG, bool owned_rows = false)
 {
     if (sys->ctx != ctx) return fail(ctx, YFD_ERR_INVALID_ARGUMENT, "system belongs to another context");
     if (use_pc != YFD_PC_NONE && use_pc != YFD_PC_JACOBI && use_pc != YFD_PC_BLOCK_JACOBI && use_pc != YFD_PC_PMG)
@@ -799,6 +799,12 @@ static yfd_status system_solve(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
         YFD_TRY(cg_device(ctx, op_of_system(sys, true), sys->rhs.p, dx.p, use_pc ? sys->pc.p : nullptr, p, info, history, history_cap,
                           p->use_normal_eqns ? &opT : nullptr, block_pc ? &opD : nullptr, pmg_pc ? sys : nullptr));
     const double *result = dx.p;
+    if (owned_rows) {
+        /* this rank's rows as the solver holds them (internal order): no permutation, no gather */
+        YFD_CUDA(ctx, cudaMemcpyAsync(x_host, dx.p, (size_t) nloc * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        return YFD_OK;
+    }
     if (dg) {
         /* x_ref[rc] = x_int[iperm[rc]]; several ranks: every rank gets the whole vector */
         double *dst = d_x_out;
@@ -822,6 +828,24 @@ yfd_status yfd_system_solve_cg(yfd_ctx *ctx, yfd_system *sys, int use_pc, const 
 {
     if (!ctx || !sys || !p || !x) return YFD_ERR_INVALID_ARGUMENT;
     return system_solve(ctx, sys, use_pc, p, x, nullptr, info, history, history_cap);
+}
+
+yfd_status yfd_system_solve_cg_owned(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,
+                                     double *x_owned, yfd_cg_info *info)
+{
+    if (!ctx || !sys || !p || !x_owned) return YFD_ERR_INVALID_ARGUMENT;
+    if (p->use_initial_guess) return fail(ctx, YFD_ERR_UNSUPPORTED, "yfd_system_solve_cg_owned starts from x0 = 0");
+    return system_solve(ctx, sys, use_pc, p, x_owned, nullptr, info, nullptr, 0, SOLVER_CG, true);
+}
+
+yfd_status yfd_system_owned_cells(yfd_system *sys, int64_t *ref_cell)
+{
+    if (!sys || !ref_cell) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_ctx *ctx = sys->ctx;
+    if (sys->kind != YFD_SYS_DG) return fail(ctx, YFD_ERR_UNSUPPORTED, "yfd_system_owned_cells: DG systems (continuous FEM rows are not partitioned)");
+    scoped_device dev(ctx->device);
+    const int64_t begin = sys->plan ? sys->plan->cell_begin : 0;
+    return download_widen(ctx, sys->perm.p + begin, sys->ncells, ref_cell);
 }
 
 yfd_status yfd_system_solve_bicgstab(yfd_ctx *ctx, yfd_system *sys, int use_pc, const yfd_cg_params *p,

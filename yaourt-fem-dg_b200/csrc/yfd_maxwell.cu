@@ -803,6 +803,26 @@ yfd_status yfd_maxwell_get_dofs(yfd_maxwell *m, double *dofs)
     return tmp.download(ctx, dofs, (size_t) m->ndofs);
 }
 
+yfd_status yfd_maxwell_get_dofs_owned(yfd_maxwell *m, double *dofs_owned)
+{
+    if (!m || !dofs_owned) return YFD_ERR_INVALID_ARGUMENT;
+    yfd_ctx *ctx = m->ctx;
+    scoped_device dev(ctx->device);
+    const size_t n = (size_t) m->ncells * 3 * m->bs;
+    YFD_CUDA(ctx, cudaMemcpyAsync(dofs_owned, m->u.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    YFD_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return YFD_OK;
+}
+
+yfd_status yfd_maxwell_owned_cells(yfd_maxwell *m, int64_t *ncells_owned, int64_t *ref_cell)
+{
+    if (!m) return YFD_ERR_INVALID_ARGUMENT;
+    if (ncells_owned) *ncells_owned = m->ncells;
+    if (!ref_cell) return YFD_OK;
+    scoped_device dev(m->ctx->device);
+    return download_widen(m->ctx, m->perm.p + m->cell_begin, m->ncells, ref_cell);
+}
+
 yfd_status yfd_maxwell_set_dofs(yfd_maxwell *m, const double *dofs)
 {
     if (!m || !dofs) return YFD_ERR_INVALID_ARGUMENT;
