@@ -80,6 +80,12 @@ def test_spmv_kernels_use_the_tma_engine():
     assert blocks
     for b in blocks:
         assert b.count("DMMA") >= 160, b.count("DMMA")
+    # the Maxwell stage on the tensor pipe: 16 block products per triangle (flux operands factored) x 2 n-tiles x 4 k-steps at k = 4
+    blocks = [b for b in out.split("Function : ")[1:] if "23maxwell_stage_class_mmaILi3ELi4E" in b.split("\n", 1)[0]]
+    assert len(blocks) == 2                                  # centred / upwind fluxes
+    for b in blocks:
+        assert 120 <= b.count("DMMA") <= 140, b.count("DMMA")
+    assert any("maxwell_rk_vector" in b.split("\n", 1)[0] for b in out.split("Function : ")[1:])
     # bs = 10: one n-tile on the tensor pipe, rows 8 and 9 on DFMA
     blocks = [b for b in out.split("Function : ")[1:] if "17dg_spmv_class_mmaILi10ELi5ELb1E" in b.split("\n", 1)[0]]
     assert blocks
