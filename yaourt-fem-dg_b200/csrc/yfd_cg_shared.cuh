@@ -26,13 +26,20 @@ struct cg_scalars {
 };
 
 /* Sum tot[0..NV) (shared memory) over all ranks through peer memory.  Called by ALL threads of the kernel's last block
- * (grid_sum returns true in all of them); warp 0 does the exchange with lane q talking to rank q -- the stores to the
- * peers and the polls of their flags run side by side instead of one after the other, which at 8 ranks took most of
- * the ~10 us a synchronisation cost -- and lane 0 then adds the slots IN RANK ORDER, so every rank ends with identical
- * bits.  Result in tot[], valid for thread 0. */
+ * (grid_sum returns true in all of them); warp 0 does the exchange with lane q talking to rank q, and lane 0 then adds the
+ * contributions IN RANK ORDER, so every rank ends with identical bits.  Result in tot[], valid for thread 0.
+ *
+ * Wire format: a value travels as two 8-byte packets { 32 bits of the double | 32-bit epoch tag } -- an aligned 8-byte store is
+ * one transaction, so a packet whose tag matches carries its data with it and NO memory fence is needed between "the values"
+ * and "a flag" (the first version stored values, fenced at system scope, raised a flag, spun, fenced again: two NVLink round
+ * trips per sum, ~12 us; a CG iteration has two sums).  Two buffers by epoch parity: a rank can send sum e + 2 only after
+ * finishing sum e + 1, i.e. after every peer has sent e + 1, i.e. after every peer has read this rank's packets of sum e.
+ * What else a sum announces (cg_update_xr: the y values stored into the peers' landing zones) is ordered by the blocks that
+ * stored it: system fence, then the ticket the last block waits for (grid_sum), then these packets. */
 template <int NV>
 __device__ __forceinline__ void xrank_sum(cg_scalars *sc, int kind, double *tot)
 {
+    static_assert(NV >= 1 && NV <= 2, "a peer_slot holds four packets");
     const peer_view *pv = sc->peer;
     if (!pv || threadIdx.x >= 32) return;
     const int lane = (int) threadIdx.x;
@@ -41,28 +48,34 @@ __device__ __forceinline__ void xrank_sum(cg_scalars *sc, int kind, double *tot)
     if (lane == 0) { e = me->red_epoch[kind] + 1; me->red_epoch[kind] = e; }
     e = __shfl_sync(0xffffffffu, e, 0);
     const int par = (int) (e & 1);
+    const unsigned long long tag = (((unsigned long long) e & 0x7fffffffull) | 0x80000000ull) << 32;     /* never the zero of a fresh region */
     const bool act = lane < pv->nranks;
+    __threadfence_system();             /* release: whatever this sum announces (see above) is ordered before the packets; this warp
+                                           has no remote stores of its own in flight, so there is nothing to wait for */
     if (act) {
-        volatile peer_slot *slot = &pv->ctl[lane]->red[par][kind][pv->me];
+        volatile unsigned long long *pk = reinterpret_cast<volatile unsigned long long *>(&pv->ctl[lane]->red[par][kind][pv->me]);
 #pragma unroll
-        for (int k = 0; k < NV; k++) slot->v[k] = tot[k];
+        for (int k = 0; k < NV; k++) {
+            const unsigned long long bits = (unsigned long long) __double_as_longlong(tot[k]);
+            pk[2 * k] = (bits & 0xffffffffull) | tag;
+            pk[2 * k + 1] = (bits >> 32) | tag;
+        }
     }
-    __threadfence_system();             /* the values (and, cumulatively, every store this kernel made to a peer) before the flag */
     double s[NV];
 #pragma unroll
     for (int k = 0; k < NV; k++) s[k] = 0.0;
     if (act) {
-        *((volatile unsigned long long *) &pv->ctl[lane]->red[par][kind][pv->me].flag) = e;
-        volatile peer_slot *slot = &me->red[par][kind][lane];
+        volatile unsigned long long *pk = reinterpret_cast<volatile unsigned long long *>(&me->red[par][kind][lane]);
         long long spins = 0;
-        while (slot->flag != e)
-            if (++spins > (1ll << 28)) { sc->comm_error = 1; sc->done = 1; break; }
-    }
-    __threadfence_system();
-    if (act) {
-        volatile peer_slot *slot = &me->red[par][kind][lane];
 #pragma unroll
-        for (int k = 0; k < NV; k++) s[k] = slot->v[k];
+        for (int k = 0; k < NV; k++) {
+            unsigned long long lo = pk[2 * k], hi = pk[2 * k + 1];
+            while ((lo & 0xffffffff00000000ull) != tag || (hi & 0xffffffff00000000ull) != tag) {
+                if (++spins > (1ll << 28)) { sc->comm_error = 1; sc->done = 1; break; }
+                lo = pk[2 * k]; hi = pk[2 * k + 1];
+            }
+            s[k] = __longlong_as_double((long long) ((lo & 0xffffffffull) | (hi << 32)));
+        }
     }
     double acc[NV];
 #pragma unroll

@@ -22,7 +22,7 @@
  * the ranks swap CUDA IPC handles once, and from then on device code stores straight into its peers' regions
  * (yfd_peer.cu).  Layout of a region: [ peer_ctl | landing zone for the neighbours' y = A d on this rank's halo cells ]. ---- */
 constexpr int YFD_MAX_RANKS = 16;
-struct peer_slot { double v[2]; unsigned long long flag, pad; };
+struct peer_slot { unsigned long long pk[4]; };       /* two values x two 8-byte packets { 32 data bits | epoch tag }: yfd_cg_shared.cuh */
 struct peer_ctl {
     unsigned long long red_epoch[4];            /* local counters, one per reduction kind            */
     unsigned long long pad1[4];
