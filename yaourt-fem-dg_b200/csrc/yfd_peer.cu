@@ -5,13 +5,13 @@
  * latency, and a CG iteration needs three of them: at 8 GPUs that is most of an iteration whose kernels take
  * ~110 us.  Here the ranks map each other's memory once (cudaMalloc + CUDA IPC handles, swapped with one
  * ncclAllGather) and the solver's own kernels communicate:
- *   - a reduction's last block stores its partial sums into a slot on every rank, fences, raises a flag, then
- *     spins until the flags of all ranks for this epoch are up and adds the slots IN RANK ORDER -- every rank
+ *   - a reduction's last block sends its partial sums to every rank as 8-byte packets { 32 data bits | epoch tag }, then
+ *     spins until the packets of all ranks for this epoch are in and adds them IN RANK ORDER -- every rank
  *     gets the same bits, so `done` flips on all ranks in the same iteration (cg_shared.cuh: xrank_sum);
  *   - there is no per-iteration halo exchange of the direction vector at all: every rank keeps halo copies of r, z
  *     and d and advances them itself with the recurrences the owner uses (same operands, same FMAs, same bits).
  *     What it needs for that is y = A d on its halo cells, which the owner stores straight into this rank's landing
- *     zone from cg_update_xr (yfd_cg.cu) BEFORE that kernel's cross-rank sum of r.r -- the sum's flags, raised after
+ *     zone from cg_update_xr (yfd_cg.cu) BEFORE that kernel's cross-rank sum of r.r -- the sum's packets, sent after
  *     a system fence, announce the halo data too.  One iteration = 3 kernels and 2 synchronisations (the two dot
  *     products CG cannot do without), against 4 kernels and 3 synchronisations with an explicit exchange.
  * Epoch counters live on the device and advance inside the kernels, so the whole iteration stays inside one
