@@ -89,7 +89,8 @@ dg_sip_cells(const dg_args a)
     /* shared tables, reused between the cell phase and each face phase */
     constexpr int CELL_DBL = NQ * (2 + 3 * BS);
     constexpr int FACE_DBL = NFQ * (2 + 4 * BS);
-    constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
+    constexpr int FACES_DBL = NV * FACE_DBL + 4 * NV;              /* all faces' tables + 4 scalars per face */
+    constexpr int WARP_DBL = CELL_DBL > FACES_DBL ? CELL_DBL : FACES_DBL;
     extern __shared__ double smem_all[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *S = smem_all + (size_t) warp * WARP_DBL;
@@ -176,9 +177,14 @@ dg_sip_cells(const dg_args a)
         const int64_t cp = a.blocks_mode ? 0 : a.cellptr[cell];
         double *vrow = a.blocks_mode ? nullptr : a.values + cp * BS2;
 
-        double *FW = S, *FG = S + NFQ, *TPHI = S + 2 * NFQ, *TGN = TPHI + NFQ * BS, *NPHI = TGN + NFQ * BS, *NGN = NPHI + NFQ * BS;
-#pragma unroll 1
-        for (int e = 0; e < NV; e++) {
+        /* tables of ALL faces at once: work item u = (face e, own / neighbour basis, quadrature point q) -- 2 nf (k+1) items, a
+         * whole warp at quadrangles k = 3 -- where the first version walked the faces one after the other with every lane
+         * repeating the face's geometry and k + 1 lanes evaluating bases (ncu: 45 % of the kernel).  Per-face scalars the
+         * contraction needs go through shared memory (FSC). */
+        double *FSC = S + NV * FACE_DBL;
+        for (int u = lane; u < NV * 2 * NFQ; u += 32) {
+            const int e = u / (2 * NFQ), rem = u - e * (2 * NFQ), which = rem / NFQ, q = rem - which * NFQ;
+            double *FW = S + e * FACE_DBL, *FG = FW + NFQ, *TPHI = FW + 2 * NFQ, *TGN = TPHI + NFQ * BS, *NPHI = TGN + NFQ * BS, *NGN = NPHI + NFQ * BS;
             const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
             const int2 fp = __ldg(&a.faces[f]);
             const int2 own = __ldg(&a.face_owners[f]);
@@ -187,7 +193,6 @@ dg_sip_cells(const dg_args a)
             const double2 A = __ldg(&a.pts[fp.x]), B = __ldg(&a.pts[fp.y]);   /* p0 < p1 by point id */
             const double ex = B.x - A.x, ey = B.y - A.y;
             const double len = sqrt((A.x - B.x) * (A.x - B.x) + (A.y - B.y) * (A.y - B.y));   /* measure == diameter for an edge */
-            const double eta_l = a.eta / len;
             /* normal(), core/mesh.hpp:505-530 */
             double nx = -ey, ny = ex;
             {
@@ -196,32 +201,36 @@ dg_sip_cells(const dg_args a)
                 const double inv = 1.0 / sqrt(nx * nx + ny * ny);
                 nx *= inv; ny *= inv;
             }
-            double nxb = 0, nyb = 0, nh = 1;
-            if (has_nb) {
-                double2 Q[NV];
-#pragma unroll
-                for (int v = 0; v < NV; v++) Q[v] = __ldg(&a.pts[a.cells[(int64_t) NV * nrc + v]]);
-                cell_frame<NV>(Q, nxb, nyb, nh);
-            }
-            for (int q = lane; q < NFQ; q += 32) {
-                /* integrate(msh, face, 2k), core/quadratures.hpp:723-746 */
-                const double t = __ldg(&a.gx[q]);
-                const double x = 0.5 * (1 - t) * A.x + 0.5 * (1 + t) * B.x;
-                const double y = 0.5 * (1 - t) * A.y + 0.5 * (1 + t) * B.y;
+            /* integrate(msh, face, 2k), core/quadratures.hpp:723-746 */
+            const double t = __ldg(&a.gx[q]);
+            const double x = 0.5 * (1 - t) * A.x + 0.5 * (1 + t) * B.x;
+            const double y = 0.5 * (1 - t) * A.y + 0.5 * (1 + t) * B.y;
+            double phi[BS], gx[BS], gy[BS];
+            if (which == 0) {
                 const double w = __ldg(&a.gw[q]) * len * 0.5;
                 FW[q] = w;
                 FG[q] = has_nb ? 0.0 : w * eval_fn(a.dir_fn, x, y);
-                double phi[BS], gx[BS], gy[BS];
                 basis_eval<K>::run(x, y, xb, yb, h, phi, gx, gy, 1);
 #pragma unroll
                 for (int i = 0; i < BS; i++) { TPHI[q * BS + i] = phi[i]; TGN[q * BS + i] = gx[i] * nx + gy[i] * ny; }
-                if (has_nb) {
-                    basis_eval<K>::run(x, y, nxb, nyb, nh, phi, gx, gy, 1);
+                if (q == 0) { FSC[4 * e] = a.eta / len; FSC[4 * e + 1] = nx; FSC[4 * e + 2] = ny; FSC[4 * e + 3] = has_nb ? 1.0 : 0.0; }
+            } else if (has_nb) {
+                double2 Q[NV];
 #pragma unroll
-                    for (int i = 0; i < BS; i++) { NPHI[q * BS + i] = phi[i]; NGN[q * BS + i] = gx[i] * nx + gy[i] * ny; }
-                }
+                for (int v = 0; v < NV; v++) Q[v] = __ldg(&a.pts[a.cells[(int64_t) NV * nrc + v]]);
+                double nxb, nyb, nh;
+                cell_frame<NV>(Q, nxb, nyb, nh);
+                basis_eval<K>::run(x, y, nxb, nyb, nh, phi, gx, gy, 1);
+#pragma unroll
+                for (int i = 0; i < BS; i++) { NPHI[q * BS + i] = phi[i]; NGN[q * BS + i] = gx[i] * nx + gy[i] * ny; }
             }
-            __syncwarp();
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int e = 0; e < NV; e++) {
+            const double *FW = S + e * FACE_DBL, *FG = FW + NFQ, *TPHI = FW + 2 * NFQ, *TGN = TPHI + NFQ * BS, *NPHI = TGN + NFQ * BS, *NGN = NPHI + NFQ * BS;
+            const double eta_l = FSC[4 * e], nx = FSC[4 * e + 1], ny = FSC[4 * e + 2];
+            const bool has_nb = FSC[4 * e + 3] != 0.0;
 
             const double c = has_nb ? 0.5 : 1.0;         /* dg2d_diffusion.cpp:171-173 vs :186-188 */
             /* advection-reaction flux coefficients (dg2d_advection.cpp:180-199) */
@@ -361,7 +370,8 @@ static yfd_status launch_cells(yfd_ctx *ctx, const dg_args &a)
     constexpr int NFQ = K + 1;
     constexpr int CELL_DBL = NQ * (2 + 3 * BS);
     constexpr int FACE_DBL = NFQ * (2 + 4 * BS);
-    constexpr int WARP_DBL = CELL_DBL > FACE_DBL ? CELL_DBL : FACE_DBL;
+    constexpr int FACES_DBL = NV * FACE_DBL + 4 * NV;
+    constexpr int WARP_DBL = CELL_DBL > FACES_DBL ? CELL_DBL : FACES_DBL;
     const size_t smem = (size_t) DG_WARPS * WARP_DBL * sizeof(double);
     if (smem > YFD_SMEM_OPTIN_FROM)
         YFD_CUDA(ctx, cudaFuncSetAttribute(dg_sip_cells<NV, K, ADV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
