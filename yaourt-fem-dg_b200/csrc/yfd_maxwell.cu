@@ -62,7 +62,7 @@ template <int NV, int K>
 struct mx_asm_shape {
     static constexpr int BS = mx_bs(K), NB = mx_nb(NV), NR = NB * BS, LD = NR | 1;
     static constexpr int NQ = dg_nq_cell(NV, K), NFQ = K + 1;
-    static constexpr int CELL_TAB = NQ * (1 + 3 * BS), FACE_TAB = NFQ * (1 + 2 * BS);
+    static constexpr int CELL_TAB = NQ * (1 + 3 * BS), FACE_TAB = NV * NFQ * (1 + 2 * BS) + NV;     /* all faces' tables + flags */
     static constexpr int LDT = (BS + 1) & ~1;                             /* transposed LU factors for the column solves */
     static constexpr int TAB0 = CELL_TAB > FACE_TAB ? CELL_TAB : FACE_TAB;
     static constexpr int TAB = TAB0 > BS * LDT + 1 ? TAB0 : BS * LDT + 1;  /* the factors' copy reuses the table area */
@@ -130,8 +130,12 @@ maxwell_assemble(const mx_asm_args a)
         const double mu = a.mu_r ? a.mu_r[rc] : 1.0, eps = a.eps_r ? a.eps_r[rc] : 1.0;
         const double Z_this = sqrt(mu / eps), Y_this = 1. / Z_this;
         if (lane == 0) { a.cs[2 * cell] = 1. / mu; a.cs[2 * cell + 1] = 1. / eps; }
-#pragma unroll 1
-        for (int e = 0; e < NV; e++) {
+        /* tables of all faces at once: work item u = (face e, own / neighbour basis, quadrature point q), 2 nf (k+1) of them, instead
+         * of face after face with every lane repeating the face's geometry and k + 1 lanes evaluating both bases */
+        constexpr int FDBL = NFQ * (1 + 2 * BS);
+        double *FH = T + NV * FDBL;                                   /* has-neighbour flags */
+        for (int u = lane; u < NV * 2 * NFQ; u += 32) {
+            const int e = u / (2 * NFQ), rem = u - e * (2 * NFQ), which = rem / NFQ, q = rem - which * NFQ;
             const int32_t f = a.cell_faces[(int64_t) NV * rc + e];
             const int2 fp = __ldg(&a.faces[f]);
             const int2 own = __ldg(&a.face_owners[f]);
@@ -139,46 +143,51 @@ maxwell_assemble(const mx_asm_args a)
             const bool has_nb = nrc >= 0;
             const double2 A = __ldg(&a.pts[fp.x]), B = __ldg(&a.pts[fp.y]);
             const double len = sqrt((A.x - B.x) * (A.x - B.x) + (A.y - B.y) * (A.y - B.y));
-            double nx, ny;
-            face_normal(A, B, xb, yb, nx, ny);
-            double nxb = 0, nyb = 0, nh = 1;
-            if (has_nb) {
+            double *FW = T + e * FDBL, *TPHI = FW + NFQ, *NPHI = TPHI + NFQ * BS;
+            const double t = __ldg(&a.gx[q]);
+            const double x = 0.5 * (1 - t) * A.x + 0.5 * (1 + t) * B.x;
+            const double y = 0.5 * (1 - t) * A.y + 0.5 * (1 + t) * B.y;
+            if (which == 0) {
+                FW[q] = __ldg(&a.gw[q]) * len * 0.5;
+                basis_eval<K>::values(x, y, xb, yb, h, TPHI + q, NFQ);
+                if (q == 0) {
+                    double nx, ny;
+                    face_normal(A, B, xb, yb, nx, ny);
+                    double kappa_E = 0.5, kappa_H = 0.5, nu_E = 0.0, nu_H = 0.0;
+                    if (a.upwind) {
+                        if (has_nb) {                                       /* :328-339 */
+                            const double mu_n = a.mu_r ? a.mu_r[nrc] : 1.0, eps_n = a.eps_r ? a.eps_r[nrc] : 1.0;
+                            const double Z_n = sqrt(mu_n / eps_n), Y_n = 1. / Z_n;
+                            kappa_E = Z_n / (Z_this + Z_n);                 /* second assignment wins; kappa_H stays 0.5 */
+                            nu_E = a.eta / (Y_this + Y_n);
+                            nu_H = a.eta / (Z_this + Z_n);
+                        } else {                                            /* :391-398 */
+                            kappa_E = 0.5 * Z_this;
+                            nu_E = a.eta / (2 * Y_this);
+                            nu_H = a.eta / (2 * Z_this);
+                        }
+                    }
+                    mx_face_coef c;
+                    c.nx = nx; c.ny = ny;
+                    if (has_nb) { c.cE = kappa_E; c.cH = kappa_H; c.vH = nu_H; c.vE = nu_E; }
+                    else        { c.cE = 2 * kappa_E; c.cH = 0.0; c.vH = 0.0; c.vE = 2 * nu_E; }    /* :404-410 */
+                    a.fc[cell * NV + e] = c;
+                    FH[e] = has_nb ? 1.0 : 0.0;
+                }
+            } else if (has_nb) {
                 double2 Q[NV];
 #pragma unroll
                 for (int v = 0; v < NV; v++) Q[v] = __ldg(&a.pts[a.cells[(int64_t) NV * nrc + v]]);
+                double nxb, nyb, nh;
                 cell_frame<NV>(Q, nxb, nyb, nh);
+                basis_eval<K>::values(x, y, nxb, nyb, nh, NPHI + q, NFQ);
             }
-            if (lane == 0) {
-                double kappa_E = 0.5, kappa_H = 0.5, nu_E = 0.0, nu_H = 0.0;
-                if (a.upwind) {
-                    if (has_nb) {                                       /* :328-339 */
-                        const double mu_n = a.mu_r ? a.mu_r[nrc] : 1.0, eps_n = a.eps_r ? a.eps_r[nrc] : 1.0;
-                        const double Z_n = sqrt(mu_n / eps_n), Y_n = 1. / Z_n;
-                        kappa_E = Z_n / (Z_this + Z_n);                 /* second assignment wins; kappa_H stays 0.5 */
-                        nu_E = a.eta / (Y_this + Y_n);
-                        nu_H = a.eta / (Z_this + Z_n);
-                    } else {                                            /* :391-398 */
-                        kappa_E = 0.5 * Z_this;
-                        nu_E = a.eta / (2 * Y_this);
-                        nu_H = a.eta / (2 * Z_this);
-                    }
-                }
-                mx_face_coef c;
-                c.nx = nx; c.ny = ny;
-                if (has_nb) { c.cE = kappa_E; c.cH = kappa_H; c.vH = nu_H; c.vE = nu_E; }
-                else        { c.cE = 2 * kappa_E; c.cH = 0.0; c.vH = 0.0; c.vE = 2 * nu_E; }    /* :404-410 */
-                a.fc[cell * NV + e] = c;
-            }
-            double *FW = T, *TPHI = T + NFQ, *NPHI = TPHI + NFQ * BS;
-            for (int q = lane; q < NFQ; q += 32) {
-                const double t = __ldg(&a.gx[q]);
-                const double x = 0.5 * (1 - t) * A.x + 0.5 * (1 + t) * B.x;
-                const double y = 0.5 * (1 - t) * A.y + 0.5 * (1 + t) * B.y;
-                FW[q] = __ldg(&a.gw[q]) * len * 0.5;
-                basis_eval<K>::values(x, y, xb, yb, h, TPHI + q, NFQ);
-                if (has_nb) basis_eval<K>::values(x, y, nxb, nyb, nh, NPHI + q, NFQ);
-            }
-            __syncwarp();
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int e = 0; e < NV; e++) {
+            const double *FW = T + e * FDBL, *TPHI = FW + NFQ, *NPHI = TPHI + NFQ * BS;
+            const bool has_nb = FH[e] != 0.0;
             for (int m = lane; m < BS2; m += 32) {
                 const int i = m / BS, j = m - i * BS;
                 double tm = 0.0, nm = 0.0;
@@ -190,8 +199,8 @@ maxwell_assemble(const mx_asm_args a)
                 R[i * LD + (2 + e) * BS + j] = tm;
                 R[i * LD + (2 + NV + e) * BS + j] = nm;
             }
-            __syncwarp();
         }
+        __syncwarp();
 
         /* ---- 3. M^-1: factor once, then independent columns ---- */
         if (!warp_lu_factor<BS>(MM, piv, lane) && lane == 0) atomicExch(a.err, 1);
