@@ -41,6 +41,8 @@ struct mx_asm_args {
     double        *op;
     mx_face_coef  *fc;
     double        *cs, *gM, *cell_pts;
+    double        *gLU;           /* factored M and its pivots, kept for the initial-condition projection */
+    int32_t       *gPiv;
     int           *err;
 };
 
@@ -204,6 +206,8 @@ maxwell_assemble(const mx_asm_args a)
 
         /* ---- 3. M^-1: factor once, then independent columns ---- */
         if (!warp_lu_factor<BS>(MM, piv, lane) && lane == 0) atomicExch(a.err, 1);
+        for (int m = lane; m < BS2; m += 32) a.gLU[cell * BS2 + m] = MM[m];
+        if (lane < BS) a.gPiv[cell * BS + lane] = piv[lane];
         {
             double *FT = T + ((reinterpret_cast<uintptr_t>(T) & 8) ? 1 : 0);        /* 16-byte aligned */
             lu_transpose_factors<BS, S::LDT>(MM, FT, lane);
@@ -234,6 +238,8 @@ namespace yfd {
 struct mx_cell_args {
     const double *cell_pts;       /* [ncells][nv][2] */
     const double *gM;
+    const double *gLU;            /* P M = L U as maxwell_assemble factored it */
+    const int32_t *gPiv;
     const double *cell_rule, *gx, *gw;
     int64_t       ncells;
     int           fields;
@@ -270,7 +276,9 @@ maxwell_project(const mx_cell_args a)
             F[q] = hx * w; F[NQ + q] = hy * w; F[2 * NQ + q] = ez * w;       /* Hx_ic(pt) * qp.weight() * phi, :533-535 */
             basis_eval<K>::values(x, y, xb, yb, h, PHI + q, NQ);
         }
-        for (int m = lane; m < BS2; m += 32) MM[m] = a.gM[cell * BS2 + m];
+        /* the factorisation of M the assembly kernel made (the same dgetf2 on the same matrix: the same bits as refactoring) */
+        for (int m = lane; m < BS2; m += 32) MM[m] = a.gLU[cell * BS2 + m];
+        if (lane < BS) piv[lane] = a.gPiv[cell * BS + lane];
         __syncwarp();
         for (int m = lane; m < 3 * BS; m += 32) {
             const int i = m / 3, fld = m - 3 * i;
@@ -279,7 +287,6 @@ maxwell_project(const mx_cell_args a)
             R[i * LD + fld] = s;
         }
         __syncwarp();
-        if (!warp_lu_factor<BS>(MM, piv, lane) && lane == 0) atomicExch(a.err, 1);
         if (lane < 3) lu_solve_column<BS>(MM, piv, R, LD, lane);
         __syncwarp();
         for (int m = lane; m < 3 * BS; m += 32) {
@@ -497,7 +504,7 @@ yfd_status fill_cell_args(yfd_maxwell *m, mx_cell_args &a)
     YFD_TRY(gauss_rule_for_degree(ctx, 2 * m->degree, &g));
     tri_rule t;
     YFD_TRY(dunavant_rule_for_degree(ctx, 2 * m->degree, &t));
-    a.cell_pts = m->cell_pts.p; a.gM = m->gM.p;
+    a.cell_pts = m->cell_pts.p; a.gM = m->gM.p; a.gLU = m->gLU.p; a.gPiv = m->gPiv.p;
     a.cell_rule = t.cw; a.gx = g.x; a.gw = g.w;
     a.ncells = m->ncells; a.fields = 0; a.t = 0.0; a.u = m->u.p; a.partial = nullptr; a.err = nullptr;
     return YFD_OK;
@@ -608,6 +615,8 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     YFD_TRY(m->fc.alloc(ctx, (size_t) nc * nv));
     YFD_TRY(m->cs.alloc(ctx, (size_t) nc * 2));
     YFD_TRY(m->gM.alloc(ctx, (size_t) nc * bs * bs));
+    YFD_TRY(m->gLU.alloc(ctx, (size_t) nc * bs * bs));
+    YFD_TRY(m->gPiv.alloc(ctx, (size_t) nc * bs));
     YFD_TRY(m->cell_pts.alloc(ctx, (size_t) nc * nv * 2));
     dbuf<double> *vecs[5] = {&m->u, &m->s1, &m->s2, &m->acc, &m->kb};
     for (int v = 0; v < 5; v++) {                 /* reset(gDofs), :138-139 */
@@ -631,7 +640,7 @@ yfd_status yfd_maxwell_create(yfd_ctx *ctx, yfd_mesh *mesh, const yfd_maxwell_co
     a.cell_rule = t.cw; a.gx = g.x; a.gw = g.w;
     a.mu_r = mu_r ? d_mu.p : nullptr; a.eps_r = mu_r ? d_eps.p : nullptr;
     a.upwind = m->upwind; a.eta = cfg->eta;
-    a.op = m->op.p; a.fc = m->fc.p; a.cs = m->cs.p; a.gM = m->gM.p; a.cell_pts = m->cell_pts.p; a.err = derr.p;
+    a.op = m->op.p; a.fc = m->fc.p; a.cs = m->cs.p; a.gM = m->gM.p; a.gLU = m->gLU.p; a.gPiv = m->gPiv.p; a.cell_pts = m->cell_pts.p; a.err = derr.p;
     gpu_timer tm;
     tm.start(ctx->stream);
     nvtx_range nr_asm("yfd: Maxwell assemble");

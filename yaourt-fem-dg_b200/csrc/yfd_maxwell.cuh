@@ -59,6 +59,8 @@ struct yfd_maxwell {
     yfd::dbuf<yfd::mx_face_coef> fc;  /* [ncells][nf]                                                     */
     yfd::dbuf<double>  cs;            /* [ncells][2] = inv_mu, inv_eps                                    */
     yfd::dbuf<double>  gM;            /* [ncells][bs][bs] row-major, internal order                       */
+    yfd::dbuf<double>  gLU;           /* the same matrices as the assembly kernel factored them (P M = L U) */
+    yfd::dbuf<int32_t> gPiv;          /* [ncells][bs] row swaps of that factorisation: the projection reuses it */
     yfd::mx_classes    classes;
     int      operator_mode = 0;       /* YFD_OPERATOR_AUTO / _STREAMED / _CLASSES                         */
     bool     classes_faster = false;  /* outcome of the timing at creation (AUTO follows it)              */
